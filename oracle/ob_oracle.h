@@ -1,0 +1,87 @@
+/* ob_oracle.h — C ABI of the CPU oracle (TEST INFRASTRUCTURE, not product code).
+ *
+ * The oracle is a CPU restatement of libopenbeam's static-solve hot path
+ *   assembleProblem()      libopenbeam/src/CFiniteElementProblem_assemble.cpp:37-437
+ *   solveStatic()          libopenbeam/src/CFiniteElementProblem_solver_static.cpp:29-219
+ *   postProcCalcStress()   libopenbeam/src/CFiniteElementProblem_postproc_stress.cpp:32-183
+ * written because the reference itself cannot be compiled in this image (it needs
+ * MRPT >= 2.4 and Eigen, both absent).  PARITY UNPINNED: the reference
+ * ships no tests or golden vectors for this path; the oracle is pinned instead by
+ * closed-form statics and independent numerics (tests/test_oracle_*.py).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load this library.  The product (openbeam_b200/) never does.
+ */
+#ifndef OB_ORACLE_H
+#define OB_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct obo_problem obo_problem;
+
+/* element types: CElementBeam_2D_{RR,RA,AR,AA} */
+enum { OBO_RR = 0, OBO_RA = 1, OBO_AR = 2, OBO_AA = 3 };
+/* solver algorithm: StaticSolverAlgorithm (CFiniteElementProblem.h:69-73) */
+enum { OBO_DENSE_LLT = 0, OBO_SPARSE_SKIP_SUBK = 1 };
+
+/* integer arrays readable with obo_get_i64 */
+enum {
+  OBO_I_DOF_NODE = 0,     /* m_problem_DoFs[k].nodeId            [n]   */
+  OBO_I_DOF_ID = 1,       /* m_problem_DoFs[k].dof (0..5)        [n]   */
+  OBO_I_FREE = 2,         /* free_dof_indices                    [n_f] */
+  OBO_I_BOUNDED = 3,      /* bounded_dof_indices                 [n_b] */
+  OBO_I_DOF_INDEX = 4,    /* m_problem_DoFs_inverse_list  [N*6], -1 = unused */
+  OBO_I_TRI_ROW = 5,      /* triplet rows                        [T]   */
+  OBO_I_TRI_COL = 6,      /* triplet cols                        [T]   */
+  OBO_I_K_OUTER = 7,      /* Eigen CSC(upper) outerIndexPtr      [n+1] */
+  OBO_I_K_INNER = 8       /* Eigen CSC(upper) innerIndexPtr      [nnz] */
+};
+/* double arrays readable with obo_get_f64 */
+enum {
+  OBO_F_TRI_VAL = 0,      /* triplet values                      [T]   */
+  OBO_F_K_VAL = 1,        /* CSC(upper) values                   [nnz] */
+  OBO_F_KFF_DENSE = 2,    /* dense K_ff lower (col-major n_f x n_f, upper part = 0) */
+  OBO_F_KBF_DENSE = 3,    /* dense K_bf (col-major n_b x n_f)          */
+  OBO_F_KBB_DENSE = 4,    /* dense K_bb upper (col-major n_b x n_b)    */
+  OBO_F_UB = 5, OBO_F_FF = 6, OBO_F_UF = 7, OBO_F_FB = 8,
+  OBO_F_STRESS = 9,       /* [E][2][6] = N,Vy,Vz,Mx,My,Mz per face     */
+  OBO_F_ELEM_R = 10,      /* [E][9] element orientation, col-major      */
+  OBO_F_ELEM_KGLOBAL = 11 /* [E][3][36] global K11,K22,K12, col-major 6x6 */
+};
+/* sizes: obo_get_sizes fills out[0..7] = N, E, n, n_f, n_b, T, nnz, reserved */
+
+obo_problem* obo_create(int64_t n_nodes, const double* node_xy, const double* node_rotz /*nullable, radians*/,
+                        int64_t n_elems, const uint32_t* elem_nodes, const uint8_t* elem_type,
+                        const double* elem_EAI,
+                        int64_t n_cons, const uint32_t* con_node, const uint8_t* con_dof, const double* con_val,
+                        int64_t n_nloads, const uint32_t* nl_node, const uint8_t* nl_dof, const double* nl_val,
+                        int64_t n_eloads, const uint32_t* el_elem, const double* el_q, const double* el_dir);
+void obo_destroy(obo_problem*);
+/* replace load values in place (same slots): node-load values and element-load q */
+int obo_set_load_values(obo_problem*, const double* nl_val, const double* el_q);
+/* replace every element's (E,A,Iz) */
+int obo_set_elem_EAI(obo_problem*, const double* elem_EAI);
+
+int obo_assemble(obo_problem*, int skip_subK);     /* assembleProblem();  0 = ok */
+int obo_solve_static(obo_problem*, int algorithm); /* solveStatic() (calls assemble) */
+int obo_stress(obo_problem*);                      /* postProcCalcStress() */
+const char* obo_last_error(const obo_problem*);
+
+void obo_get_sizes(const obo_problem*, int64_t out[8]);
+int64_t obo_get_i64(const obo_problem*, int which, int64_t* out, int64_t cap);
+int64_t obo_get_f64(const obo_problem*, int which, double* out, int64_t cap);
+
+/* CPU-baseline driver: clone the problem per thread; for each case c set the load
+ * values (case-major arrays: nl_val[c*n_nloads+..], el_q[c*n_eloads+..], optional
+ * per-case elem_EAI[c*3E+..]) and run solveStatic + postProcCalcStress, writing
+ * U_f [c][n_f], F_b [c][n_b], stress [c][E][2][6] (any may be NULL).
+ * Returns wall seconds spent inside the threaded region, <0 on error. */
+double obo_run_cases(const obo_problem* tmpl, int64_t n_cases, const double* nl_val, const double* el_q,
+                     const double* elem_EAI, int n_threads, double* U_f, double* F_b, double* stress);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
