@@ -1,0 +1,165 @@
+/* obgpu.h — C ABI of libobgpu, the B200-native static-solve path behind libopenbeam's
+ *   CFiniteElementProblem::assembleProblem(BuildProblemInfo&)          include/openbeam/CFiniteElementProblem.h:435
+ *   CFiniteElementProblem::solveStatic(StaticSolveProblemInfo&, opts)  include/openbeam/CFiniteElementProblem.h:444-446
+ *   CFiniteElementProblem::postProcCalcStress(StressInfo&, info)       include/openbeam/CFiniteElementProblem.h:453-454
+ * (reference paths relative to /root/reference/libopenbeam/).  The reference has no FFI or plugin
+ * interface for this path; these entry points are what a GPU_* case added to
+ * StaticSolverOptions::algorithm (CFiniteElementProblem.h:69-73,165-171) would bind — see INTEGRATION.md
+ * and include/obhost.hpp for the C++ mirror of the reference's method and field names.
+ *
+ * Plain pointers and sizes only; the caller owns every host buffer, the library owns device memory
+ * inside the opaque ctx.  Calls on one ctx must be serialised by the caller; different ctxs may be
+ * used from different threads/processes (one ctx per GPU).  There is no CPU fallback: every call
+ * fails with OBGPU_ECUDA when no sm_100 device is usable.
+ */
+#ifndef OBGPU_H
+#define OBGPU_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct obgpu_ctx obgpu_ctx;
+
+/* status codes (the C++ shim rethrows the reference's exception strings, solver_static.cpp:98-105) */
+enum {
+  OBGPU_OK = 0,
+  OBGPU_EINVAL = 1,        /* malformed description (MRPT ASSERT_ in the reference)             */
+  OBGPU_ECUDA = 2,         /* CUDA error / no device                                           */
+  OBGPU_ESINGULAR = 3,     /* >=1 system had a non-positive pivot (reference: runtime_error)    */
+  OBGPU_ENOTCONVERGED = 4, /* PCG hit max_iter                                                  */
+  OBGPU_EUNSUPPORTED = 5,  /* valid input outside what the GPU path implements (stated in text) */
+  OBGPU_ESEQUENCE = 6      /* call order violated (e.g. solve before symbolic)                  */
+};
+
+/* element types: CElementBeam_2D_{RR,RA,AR,AA}.cpp */
+enum { OBGPU_BEAM2D_RR = 0, OBGPU_BEAM2D_RA = 1, OBGPU_BEAM2D_AR = 2, OBGPU_BEAM2D_AA = 3 };
+/* DoF_index, CFiniteElementProblem.h:53-67 */
+enum { OBGPU_DX = 0, OBGPU_DY = 1, OBGPU_DZ = 2, OBGPU_RX = 3, OBGPU_RY = 4, OBGPU_RZ = 5 };
+
+/* A batch of S independent structures (CSR-of-structures SoA) x L load cases.
+ * System (s, c) = structure s under load case c; there are S*L systems.
+ * Element/constraint/load node indices are LOCAL to their structure.
+ * Constraints and node loads on DOFs that do not exist in the problem are ignored, as the
+ * reference's parser does (parse_file.cpp:653-662,747-756). */
+typedef struct obgpu_batch_desc {
+  int64_t n_structures;       /* S >= 1 */
+  const int64_t* node_off;    /* [S+1] */
+  const int64_t* elem_off;    /* [S+1] */
+  const int64_t* con_off;     /* [S+1] */
+  const int64_t* nload_off;   /* [S+1] */
+  const int64_t* eload_off;   /* [S+1] */
+  const double* node_xy;      /* [2*Ntot] x,y  (m_node_poses[i].t, z = 0)                         */
+  const double* node_rotz;    /* NULL or [Ntot] nodal frame yaw in radians (parse_file.cpp:467)   */
+  const uint32_t* elem_nodes; /* [2*Etot] conected_nodes_ids[0..1]                                */
+  const uint8_t* elem_type;   /* [Etot]   OBGPU_BEAM2D_*                                          */
+  const double* elem_EAI;     /* [3*Etot] E, A, Iz  (G = J = 0 as CBaseElementBeam.h:45-46)       */
+  const uint32_t* con_node;   /* [Ctot] */
+  const uint8_t* con_dof;     /* [Ctot] OBGPU_DX..RZ */
+  const double* con_val;      /* [Ctot] prescribed displacement (m_DoF_constraints)               */
+  const uint32_t* nload_node; /* [NLtot] */
+  const uint8_t* nload_dof;   /* [NLtot] */
+  const double* nload_val;    /* [NLtot] addLoadAtDOF values (m_loads_at_each_dof)                */
+  const uint32_t* eload_elem; /* [ELtot] element index (local) carrying a DISTRIB_UNIFORM load    */
+  const double* eload_q;      /* [ELtot] q (N/m)                                                  */
+  const double* eload_dir;    /* [3*ELtot] unit direction (CLoadDistributedUniform::dir)          */
+  /* load cases: case-major overrides of the value arrays above (NULL = use the base values) */
+  int64_t n_cases;              /* L >= 1 */
+  const double* case_nload_val; /* NULL or [L][NLtot] */
+  const double* case_eload_q;   /* NULL or [L][ELtot] */
+  const double* case_elem_EAI;  /* NULL or [L][3*Etot] per-case section sweep */
+} obgpu_batch_desc;
+
+enum { OBGPU_BATCHED_LDLT = 0, OBGPU_PCG_JACOBI = 1, OBGPU_PCG_BJ3 = 2, OBGPU_PCG_IC0 = 3 };
+typedef struct obgpu_solve_opts {
+  int method;        /* OBGPU_BATCHED_LDLT (default) or a PCG variant            */
+  int with_stress;   /* fuse postProcCalcStress into the solve kernel (default 1) */
+  double rtol;       /* PCG: ||r||_2 <= rtol*||b||_2 (default 1e-12)             */
+  int max_iter;      /* PCG: default 20*sqrt(n_f)+1000                            */
+  int reserved;
+} obgpu_solve_opts;
+
+/* sizes: obgpu_get_sizes fills out[0..11] with
+ * S, L, Ntot, Etot, n_tot, nf_tot, nb_tot, T_tot (triplets), nnz_tot (K upper), Ctot, NLtot, ELtot */
+enum { OBGPU_NSIZES = 12 };
+/* int64 offset arrays [S+1] readable with obgpu_get_offsets */
+enum { OBGPU_OFF_DOF = 0, OBGPU_OFF_FREE = 1, OBGPU_OFF_BOUNDED = 2, OBGPU_OFF_NNZ = 3, OBGPU_OFF_TRIPLET = 4 };
+/* int32 symbolic arrays readable with obgpu_get_symbolic (all indices local to their structure) */
+enum {
+  OBGPU_SYM_DOF_NODE = 0,   /* [n_tot]    m_problem_DoFs[k].nodeId                                  */
+  OBGPU_SYM_DOF_ID = 1,     /* [n_tot]    m_problem_DoFs[k].dof                                     */
+  OBGPU_SYM_FREE = 2,       /* [nf_tot]   BuildProblemInfo::free_dof_indices                        */
+  OBGPU_SYM_BOUNDED = 3,    /* [nb_tot]   BuildProblemInfo::bounded_dof_indices                     */
+  OBGPU_SYM_DOF_INDEX = 4,  /* [6*Ntot]   m_problem_DoFs_inverse_list[node].dof_index[d], -1 unused */
+  OBGPU_SYM_K_ROWPTR = 5,   /* [n_tot+S]  CSR(lower) row pointers == Eigen CSC(upper) outerIndexPtr */
+  OBGPU_SYM_K_COL = 6,      /* [nnz_tot]  CSR(lower) columns     == Eigen CSC(upper) innerIndexPtr  */
+  OBGPU_SYM_TRI_NNZ = 7     /* [T_tot]    element->nnz map: triplet t (reference emission order) -> nnz slot */
+};
+/* device/host result arrays */
+enum {
+  OBGPU_RES_UF = 0,      /* [L][nf_tot]        StaticSolveProblemInfo::U_f                          */
+  OBGPU_RES_FB = 1,      /* [L][nb_tot]        StaticSolveProblemInfo::F_b                          */
+  OBGPU_RES_STRESS = 2,  /* [L][Etot][2][6]    StressInfo::element_stress[e][face].{N,Vy,Vz,Mx,My,Mz} */
+  OBGPU_RES_INFO = 3,    /* int32 [L][S]       0 ok; k>0: first non-positive pivot at free row k-1  */
+  OBGPU_RES_FF = 4,      /* [L][nf_tot]        BuildProblemInfo::F_f                                */
+  OBGPU_RES_UB = 5,      /* [nb_tot]           BuildProblemInfo::U_b                                */
+  OBGPU_RES_KVAL = 6,    /* [LK][nnz_tot]      values of K (upper, CSC order); LK = L if case_elem_EAI else 1 */
+  OBGPU_RES_ELEM_K = 7   /* [LK][Etot][21]     compact global element blocks        */
+};
+
+int obgpu_create(int device, obgpu_ctx** out);
+void obgpu_destroy(obgpu_ctx*);
+const char* obgpu_last_error(const obgpu_ctx*);
+/* human-readable text for a status code; for OBGPU_ESINGULAR it is the reference's message */
+const char* obgpu_status_string(int status);
+
+/* pinned host memory for callers that want full-speed PCIe transfers */
+int obgpu_host_alloc(void** p, size_t bytes);
+int obgpu_host_free(void* p);
+
+/* upload a batch (copies everything it needs; host buffers may be freed afterwards) */
+int obgpu_batch_upload(obgpu_ctx*, const obgpu_batch_desc*);
+/* replace the per-case value arrays of the uploaded batch (same S and topology; L may change).
+ * Host pointers; NULL = keep base values.  This is the per-step H2D traffic of a load-case sweep. */
+int obgpu_update_cases(obgpu_ctx*, int64_t n_cases, const double* case_nload_val, const double* case_eload_q,
+                       const double* case_elem_EAI);
+/* K3: DOF numbering, free/bounded partition, K pattern, element->nnz map (once per topology) */
+int obgpu_symbolic(obgpu_ctx*);
+/* K1+K2+K4: element stiffness + deterministic segmented-reduction assembly of K (CSC upper values) */
+int obgpu_assemble(obgpu_ctx*);
+/* K5+K6(+K10): BC gather, factor/solve, reactions, optionally element end forces */
+int obgpu_solve_static(obgpu_ctx*, const obgpu_solve_opts* /*NULL = defaults*/);
+/* K10 alone (when with_stress was 0) */
+int obgpu_stress(obgpu_ctx*);
+
+int obgpu_get_sizes(const obgpu_ctx*, int64_t out[OBGPU_NSIZES]);
+int obgpu_get_offsets(const obgpu_ctx*, int which, int64_t* out);
+int obgpu_get_symbolic(const obgpu_ctx*, int which, int32_t* out);
+/* copy one result array to a host buffer (blocking); returns OBGPU_ESINGULAR if any info != 0 when which==INFO */
+int obgpu_download(obgpu_ctx*, int which, void* host_out);
+/* device pointer of a result array (valid until the next upload/update), for zero-copy consumers */
+int obgpu_device_ptr(obgpu_ctx*, int which, void** dptr);
+/* wait for all work queued on the ctx */
+int obgpu_synchronize(obgpu_ctx*);
+
+/* End-to-end convenience for load-case sweeps over the uploaded structures, HOST buffers in and out:
+ * streams chunks H2D -> fused solve -> D2H on the ctx's copy/compute streams.  Any output may be NULL. */
+int obgpu_solve_cases_host(obgpu_ctx*, int64_t n_cases, const double* case_nload_val, const double* case_eload_q,
+                           const double* case_elem_EAI, double* U_f, double* F_b, double* stress, int32_t* info);
+
+/* per-structure summaries {max|U_f|, sum F_b over DX dofs, sum F_b over DY dofs, info} = 4 doubles per system,
+ * written to a caller-provided DEVICE buffer [L*S*4] (e.g. a torch tensor that is then NCCL-gathered) */
+int obgpu_summaries_device(obgpu_ctx*, double* d_out);
+
+/* timings of the last call of each phase, in ms, measured with CUDA events on the ctx stream; section
+ * names follow the reference's CTimeLogger entries (assemble.cpp:39-346, solver_static.cpp:53-121):
+ * out[0] symbolic (host), [1] assembleProblem, [2] solveStatic.2_solve, [3] postProcCalcStress, [4] H2D, [5] D2H,
+ * [6] kernel launches in the last solve/assemble call (count), [7] PCG iterations of the last solve */
+int obgpu_get_timings(const obgpu_ctx*, double out[8]);
+/* the CUDA stream the ctx launches on (a cudaStream_t), so callers can record their own events on it */
+int obgpu_get_stream(obgpu_ctx*, void** stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

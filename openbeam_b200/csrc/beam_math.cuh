@@ -1,0 +1,122 @@
+// beam_math.cuh — device-side element arithmetic shared by every kernel of libobgpu (FP64).
+//
+// What the reference computes with virtual calls, heap vectors and dense 6x6 Eigen products
+//   orientation        src/internals.cpp:30-123            (2D: R = [[c,-s,0],[s,c,0],[0,0,1]])
+//   local stiffness    src/CElementBeam_2D_{RR,RA,AR,AA}.cpp:41-127
+//   rotation to global src/CElement.cpp:53-79              (B <- R B R^T per non-zero 3x3 sub-block)
+//   equivalent loads   src/CLoadDistributedUniform.cpp:33-159
+//   end forces         src/CFiniteElementProblem_postproc_stress.cpp:86-165
+// is written here in closed form over the only DOFs a planar beam touches (DX,DY,RZ per end).
+// Results agree with the reference to rounding (<= a few ulp; the contract is 1e-9 relative).
+#pragma once
+#include "obgpu_internal.h"
+
+namespace obgpu {
+
+struct ElemGeom {
+  double c, s, L, invL;
+};
+
+// internals.cpp:35-52 : len = |p2-p1|, X = p12 * (1/len)
+__device__ __forceinline__ ElemGeom elem_geom(double x0, double y0, double x1, double y1) {
+  ElemGeom g;
+  const double dx = x1 - x0, dy = y1 - y0;
+  const double L2 = dx * dx + dy * dy;
+  g.L = sqrt(L2);
+  g.invL = 1.0 / g.L;
+  g.c = dx * g.invL;
+  g.s = dy * g.invL;
+  return g;
+}
+
+// Non-zero coefficients of the local blocks (all four element types):
+//   K11 = [[a,0,0],[0,b,p11],[0,p11,r11]]   K22 = [[a,0,0],[0,b,p22],[0,p22,r22]]
+//   K12 = [[-a,0,0],[0,-b,q15],[0,q51,q55]]          (rows/cols = local x, y, rz)
+struct ElemLocalK {
+  double a, b, p11, r11, p22, r22, q15, q51, q55;
+};
+
+__device__ __forceinline__ ElemLocalK elem_local_k(int type, double E, double A, double Iz, const ElemGeom& g) {
+  ElemLocalK k;
+  const double EI = E * Iz;
+  const double EI_L = EI * g.invL, EI_L2 = EI_L * g.invL, EI_L3 = EI_L2 * g.invL;
+  k.a = E * A * g.invL;
+  k.p11 = k.r11 = k.p22 = k.r22 = k.q15 = k.q51 = k.q55 = 0.0;
+  if (type == OBGPU_BEAM2D_RR) {  // CElementBeam_2D_RR.cpp:104-126
+    k.b = 12.0 * EI_L3;
+    k.p11 = 6.0 * EI_L2;
+    k.r11 = 4.0 * EI_L;
+    k.p22 = -k.p11;
+    k.r22 = k.r11;
+    k.q15 = k.p11;
+    k.q51 = -k.p11;
+    k.q55 = 2.0 * EI_L;
+  } else if (type == OBGPU_BEAM2D_RA) {  // CElementBeam_2D_RA.cpp:92-107
+    k.b = 3.0 * EI_L3;
+    k.p11 = 3.0 * EI_L2;
+    k.r11 = 3.0 * EI_L;
+    k.q51 = -k.p11;
+  } else if (type == OBGPU_BEAM2D_AR) {  // CElementBeam_2D_AR.cpp:92-107
+    k.b = 3.0 * EI_L3;
+    k.p22 = -3.0 * EI_L2;
+    k.r22 = 3.0 * EI_L;
+    k.q15 = -k.p22;
+  } else {  // AA, CElementBeam_2D_AA.cpp:86-94
+    k.b = 0.0;
+  }
+  return k;
+}
+
+// Global blocks in the compact ELEM_K order (see obgpu_internal.h): R B R^T with R the z-rotation (c,s).
+__device__ __forceinline__ void elem_global_k(const ElemLocalK& k, const ElemGeom& g, double ke[ELEM_K]) {
+  const double c = g.c, s = g.s;
+  const double cc = c * c, ss = s * s, cs = c * s;
+  const double g00 = k.a * cc + k.b * ss, g01 = (k.a - k.b) * cs, g11 = k.a * ss + k.b * cc;
+  ke[0] = g00;  ke[1] = g01;  ke[2] = -s * k.p11;  ke[3] = g11;  ke[4] = c * k.p11;  ke[5] = k.r11;
+  ke[6] = g00;  ke[7] = g01;  ke[8] = -s * k.p22;  ke[9] = g11;  ke[10] = c * k.p22; ke[11] = k.r22;
+  ke[12] = -g00; ke[13] = -g01; ke[14] = -s * k.q15;
+  ke[15] = -g01; ke[16] = -g11; ke[17] = c * k.q15;
+  ke[18] = -s * k.q51; ke[19] = c * k.q51; ke[20] = k.q55;
+}
+
+// CLoadDistributedUniform.cpp:33-159.  Outputs:
+//   gl[6]  equivalent nodal loads in global axes (Fx,Fy,Mz at end 0; Fx,Fy,Mz at end 1)
+//   ex[6]  fixed-end stress to add in postProcCalcStress (N,Vy,Mz at face 0; N,Vy,Mz at face 1)
+__device__ __forceinline__ void uniform_load(int type, const ElemGeom& g, double q, double dx, double dy, double gl[6],
+                                             double ex[6]) {
+  const double L = g.L;
+  const double proy_long = g.c * dx + g.s * dy;                 // Az = 0 in plane
+  const double cross_z = g.c * dy - g.s * dx;
+  const double proy_perp = sqrt(1.0 - proy_long * proy_long) * (cross_z < 0 ? 1.0 : -1.0);
+  const double q_t = q * proy_long, q_n = q * proy_perp;
+  const double fx = -q_t * L * 0.5;
+  double f1y, f2y, m1, m2;
+  if (type == OBGPU_BEAM2D_AA) {
+    f1y = q_n * L * 0.5; f2y = f1y; m1 = 0.0; m2 = 0.0;
+  } else if (type == OBGPU_BEAM2D_RR) {
+    f1y = q_n * L * 0.5; f2y = f1y; m1 = q_n * L * L / 12.0; m2 = -m1;
+  } else if (type == OBGPU_BEAM2D_RA) {
+    f1y = q_n * L * (5.0 / 8.0); f2y = q_n * L * (3.0 / 8.0); m1 = q_n * L * L / 8.0; m2 = 0.0;
+  } else {
+    f1y = q_n * L * (3.0 / 8.0); f2y = q_n * L * (5.0 / 8.0); m1 = 0.0; m2 = -(q_n * L * L / 8.0);
+  }
+  ex[0] = -fx; ex[1] = -f1y; ex[2] = -m1;
+  ex[3] = fx;  ex[4] = f2y;  ex[5] = m2;
+  gl[0] = -(g.c * fx - g.s * f1y); gl[1] = -(g.s * fx + g.c * f1y); gl[2] = -m1;
+  gl[3] = -(g.c * fx - g.s * f2y); gl[4] = -(g.s * fx + g.c * f2y); gl[5] = -m2;
+}
+
+// postproc_stress.cpp:86-146 : raw end forces es = K_local * U_local (before the face-0 sign flip).
+// ug = global (ux,uy,rz) of end 0 then end 1.  es = (N,Vy,Mz) at end 0 then end 1.
+__device__ __forceinline__ void elem_end_forces(const ElemLocalK& k, const ElemGeom& g, const double ug[6], double es[6]) {
+  const double u0x = g.c * ug[0] + g.s * ug[1], u0y = -g.s * ug[0] + g.c * ug[1], t0 = ug[2];
+  const double u1x = g.c * ug[3] + g.s * ug[4], u1y = -g.s * ug[3] + g.c * ug[4], t1 = ug[5];
+  es[0] = k.a * (u0x - u1x);
+  es[1] = k.b * (u0y - u1y) + k.p11 * t0 + k.q15 * t1;
+  es[2] = k.p11 * u0y + k.r11 * t0 + k.q51 * u1y + k.q55 * t1;
+  es[3] = k.a * (u1x - u0x);
+  es[4] = k.b * (u1y - u0y) + k.p22 * t1 + k.q51 * t0;
+  es[5] = k.p22 * u1y + k.r22 * t1 + k.q15 * u0y + k.q55 * t0;
+}
+
+}  // namespace obgpu

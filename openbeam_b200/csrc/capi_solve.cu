@@ -1,0 +1,213 @@
+// capi_solve.cu — solveStatic / postProcCalcStress entry points, downloads, the host-buffer sweep.
+#include <algorithm>
+#include <cstring>
+
+#include "ctx.h"
+
+using namespace obgpu;
+
+namespace obgpu {
+int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o);   // capi_general.cu
+int assemble_general(obgpu_ctx* c);                            // capi_general.cu
+int download_general(obgpu_ctx* c, int which, void* host_out, bool& handled);
+}
+
+static int ensure_symbolic(obgpu_ctx* c) {
+  if (!c->uploaded) return fail(c, OBGPU_ESEQUENCE, "no batch uploaded");
+  if (!c->sym.valid) return obgpu_symbolic(c);
+  return OBGPU_OK;
+}
+
+static int alloc_results(obgpu_ctx* c, int64_t L, bool stress) {
+  const Symbolic& s = c->sym;
+  OB_CUDA(c, c->d_Uf.reserve(size_t(L) * std::max<int64_t>(s.nf_tot(), 1)));
+  OB_CUDA(c, c->d_Ff.reserve(size_t(L) * std::max<int64_t>(s.nf_tot(), 1)));
+  OB_CUDA(c, c->d_Fb.reserve(size_t(L) * std::max<int64_t>(s.nb_tot(), 1)));
+  OB_CUDA(c, c->d_info.reserve(size_t(L) * c->hb.S));
+  OB_CUDA(c, c->d_fail.reserve(1));
+  if (stress) OB_CUDA(c, c->d_stress.reserve(size_t(L) * c->hb.Etot() * 12));
+  return OBGPU_OK;
+}
+
+static TinyArgs tiny_args(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai, double* Uf,
+                          double* Fb, double* stress, double* Ff, int32_t* info) {
+  TinyArgs a;
+  a.prog_i = c->d_prog_i.p;
+  a.prog_d = c->d_prog_d.p;
+  a.n_ints = int(c->prog.ints.size());
+  a.n_dbls = int(c->prog.dbls.size());
+  a.n_cases = L;
+  a.case_nl = nl; a.case_q = q; a.case_eai = eai;
+  a.U_f = Uf; a.F_b = Fb; a.stress = stress; a.F_f = Ff; a.info = info;
+  a.fail = c->d_fail.p;
+  return a;
+}
+
+extern "C" {
+
+int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
+  if (!c) return OBGPU_EINVAL;
+  OB_CUDA(c, cudaSetDevice(c->device));
+  int rc = ensure_symbolic(c);
+  if (rc != OBGPU_OK) return rc;
+  obgpu_solve_opts o;
+  o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.reserved = 0;
+  if (opts) o = *opts;
+  if (o.method == OBGPU_BATCHED_LDLT && c->prog.valid) {
+    rc = alloc_results(c, c->L, o.with_stress != 0);
+    if (rc != OBGPU_OK) return rc;
+    OB_CUDA(c, cudaMemsetAsync(c->d_fail.p, 0, sizeof(int32_t), c->stream));
+    TinyArgs a = tiny_args(c, c->L, c->has_case_nl ? c->d_case_nl.p : nullptr, c->has_case_q ? c->d_case_q.p : nullptr,
+                           c->has_case_eai ? c->d_case_eai.p : nullptr, c->d_Uf.p, c->d_Fb.p,
+                           o.with_stress ? c->d_stress.p : nullptr, c->d_Ff.p, c->d_info.p);
+    OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream));
+    OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+    c->t_have[1] = true;
+    c->launches = 1;
+    c->pcg_iters = 0;
+    c->solved = true;
+    c->have_stress = o.with_stress != 0;
+    return OBGPU_OK;
+  }
+  return solve_general(c, o);
+}
+
+int obgpu_assemble(obgpu_ctx* c) {
+  if (!c) return OBGPU_EINVAL;
+  OB_CUDA(c, cudaSetDevice(c->device));
+  int rc = ensure_symbolic(c);
+  if (rc != OBGPU_OK) return rc;
+  return assemble_general(c);
+}
+
+int obgpu_stress(obgpu_ctx* c) {
+  if (!c) return OBGPU_EINVAL;
+  if (!c->solved) return fail(c, OBGPU_ESEQUENCE, "obgpu_stress before obgpu_solve_static");
+  if (c->have_stress) return OBGPU_OK;
+  obgpu_solve_opts o;
+  o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.reserved = 0;
+  return obgpu_solve_static(c, &o);  // the fused kernels recompute; cheap relative to a second pass over HBM
+}
+
+int obgpu_device_ptr(obgpu_ctx* c, int which, void** p) {
+  if (!c || !p) return OBGPU_EINVAL;
+  switch (which) {
+    case OBGPU_RES_UF: *p = c->d_Uf.p; break;
+    case OBGPU_RES_FB: *p = c->d_Fb.p; break;
+    case OBGPU_RES_STRESS: *p = c->d_stress.p; break;
+    case OBGPU_RES_INFO: *p = c->d_info.p; break;
+    case OBGPU_RES_FF: *p = c->d_Ff.p; break;
+    case OBGPU_RES_UB: *p = c->d_Ub.p; break;
+    default: return OBGPU_EINVAL;
+  }
+  return OBGPU_OK;
+}
+
+int obgpu_download(obgpu_ctx* c, int which, void* out) {
+  if (!c || !out) return OBGPU_EINVAL;
+  OB_CUDA(c, cudaSetDevice(c->device));
+  bool handled = false;
+  int rc = download_general(c, which, out, handled);
+  if (handled) return rc;
+  if (!c->solved) return fail(c, OBGPU_ESEQUENCE, "obgpu_download before obgpu_solve_static");
+  const Symbolic& s = c->sym;
+  const void* src = nullptr;
+  size_t bytes = 0;
+  switch (which) {
+    case OBGPU_RES_UF: src = c->d_Uf.p; bytes = size_t(c->L) * s.nf_tot() * 8; break;
+    case OBGPU_RES_FF: src = c->d_Ff.p; bytes = size_t(c->L) * s.nf_tot() * 8; break;
+    case OBGPU_RES_FB: src = c->d_Fb.p; bytes = size_t(c->L) * s.nb_tot() * 8; break;
+    case OBGPU_RES_UB: src = c->d_Ub.p; bytes = size_t(s.nb_tot()) * 8; break;
+    case OBGPU_RES_STRESS:
+      if (!c->have_stress) return fail(c, OBGPU_ESEQUENCE, "stress was not computed (with_stress = 0)");
+      src = c->d_stress.p; bytes = size_t(c->L) * c->hb.Etot() * 12 * 8; break;
+    case OBGPU_RES_INFO: src = c->d_info.p; bytes = size_t(c->L) * c->hb.S * 4; break;
+    default: return fail(c, OBGPU_EINVAL, "unknown result id");
+  }
+  OB_CUDA(c, cudaEventRecord(c->ev[4], c->stream));
+  if (bytes) OB_CUDA(c, cudaMemcpyAsync(out, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+  OB_CUDA(c, cudaEventRecord(c->ev[5], c->stream));
+  c->t_have[2] = true;
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (which == OBGPU_RES_INFO) {
+    const int32_t* info = static_cast<const int32_t*>(out);
+    for (int64_t i = 0; i < c->L * c->hb.S; i++)
+      if (info[i] != 0) return fail(c, OBGPU_ESINGULAR, obgpu_status_string(OBGPU_ESINGULAR));
+  }
+  return OBGPU_OK;
+}
+
+int obgpu_get_timings(const obgpu_ctx* cc, double out[8]) {
+  if (!cc || !out) return OBGPU_EINVAL;
+  obgpu_ctx* c = const_cast<obgpu_ctx*>(cc);
+  for (int i = 0; i < 8; i++) out[i] = 0;
+  out[0] = c->t_symbolic_ms;
+  float ms = 0;
+  if (c->t_have[0] && cudaEventSynchronize(c->ev[1]) == cudaSuccess && cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]) == cudaSuccess) out[4] = ms;
+  if (c->t_have[1] && cudaEventSynchronize(c->ev[3]) == cudaSuccess && cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]) == cudaSuccess) out[2] = ms;
+  if (c->t_have[2] && cudaEventSynchronize(c->ev[5]) == cudaSuccess && cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]) == cudaSuccess) out[5] = ms;
+  if (c->t_have[3] && cudaEventSynchronize(c->ev[7]) == cudaSuccess && cudaEventElapsedTime(&ms, c->ev[6], c->ev[7]) == cudaSuccess) out[1] = ms;
+  out[6] = c->launches;
+  out[7] = c->pcg_iters;
+  cudaGetLastError();
+  return OBGPU_OK;
+}
+
+// Host-buffer sweep: chunks of cases stream H2D -> fused kernel -> D2H over NSLOT streams so the PCIe
+// copies in both directions overlap each other and the compute.
+int obgpu_solve_cases_host(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai, double* U_f,
+                           double* F_b, double* stress, int32_t* info) {
+  if (!c) return OBGPU_EINVAL;
+  OB_CUDA(c, cudaSetDevice(c->device));
+  int rc = ensure_symbolic(c);
+  if (rc != OBGPU_OK) return rc;
+  if (!c->prog.valid || c->hb.S != 1)
+    return fail(c, OBGPU_EUNSUPPORTED, "obgpu_solve_cases_host needs one shared small topology (use update_cases + solve_static)");
+  if (L < 1) return fail(c, OBGPU_EINVAL, "n_cases must be >= 1");
+  const int64_t NL = c->hb.NLtot(), EL = c->hb.ELtot(), E = c->hb.Etot(), nf = c->sym.nf_tot(), nb = c->sym.nb_tot();
+  if (NL == 0) nl = nullptr;
+  if (EL == 0) q = nullptr;
+  const int64_t CH = std::min<int64_t>(L, 1 << 17);
+  OB_CUDA(c, c->d_fail.reserve(1));
+  OB_CUDA(c, cudaMemsetAsync(c->d_fail.p, 0, sizeof(int32_t), c->stream));
+  OB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
+  for (int i = 0; i < obgpu_ctx::NSLOT; i++) {
+    auto& sl = c->slot[i];
+    if (nl) OB_CUDA(c, sl.nl.reserve(size_t(CH) * NL));
+    if (q) OB_CUDA(c, sl.q.reserve(size_t(CH) * EL));
+    if (eai) OB_CUDA(c, sl.eai.reserve(size_t(CH) * 3 * E));
+    OB_CUDA(c, sl.Uf.reserve(size_t(CH) * std::max<int64_t>(nf, 1)));
+    OB_CUDA(c, sl.Fb.reserve(size_t(CH) * std::max<int64_t>(nb, 1)));
+    if (stress) OB_CUDA(c, sl.stress.reserve(size_t(CH) * E * 12));
+    OB_CUDA(c, sl.info.reserve(size_t(CH)));
+    OB_CUDA(c, cudaStreamWaitEvent(c->slot_stream[i], c->ev[0], 0));
+  }
+  int64_t launches = 0;
+  for (int64_t c0 = 0, k = 0; c0 < L; c0 += CH, k++) {
+    const int64_t n = std::min(CH, L - c0);
+    const int si = int(k % obgpu_ctx::NSLOT);
+    auto& sl = c->slot[si];
+    cudaStream_t st = c->slot_stream[si];
+    if (nl) OB_CUDA(c, cudaMemcpyAsync(sl.nl.p, nl + c0 * NL, size_t(n) * NL * 8, cudaMemcpyHostToDevice, st));
+    if (q) OB_CUDA(c, cudaMemcpyAsync(sl.q.p, q + c0 * EL, size_t(n) * EL * 8, cudaMemcpyHostToDevice, st));
+    if (eai) OB_CUDA(c, cudaMemcpyAsync(sl.eai.p, eai + c0 * 3 * E, size_t(n) * 3 * E * 8, cudaMemcpyHostToDevice, st));
+    TinyArgs a = tiny_args(c, n, nl ? sl.nl.p : nullptr, q ? sl.q.p : nullptr, eai ? sl.eai.p : nullptr, sl.Uf.p, sl.Fb.p,
+                           stress ? sl.stress.p : nullptr, nullptr, sl.info.p);
+    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st));
+    launches++;
+    if (U_f && nf) OB_CUDA(c, cudaMemcpyAsync(U_f + c0 * nf, sl.Uf.p, size_t(n) * nf * 8, cudaMemcpyDeviceToHost, st));
+    if (F_b && nb) OB_CUDA(c, cudaMemcpyAsync(F_b + c0 * nb, sl.Fb.p, size_t(n) * nb * 8, cudaMemcpyDeviceToHost, st));
+    if (stress) OB_CUDA(c, cudaMemcpyAsync(stress + c0 * E * 12, sl.stress.p, size_t(n) * E * 96, cudaMemcpyDeviceToHost, st));
+    if (info) OB_CUDA(c, cudaMemcpyAsync(info + c0, sl.info.p, size_t(n) * 4, cudaMemcpyDeviceToHost, st));
+  }
+  int32_t failed = 0;
+  for (int i = 0; i < obgpu_ctx::NSLOT; i++) OB_CUDA(c, cudaStreamSynchronize(c->slot_stream[i]));
+  OB_CUDA(c, cudaMemcpyAsync(&failed, c->d_fail.p, 4, cudaMemcpyDeviceToHost, c->stream));
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->launches = double(launches);
+  if (failed) return fail(c, OBGPU_ESINGULAR, obgpu_status_string(OBGPU_ESINGULAR));
+  return OBGPU_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,49 @@
+// ctx.h — the opaque obgpu_ctx.
+#pragma once
+#include "kernels.h"
+
+struct obgpu_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  static constexpr int NSLOT = 3;
+  cudaStream_t slot_stream[NSLOT] = {nullptr, nullptr, nullptr};
+  cudaEvent_t ev[8] = {};
+  std::string err;
+
+  obgpu::HostBatch hb;
+  obgpu::Symbolic sym;
+  obgpu::TinyProgram prog;
+  bool uploaded = false;
+  int64_t L = 1;
+  bool has_case_nl = false, has_case_q = false, has_case_eai = false;
+
+  obgpu::DevBuf<double> d_case_nl, d_case_q, d_case_eai;
+  obgpu::DevBuf<int32_t> d_prog_i;
+  obgpu::DevBuf<double> d_prog_d;
+  obgpu::DevBuf<double> d_Uf, d_Fb, d_stress, d_Ff, d_Ub;
+  obgpu::DevBuf<int32_t> d_info;
+  obgpu::DevBuf<int32_t> d_fail;  // [1] OR of per-system failures of the last solve
+  bool solved = false, have_stress = false;
+
+  // chunk slots of obgpu_solve_cases_host
+  struct Slot {
+    obgpu::DevBuf<double> nl, q, eai, Uf, Fb, stress;
+    obgpu::DevBuf<int32_t> info;
+  } slot[NSLOT];
+
+  double t_symbolic_ms = 0;
+  bool t_have[6] = {false, false, false, false, false, false};  // event pairs recorded
+  double launches = 0, pcg_iters = 0;
+};
+
+namespace obgpu {
+int fail(obgpu_ctx* c, int code, const std::string& msg);
+int cuda_fail(obgpu_ctx* c, cudaError_t e, const char* where);
+}  // namespace obgpu
+
+#define OB_CUDA(c, call)                                             \
+  do {                                                               \
+    cudaError_t _e = (call);                                         \
+    if (_e != cudaSuccess) return obgpu::cuda_fail(c, _e, #call);    \
+  } while (0)

@@ -1,0 +1,101 @@
+// obgpu_internal.h — internal declarations of libobgpu (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/obgpu.h"
+
+namespace obgpu {
+
+// Compact per-element global stiffness ("ELEM_K", 21 doubles): 2D beam elements only touch the
+// node DOFs {DX,DY,RZ} (= 6x6 indices 0,1,5), so of the three 6x6 blocks the reference builds
+// (CElement.h:37-41) only 3x3 sub-blocks are ever non-zero:
+//   [0..5]   K11 upper: (0,0)(0,1)(0,5)(1,1)(1,5)(5,5)
+//   [6..11]  K22 upper, same order
+//   [12..20] K12 full row-major over {0,1,5}x{0,1,5}
+constexpr int ELEM_K = 21;
+constexpr int TINY_MAX_NF = 12;   // thread-per-system kernel: K_ff lives in registers up to this size
+constexpr int TINY_MAX_N = 48;
+constexpr int TINY_MAX_E = 32;
+
+template <class T>
+struct DevBuf {  // owning device buffer (grow-only)
+  T* p = nullptr;
+  size_t cap = 0;
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  cudaError_t reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    release();
+    if (n == 0) return cudaSuccess;
+    cudaError_t e = cudaMalloc((void**)&p, n * sizeof(T));
+    if (e == cudaSuccess) cap = n;
+    return e;
+  }
+  cudaError_t upload(const T* h, size_t n, cudaStream_t s) {
+    cudaError_t e = reserve(n);
+    if (e != cudaSuccess || n == 0) return e;
+    return cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s);
+  }
+  cudaError_t upload(const std::vector<T>& v, cudaStream_t s) { return upload(v.data(), v.size(), s); }
+};
+
+// Host copy of the uploaded batch (CSR-of-structures SoA; see obgpu_batch_desc)
+struct HostBatch {
+  int64_t S = 0, L = 1;
+  std::vector<int64_t> node_off, elem_off, con_off, nload_off, eload_off;
+  std::vector<double> node_xy, node_rotz, elem_EAI, con_val, nload_val, eload_q, eload_dir;
+  std::vector<uint32_t> elem_nodes, con_node, nload_node, eload_elem;
+  std::vector<uint8_t> elem_type, con_dof, nload_dof;
+  bool has_rotz = false;
+  int64_t Ntot() const { return node_off.empty() ? 0 : node_off.back(); }
+  int64_t Etot() const { return elem_off.empty() ? 0 : elem_off.back(); }
+  int64_t Ctot() const { return con_off.empty() ? 0 : con_off.back(); }
+  int64_t NLtot() const { return nload_off.empty() ? 0 : nload_off.back(); }
+  int64_t ELtot() const { return eload_off.empty() ? 0 : eload_off.back(); }
+};
+
+// Result of the symbolic phase K3 (all integer; once per topology).
+struct Symbolic {
+  bool valid = false;
+  std::vector<int64_t> dof_off, free_off, bnd_off, nnz_off, tri_off;  // [S+1]
+  std::vector<int32_t> dof_node, dof_id;     // [n_tot]
+  std::vector<int32_t> dof_type;             // [n_tot] >=0: free index, <0: -(bounded index)-1
+  std::vector<int32_t> free_idx, bnd_idx;    // [nf_tot], [nb_tot]
+  std::vector<int32_t> dof_index;            // [6*Ntot]
+  std::vector<int32_t> k_rowptr;             // [n_tot+S]
+  std::vector<int32_t> k_col;                // [nnz_tot]
+  std::vector<int32_t> tri_nnz;              // [T_tot] triplet -> nnz slot (local to structure)
+  std::vector<int32_t> tri_src;              // [T_tot] triplet -> e_local*21+cid, or -1 (structural zero)
+  std::vector<double> U_b;                   // [nb_tot]
+  // K4 segmented-reduction program: for global nnz slot g, sources seg_src[seg_ptr[g]..seg_ptr[g+1])
+  // (global element index*21+cid, or -1), in the reference's triplet (= element) order.
+  std::vector<int64_t> seg_ptr;              // [nnz_tot+1]
+  std::vector<int64_t> seg_src;              // [T_tot]
+  int64_t n_tot() const { return dof_off.empty() ? 0 : dof_off.back(); }
+  int64_t nf_tot() const { return free_off.empty() ? 0 : free_off.back(); }
+  int64_t nb_tot() const { return bnd_off.empty() ? 0 : bnd_off.back(); }
+  int64_t nnz_tot() const { return nnz_off.empty() ? 0 : nnz_off.back(); }
+  int64_t T_tot() const { return tri_off.empty() ? 0 : tri_off.back(); }
+};
+
+// "Program" of one shared topology for the thread-per-system kernel (uploaded as one int32 blob +
+// one double blob).  Layout documented in kernels_tiny.cu.
+struct TinyProgram {
+  bool valid = false;
+  int N = 0, E = 0, n = 0, nf = 0, nb = 0, NL = 0, EL = 0;
+  std::vector<int32_t> ints;
+  std::vector<double> dbls;
+};
+
+int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want_pattern);
+int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& prog, std::string& err);
+
+}  // namespace obgpu

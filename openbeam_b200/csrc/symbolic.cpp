@@ -1,0 +1,233 @@
+// symbolic.cpp — K3, the integer "symbolic phase" of libobgpu (host, once per topology).
+//
+// Produces what the reference rebuilds on every assembleProblem() call:
+//   * DOF numbering      (updateNodeConnections + updateListDoFs, src/CFiniteElementProblem.cpp:179-245,
+//                         with the per-end global DOF masks of CElement::getGlobalDoFs, src/CElement.cpp:192-247)
+//   * free/bounded split (src/CFiniteElementProblem_assemble.cpp:74-99) and U_b (:304-313)
+//   * the pattern of K   (upper triangle, Eigen CSC order == CSR of the lower triangle; :123-233)
+//   * the element->nnz map that turns the reference's triplet scatter into a deterministic
+//     segmented reduction (sources listed per nnz in the reference's triplet order).
+// Integer results must match the reference bit-exactly (tests compare them with the oracle).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "obgpu_internal.h"
+
+namespace obgpu {
+
+// 6x6 index -> compact index inside {DX,DY,RZ} (0,1,5 -> 0,1,2), -1 otherwise
+static inline int c3(int d) { return d == 0 ? 0 : d == 1 ? 1 : d == 5 ? 2 : -1; }
+// compact id inside ELEM_K of entry (r,c) of block j (0=K11, 1=K22, 2=K12); -1 = structural zero
+static inline int elemk_cid(int j, int r, int c) {
+  const int a = c3(r), b = c3(c);
+  if (a < 0 || b < 0) return -1;
+  if (j == 2) return 12 + a * 3 + b;
+  static const int up[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+  return (j == 0 ? 0 : 6) + up[a][b];
+}
+
+// Global DOF masks of the two element ends (bit d = DOF d used), CElement.cpp:192-247 specialised to
+// the four beam types' local masks (getLocalDoFs: RR.cpp:129-139, RA.cpp:110-119, AR.cpp:110-119, AA.cpp:97-106).
+// Orientation as internals.cpp:30-123 with z = 0: X = p12 * (1/len), Z = (0,0,1), Y = Z x X.
+static bool element_end_masks(const double* p1, const double* p2, int type, unsigned& m0, unsigned& m1) {
+  const double dx = p2[0] - p1[0], dy = p2[1] - p1[1], dz = 0.0;
+  const double len = std::sqrt(dx * dx + dy * dy + dz * dz);
+  double R[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  if (len > 0) {
+    const double inv = 1 / len;
+    const double X0 = dx * inv, X1 = dy * inv, X2 = dz * inv;
+    const double Y0 = 0 * X2 - 1 * X1, Y1 = 1 * X0 - 0 * X2, Y2 = 0 * X1 - 0 * X0;
+    R[0][0] = X0; R[0][1] = Y0; R[0][2] = 0;
+    R[1][0] = X1; R[1][1] = Y1; R[1][2] = 0;
+    R[2][0] = X2; R[2][1] = Y2; R[2][2] = 1;
+  }
+  bool nz[3][3];
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 3; c++) nz[r][c] = std::fabs(R[r][c]) > 1e-10;
+  auto glob = [&](unsigned local) {
+    unsigned g = 0;
+    for (int blk = 0; blk < 2; blk++) {
+      const unsigned l = (local >> (3 * blk)) & 7u;
+      unsigned o = 0;
+      if (l == 7u) {
+        o = 7u;
+      } else {
+        for (int gi = 0; gi < 3; gi++)
+          if (((l & 1u) && nz[gi][0]) || ((l & 2u) && nz[gi][1]) || ((l & 4u) && nz[gi][2])) o |= 1u << gi;
+      }
+      g |= o << (3 * blk);
+    }
+    return g;
+  };
+  const unsigned R_ = 0x23 /*DX,DY,RZ*/, A2 = 0x03 /*DX,DY*/, A1 = 0x01 /*DX*/;
+  unsigned l0, l1;
+  switch (type) {
+    case OBGPU_BEAM2D_RR: l0 = R_; l1 = R_; break;
+    case OBGPU_BEAM2D_RA: l0 = R_; l1 = A2; break;
+    case OBGPU_BEAM2D_AR: l0 = A2; l1 = R_; break;
+    case OBGPU_BEAM2D_AA: l0 = A1; l1 = A1; break;
+    default: return false;
+  }
+  m0 = glob(l0);
+  m1 = glob(l1);
+  return true;
+}
+
+int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want_pattern) {
+  const int64_t S = hb.S;
+  sym = Symbolic();
+  sym.dof_off.assign(S + 1, 0);
+  sym.free_off.assign(S + 1, 0);
+  sym.bnd_off.assign(S + 1, 0);
+  sym.nnz_off.assign(S + 1, 0);
+  sym.tri_off.assign(S + 1, 0);
+  sym.dof_index.assign(size_t(6) * hb.Ntot(), -1);
+  sym.seg_ptr.assign(1, 0);
+  std::vector<unsigned> node_mask;
+  std::vector<int64_t> keys;       // per-structure triplet keys col*n+row
+  std::vector<int64_t> uniq;
+  std::vector<int32_t> order;
+
+  for (int64_t s = 0; s < S; s++) {
+    const int64_t n0 = hb.node_off[s], N = hb.node_off[s + 1] - n0;
+    const int64_t e0 = hb.elem_off[s], E = hb.elem_off[s + 1] - e0;
+    // ---- node DOF masks (updateNodeConnections) ----
+    node_mask.assign(N, 0u);
+    for (int64_t e = 0; e < E; e++) {
+      const uint32_t a = hb.elem_nodes[2 * (e0 + e)], b = hb.elem_nodes[2 * (e0 + e) + 1];
+      if (a >= N || b >= N) {
+        err = "element node index out of range (ASSERT_(conected_nodes_ids[k] < nNodes))";
+        return OBGPU_EINVAL;
+      }
+      unsigned m0, m1;
+      if (!element_end_masks(&hb.node_xy[2 * (n0 + a)], &hb.node_xy[2 * (n0 + b)], hb.elem_type[e0 + e], m0, m1)) {
+        err = "unknown element type";
+        return OBGPU_EINVAL;
+      }
+      node_mask[a] |= m0;
+      node_mask[b] |= m1;
+    }
+    // ---- numbering (updateListDoFs): node-major, dof-minor ----
+    const int64_t k0 = sym.dof_off[s];
+    int32_t n = 0;
+    for (int64_t i = 0; i < N; i++)
+      for (int d = 0; d < 6; d++)
+        if (node_mask[i] & (1u << d)) {
+          sym.dof_node.push_back(int32_t(i));
+          sym.dof_id.push_back(d);
+          sym.dof_index[6 * (n0 + i) + d] = n++;
+        }
+    if (n == 0) {
+      err = "structure without DOFs (ASSERT_(nDOFs > 0))";
+      return OBGPU_EINVAL;
+    }
+    sym.dof_off[s + 1] = k0 + n;
+    // ---- constraints -> partition (assemble.cpp:74-99) and U_b (:304-313) ----
+    std::vector<char> bounded(n, 0);
+    std::vector<double> cval(n, 0.0);
+    for (int64_t c = hb.con_off[s]; c < hb.con_off[s + 1]; c++) {
+      if (hb.con_node[c] >= N || hb.con_dof[c] > 5) {
+        err = "constraint node/dof out of range";
+        return OBGPU_EINVAL;
+      }
+      const int32_t k = sym.dof_index[6 * (n0 + hb.con_node[c]) + hb.con_dof[c]];
+      if (k >= 0) {
+        bounded[k] = 1;
+        cval[k] = hb.con_val[c];  // insertConstraint overwrites
+      }
+    }
+    int32_t nf = 0, nb = 0;
+    for (int32_t k = 0; k < n; k++) {
+      if (bounded[k]) {
+        sym.bnd_idx.push_back(k);
+        sym.U_b.push_back(cval[k]);
+        sym.dof_type.push_back(-(nb++) - 1);
+      } else {
+        sym.free_idx.push_back(k);
+        sym.dof_type.push_back(nf++);
+      }
+    }
+    sym.free_off[s + 1] = sym.free_off[s] + nf;
+    sym.bnd_off[s + 1] = sym.bnd_off[s] + nb;
+    for (int64_t l = hb.nload_off[s]; l < hb.nload_off[s + 1]; l++)
+      if (hb.nload_node[l] >= N || hb.nload_dof[l] > 5) {
+        err = "node load node/dof out of range";
+        return OBGPU_EINVAL;
+      }
+    for (int64_t l = hb.eload_off[s]; l < hb.eload_off[s + 1]; l++)
+      if (hb.eload_elem[l] >= E) {
+        err = "element load element index out of range";
+        return OBGPU_EINVAL;
+      }
+    if (!want_pattern) {
+      sym.nnz_off[s + 1] = sym.nnz_off[s];
+      sym.tri_off[s + 1] = sym.tri_off[s];
+      continue;
+    }
+    // ---- triplets in the reference's emission order (assemble.cpp:123-223) ----
+    keys.clear();
+    const size_t t0 = sym.tri_src.size();
+    for (int64_t e = 0; e < E; e++) {
+      const uint32_t nd[2] = {hb.elem_nodes[2 * (e0 + e)], hb.elem_nodes[2 * (e0 + e) + 1]};
+      static const int bi[3] = {0, 1, 0}, bj[3] = {0, 1, 1};
+      for (int j = 0; j < 3; j++) {
+        const uint32_t in = nd[bi[j]], jn = nd[bj[j]];
+        const int32_t* ri = &sym.dof_index[6 * (n0 + in)];
+        const int32_t* ci = &sym.dof_index[6 * (n0 + jn)];
+        for (int r = 0; r < 6; r++) {
+          if (ri[r] < 0) continue;
+          for (int c = (in == jn ? r : 0); c < 6; c++) {
+            if (ci[c] < 0) continue;
+            const int64_t lo = std::min(ri[r], ci[c]), hi = std::max(ri[r], ci[c]);
+            keys.push_back(hi * int64_t(n) + lo);  // CSC(upper): column = hi, row = lo
+            const int cid = elemk_cid(j, r, c);
+            sym.tri_src.push_back(cid < 0 ? -1 : int32_t(e * ELEM_K + cid));
+          }
+        }
+      }
+    }
+    const size_t T = keys.size();
+    sym.tri_off[s + 1] = sym.tri_off[s] + int64_t(T);
+    // ---- pattern: unique keys sorted by (col,row) == Eigen's compressed CSC after setFromTriplets ----
+    uniq = keys;
+    std::sort(uniq.begin(), uniq.end());
+    uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+    const int64_t z0 = sym.nnz_off[s];
+    const int64_t nnz = int64_t(uniq.size());
+    sym.nnz_off[s + 1] = z0 + nnz;
+    {
+      const size_t rp0 = sym.k_rowptr.size();
+      sym.k_rowptr.resize(rp0 + n + 1, 0);
+      int32_t* rp = &sym.k_rowptr[rp0];
+      for (int64_t u : uniq) {
+        rp[u / n + 1]++;
+        sym.k_col.push_back(int32_t(u % n));
+      }
+      for (int32_t k = 0; k < n; k++) rp[k + 1] += rp[k];
+    }
+    // ---- triplet -> slot, and per-slot source lists in triplet order (stable counting sort) ----
+    const size_t tn0 = sym.tri_nnz.size();
+    sym.tri_nnz.resize(tn0 + T);
+    std::vector<int64_t> cnt(nnz + 1, 0);
+    for (size_t t = 0; t < T; t++) {
+      const int32_t slot = int32_t(std::lower_bound(uniq.begin(), uniq.end(), keys[t]) - uniq.begin());
+      sym.tri_nnz[tn0 + t] = slot;
+      cnt[slot + 1]++;
+    }
+    for (int64_t g = 0; g < nnz; g++) cnt[g + 1] += cnt[g];
+    const int64_t sp0 = sym.seg_ptr.back();
+    for (int64_t g = 1; g <= nnz; g++) sym.seg_ptr.push_back(sp0 + cnt[g]);
+    const size_t ss0 = sym.seg_src.size();
+    sym.seg_src.resize(ss0 + T);
+    std::vector<int64_t> fill(cnt.begin(), cnt.end() - 1);
+    for (size_t t = 0; t < T; t++) {
+      const int32_t src = sym.tri_src[t0 + t];
+      sym.seg_src[ss0 + fill[sym.tri_nnz[tn0 + t]]++] = src < 0 ? -1 : int64_t(e0) * ELEM_K + src;
+    }
+  }
+  sym.valid = true;
+  return OBGPU_OK;
+}
+
+}  // namespace obgpu
