@@ -107,6 +107,9 @@ enum {
   OBGPU_RES_ELEM_K = 7   /* [LK][Etot][21]     compact global element blocks        */
 };
 
+/* device >= 0: CUDA ordinal (must be sm_100).  OBGPU_DEVICE_NONE: symbolic-only ctx — batch_upload,
+ * symbolic, get_sizes/offsets/symbolic work (integer host phase K3); every compute call returns OBGPU_ECUDA. */
+enum { OBGPU_DEVICE_NONE = -1 };
 int obgpu_create(int device, obgpu_ctx** out);
 void obgpu_destroy(obgpu_ctx*);
 const char* obgpu_last_error(const obgpu_ctx*);

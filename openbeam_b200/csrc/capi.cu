@@ -41,6 +41,12 @@ const char* obgpu_status_string(int s) {
 int obgpu_create(int device, obgpu_ctx** out) {
   if (!out) return OBGPU_EINVAL;
   *out = nullptr;
+  if (device == OBGPU_DEVICE_NONE) {  // symbolic-only ctx: integer host phase works, every compute call fails
+    auto* c = new obgpu_ctx;
+    c->device = OBGPU_DEVICE_NONE;
+    *out = c;
+    return OBGPU_OK;
+  }
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
     cudaGetLastError();
@@ -67,6 +73,10 @@ int obgpu_create(int device, obgpu_ctx** out) {
 
 void obgpu_destroy(obgpu_ctx* c) {
   if (!c) return;
+  if (c->device == OBGPU_DEVICE_NONE) {
+    delete c;
+    return;
+  }
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   for (auto& e : c->ev)
@@ -90,6 +100,8 @@ static int upload_cases(obgpu_ctx* c, int64_t L, const double* nl, const double*
   c->has_case_nl = nl != nullptr && c->hb.NLtot() > 0;
   c->has_case_q = q != nullptr && c->hb.ELtot() > 0;
   c->has_case_eai = eai != nullptr;
+  c->solved = false;
+  if (c->device == OBGPU_DEVICE_NONE) return OBGPU_OK;
   OB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
   if (c->has_case_nl) OB_CUDA(c, c->d_case_nl.upload(nl, size_t(L) * c->hb.NLtot(), c->stream));
   if (c->has_case_q) OB_CUDA(c, c->d_case_q.upload(q, size_t(L) * c->hb.ELtot(), c->stream));
@@ -102,7 +114,7 @@ static int upload_cases(obgpu_ctx* c, int64_t L, const double* nl, const double*
 
 int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   if (!c || !d) return OBGPU_EINVAL;
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_DEVICE(c);
   if (d->n_structures < 1) return fail(c, OBGPU_EINVAL, "n_structures must be >= 1");
   if (!d->node_off || !d->elem_off || !d->con_off || !d->nload_off || !d->eload_off)
     return fail(c, OBGPU_EINVAL, "offset arrays are mandatory");
@@ -159,14 +171,14 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
 int obgpu_update_cases(obgpu_ctx* c, int64_t n_cases, const double* nl, const double* q, const double* eai) {
   if (!c) return OBGPU_EINVAL;
   if (!c->uploaded) return fail(c, OBGPU_ESEQUENCE, "obgpu_update_cases before obgpu_batch_upload");
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_DEVICE(c);
   return upload_cases(c, n_cases, nl, q, eai);
 }
 
 int obgpu_symbolic(obgpu_ctx* c) {
   if (!c) return OBGPU_EINVAL;
   if (!c->uploaded) return fail(c, OBGPU_ESEQUENCE, "obgpu_symbolic before obgpu_batch_upload");
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_DEVICE(c);
   const auto t0 = std::chrono::steady_clock::now();
   std::string err;
   int rc = run_symbolic(c->hb, c->sym, err, true);
@@ -180,15 +192,18 @@ int obgpu_symbolic(obgpu_ctx* c) {
         return fail(c, OBGPU_EINVAL, "zero-length element (ASSERT_(L > 0))");
     }
   c->prog = TinyProgram();
+  const bool dev = c->device != OBGPU_DEVICE_NONE;
   if (c->hb.S == 1) {
     std::string perr;
-    if (build_tiny_program(c->hb, c->sym, c->prog, perr) == OBGPU_OK) {
+    if (build_tiny_program(c->hb, c->sym, c->prog, perr) == OBGPU_OK && dev) {
       OB_CUDA(c, c->d_prog_i.upload(c->prog.ints, c->stream));
       OB_CUDA(c, c->d_prog_d.upload(c->prog.dbls, c->stream));
     }
   }
-  OB_CUDA(c, c->d_Ub.upload(c->sym.U_b, c->stream));
-  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (dev) {
+    OB_CUDA(c, c->d_Ub.upload(c->sym.U_b, c->stream));
+    OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
   c->t_symbolic_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return OBGPU_OK;
 }
@@ -237,13 +252,14 @@ int obgpu_get_symbolic(const obgpu_ctx* c, int which, int32_t* out) {
 
 int obgpu_get_stream(obgpu_ctx* c, void** s) {
   if (!c || !s) return OBGPU_EINVAL;
+  OB_NEED_DEVICE(c);
   *s = (void*)c->stream;
   return OBGPU_OK;
 }
 
 int obgpu_synchronize(obgpu_ctx* c) {
   if (!c) return OBGPU_EINVAL;
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_NEED_DEVICE(c);
   OB_CUDA(c, cudaStreamSynchronize(c->stream));
   for (auto s : c->slot_stream) OB_CUDA(c, cudaStreamSynchronize(s));
   return OBGPU_OK;

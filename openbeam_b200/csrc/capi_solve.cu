@@ -47,7 +47,7 @@ extern "C" {
 
 int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
   if (!c) return OBGPU_EINVAL;
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_NEED_DEVICE(c);
   int rc = ensure_symbolic(c);
   if (rc != OBGPU_OK) return rc;
   obgpu_solve_opts o;
@@ -75,7 +75,7 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
 
 int obgpu_assemble(obgpu_ctx* c) {
   if (!c) return OBGPU_EINVAL;
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_NEED_DEVICE(c);
   int rc = ensure_symbolic(c);
   if (rc != OBGPU_OK) return rc;
   return assemble_general(c);
@@ -92,6 +92,7 @@ int obgpu_stress(obgpu_ctx* c) {
 
 int obgpu_device_ptr(obgpu_ctx* c, int which, void** p) {
   if (!c || !p) return OBGPU_EINVAL;
+  OB_NEED_DEVICE(c);
   switch (which) {
     case OBGPU_RES_UF: *p = c->d_Uf.p; break;
     case OBGPU_RES_FB: *p = c->d_Fb.p; break;
@@ -106,7 +107,7 @@ int obgpu_device_ptr(obgpu_ctx* c, int which, void** p) {
 
 int obgpu_download(obgpu_ctx* c, int which, void* out) {
   if (!c || !out) return OBGPU_EINVAL;
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_NEED_DEVICE(c);
   bool handled = false;
   int rc = download_general(c, which, out, handled);
   if (handled) return rc;
@@ -159,7 +160,7 @@ int obgpu_get_timings(const obgpu_ctx* cc, double out[8]) {
 int obgpu_solve_cases_host(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai, double* U_f,
                            double* F_b, double* stress, int32_t* info) {
   if (!c) return OBGPU_EINVAL;
-  OB_CUDA(c, cudaSetDevice(c->device));
+  OB_NEED_DEVICE(c);
   int rc = ensure_symbolic(c);
   if (rc != OBGPU_OK) return rc;
   if (!c->prog.valid || c->hb.S != 1)

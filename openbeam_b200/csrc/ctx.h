@@ -47,3 +47,15 @@ int cuda_fail(obgpu_ctx* c, cudaError_t e, const char* where);
     cudaError_t _e = (call);                                         \
     if (_e != cudaSuccess) return obgpu::cuda_fail(c, _e, #call);    \
   } while (0)
+// select the ctx's device; a symbolic-only ctx (OBGPU_DEVICE_NONE) skips it
+#define OB_DEVICE(c)                                                      \
+  do {                                                                    \
+    if ((c)->device != OBGPU_DEVICE_NONE) OB_CUDA(c, cudaSetDevice((c)->device)); \
+  } while (0)
+// compute entry points: no device => fail loudly (there is no CPU fallback)
+#define OB_NEED_DEVICE(c)                                                                                  \
+  do {                                                                                                     \
+    if ((c)->device == OBGPU_DEVICE_NONE)                                                                  \
+      return obgpu::fail(c, OBGPU_ECUDA, "symbolic-only ctx: this call needs an sm_100 device (no CPU fallback)"); \
+    OB_CUDA(c, cudaSetDevice((c)->device));                                                                \
+  } while (0)

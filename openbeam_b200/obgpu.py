@@ -1,0 +1,300 @@
+"""ctypes binding of libobgpu.so (include/obgpu.h) plus the host-side mirror of the reference's
+problem interface for the static-solve path:
+
+    CFiniteElementProblem::assembleProblem()     libopenbeam/include/openbeam/CFiniteElementProblem.h:435
+    CFiniteElementProblem::solveStatic()         ...:444-446
+    CFiniteElementProblem::postProcCalcStress()  ...:453-454
+
+No arithmetic of the path happens in this file: it packs SoA arrays, calls the C ABI and wraps
+device results.  There is NO CPU fallback — if libobgpu.so is missing or no sm_100 device is
+usable, every entry point raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import weakref
+
+import numpy as np
+
+from .structure import Structure
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libobgpu.so")
+
+OK, EINVAL, ECUDA, ESINGULAR, ENOTCONVERGED, EUNSUPPORTED, ESEQUENCE = range(7)
+BATCHED_LDLT, PCG_JACOBI, PCG_BJ3, PCG_IC0 = range(4)
+(RES_UF, RES_FB, RES_STRESS, RES_INFO, RES_FF, RES_UB, RES_KVAL, RES_ELEM_K) = range(8)
+(SYM_DOF_NODE, SYM_DOF_ID, SYM_FREE, SYM_BOUNDED, SYM_DOF_INDEX, SYM_K_ROWPTR, SYM_K_COL, SYM_TRI_NNZ) = range(8)
+OFF_DOF, OFF_FREE, OFF_BOUNDED, OFF_NNZ, OFF_TRIPLET = range(5)
+SIZE_NAMES = ("S", "L", "Ntot", "Etot", "n_tot", "nf_tot", "nb_tot", "T_tot", "nnz_tot", "Ctot", "NLtot", "ELtot")
+
+# every symbol include/obgpu.h declares (tests check the library exports all of them)
+ABI_SYMBOLS = (
+    "obgpu_create", "obgpu_destroy", "obgpu_last_error", "obgpu_status_string", "obgpu_host_alloc",
+    "obgpu_host_free", "obgpu_batch_upload", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
+    "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
+    "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host",
+    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_get_stream",
+)
+
+
+class BatchDesc(C.Structure):
+    _fields_ = [
+        ("n_structures", C.c_int64),
+        ("node_off", C.c_void_p), ("elem_off", C.c_void_p), ("con_off", C.c_void_p),
+        ("nload_off", C.c_void_p), ("eload_off", C.c_void_p),
+        ("node_xy", C.c_void_p), ("node_rotz", C.c_void_p),
+        ("elem_nodes", C.c_void_p), ("elem_type", C.c_void_p), ("elem_EAI", C.c_void_p),
+        ("con_node", C.c_void_p), ("con_dof", C.c_void_p), ("con_val", C.c_void_p),
+        ("nload_node", C.c_void_p), ("nload_dof", C.c_void_p), ("nload_val", C.c_void_p),
+        ("eload_elem", C.c_void_p), ("eload_q", C.c_void_p), ("eload_dir", C.c_void_p),
+        ("n_cases", C.c_int64),
+        ("case_nload_val", C.c_void_p), ("case_eload_q", C.c_void_p), ("case_elem_EAI", C.c_void_p),
+    ]
+
+
+class SolveOpts(C.Structure):
+    _fields_ = [("method", C.c_int), ("with_stress", C.c_int), ("rtol", C.c_double), ("max_iter", C.c_int),
+                ("reserved", C.c_int)]
+
+
+class ObgpuError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(msg)
+        self.status = status
+
+
+_LIB = None
+
+
+def lib():
+    """Load libobgpu.so (fails loudly when it has not been built: no fallback)."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise ObgpuError(ECUDA, f"{LIB_PATH} not built — run `python -c 'import __graft_entry__ as g; g.build()'`")
+        L = C.CDLL(LIB_PATH)
+        vp, i64 = C.c_void_p, C.c_int64
+        L.obgpu_create.argtypes = [C.c_int, C.POINTER(vp)]
+        L.obgpu_destroy.argtypes = [vp]
+        L.obgpu_destroy.restype = None
+        L.obgpu_last_error.argtypes = [vp]
+        L.obgpu_last_error.restype = C.c_char_p
+        L.obgpu_status_string.argtypes = [C.c_int]
+        L.obgpu_status_string.restype = C.c_char_p
+        L.obgpu_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+        L.obgpu_host_free.argtypes = [vp]
+        L.obgpu_batch_upload.argtypes = [vp, C.POINTER(BatchDesc)]
+        L.obgpu_update_cases.argtypes = [vp, i64, vp, vp, vp]
+        for f in ("obgpu_symbolic", "obgpu_assemble", "obgpu_stress", "obgpu_synchronize"):
+            getattr(L, f).argtypes = [vp]
+        L.obgpu_solve_static.argtypes = [vp, C.POINTER(SolveOpts)]
+        L.obgpu_get_sizes.argtypes = [vp, vp]
+        L.obgpu_get_offsets.argtypes = [vp, C.c_int, vp]
+        L.obgpu_get_symbolic.argtypes = [vp, C.c_int, vp]
+        L.obgpu_download.argtypes = [vp, C.c_int, vp]
+        L.obgpu_device_ptr.argtypes = [vp, C.c_int, C.POINTER(vp)]
+        L.obgpu_solve_cases_host.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp]
+        L.obgpu_summaries_device.argtypes = [vp, vp]
+        L.obgpu_get_timings.argtypes = [vp, vp]
+        L.obgpu_get_stream.argtypes = [vp, C.POINTER(vp)]
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _free_pinned(addr):
+    if _LIB is not None:
+        _LIB.obgpu_host_free(C.c_void_p(addr))
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """numpy array over cudaHostAlloc'ed memory (obgpu_host_alloc); freed when the last view dies."""
+    count = int(np.prod(shape))
+    n = max(count * np.dtype(dtype).itemsize, 8)
+    ptr = C.c_void_p()
+    if lib().obgpu_host_alloc(C.byref(ptr), n) != OK:
+        raise ObgpuError(ECUDA, "obgpu_host_alloc failed")
+    buf = (C.c_char * n).from_address(ptr.value)
+    weakref.finalize(buf, _free_pinned, ptr.value)  # numpy keeps buf alive through the buffer protocol
+    return np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+
+
+def pack_batch(structures):
+    """CSR-of-structures SoA arrays of obgpu_batch_desc from a list of Structure."""
+    S = len(structures)
+
+    def off(counts):
+        o = np.zeros(S + 1, np.int64)
+        np.cumsum(counts, out=o[1:])
+        return o
+
+    def cat(arrs, dt, shape=None):
+        a = np.concatenate([np.asarray(x, dt).reshape(-1) for x in arrs]) if arrs else np.zeros(0, dt)
+        return np.ascontiguousarray(a, dt)
+
+    b = dict(
+        S=S,
+        node_off=off([s.n_nodes for s in structures]),
+        elem_off=off([s.n_elems for s in structures]),
+        con_off=off([len(s.con_node) for s in structures]),
+        nload_off=off([len(s.nload_node) for s in structures]),
+        eload_off=off([len(s.eload_elem) for s in structures]),
+        node_xy=cat([s.node_xy for s in structures], np.float64),
+        elem_nodes=cat([s.elem_nodes for s in structures], np.uint32),
+        elem_type=cat([s.elem_type for s in structures], np.uint8),
+        elem_EAI=cat([s.elem_EAI for s in structures], np.float64),
+        con_node=cat([s.con_node for s in structures], np.uint32),
+        con_dof=cat([s.con_dof for s in structures], np.uint8),
+        con_val=cat([s.con_val for s in structures], np.float64),
+        nload_node=cat([s.nload_node for s in structures], np.uint32),
+        nload_dof=cat([s.nload_dof for s in structures], np.uint8),
+        nload_val=cat([s.nload_val for s in structures], np.float64),
+        eload_elem=cat([s.eload_elem for s in structures], np.uint32),
+        eload_q=cat([s.eload_q for s in structures], np.float64),
+        eload_dir=cat([s.eload_dir for s in structures], np.float64),
+        node_rotz=None,
+    )
+    if any(s.node_rotz is not None for s in structures):
+        b["node_rotz"] = cat([s.node_rotz if s.node_rotz is not None else np.zeros(s.n_nodes) for s in structures],
+                             np.float64)
+    return b
+
+
+class Context:
+    """One obgpu_ctx (one GPU).  Thin: every method is one C-ABI call."""
+
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        rc = lib().obgpu_create(int(device), C.byref(self.h))
+        if rc != OK:
+            self.h = None
+            raise ObgpuError(rc, "obgpu_create: " + lib().obgpu_status_string(rc).decode())
+        self.device = device
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().obgpu_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _chk(self, rc):
+        if rc != OK:
+            msg = lib().obgpu_last_error(self.h).decode() or lib().obgpu_status_string(rc).decode()
+            raise ObgpuError(rc, msg)
+
+    # ---- upload ----
+    def upload(self, batch, n_cases=1, case_nload_val=None, case_eload_q=None, case_elem_EAI=None):
+        if isinstance(batch, Structure):
+            batch = pack_batch([batch])
+        elif isinstance(batch, (list, tuple)):
+            batch = pack_batch(list(batch))
+        d = BatchDesc()
+        d.n_structures = batch["S"]
+        for k in ("node_off", "elem_off", "con_off", "nload_off", "eload_off", "node_xy", "node_rotz", "elem_nodes",
+                  "elem_type", "elem_EAI", "con_node", "con_dof", "con_val", "nload_node", "nload_dof", "nload_val",
+                  "eload_elem", "eload_q", "eload_dir"):
+            a = batch.get(k)
+            setattr(d, k, None if a is None or a.size == 0 else a.ctypes.data)
+        d.n_cases = n_cases
+        cn, cq, ce = (None if a is None else np.ascontiguousarray(a, np.float64)
+                      for a in (case_nload_val, case_eload_q, case_elem_EAI))
+        d.case_nload_val = None if cn is None else cn.ctypes.data
+        d.case_eload_q = None if cq is None else cq.ctypes.data
+        d.case_elem_EAI = None if ce is None else ce.ctypes.data
+        self._keep = (batch, cn, cq, ce)
+        self._chk(lib().obgpu_batch_upload(self.h, C.byref(d)))
+        self._keep = None
+        return self
+
+    def update_cases(self, n_cases, case_nload_val=None, case_eload_q=None, case_elem_EAI=None):
+        self._chk(lib().obgpu_update_cases(self.h, n_cases, _p(case_nload_val), _p(case_eload_q), _p(case_elem_EAI)))
+
+    # ---- phases ----
+    def symbolic(self):
+        self._chk(lib().obgpu_symbolic(self.h))
+
+    def assemble(self):
+        self._chk(lib().obgpu_assemble(self.h))
+
+    def solve_static(self, method=BATCHED_LDLT, with_stress=True, rtol=1e-12, max_iter=0):
+        o = SolveOpts(method, int(with_stress), rtol, max_iter, 0)
+        self._chk(lib().obgpu_solve_static(self.h, C.byref(o)))
+
+    def stress(self):
+        self._chk(lib().obgpu_stress(self.h))
+
+    def synchronize(self):
+        self._chk(lib().obgpu_synchronize(self.h))
+
+    def solve_cases_host(self, n_cases, case_nload_val, case_eload_q, case_elem_EAI, U_f, F_b, stress, info):
+        self._chk(lib().obgpu_solve_cases_host(self.h, n_cases, _p(case_nload_val), _p(case_eload_q),
+                                               _p(case_elem_EAI), _p(U_f), _p(F_b), _p(stress), _p(info)))
+
+    def summaries_device(self, dptr):
+        self._chk(lib().obgpu_summaries_device(self.h, _p(int(dptr))))
+
+    # ---- read-back ----
+    def sizes(self):
+        out = np.zeros(12, np.int64)
+        self._chk(lib().obgpu_get_sizes(self.h, _p(out)))
+        return dict(zip(SIZE_NAMES, out.tolist()))
+
+    def offsets(self, which):
+        out = np.zeros(self.sizes()["S"] + 1, np.int64)
+        self._chk(lib().obgpu_get_offsets(self.h, which, _p(out)))
+        return out
+
+    def symbolic_array(self, which):
+        z = self.sizes()
+        n = {SYM_DOF_NODE: z["n_tot"], SYM_DOF_ID: z["n_tot"], SYM_FREE: z["nf_tot"], SYM_BOUNDED: z["nb_tot"],
+             SYM_DOF_INDEX: 6 * z["Ntot"], SYM_K_ROWPTR: z["n_tot"] + z["S"], SYM_K_COL: z["nnz_tot"],
+             SYM_TRI_NNZ: z["T_tot"]}[which]
+        out = np.zeros(max(n, 1), np.int32)
+        self._chk(lib().obgpu_get_symbolic(self.h, which, _p(out)))
+        return out[:n]
+
+    def result_shape(self, which):
+        z = self.sizes()
+        L = z["L"]
+        return {RES_UF: ((L, z["nf_tot"]), np.float64), RES_FF: ((L, z["nf_tot"]), np.float64),
+                RES_FB: ((L, z["nb_tot"]), np.float64), RES_UB: ((z["nb_tot"],), np.float64),
+                RES_STRESS: ((L, z["Etot"], 2, 6), np.float64), RES_INFO: ((L, z["S"]), np.int32),
+                RES_KVAL: ((-1, z["nnz_tot"]), np.float64), RES_ELEM_K: ((-1, z["Etot"], 21), np.float64)}[which]
+
+    def download(self, which, out=None, lk=None):
+        shape, dt = self.result_shape(which)
+        if shape[0] == -1:
+            shape = ((lk or 1),) + shape[1:]
+        if out is None:
+            out = np.zeros(shape, dt)
+        rc = lib().obgpu_download(self.h, which, _p(out))
+        if rc != OK and not (which == RES_INFO and rc == ESINGULAR):
+            self._chk(rc)
+        return out
+
+    def device_ptr(self, which):
+        p = C.c_void_p()
+        self._chk(lib().obgpu_device_ptr(self.h, which, C.byref(p)))
+        return p.value
+
+    def timings(self):
+        out = np.zeros(8)
+        self._chk(lib().obgpu_get_timings(self.h, _p(out)))
+        return dict(zip(("symbolic", "assembleProblem", "solveStatic.2_solve", "postProcCalcStress", "H2D", "D2H",
+                         "launches", "pcg_iters"), out.tolist()))
+
+    def stream(self):
+        p = C.c_void_p()
+        self._chk(lib().obgpu_get_stream(self.h, C.byref(p)))
+        return p.value

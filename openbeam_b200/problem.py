@@ -1,0 +1,145 @@
+"""Host-side mirror of the reference's problem interface for the static-solve path, over the C ABI.
+
+Names, argument meaning and error behaviour follow libopenbeam (paths under
+/root/reference/libopenbeam/include/openbeam/):
+    BuildProblemInfo            CFiniteElementProblem.h:76-102
+    StaticSolveProblemInfo      CFiniteElementProblem.h:105-123
+    StaticSolverAlgorithm       CFiniteElementProblem.h:69-73   (extended with the GPU_* cases)
+    StaticSolverOptions         CFiniteElementProblem.h:165-171
+    StressInfo / FaceStress     CFiniteElementProblem.h:173-183, types.h:78-157
+    assembleProblem/solveStatic/postProcCalcStress   CFiniteElementProblem.h:435-454
+The C++ twin of this file is include/obhost.hpp.  Nothing here computes: all arithmetic is in libobgpu.
+"""
+from __future__ import annotations
+
+import enum
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import obgpu
+from .structure import Structure
+
+NPOS = np.iinfo(np.uint64).max  # std::string::npos, used by dof_types for "n/a" (assemble.cpp:83-97)
+
+
+class StaticSolverAlgorithm(enum.IntEnum):
+    # the reference's two CPU algorithms are NOT available here (no CPU fallback); selecting them raises
+    Dense_LLT = -1
+    Sparse_LLT = -2
+    GPU_Batched_LDLT = obgpu.BATCHED_LDLT
+    GPU_PCG_Jacobi = obgpu.PCG_JACOBI
+    GPU_PCG_BJ3 = obgpu.PCG_BJ3
+    GPU_PCG_IC0 = obgpu.PCG_IC0
+
+
+@dataclass
+class StaticSolverOptions:
+    algorithm: StaticSolverAlgorithm = StaticSolverAlgorithm.GPU_Batched_LDLT
+    nonLinearIterative: bool = False
+    pcg_rtol: float = 1e-12
+    pcg_max_iter: int = 0
+
+
+@dataclass
+class BuildProblemInfo:
+    free_dof_indices: np.ndarray = None
+    bounded_dof_indices: np.ndarray = None
+    dof_types: np.ndarray = None          # [n,2] uint64: (bounded_index, free_index), NPOS = n/a
+    K_outer: np.ndarray = None            # K: Eigen CSC(upper) == CSR(lower): outerIndexPtr
+    K_inner: np.ndarray = None            #    innerIndexPtr
+    K_values: np.ndarray = None           #    valuePtr
+    U_b: np.ndarray = None
+    F_f: np.ndarray = None
+
+
+@dataclass
+class StaticSolveProblemInfo:
+    build_info: BuildProblemInfo = field(default_factory=BuildProblemInfo)
+    U_f: np.ndarray = None
+    F_b: np.ndarray = None
+
+
+@dataclass
+class StressInfo:
+    element_stress: np.ndarray = None     # [E][2] x {N,Vy,Vz,Mx,My,Mz}
+
+
+class CStructureProblem:
+    """One structure on one GPU context.  ``solveStatic`` raises RuntimeError with the reference's message
+    when K_ff is not positive definite (solver_static.cpp:98-105)."""
+
+    def __init__(self, structure: Structure, ctx: obgpu.Context | None = None, device: int = 0):
+        self.structure = structure
+        self.ctx = ctx or obgpu.Context(device)
+        self.ctx.upload(structure)
+        self._sym = False
+
+    # ---- getters named as in CFiniteElementProblem.h ----
+    def getNumberOfNodes(self):
+        return self.structure.n_nodes
+
+    def getNumberOfElements(self):
+        return self.structure.n_elems
+
+    def updateAll(self):
+        self.ctx.symbolic()
+        self._sym = True
+
+    def getProblemDoFs(self):
+        """m_problem_DoFs as [n,2] (nodeId, dof)."""
+        if not self._sym:
+            self.updateAll()
+        return np.stack([self.ctx.symbolic_array(obgpu.SYM_DOF_NODE), self.ctx.symbolic_array(obgpu.SYM_DOF_ID)], 1)
+
+    def getDOFIndex(self, node, dof):
+        """CFiniteElementProblem.cpp:308-317 — index or NPOS."""
+        if not self._sym:
+            self.updateAll()
+        k = int(self.ctx.symbolic_array(obgpu.SYM_DOF_INDEX)[6 * node + dof])
+        return NPOS if k < 0 else k
+
+    def _fill_lists(self, bi: BuildProblemInfo):
+        c = self.ctx
+        bi.free_dof_indices = c.symbolic_array(obgpu.SYM_FREE).astype(np.uint64)
+        bi.bounded_dof_indices = c.symbolic_array(obgpu.SYM_BOUNDED).astype(np.uint64)
+        n = c.sizes()["n_tot"]
+        dt = np.full((n, 2), NPOS, np.uint64)
+        dt[bi.bounded_dof_indices.astype(np.int64), 0] = np.arange(len(bi.bounded_dof_indices), dtype=np.uint64)
+        dt[bi.free_dof_indices.astype(np.int64), 1] = np.arange(len(bi.free_dof_indices), dtype=np.uint64)
+        bi.dof_types = dt
+        bi.K_outer = c.symbolic_array(obgpu.SYM_K_ROWPTR)
+        bi.K_inner = c.symbolic_array(obgpu.SYM_K_COL)
+
+    def assembleProblem(self, out_info: BuildProblemInfo):
+        self.updateAll()
+        self.ctx.assemble()
+        self._fill_lists(out_info)
+        out_info.K_values = self.ctx.download(obgpu.RES_KVAL)[0]
+        out_info.U_b = self.ctx.download(obgpu.RES_UB)
+        out_info.F_f = self.ctx.download(obgpu.RES_FF)[0]
+        return out_info
+
+    def solveStatic(self, out_info: StaticSolveProblemInfo, options: StaticSolverOptions | None = None):
+        options = options or StaticSolverOptions()
+        if options.algorithm < 0:
+            raise RuntimeError("StaticSolverAlgorithm::%s is the reference's CPU path; libobgpu has no CPU fallback"
+                               % options.algorithm.name)
+        if options.nonLinearIterative:
+            raise RuntimeError("nonLinearIterative is outside the GPU path (SURVEY.md §8f)")
+        self.updateAll()
+        self.ctx.solve_static(int(options.algorithm), True, options.pcg_rtol, options.pcg_max_iter)
+        info = self.ctx.download(obgpu.RES_INFO)
+        if np.any(info != 0):
+            raise RuntimeError(obgpu.lib().obgpu_status_string(obgpu.ESINGULAR).decode())
+        self._fill_lists(out_info.build_info)
+        out_info.build_info.U_b = self.ctx.download(obgpu.RES_UB)
+        out_info.build_info.F_f = self.ctx.download(obgpu.RES_FF)[0]
+        out_info.U_f = self.ctx.download(obgpu.RES_UF)[0]
+        out_info.F_b = self.ctx.download(obgpu.RES_FB)[0]
+        return out_info
+
+    def postProcCalcStress(self, out_stress: StressInfo, solver_info: StaticSolveProblemInfo | None = None):
+        self.ctx.stress()
+        out_stress.element_stress = self.ctx.download(obgpu.RES_STRESS)[0]
+        return out_stress
