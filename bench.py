@@ -1,0 +1,291 @@
+#!/usr/bin/env python
+"""bench.py — static solves/s of the openbeam hot path on B200 (BASELINE.json metric).
+
+Workload at N=1 (BASELINE.json configs[1]): demo3_frame.yaml x 1,000,000 randomized load cases; a *step* is one
+pass over the whole batch: per case the full  assembleProblem -> solveStatic -> postProcCalcStress  pipeline
+(element stiffness, assembly, BC elimination, LDL^T factor + solve, reactions, element end forces), i.e. what
+one ob-solve run does per structure.  Weak scaling: every rank owns its own 1M cases (case index offset by
+rank), no data-path collective; one NCCL all-gather of per-case summaries ends each step when N > 1.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--cases L]
+
+Prints ONE JSON line on rank 0 (contract in the task statement).  `--impl reference` times the CPU oracle
+(restatement of the reference's algorithm; the reference itself cannot be built here) on all host
+cores.  The oracle is only ever the baseline / checker here — the product path is libobgpu.so.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "static solves/s (FP64; full assemble+factor+solve+stress per load case)"
+UNIT = "solves/s"
+N_DOF = 12           # m_problem_DoFs.size() of demo3_frame (n_f = 6, n_b = 6)
+ALG_BYTES_PER_CASE = 440  # 8*(7 + n_f + n_b + 12E)
+QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cases", type=int, default=1_000_000, help="load cases per GPU per step")
+    ap.add_argument("--per-case-section", action="store_true", help="variant C2b: per-case A, Iz sweep")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def config_dict(args, world):
+    return {
+        "workload": "C2: demo3_frame.yaml x %d randomized load cases per GPU (q on beam + Fx,Fy,Mz on 2 nodes%s); "
+                    "each case = full assembleProblem+solveStatic(LDLt)+postProcCalcStress" %
+                    (args.cases, "; per-case section sweep" if args.per_case_section else ""),
+        "cases_per_gpu": args.cases, "n_dof": N_DOF, "n_free": 6, "n_bounded": 6, "elements": 3,
+        "parallelism": "independent load cases sharded over %d GPU(s), final NCCL all-gather of summaries" % world,
+        "l2_policy": "no flush: per-step inputs+outputs (%.0f MB) exceed the 126 MB L2" %
+                     (args.cases * (ALG_BYTES_PER_CASE + 48 + 36) / 1e6),
+    }
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 50 ms DURING the timed region."""
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + QUERY,
+                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f:
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); smax.append(float(c[2])); power.append(float(c[3]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if c[5 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        self.f.close()
+        os.unlink(self.f.name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(smax)), "power_w_max": float(max(power)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_run(args, n_cases, threads, repeats=1):
+    """Times the CPU oracle (oracle/: restatement of the reference's solveStatic path, 'faithful mode') on
+    `n_cases` of the same workload with `threads` host threads (one case per thread at a time).  Only this
+    function (cpu_baseline / --impl reference) touches oracle/."""
+    from openbeam_b200 import workloads
+    from oracle.pyoracle import OracleProblem
+    st = workloads.demo3_frame()
+    nl, q, eai = workloads.c2_cases(0, n_cases, args.per_case_section)
+    o = OracleProblem(st)
+    best = None
+    for _ in range(repeats):
+        dt, *_ = o.run_cases(n_cases, nl, q, eai, n_threads=threads, want_outputs=True)
+        best = dt if best is None else min(best, dt)
+    return best
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    # one step = a bounded sample of the workload: 250k of the 1M cases (~0.1-2 s on all cores)
+    sample = min(args.cases, 250_000)
+    from openbeam_b200 import workloads
+    from oracle.pyoracle import OracleProblem
+    st = workloads.demo3_frame()
+    nl, q, eai = workloads.c2_cases(0, sample, args.per_case_section)
+    o = OracleProblem(st)
+    for _ in range(args.warmup):
+        o.run_cases(sample, nl, q, eai, n_threads=cores)
+    total = 0.0
+    for _ in range(args.steps):
+        dt, *_ = o.run_cases(sample, nl, q, eai, n_threads=cores)
+        total += dt
+    v = sample * args.steps / total
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args, world),
+        "dof_per_s": v * N_DOF,
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d of the %d cases per step, one solveStatic+postProcCalcStress per case, "
+                                   "%d host threads (the reference is single-threaded; harness-level threads)"
+                                   % (sample, args.cases, cores)},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference unbuildable here (needs MRPT>=2.4 + Eigen): this is the oracle port in faithful mode",
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def ours_arm(args, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    from openbeam_b200 import obgpu, workloads
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — libobgpu has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L, K, W = args.cases, args.steps, args.warmup
+    ctx = obgpu.Context(local_rank)
+    st = workloads.demo3_frame()
+    # pinned host buffers: this rank's cases [rank*L, (rank+1)*L)
+    h_nl, h_q = obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 1))
+    h_eai = obgpu.pinned_empty((L, 9)) if args.per_case_section else None
+    workloads.c2_cases(rank * L, L, args.per_case_section, h_nl, h_q, h_eai)
+    h_U, h_Fb, h_S = obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 3, 2, 6))
+    h_info = obgpu.pinned_empty((L,), np.int32)
+
+    ctx.upload(st, L, h_nl, h_q, h_eai)   # inputs resident in HBM from here on
+    ctx.symbolic()
+    ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+    summ = torch.empty((L, 4), dtype=torch.float64, device=dev)
+    gathered = torch.empty((world * L, 4), dtype=torch.float64, device=dev) if world > 1 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step():
+        ctx.solve_static()                       # 1 fused kernel: K1+K2+K4+K5+K6+K10 per case
+        ctx.summaries_device(summ.data_ptr())    # 1 kernel: per-case {max|U|, sum Fb_x, sum Fb_y, info}
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, summ)   # the only collective
+
+    with torch.cuda.stream(ext):
+        for _ in range(W):
+            step()
+        barrier()
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        for _ in range(K):
+            step()
+        e1.record(ext)
+        barrier()
+        ms_total = e0.elapsed_time(e1)
+        # dominant kernel alone: CUDA-event pair around each fused-kernel launch (obgpu_get_timings)
+        kern_ms = []
+        for _ in range(K):
+            ctx.solve_static()
+            ctx.synchronize()
+            kern_ms.append(ctx.timings()["solveStatic.2_solve"])
+        barrier()
+        # end-to-end through the public host-buffer entry point: H2D + solve + D2H inside the timed region
+        for _ in range(min(W, 3)):
+            ctx.solve_cases_host(L, h_nl, h_q, h_eai, h_U, h_Fb, h_S, h_info)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            ctx.solve_cases_host(L, h_nl, h_q, h_eai, h_U, h_Fb, h_S, h_info)
+        torch.cuda.synchronize(dev)
+        e2e_s = time.perf_counter() - t0
+        e2e_launches = ctx.timings()["launches"]
+        barrier()
+        clocks = sampler.stop() if sampler else None
+    if h_info.any():
+        raise SystemExit("bench.py: a system reported a non-positive pivot")
+    t = torch.tensor([ms_total, e2e_s, float(np.mean(kern_ms))], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_s, kern_avg_ms = t.tolist()
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (measured copy)"
+        else:
+            peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+        value = world * L * K / (ms_total * 1e-3)
+        achieved = ALG_BYTES_PER_CASE * L / (kern_avg_ms * 1e-3) / 1e9
+        in_bytes = (h_nl.nbytes + h_q.nbytes + (h_eai.nbytes if h_eai is not None else 0))
+        out_bytes = h_U.nbytes + h_Fb.nbytes + h_S.nbytes + h_info.nbytes
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": config_dict(args, world),
+            "dof_per_s": value * N_DOF,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": TRAFFIC_BYTES_PER_LAUNCH, "kernel": "k_tiny_fused<6,128>",
+                         "kernel_ms": kern_avg_ms, "algorithmic_bytes_per_launch": ALG_BYTES_PER_CASE * L,
+                         "peak_source": peak_src},
+            "e2e": {"value": world * L * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes,
+                    "d2h_bytes_per_step": out_bytes,
+                    "api": "obgpu_solve_cases_host (pinned host buffers in and out, chunked over 3 streams)"},
+            "gpu_launches": int(K * 2), "e2e_launches_per_step": int(e2e_launches),
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            sample = min(L, 1_000_000)
+            dt_all = cpu_run(args, sample, cores)
+            dt_1 = cpu_run(args, min(sample, 200_000), 1)
+            line["cpu_baseline"] = {
+                "value": sample / dt_all, "unit": UNIT, "cores": cores, "kind": "port",
+                "value_1core": min(sample, 200_000) / dt_1,
+                "sample": "%d cases of the same workload on %d host threads (and %d cases on 1 thread): oracle port "
+                          "of the reference's solveStatic+postProcCalcStress, one call per case"
+                          % (sample, cores, min(sample, 200_000))}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_tiny_fused launch at 1M cases, from the committed
+# `ncu --set full` capture (profiles/); None until a capture exists
+TRAFFIC_BYTES_PER_LAUNCH = None
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+    return ours_arm(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -23,6 +23,8 @@ struct obgpu_ctx {
   obgpu::DevBuf<double> d_prog_d;
   obgpu::DevBuf<double> d_Uf, d_Fb, d_stress, d_Ff, d_Ub;
   obgpu::DevBuf<int32_t> d_info;
+  obgpu::DevBuf<int64_t> d_free_off, d_bnd_off;  // [S+1]
+  obgpu::DevBuf<uint8_t> d_bnd_dofid;            // [nb_tot]
   obgpu::DevBuf<int32_t> d_fail;  // [1] OR of per-system failures of the last solve
   bool solved = false, have_stress = false;
 

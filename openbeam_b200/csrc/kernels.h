@@ -21,4 +21,16 @@ struct TinyArgs {
 };
 cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st);
 
+struct SummaryArgs {
+  int64_t L, S, nf_tot, nb_tot;
+  const int64_t* free_off;   // [S+1]
+  const int64_t* bnd_off;    // [S+1]
+  const uint8_t* bnd_dofid;  // [nb_tot] DoF_index of each bounded DOF
+  const double* U_f;         // [L][nf_tot]
+  const double* F_b;         // [L][nb_tot]
+  const int32_t* info;       // [L][S]
+  double* out;               // [L][S][4], 32-byte aligned
+};
+cudaError_t launch_summaries(const SummaryArgs& a, int sm_count, cudaStream_t st);
+
 }  // namespace obgpu

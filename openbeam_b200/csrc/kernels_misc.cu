@@ -1,0 +1,38 @@
+// kernels_misc.cu — small helper kernels: per-system summaries for the final NCCL gather.
+#include "kernels.h"
+
+namespace obgpu {
+
+// One thread per system (c, s): {max|U_f|, sum of F_b over DX dofs, sum of F_b over DY dofs, info}.
+// Results are laid out [L][S][4] like OBGPU_RES_INFO.  Memory-bound: every U_f/F_b value is read once.
+__global__ void __launch_bounds__(256) k_summaries(SummaryArgs a) {
+  const int64_t total = a.L * a.S;
+  for (int64_t sys = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; sys < total; sys += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t c = sys / a.S, s = sys - c * a.S;
+    const int64_t f0 = a.free_off[s], f1 = a.free_off[s + 1], b0 = a.bnd_off[s], b1 = a.bnd_off[s + 1];
+    const double* U = a.U_f + c * a.nf_tot;
+    const double* F = a.F_b + c * a.nb_tot;
+    double umax = 0.0, fx = 0.0, fy = 0.0;
+    for (int64_t i = f0; i < f1; i++) umax = fmax(umax, fabs(U[i]));
+    for (int64_t i = b0; i < b1; i++) {
+      const int d = a.bnd_dofid[i];
+      const double v = F[i];
+      if (d == OBGPU_DX) fx += v;
+      if (d == OBGPU_DY) fy += v;
+    }
+    double4 o = make_double4(umax, fx, fy, double(a.info[sys]));
+    reinterpret_cast<double4*>(a.out)[sys] = o;
+  }
+}
+
+cudaError_t launch_summaries(const SummaryArgs& a, int sm_count, cudaStream_t st) {
+  const int64_t total = a.L * a.S;
+  int64_t grid = (total + 255) / 256;
+  const int64_t cap = int64_t(sm_count) * 8;
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  k_summaries<<<unsigned(grid), 256, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace obgpu

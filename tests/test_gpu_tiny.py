@@ -1,0 +1,138 @@
+"""GPU parity tests of the thread-per-system fused path (BASELINE configs C1, C2): libobgpu through the C ABI
+vs the CPU oracle on the same inputs.  Tolerance: 1e-9 relative (norm-wise, per result vector) as north_star
+states; integer artefacts bit-exact."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import fixtures
+from openbeam_b200 import obgpu, workloads
+from openbeam_b200.problem import (CStructureProblem, StaticSolveProblemInfo, StaticSolverAlgorithm,
+                                   StaticSolverOptions, StressInfo)
+from oracle.pyoracle import OracleProblem
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RTOL = 1e-9
+
+
+def relerr(a, b):
+    a, b = np.asarray(a, float).ravel(), np.asarray(b, float).ravel()
+    assert a.shape == b.shape
+    if a.size == 0:
+        return 0.0
+    den = np.max(np.abs(b))
+    return float(np.max(np.abs(a - b)) / den) if den > 0 else float(np.max(np.abs(a)))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = obgpu.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("name", fixtures.PLAIN)
+def test_fixture_parity(ctx, name):
+    st = fixtures.ALL[name]()
+    p = CStructureProblem(st, ctx=ctx)
+    info, sinfo = StaticSolveProblemInfo(), StressInfo()
+    p.solveStatic(info)
+    p.postProcCalcStress(sinfo, info)
+    o = OracleProblem(st).solveStatic().postProcCalcStress()
+    assert np.array_equal(info.build_info.free_dof_indices, o.free_dof_indices)
+    assert np.array_equal(info.build_info.bounded_dof_indices, o.bounded_dof_indices)
+    assert np.array_equal(p.getProblemDoFs(), o.problem_DoFs)
+    assert relerr(info.build_info.F_f, o.F_f) <= RTOL
+    assert relerr(info.U_f, o.U_f) <= RTOL
+    assert relerr(info.F_b, o.F_b) <= RTOL
+    assert relerr(sinfo.element_stress, o.element_stress) <= RTOL
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", name + ".json")))
+    unhex = lambda v: np.array([float.fromhex(x) for x in v])
+    assert relerr(info.U_f, unhex(g["U_f"])) <= RTOL
+    assert relerr(info.F_b, unhex(g["F_b"])) <= RTOL
+    assert relerr(sinfo.element_stress, unhex(g["stress"])) <= RTOL
+
+
+def test_demo1_closed_form(ctx):
+    """statically determinate truss."""
+    p = CStructureProblem(fixtures.demo1(), ctx=ctx)
+    info, s = StaticSolveProblemInfo(), StressInfo()
+    p.solveStatic(info)
+    p.postProcCalcStress(s)
+    assert info.build_info.free_dof_indices.tolist() == [2, 4, 5]
+    assert np.allclose(info.U_f, [1.25e-5, 2.5225424859373689e-4, 5.0e-5], rtol=1e-12)
+    assert np.allclose(info.F_b, [-1000, -2000, 2000], rtol=1e-12)
+    assert np.allclose(s.element_stress[:, 1, 0], [1000, -1000 * np.sqrt(5), 2000], rtol=1e-12)
+
+
+def test_singular_raises_reference_message(ctx):
+    p = CStructureProblem(fixtures.mechanism(), ctx=ctx)
+    with pytest.raises(RuntimeError, match="Ill-conditioned matrix. Too few restrictions"):
+        p.solveStatic(StaticSolveProblemInfo())
+
+
+def test_cpu_algorithms_refused(ctx):
+    p = CStructureProblem(fixtures.demo1(), ctx=ctx)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        p.solveStatic(StaticSolveProblemInfo(), StaticSolverOptions(algorithm=StaticSolverAlgorithm.Dense_LLT))
+
+
+@pytest.mark.parametrize("per_case_section", [False, True])
+def test_c2_sample_parity(ctx, per_case_section):
+    """Config C2: demo3_frame x load cases; 10^4-case sample against the oracle's per-case solveStatic."""
+    st = workloads.demo3_frame()
+    L = 10000
+    nl, q, eai = workloads.c2_cases(123456, L, per_case_section)
+    ctx.upload(st, L, nl, q, eai)
+    ctx.solve_static()
+    U, Fb, S, Ff = (ctx.download(w) for w in (obgpu.RES_UF, obgpu.RES_FB, obgpu.RES_STRESS, obgpu.RES_FF))
+    assert not ctx.download(obgpu.RES_INFO).any()
+    _, oU, oF, oS = OracleProblem(st).run_cases(L, nl, q, eai, n_threads=4)
+    for c in range(0, L, 97):
+        assert relerr(U[c], oU[c]) <= RTOL and relerr(Fb[c], oF[c]) <= RTOL and relerr(S[c], oS[c]) <= RTOL
+    assert relerr(U, oU) <= RTOL and relerr(Fb, oF) <= RTOL and relerr(S, oS) <= RTOL
+    # host-buffer sweep (the e2e entry point) gives the same bits as upload + solve + download
+    U2, F2, S2 = np.empty_like(U), np.empty_like(Fb), np.empty_like(S)
+    info = np.empty(L, np.int32)
+    ctx.solve_cases_host(L, nl, q, eai, U2, F2, S2, info)
+    assert np.array_equal(U, U2) and np.array_equal(Fb, F2) and np.array_equal(S, S2) and not info.any()
+    assert Ff.shape == U.shape
+
+
+def test_c2_full_size_equilibrium(ctx):
+    """All 10^6 cases: global equilibrium  sum(F_b) + sum(F_ext) = 0  per case (size-independent property),
+    and linearity: solution of (a + b) = solution(a) + solution(b)."""
+    st = workloads.demo3_frame()
+    L = 1_000_000
+    nl, q, _ = workloads.c2_cases(0, L)
+    ctx.upload(st, L, nl, q)
+    ctx.solve_static()
+    Fb = ctx.download(obgpu.RES_FB)
+    assert not ctx.download(obgpu.RES_INFO).any()
+    # bounded DOFs: node0 (DX,DY,RZ), node3 (DX,DY,RZ); beam length 4 m, UDL q down
+    fx = Fb[:, 0] + Fb[:, 3] + nl[:, 0] + nl[:, 3]
+    fy = Fb[:, 1] + Fb[:, 4] + nl[:, 1] + nl[:, 4] - 4.0 * q[:, 0]
+    scale = np.abs(Fb).max()
+    assert np.abs(fx).max() <= 1e-9 * scale and np.abs(fy).max() <= 1e-9 * scale
+    # moment equilibrium about node 0: nodes at (0,0),(0,2),(4,2),(4,0); UDL resultant 4q at x = 2
+    mz = (Fb[:, 2] + Fb[:, 5] + nl[:, 2] + nl[:, 5] + 4.0 * Fb[:, 4] + 4.0 * nl[:, 4] - 2.0 * nl[:, 0]
+          - 2.0 * nl[:, 3] - 2.0 * 4.0 * q[:, 0])
+    assert np.abs(mz).max() <= 1e-9 * scale * 4
+    U = ctx.download(obgpu.RES_UF)
+    n = 1000
+    ctx.update_cases(n, np.ascontiguousarray(nl[:n] + nl[n:2 * n]), np.ascontiguousarray(q[:n] + q[n:2 * n]))
+    ctx.solve_static()
+    assert relerr(ctx.download(obgpu.RES_UF), U[:n] + U[n:2 * n]) <= 1e-9
+
+
+def test_timings_and_launch_count(ctx):
+    st = workloads.demo3_frame()
+    nl, q, _ = workloads.c2_cases(0, 4096)
+    ctx.upload(st, 4096, nl, q)
+    ctx.solve_static()
+    ctx.synchronize()
+    t = ctx.timings()
+    assert t["launches"] == 1 and t["solveStatic.2_solve"] > 0
