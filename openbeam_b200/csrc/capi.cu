@@ -164,6 +164,7 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   hb.L = d->n_cases < 1 ? 1 : d->n_cases;
   c->uploaded = true;
   c->sym = Symbolic();
+  c->dev_batch = false;
   c->prog = TinyProgram();
   return upload_cases(c, hb.L, d->case_nload_val, d->case_eload_q, d->case_elem_EAI);
 }
@@ -181,7 +182,9 @@ int obgpu_symbolic(obgpu_ctx* c) {
   OB_DEVICE(c);
   const auto t0 = std::chrono::steady_clock::now();
   std::string err;
-  int rc = run_symbolic(c->hb, c->sym, err, true);
+  c->dev_batch = false;
+  // the K pattern costs O(T log T) host work: built eagerly for moderate batches, on demand otherwise
+  int rc = run_symbolic(c->hb, c->sym, err, c->hb.Etot() <= (int64_t(1) << 22));
   if (rc != OBGPU_OK) return fail(c, rc, err);
   // ASSERT_(L > 0), CElementBeam_2D_RR.cpp:63
   for (int64_t s = 0; s < c->hb.S; s++)

@@ -1,16 +1,107 @@
-// capi_general.cu — general (any-size, any-topology) path: K1/K2 element kernels, K4 segmented-reduction
-// assembly, K5 BC gather, CTA-per-structure LDL^T, PCG.  (filled in incrementally)
+// capi_general.cu — general (any-topology) path: device copies of the batch, the warp-per-structure fused
+// kernel for small structures, summaries.  Assembly of the global K and the PCG route live in capi_sparse.cu.
+#include <algorithm>
+
 #include "ctx.h"
 
 namespace obgpu {
-int solve_general(obgpu_ctx* c, const obgpu_solve_opts&) {
-  return fail(c, OBGPU_EUNSUPPORTED, "general solve path not built yet");
-}
-int assemble_general(obgpu_ctx* c) { return fail(c, OBGPU_EUNSUPPORTED, "general assembly path not built yet"); }
-int download_general(obgpu_ctx*, int, void*, bool& handled) {
-  handled = false;
+
+int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o);  // capi_sparse.cu
+
+// Upload the batch arrays and the per-structure records once per (upload, symbolic).
+int ensure_device_batch(obgpu_ctx* c) {
+  if (c->dev_batch) return OBGPU_OK;
+  const HostBatch& hb = c->hb;
+  const Symbolic& sy = c->sym;
+  cudaStream_t st = c->stream;
+  OB_CUDA(c, c->d_node_xy.upload(hb.node_xy, st));
+  OB_CUDA(c, c->d_elem_nodes.upload(hb.elem_nodes, st));
+  OB_CUDA(c, c->d_elem_type.upload(hb.elem_type, st));
+  OB_CUDA(c, c->d_elem_EAI.upload(hb.elem_EAI, st));
+  OB_CUDA(c, c->d_nload_val.upload(hb.nload_val, st));
+  OB_CUDA(c, c->d_eload_q.upload(hb.eload_q, st));
+  OB_CUDA(c, c->d_eload_dir.upload(hb.eload_dir, st));
+  OB_CUDA(c, c->d_node_slot.upload(sy.node_slot, st));
+  OB_CUDA(c, c->d_nload_slot.upload(sy.nload_slot, st));
+  OB_CUDA(c, c->d_el_ptr.upload(sy.el_ptr, st));
+  OB_CUDA(c, c->d_el_order.upload(sy.el_order, st));
+  std::vector<FrameMeta> meta(hb.S);
+  c->max_band = c->max_nf = c->max_nb = 0;
+  for (int64_t s = 0; s < hb.S; s++) {
+    FrameMeta& m = meta[s];
+    m.n0 = hb.node_off[s]; m.e0 = hb.elem_off[s]; m.nl0 = hb.nload_off[s];
+    m.f0 = sy.free_off[s]; m.b0 = sy.bnd_off[s];
+    m.N = int32_t(hb.node_off[s + 1] - hb.node_off[s]);
+    m.E = int32_t(hb.elem_off[s + 1] - hb.elem_off[s]);
+    m.NL = int32_t(hb.nload_off[s + 1] - hb.nload_off[s]);
+    m.n = int32_t(sy.dof_off[s + 1] - sy.dof_off[s]);
+    m.nf = int32_t(sy.free_off[s + 1] - sy.free_off[s]);
+    m.nb = int32_t(sy.bnd_off[s + 1] - sy.bnd_off[s]);
+    m.hb = std::min(sy.half_bw[s], std::max(m.nf - 1, 0));
+    m.pad = 0;
+    c->max_band = std::max<int64_t>(c->max_band, int64_t(m.hb + 1) * m.nf);
+    c->max_nf = std::max(c->max_nf, m.nf);
+    c->max_nb = std::max(c->max_nb, m.nb);
+  }
+  OB_CUDA(c, c->d_meta.upload(meta, st));
+  OB_CUDA(c, cudaStreamSynchronize(st));  // meta is a stack vector
+  c->dev_batch = true;
   return OBGPU_OK;
 }
+
+static bool frame_kernel_fits(const obgpu_ctx* c) {
+  return frame_smem_per_warp(c->max_band, c->max_nf, c->max_nb) * 4 <= size_t(227) * 1024;
+}
+
+int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
+  int rc = ensure_device_batch(c);
+  if (rc != OBGPU_OK) return rc;
+  for (double v : c->sym.U_b)
+    if (v != 0.0)
+      return fail(c, OBGPU_EUNSUPPORTED, "non-zero prescribed displacements are not implemented on the GPU path yet");
+  if (c->hb.has_rotz) return fail(c, OBGPU_EUNSUPPORTED, "nodal rotated frames are not implemented on the GPU path yet");
+  if (o.method != OBGPU_BATCHED_LDLT || !frame_kernel_fits(c)) {
+    if (o.method == OBGPU_BATCHED_LDLT)
+      return fail(c, OBGPU_EUNSUPPORTED, "structure too large for the batched LDLt kernel: use a PCG method");
+    return solve_sparse(c, o);
+  }
+  const Symbolic& sy = c->sym;
+  const int64_t L = c->L;
+  OB_CUDA(c, c->d_Uf.reserve(size_t(L) * std::max<int64_t>(sy.nf_tot(), 1)));
+  OB_CUDA(c, c->d_Ff.reserve(size_t(L) * std::max<int64_t>(sy.nf_tot(), 1)));
+  OB_CUDA(c, c->d_Fb.reserve(size_t(L) * std::max<int64_t>(sy.nb_tot(), 1)));
+  OB_CUDA(c, c->d_info.reserve(size_t(L) * c->hb.S));
+  OB_CUDA(c, c->d_fail.reserve(1));
+  if (o.with_stress) OB_CUDA(c, c->d_stress.reserve(size_t(L) * c->hb.Etot() * 12));
+  OB_CUDA(c, cudaMemsetAsync(c->d_fail.p, 0, sizeof(int32_t), c->stream));
+  FrameArgs a;
+  a.S = c->hb.S; a.L = L;
+  a.Ntot = c->hb.Ntot(); a.Etot = c->hb.Etot(); a.NLtot = c->hb.NLtot(); a.ELtot = c->hb.ELtot();
+  a.nf_tot = sy.nf_tot(); a.nb_tot = sy.nb_tot();
+  a.meta = c->d_meta.p;
+  a.node_xy = reinterpret_cast<const double2*>(c->d_node_xy.p);
+  a.elem_nodes = reinterpret_cast<const uint2*>(c->d_elem_nodes.p);
+  a.elem_type = c->d_elem_type.p; a.elem_EAI = c->d_elem_EAI.p;
+  a.node_slot = c->d_node_slot.p; a.nload_slot = c->d_nload_slot.p; a.nload_val = c->d_nload_val.p;
+  a.el_ptr = c->d_el_ptr.p; a.el_order = c->d_el_order.p; a.eload_q = c->d_eload_q.p; a.eload_dir = c->d_eload_dir.p;
+  a.case_nl = c->has_case_nl ? c->d_case_nl.p : nullptr;
+  a.case_q = c->has_case_q ? c->d_case_q.p : nullptr;
+  a.case_eai = c->has_case_eai ? c->d_case_eai.p : nullptr;
+  a.U_f = c->d_Uf.p; a.F_b = c->d_Fb.p; a.F_f = c->d_Ff.p;
+  a.stress = o.with_stress ? c->d_stress.p : nullptr;
+  a.info = c->d_info.p; a.fail = c->d_fail.p;
+  a.max_band = c->max_band; a.max_nf = c->max_nf; a.max_nb = c->max_nb;
+  OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+  OB_CUDA(c, launch_frame_fused(a, c->sm_count, c->stream));
+  OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+  c->t_have[1] = true;
+  c->launches = 1;
+  c->pcg_iters = 0;
+  c->solved = true;
+  c->have_stress = o.with_stress != 0;
+  return OBGPU_OK;
+}
+
 }  // namespace obgpu
 
 extern "C" int obgpu_summaries_device(obgpu_ctx* c, double* d_out) {

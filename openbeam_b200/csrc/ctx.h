@@ -27,6 +27,14 @@ struct obgpu_ctx {
   obgpu::DevBuf<uint8_t> d_bnd_dofid;            // [nb_tot]
   obgpu::DevBuf<int32_t> d_fail;  // [1] OR of per-system failures of the last solve
   bool solved = false, have_stress = false;
+  // general path: the batch arrays + symbolic slots on the device
+  bool dev_batch = false;
+  obgpu::DevBuf<double> d_node_xy, d_elem_EAI, d_nload_val, d_eload_q, d_eload_dir;
+  obgpu::DevBuf<uint32_t> d_elem_nodes;
+  obgpu::DevBuf<uint8_t> d_elem_type;
+  obgpu::DevBuf<int32_t> d_node_slot, d_nload_slot, d_el_ptr, d_el_order;
+  obgpu::DevBuf<obgpu::FrameMeta> d_meta;
+  int max_band = 0, max_nf = 0, max_nb = 0;
 
   // chunk slots of obgpu_solve_cases_host
   struct Slot {

@@ -21,6 +21,45 @@ struct TinyArgs {
 };
 cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st);
 
+// Per-structure record of the batched kernels (one 64-byte line per structure).
+struct __align__(16) FrameMeta {
+  int64_t n0, e0, nl0;   // first node / element / node-load of the structure in the batch arrays
+  int64_t f0, b0;        // first free / bounded DOF in the result arrays (per case)
+  int32_t N, E, NL, n, nf, nb, hb, pad;
+};
+static_assert(sizeof(FrameMeta) == 80, "FrameMeta layout");
+
+// Batch arrays on the device (SoA, see obgpu_batch_desc) + symbolic slots.
+struct FrameArgs {
+  int64_t S, L;                 // structures x load cases; system = c*S + s
+  int64_t Ntot, Etot, NLtot, ELtot, nf_tot, nb_tot;
+  const FrameMeta* meta;        // [S]
+  const double2* node_xy;       // [Ntot]
+  const uint2* elem_nodes;      // [Etot] local node ids
+  const uint8_t* elem_type;     // [Etot]
+  const double* elem_EAI;       // [3*Etot]
+  const int32_t* node_slot;     // [3*Ntot]
+  const int32_t* nload_slot;    // [NLtot]
+  const double* nload_val;      // [NLtot]
+  const int32_t* el_ptr;        // [Etot+1]
+  const int32_t* el_order;      // [ELtot]
+  const double* eload_q;        // [ELtot]
+  const double* eload_dir;      // [3*ELtot]
+  const double* case_nl;        // [L][NLtot] or null
+  const double* case_q;         // [L][ELtot] or null
+  const double* case_eai;       // [L][3*Etot] or null
+  double* U_f;                  // [L][nf_tot]
+  double* F_b;                  // [L][nb_tot]
+  double* F_f;                  // [L][nf_tot] or null
+  double* stress;               // [L][Etot][12] or null
+  int32_t* info;                // [L][S]
+  int32_t* fail;                // [1]
+  int max_band;                 // max over structures of (hb+1)*nf   (doubles)
+  int max_nf, max_nb;
+};
+cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st);
+size_t frame_smem_per_warp(int max_band, int max_nf, int max_nb);
+
 struct SummaryArgs {
   int64_t L, S, nf_tot, nb_tot;
   const int64_t* free_off;   // [S+1]

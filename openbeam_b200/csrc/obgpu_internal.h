@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <limits.h>
 
 #include <string>
 #include <vector>
@@ -20,6 +21,7 @@ constexpr int ELEM_K = 21;
 constexpr int TINY_MAX_NF = 12;   // thread-per-system kernel: K_ff lives in registers up to this size
 constexpr int TINY_MAX_N = 48;
 constexpr int TINY_MAX_E = 32;
+constexpr int32_t SLOT_NONE = INT32_MIN;  // DOF absent from the problem
 
 template <class T>
 struct DevBuf {  // owning device buffer (grow-only)
@@ -75,6 +77,13 @@ struct Symbolic {
   std::vector<int32_t> tri_nnz;              // [T_tot] triplet -> nnz slot (local to structure)
   std::vector<int32_t> tri_src;              // [T_tot] triplet -> e_local*21+cid, or -1 (structural zero)
   std::vector<double> U_b;                   // [nb_tot]
+  // per-node compact slots for the planar DOFs (DX,DY,RZ): >= 0 free index, < 0 && != SLOT_NONE: -(bounded index)-1
+  std::vector<int32_t> node_slot;            // [3*Ntot]
+  std::vector<int32_t> nload_slot;           // [NLtot] same encoding for the loaded DOF
+  std::vector<int32_t> el_ptr;               // [Etot+1] CSR over GLOBAL element index -> el_order
+  std::vector<int32_t> el_order;             // [ELtot] global element-load slot, reference multimap order
+  std::vector<int32_t> half_bw;              // [S] half bandwidth of K_ff in free numbering
+  bool has_pattern = false;
   // K4 segmented-reduction program: for global nnz slot g, sources seg_src[seg_ptr[g]..seg_ptr[g+1])
   // (global element index*21+cid, or -1), in the reference's triplet (= element) order.
   std::vector<int64_t> seg_ptr;              // [nnz_tot+1]

@@ -84,6 +84,12 @@ int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want
   sym.tri_off.assign(S + 1, 0);
   sym.dof_index.assign(size_t(6) * hb.Ntot(), -1);
   sym.seg_ptr.assign(1, 0);
+  sym.node_slot.assign(size_t(3) * hb.Ntot(), SLOT_NONE);
+  sym.nload_slot.assign(hb.NLtot(), SLOT_NONE);
+  sym.el_ptr.assign(hb.Etot() + 1, int32_t(hb.ELtot()));
+  sym.el_order.assign(hb.ELtot(), 0);
+  sym.half_bw.assign(S, 0);
+  sym.has_pattern = want_pattern;
   std::vector<unsigned> node_mask;
   std::vector<int64_t> keys;       // per-structure triplet keys col*n+row
   std::vector<int64_t> uniq;
@@ -160,6 +166,43 @@ int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want
         err = "element load element index out of range";
         return OBGPU_EINVAL;
       }
+    // ---- compact planar slots, element-load CSR, half bandwidth (inputs of the batched-LDLt kernels) ----
+    {
+      static const int d3[3] = {0, 1, 5};
+      for (int64_t i = 0; i < N; i++)
+        for (int a = 0; a < 3; a++) {
+          const int32_t k = sym.dof_index[6 * (n0 + i) + d3[a]];
+          sym.node_slot[3 * (n0 + i) + a] = k < 0 ? SLOT_NONE : sym.dof_type[k0 + k];
+        }
+      for (int64_t l = hb.nload_off[s]; l < hb.nload_off[s + 1]; l++) {
+        const int32_t k = sym.dof_index[6 * (n0 + hb.nload_node[l]) + hb.nload_dof[l]];
+        sym.nload_slot[l] = k < 0 ? SLOT_NONE : sym.dof_type[k0 + k];
+      }
+      const int64_t l0 = hb.eload_off[s], EL = hb.eload_off[s + 1] - l0;
+      order.resize(EL);
+      for (int64_t i = 0; i < EL; i++) order[i] = int32_t(i);
+      std::stable_sort(order.begin(), order.end(),
+                       [&](int32_t a, int32_t b) { return hb.eload_elem[l0 + a] < hb.eload_elem[l0 + b]; });
+      int64_t p = 0;
+      for (int64_t e = 0; e < E; e++) {
+        sym.el_ptr[e0 + e] = int32_t(l0 + p);
+        while (p < EL && int64_t(hb.eload_elem[l0 + order[p]]) == e) {
+          sym.el_order[l0 + p] = int32_t(l0 + order[p]);
+          p++;
+        }
+      }
+      int32_t bw = 0;
+      for (int64_t e = 0; e < E; e++) {
+        int32_t lo = INT32_MAX, hi = -1;
+        for (int f = 0; f < 2; f++)
+          for (int a = 0; a < 3; a++) {
+            const int32_t t = sym.node_slot[3 * (n0 + hb.elem_nodes[2 * (e0 + e) + f]) + a];
+            if (t >= 0) { lo = std::min(lo, t); hi = std::max(hi, t); }
+          }
+        if (hi >= 0) bw = std::max(bw, hi - lo);
+      }
+      sym.half_bw[s] = bw;
+    }
     if (!want_pattern) {
       sym.nnz_off[s + 1] = sym.nnz_off[s];
       sym.tri_off[s + 1] = sym.tri_off[s];
