@@ -79,6 +79,7 @@ void obgpu_destroy(obgpu_ctx* c) {
   }
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
+  if (c->h_scal) cudaFreeHost(c->h_scal);
   for (auto& e : c->ev)
     if (e) cudaEventDestroy(e);
   for (auto& s : c->slot_stream)
@@ -101,6 +102,7 @@ static int upload_cases(obgpu_ctx* c, int64_t L, const double* nl, const double*
   c->has_case_q = q != nullptr && c->hb.ELtot() > 0;
   c->has_case_eai = eai != nullptr;
   c->solved = false;
+  c->assembled = false;
   if (c->device == OBGPU_DEVICE_NONE) return OBGPU_OK;
   OB_CUDA(c, cudaEventRecord(c->ev[0], c->stream));
   if (c->has_case_nl) OB_CUDA(c, c->d_case_nl.upload(nl, size_t(L) * c->hb.NLtot(), c->stream));
@@ -165,6 +167,8 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   c->uploaded = true;
   c->sym = Symbolic();
   c->dev_batch = false;
+  c->dev_plan = false;
+  c->assembled = false;
   c->prog = TinyProgram();
   return upload_cases(c, hb.L, d->case_nload_val, d->case_eload_q, d->case_elem_EAI);
 }
@@ -183,6 +187,8 @@ int obgpu_symbolic(obgpu_ctx* c) {
   const auto t0 = std::chrono::steady_clock::now();
   std::string err;
   c->dev_batch = false;
+  c->dev_plan = false;
+  c->assembled = false;
   // the K pattern costs O(T log T) host work: built eagerly for moderate batches, on demand otherwise
   int rc = run_symbolic(c->hb, c->sym, err, c->hb.Etot() <= (int64_t(1) << 22));
   if (rc != OBGPU_OK) return fail(c, rc, err);

@@ -1,11 +1,228 @@
-// capi_sparse.cu — global K assembly (K1+K4), BC gather (K5) and the PCG route (K7-K9) for large structures.
+// capi_sparse.cu — global K assembly (K1+K4), BC gather (K5) and the PCG route (K7-K9, K10) for large structures.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
 #include "ctx.h"
 
 namespace obgpu {
-int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts&) { return fail(c, OBGPU_EUNSUPPORTED, "PCG route not built yet"); }
-int assemble_general(obgpu_ctx* c) { return fail(c, OBGPU_EUNSUPPORTED, "general assembly path not built yet"); }
-int download_general(obgpu_ctx*, int, void*, bool& handled) {
-  handled = false;
+
+int ensure_device_batch(obgpu_ctx* c);  // capi_general.cu
+
+static int ensure_plan(obgpu_ctx* c) {
+  if (c->dev_plan) return OBGPU_OK;
+  int rc = ensure_device_batch(c);
+  if (rc != OBGPU_OK) return rc;
+  std::string err;
+  if (!c->sym.has_pattern) {  // pattern was skipped for a very large batch: build it now
+    rc = run_symbolic(c->hb, c->sym, err, true);
+    if (rc != OBGPU_OK) return fail(c, rc, err);
+  }
+  rc = build_sparse_plan(c->hb, c->sym, c->plan, err);
+  if (rc != OBGPU_OK) return fail(c, rc, err);
+  const HostBatch& hb = c->hb;
+  const SparsePlan& P = c->plan;
+  cudaStream_t st = c->stream;
+  std::vector<int32_t> node0(hb.Etot()), f0(hb.Etot()), eg(hb.ELtot());
+  for (int64_t s = 0; s < hb.S; s++) {
+    for (int64_t e = hb.elem_off[s]; e < hb.elem_off[s + 1]; e++) {
+      node0[e] = int32_t(hb.node_off[s]);
+      f0[e] = int32_t(c->sym.free_off[s]);
+    }
+    for (int64_t l = hb.eload_off[s]; l < hb.eload_off[s + 1]; l++) eg[l] = int32_t(hb.elem_off[s] + hb.eload_elem[l]);
+  }
+  OB_CUDA(c, c->d_elem_node0.upload(node0, st));
+  OB_CUDA(c, c->d_elem_f0.upload(f0, st));
+  OB_CUDA(c, c->d_eload_elem_g.upload(eg, st));
+  OB_CUDA(c, c->d_seg_ptr.upload(P.seg_ptr, st));
+  OB_CUDA(c, c->d_seg_src.upload(P.seg_src, st));
+  OB_CUDA(c, c->d_ff_rowptr.upload(P.ff_rowptr, st));
+  OB_CUDA(c, c->d_ff_col.upload(P.ff_col, st));
+  OB_CUDA(c, c->d_ff_src.upload(P.ff_src, st));
+  OB_CUDA(c, c->d_ff_diag.upload(P.ff_diag, st));
+  OB_CUDA(c, c->d_bf_rowptr.upload(P.bf_rowptr, st));
+  OB_CUDA(c, c->d_bf_col.upload(P.bf_col, st));
+  OB_CUDA(c, c->d_bf_src.upload(P.bf_src, st));
+  OB_CUDA(c, c->d_fseg_ptr.upload(P.fseg_ptr, st));
+  OB_CUDA(c, c->d_fseg_src.upload(P.fseg_src, st));
+  OB_CUDA(c, c->d_eload_g.reserve(std::max<size_t>(size_t(hb.ELtot()) * 6, 1)));
+  OB_CUDA(c, c->d_Eq.reserve(std::max<size_t>(c->sym.nb_tot(), 1)));
+  OB_CUDA(c, cudaStreamSynchronize(st));  // node0/f0/eg are stack vectors
+  c->dev_plan = true;
   return OBGPU_OK;
 }
+
+static SparseDev sparse_dev(obgpu_ctx* c, int64_t k /* K copy */) {
+  SparseDev d;
+  d.Etot = c->hb.Etot(); d.ELtot = c->hb.ELtot(); d.nnz = c->sym.nnz_tot();
+  d.nf = c->sym.nf_tot(); d.nb = c->sym.nb_tot();
+  d.nnz_ff = int64_t(c->plan.ff_col.size()); d.nnz_bf = int64_t(c->plan.bf_col.size());
+  d.elem_nodes = reinterpret_cast<const uint2*>(c->d_elem_nodes.p);
+  d.elem_type = c->d_elem_type.p;
+  d.node_xy = reinterpret_cast<const double2*>(c->d_node_xy.p);
+  d.elem_node0 = c->d_elem_node0.p; d.elem_f0 = c->d_elem_f0.p;
+  d.node_slot = c->d_node_slot.p; d.el_ptr = c->d_el_ptr.p; d.el_order = c->d_el_order.p;
+  d.eload_elem_g = c->d_eload_elem_g.p; d.eload_dir = c->d_eload_dir.p;
+  d.seg_ptr = c->d_seg_ptr.p; d.seg_src = c->d_seg_src.p;
+  d.ff_rowptr = c->d_ff_rowptr.p; d.ff_col = c->d_ff_col.p; d.ff_src = c->d_ff_src.p; d.ff_diag = c->d_ff_diag.p;
+  d.bf_rowptr = c->d_bf_rowptr.p; d.bf_col = c->d_bf_col.p; d.bf_src = c->d_bf_src.p;
+  d.fseg_ptr = c->d_fseg_ptr.p; d.fseg_src = c->d_fseg_src.p;
+  d.elem_k = c->d_elem_k.p + size_t(k) * d.Etot * ELEM_K;
+  d.kval = c->d_kval.p + size_t(k) * d.nnz;
+  d.ff_val = c->d_ff_val.p; d.bf_val = c->d_bf_val.p; d.eload_g = c->d_eload_g.p; d.Eq = c->d_Eq.p;
+  return d;
+}
+
+// K1 + K4 for every K copy, and F_f for every case (what assembleProblem() leaves in BuildProblemInfo).
+int assemble_general(obgpu_ctx* c) {
+  int rc = ensure_plan(c);
+  if (rc != OBGPU_OK) return rc;
+  if (c->hb.has_rotz) return fail(c, OBGPU_EUNSUPPORTED, "nodal rotated frames are not implemented on the GPU path yet");
+  const int64_t L = c->L, LK = c->has_case_eai ? L : 1;
+  c->LK = LK;
+  const int64_t Etot = c->hb.Etot(), nnz = c->sym.nnz_tot(), nf = c->sym.nf_tot();
+  OB_CUDA(c, c->d_elem_k.reserve(size_t(LK) * Etot * ELEM_K));
+  OB_CUDA(c, c->d_kval.reserve(size_t(LK) * std::max<int64_t>(nnz, 1)));
+  OB_CUDA(c, c->d_ff_val.reserve(std::max<size_t>(c->plan.ff_col.size(), 1)));
+  OB_CUDA(c, c->d_bf_val.reserve(std::max<size_t>(c->plan.bf_col.size(), 1)));
+  OB_CUDA(c, c->d_Ff.reserve(size_t(L) * std::max<int64_t>(nf, 1)));
+  OB_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
+  double launches = 0;
+  for (int64_t k = 0; k < LK; k++) {
+    SparseDev d = sparse_dev(c, k);
+    const double* eai = c->has_case_eai ? c->d_case_eai.p + size_t(k) * 3 * Etot : c->d_elem_EAI.p;
+    OB_CUDA(c, launch_elem_stiff(d, eai, c->stream));
+    OB_CUDA(c, launch_assemble(d, c->stream));
+    launches += 2;
+  }
+  for (int64_t cs = 0; cs < L; cs++) {
+    SparseDev d = sparse_dev(c, 0);
+    const double* nl = c->has_case_nl ? c->d_case_nl.p + size_t(cs) * c->hb.NLtot() : c->d_nload_val.p;
+    const double* q = c->has_case_q ? c->d_case_q.p + size_t(cs) * c->hb.ELtot() : c->d_eload_q.p;
+    OB_CUDA(c, launch_load_vector(d, nl, q, c->d_Ff.p + size_t(cs) * nf, c->stream));
+    launches += d.ELtot ? 2 : 1;
+  }
+  OB_CUDA(c, cudaEventRecord(c->ev[7], c->stream));
+  c->t_have[3] = true;
+  c->launches = launches;
+  c->assembled = true;
+  return OBGPU_OK;
+}
+
+int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
+  if (o.method != OBGPU_PCG_JACOBI)
+    return fail(c, OBGPU_EUNSUPPORTED, "only OBGPU_PCG_JACOBI is implemented on the sparse route so far");
+  int rc = assemble_general(c);
+  if (rc != OBGPU_OK) return rc;
+  const Symbolic& sy = c->sym;
+  const int64_t L = c->L, S = c->hb.S, nf = sy.nf_tot(), nb = sy.nb_tot(), Etot = c->hb.Etot();
+  double launches = c->launches;
+  OB_CUDA(c, c->d_Uf.reserve(size_t(L) * std::max<int64_t>(nf, 1)));
+  OB_CUDA(c, c->d_Fb.reserve(size_t(L) * std::max<int64_t>(nb, 1)));
+  OB_CUDA(c, c->d_info.reserve(size_t(L) * S));
+  OB_CUDA(c, c->d_fail.reserve(1));
+  if (o.with_stress) OB_CUDA(c, c->d_stress.reserve(size_t(L) * Etot * 12));
+  for (auto* b : {&c->d_minv, &c->d_r, &c->d_z, &c->d_p, &c->d_ap}) OB_CUDA(c, b->reserve(std::max<int64_t>(nf, 1)));
+  OB_CUDA(c, c->d_scal.reserve(16));
+  OB_CUDA(c, c->d_partial.reserve(size_t(2) * c->sm_count * 8));
+  OB_CUDA(c, c->d_counter.reserve(1));
+  if (!c->h_scal) OB_CUDA(c, cudaHostAlloc((void**)&c->h_scal, 8 * sizeof(double), cudaHostAllocDefault));
+  OB_CUDA(c, cudaMemsetAsync(c->d_counter.p, 0, sizeof(unsigned int), c->stream));
+  OB_CUDA(c, cudaMemsetAsync(c->d_fail.p, 0, sizeof(int32_t), c->stream));
+  OB_CUDA(c, cudaMemsetAsync(c->d_info.p, 0, size_t(L) * S * sizeof(int32_t), c->stream));
+  OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+  const double rtol = o.rtol > 0 ? o.rtol : 1e-12;
+  const int chk = 25;
+  double iters_total = 0, worst_rel = 0;
+  bool all_converged = true;
+  std::vector<int32_t> h_info(size_t(L) * S, 0);
+  for (int64_t cs = 0; cs < L; cs++) {
+    const int64_t k = c->has_case_eai ? cs : 0;
+    SparseDev d = sparse_dev(c, k);
+    if (cs == 0 || c->has_case_eai) {  // K5: BC elimination as gathers, Jacobi diagonal
+      OB_CUDA(c, launch_bc_gather(d, c->stream));
+      OB_CUDA(c, launch_inv_diag(nf, d.ff_diag, d.ff_val, c->d_minv.p, c->stream));
+      launches += 3;
+    }
+    const double* nl = c->has_case_nl ? c->d_case_nl.p + size_t(cs) * c->hb.NLtot() : c->d_nload_val.p;
+    const double* q = c->has_case_q ? c->d_case_q.p + size_t(cs) * c->hb.ELtot() : c->d_eload_q.p;
+    const double* eai = c->has_case_eai ? c->d_case_eai.p + size_t(cs) * 3 * Etot : c->d_elem_EAI.p;
+    if (L > 1) {  // Eq (equivalent loads on bounded DOFs) of THIS case; F_f was filled by assemble_general
+      OB_CUDA(c, launch_load_vector(d, nl, q, c->d_Ff.p + size_t(cs) * nf, c->stream));
+      launches += 2;
+    }
+    for (int64_t s = 0; s < S; s++) {
+      PcgArgs a;
+      a.r0 = int32_t(sy.free_off[s]); a.r1 = int32_t(sy.free_off[s + 1]);
+      if (a.r1 == a.r0) continue;
+      a.rowptr = d.ff_rowptr; a.col = d.ff_col; a.val = d.ff_val; a.minv = c->d_minv.p;
+      a.b = c->d_Ff.p + size_t(cs) * nf;
+      a.x = c->d_Uf.p + size_t(cs) * nf;
+      a.r = c->d_r.p; a.z = c->d_z.p; a.p = c->d_p.p; a.ap = c->d_ap.p;
+      a.scal = c->d_scal.p; a.partial = c->d_partial.p; a.counter = c->d_counter.p;
+      OB_CUDA(c, launch_pcg_init(a, c->sm_count, c->stream));
+      launches += 1;
+      const int nrows = a.r1 - a.r0;
+      const int max_iter = o.max_iter > 0 ? o.max_iter : int(20.0 * std::sqrt(double(nrows))) + 1000;
+      int it = 0;
+      bool conv = false;
+      double rr = 0, bb = 0;
+      while (true) {
+        OB_CUDA(c, cudaMemcpyAsync(c->h_scal, c->d_scal.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        OB_CUDA(c, cudaStreamSynchronize(c->stream));
+        rr = c->h_scal[3]; bb = c->h_scal[4];
+        if (it == 0) rr = bb;
+        if (!(rr == rr)) break;                                  // NaN: breakdown (K_ff not positive definite)
+        if (rr <= rtol * rtol * bb) { conv = true; break; }
+        if (it >= max_iter) break;
+        const int n_it = std::min(chk, max_iter - it);
+        for (int j = 0; j < n_it; j++, it++) OB_CUDA(c, launch_pcg_iter(a, it, c->sm_count, c->stream));
+        launches += 3.0 * n_it;
+      }
+      iters_total += it;
+      const double rel = bb > 0 ? std::sqrt(rr / bb) : 0.0;
+      worst_rel = std::max(worst_rel, rel == rel ? rel : 1.0);
+      if (!conv) {
+        all_converged = false;
+        h_info[size_t(cs) * S + s] = -1;
+      }
+    }
+    // reactions F_b = K_bf U_f - Eq, element end forces
+    OB_CUDA(c, launch_reactions(d, c->d_Uf.p + size_t(cs) * nf, c->d_Fb.p + size_t(cs) * nb, c->stream));
+    launches += 1;
+    if (o.with_stress) {
+      OB_CUDA(c, launch_stress(d, eai, q, c->d_Uf.p + size_t(cs) * nf, c->d_stress.p + size_t(cs) * Etot * 12, c->stream));
+      launches += 1;
+    }
+  }
+  if (!all_converged)
+    OB_CUDA(c, cudaMemcpyAsync(c->d_info.p, h_info.data(), h_info.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+  OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->t_have[1] = true;
+  c->launches = launches;
+  c->pcg_iters = iters_total;
+  c->pcg_relres = worst_rel;
+  c->solved = true;
+  c->have_stress = o.with_stress != 0;
+  if (!all_converged) return fail(c, OBGPU_ENOTCONVERGED, "PCG did not converge (or broke down: K_ff not positive definite?)");
+  return OBGPU_OK;
+}
+
+int download_general(obgpu_ctx* c, int which, void* out, bool& handled) {
+  handled = false;
+  if (which != OBGPU_RES_KVAL && which != OBGPU_RES_ELEM_K && !(which == OBGPU_RES_FF && c->assembled && !c->solved))
+    return OBGPU_OK;
+  handled = true;
+  if (!c->assembled) return fail(c, OBGPU_ESEQUENCE, "obgpu_download(K) before obgpu_assemble");
+  const void* src;
+  size_t bytes;
+  if (which == OBGPU_RES_KVAL) { src = c->d_kval.p; bytes = size_t(c->LK) * c->sym.nnz_tot() * 8; }
+  else if (which == OBGPU_RES_ELEM_K) { src = c->d_elem_k.p; bytes = size_t(c->LK) * c->hb.Etot() * ELEM_K * 8; }
+  else { src = c->d_Ff.p; bytes = size_t(c->L) * c->sym.nf_tot() * 8; }
+  if (bytes) OB_CUDA(c, cudaMemcpyAsync(out, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return OBGPU_OK;
+}
+
 }  // namespace obgpu

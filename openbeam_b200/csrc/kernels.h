@@ -60,6 +60,42 @@ struct FrameArgs {
 cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st);
 size_t frame_smem_per_warp(int max_band, int max_nf, int max_nb);
 
+// Device view of the sparse route (global indices over the batch).
+struct SparseDev {
+  int64_t Etot, ELtot, nnz, nf, nb, nnz_ff, nnz_bf;
+  const uint2* elem_nodes; const uint8_t* elem_type; const double2* node_xy;
+  const int32_t* elem_node0;   // [Etot] first node of the element's structure
+  const int32_t* elem_f0;      // [Etot] first free DOF of the element's structure
+  const int32_t* node_slot; const int32_t* el_ptr; const int32_t* el_order;
+  const int32_t* eload_elem_g; // [ELtot] global element of each element load (caller slot order)
+  const double* eload_dir;
+  const int32_t *seg_ptr, *seg_src, *ff_rowptr, *ff_col, *ff_src, *ff_diag, *bf_rowptr, *bf_col, *bf_src, *fseg_ptr, *fseg_src;
+  double *elem_k, *kval, *ff_val, *bf_val, *eload_g, *Eq;
+};
+cudaError_t launch_elem_stiff(const SparseDev& d, const double* eai, cudaStream_t st);
+cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st);
+cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st);
+cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, double* F_f, cudaStream_t st);
+cudaError_t launch_stress(const SparseDev& d, const double* eai, const double* q, const double* U_f, double* stress,
+                          cudaStream_t st);
+
+// Jacobi-PCG on rows [r0, r1) of the K_ff CSR (one structure).  Device scalars live in `scal` (16 doubles).
+struct PcgArgs {
+  int32_t r0, r1;
+  const int32_t *rowptr, *col;
+  const double* val;
+  const double* minv;   // [nf] inverse diagonal
+  const double* b;      // rhs (F_f)
+  double *x, *r, *z, *p, *ap;
+  double* scal;         // [0..1] rz ping-pong, [2] pAp, [3] rr, [4] bb
+  double* partial;      // [2 * max blocks]
+  unsigned int* counter;
+};
+cudaError_t launch_pcg_init(const PcgArgs& a, int sm_count, cudaStream_t st);
+cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t st);
+cudaError_t launch_inv_diag(int64_t nf, const int32_t* ff_diag, const double* ff_val, double* minv, cudaStream_t st);
+cudaError_t launch_reactions(const SparseDev& d, const double* U_f, double* F_b, cudaStream_t st);
+
 struct SummaryArgs {
   int64_t L, S, nf_tot, nb_tot;
   const int64_t* free_off;   // [S+1]

@@ -1,0 +1,174 @@
+// kernels_pcg.cu — Jacobi-preconditioned CG for the large-structure route (replaces the SimplicialLLT branch of
+// solveStatic, solver_static.cpp:110-129): memory-bound CSR SpMV fused with the p.Ap dot, and fused
+// axpy / preconditioner / dot kernels.  Dots finish in-kernel (last-block pattern, fixed summation order), the
+// step lengths alpha/beta are computed on the device from `scal`, so an iteration is 3 launches with no host sync.
+#include "kernels.h"
+
+namespace obgpu {
+
+constexpr int PCG_BLOCK = 256;
+constexpr int LPR = 8;  // lanes per CSR row (K_ff of a frame grid has ~15 entries per row)
+
+__device__ __forceinline__ double block_sum(double v, double* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) sh[w] = v;
+  __syncthreads();
+  double t = 0.0;
+  if (w == 0) {
+    t = l < PCG_BLOCK / 32 ? sh[l] : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  }
+  return t;  // valid in thread 0
+}
+
+// Finish NV dots: every block deposits its partials; the last block to arrive sums them in index order.
+template <int NV>
+__device__ __forceinline__ void finish_dots(const double (&v)[NV], double* partial, unsigned int* counter, double* sh,
+                                            double* (&out)[NV]) {
+  __shared__ bool last;
+  double t[NV];
+#pragma unroll
+  for (int k = 0; k < NV; k++) t[k] = block_sum(v[k], sh);
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) partial[k * gridDim.x + blockIdx.x] = t[k];
+    __threadfence();
+    const unsigned int ticket = atomicInc(counter, gridDim.x - 1);  // wraps to 0: self-resetting
+    last = ticket == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (last) {
+    __threadfence();
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+      double acc = 0.0;
+      for (unsigned i = threadIdx.x; i < gridDim.x; i += PCG_BLOCK) acc += __ldcg(partial + k * gridDim.x + i);
+      acc = block_sum(acc, sh);
+      if (threadIdx.x == 0) *out[k] = acc;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(PCG_BLOCK) k_pcg_init(PcgArgs a) {
+  __shared__ double sh[PCG_BLOCK / 32];
+  double v[2] = {0.0, 0.0};
+  for (int64_t i = a.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; i < a.r1; i += int64_t(gridDim.x) * PCG_BLOCK) {
+    const double b = a.b[i], z = a.minv[i] * b;
+    a.x[i] = 0.0;
+    a.r[i] = b;
+    a.z[i] = z;
+    a.p[i] = z;
+    v[0] += b * z;
+    v[1] += b * b;
+  }
+  double* out[2] = {a.scal + 0, a.scal + 4};
+  finish_dots<2>(v, a.partial, a.counter, sh, out);
+  if (blockIdx.x == 0 && threadIdx.x == 0) a.scal[1] = 0.0;
+}
+
+// ap = A p on rows [r0, r1); scal[2] = p.Ap
+__global__ void __launch_bounds__(PCG_BLOCK) k_spmv_dot(PcgArgs a) {
+  __shared__ double sh[PCG_BLOCK / 32];
+  const int sub = threadIdx.x % LPR;
+  const int64_t groups = int64_t(gridDim.x) * (PCG_BLOCK / LPR);
+  double v[1] = {0.0};
+  for (int64_t base = a.r0 + int64_t(blockIdx.x) * (PCG_BLOCK / LPR); base < a.r1; base += groups) {
+    const int64_t row = base + threadIdx.x / LPR;
+    double sum = 0.0;
+    if (row < a.r1) {
+      const int32_t k1 = a.rowptr[row + 1];
+      for (int32_t k = a.rowptr[row] + sub; k < k1; k += LPR) sum += a.val[k] * a.p[a.col[k]];
+    }
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (sub == 0 && row < a.r1) {
+      a.ap[row] = sum;
+      v[0] += sum * a.p[row];
+    }
+  }
+  double* out[1] = {a.scal + 2};
+  finish_dots<1>(v, a.partial, a.counter, sh, out);
+}
+
+// alpha = rz/pAp; x += alpha p; r -= alpha Ap; z = M^-1 r; rz_next = r.z; rr = r.r
+__global__ void __launch_bounds__(PCG_BLOCK) k_pcg_update(PcgArgs a, int cur) {
+  __shared__ double sh[PCG_BLOCK / 32];
+  const double rz = a.scal[cur], pap = a.scal[2];
+  const double alpha = pap != 0.0 ? rz / pap : 0.0;
+  double v[2] = {0.0, 0.0};
+  for (int64_t i = a.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; i < a.r1; i += int64_t(gridDim.x) * PCG_BLOCK) {
+    a.x[i] += alpha * a.p[i];
+    const double r = a.r[i] - alpha * a.ap[i];
+    const double z = a.minv[i] * r;
+    a.r[i] = r;
+    a.z[i] = z;
+    v[0] += r * z;
+    v[1] += r * r;
+  }
+  double* out[2] = {a.scal + (cur ^ 1), a.scal + 3};
+  finish_dots<2>(v, a.partial, a.counter, sh, out);
+}
+
+// beta = rz_next/rz; p = z + beta p
+__global__ void __launch_bounds__(PCG_BLOCK) k_pcg_dir(PcgArgs a, int cur) {
+  const double rz = a.scal[cur], rzn = a.scal[cur ^ 1];
+  const double beta = rz != 0.0 ? rzn / rz : 0.0;
+  for (int64_t i = a.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; i < a.r1; i += int64_t(gridDim.x) * PCG_BLOCK)
+    a.p[i] = a.z[i] + beta * a.p[i];
+}
+
+static unsigned pcg_grid(int64_t work_items, int sm_count) {
+  int64_t g = (work_items + PCG_BLOCK - 1) / PCG_BLOCK;
+  const int64_t cap = int64_t(sm_count) * 8;  // persistent-ish: a whole number of CTAs per SM, grid-stride inside
+  if (g > cap) g = cap;
+  return unsigned(g < 1 ? 1 : g);
+}
+
+cudaError_t launch_pcg_init(const PcgArgs& a, int sm_count, cudaStream_t st) {
+  k_pcg_init<<<pcg_grid(a.r1 - a.r0, sm_count), PCG_BLOCK, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t st) {
+  const int64_t n = a.r1 - a.r0;
+  const int cur = it & 1;
+  k_spmv_dot<<<pcg_grid(n * LPR, sm_count), PCG_BLOCK, 0, st>>>(a);
+  k_pcg_update<<<pcg_grid(n, sm_count), PCG_BLOCK, 0, st>>>(a, cur);
+  k_pcg_dir<<<pcg_grid(n, sm_count), PCG_BLOCK, 0, st>>>(a, cur);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) k_inv_diag(int64_t nf, const int32_t* __restrict__ ff_diag,
+                                                  const double* __restrict__ ff_val, double* __restrict__ minv) {
+  const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i < nf) minv[i] = 1.0 / ff_val[ff_diag[i]];
+}
+cudaError_t launch_inv_diag(int64_t nf, const int32_t* ff_diag, const double* ff_val, double* minv, cudaStream_t st) {
+  k_inv_diag<<<unsigned((nf + 255) / 256), 256, 0, st>>>(nf, ff_diag, ff_val, minv);
+  return cudaGetLastError();
+}
+
+// F_b = K_bf U_f - equivalent loads on the bounded DOFs (solver_static.cpp:196-218); one warp per bounded row
+__global__ void __launch_bounds__(256) k_reactions(int64_t nb, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                                   const double* __restrict__ val, const double* __restrict__ U,
+                                                   const double* __restrict__ Eq, double* __restrict__ F_b) {
+  const int64_t row = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= nb) return;
+  double s = 0.0;
+  for (int32_t k = rowptr[row] + lane; k < rowptr[row + 1]; k += 32) s += val[k] * U[col[k]];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) F_b[row] = s - Eq[row];
+}
+cudaError_t launch_reactions(const SparseDev& d, const double* U_f, double* F_b, cudaStream_t st) {
+  if (d.nb == 0) return cudaSuccess;
+  k_reactions<<<unsigned((d.nb * 32 + 255) / 256), 256, 0, st>>>(d.nb, d.bf_rowptr, d.bf_col, d.bf_val, U_f, d.Eq, F_b);
+  return cudaGetLastError();
+}
+
+}  // namespace obgpu

@@ -104,7 +104,20 @@ struct TinyProgram {
   std::vector<double> dbls;
 };
 
+// Plan of the sparse route (K4 segmented reduction, K5 BC gathers, PCG): all indices GLOBAL over the batch.
+struct SparsePlan {
+  bool valid = false;
+  std::vector<int32_t> seg_ptr, seg_src;      // [nnz_tot+1], [T_tot]: K slot <- ELEM_K entries (elem*21+cid, -1 = zero)
+  std::vector<int32_t> ff_rowptr, ff_col, ff_src;  // K_ff, full symmetric CSR over global free indices; src = K slot
+  std::vector<int32_t> ff_diag;               // [nf_tot] position of the diagonal entry inside ff_col/ff_src
+  std::vector<int32_t> bf_rowptr, bf_col, bf_src;  // K_bf: rows = global bounded index, cols = global free index
+  // load vector gather: target t < nf_tot -> F_f[t]; t >= nf_tot -> Eq[t - nf_tot] (equivalent loads on bounded DOFs)
+  // src >= 0: ELOAD_G entry (multimap position*6 + k); src < 0: nodal load -(l+1)
+  std::vector<int32_t> fseg_ptr, fseg_src;
+};
+
 int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want_pattern);
+int build_sparse_plan(const HostBatch& hb, const Symbolic& sym, SparsePlan& plan, std::string& err);
 int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& prog, std::string& err);
 
 }  // namespace obgpu

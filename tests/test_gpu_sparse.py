@@ -1,0 +1,128 @@
+"""GPU parity tests of the sparse route (BASELINE configs C4/C5): K1+K4 global assembly (values of K in the
+reference's CSC order), K5 BC gather, Jacobi-PCG, reactions and stress, against the CPU oracle and scipy."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import scipy.sparse.linalg as spla
+
+import fixtures
+from openbeam_b200 import obgpu, workloads
+from oracle.pyoracle import OracleProblem
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+def relerr(a, b):
+    a, b = np.asarray(a, float).ravel(), np.asarray(b, float).ravel()
+    assert a.shape == b.shape
+    if a.size == 0:
+        return 0.0
+    den = np.max(np.abs(b))
+    return float(np.max(np.abs(a - b)) / den) if den > 0 else float(np.max(np.abs(a)))
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = obgpu.Context(0)
+    yield c
+    c.close()
+
+
+def test_assemble_matches_oracle(ctx):
+    """obgpu_assemble: values of K (upper CSC == lower CSR, explicit zeros kept) and F_f, structure by structure."""
+    sts = [fixtures.ALL[k]() for k in fixtures.PLAIN] + [workloads.c3_frame(i) for i in range(50)] + \
+          [workloads.grid_frame(9, 7), workloads.grid_frame(5, 6, etype=3)]
+    ctx.upload(sts)
+    ctx.symbolic()
+    ctx.assemble()
+    kval = ctx.download(obgpu.RES_KVAL)[0]
+    Ff = ctx.download(obgpu.RES_FF)[0]
+    zo, fo = ctx.offsets(obgpu.OFF_NNZ), ctx.offsets(obgpu.OFF_FREE)
+    for s, st in enumerate(sts):
+        o = OracleProblem(st).assembleProblem(skip_subK=True)
+        _, _, oval = o.K_csc_upper()
+        mine = kval[zo[s]:zo[s + 1]]
+        assert relerr(mine, oval) <= 1e-13, s
+        assert np.array_equal(mine == 0, oval == 0)   # structural zeros stay exact zeros
+        assert relerr(Ff[fo[s]:fo[s + 1]], o.F_f) <= 1e-13, s
+
+
+def test_assemble_per_case_sections(ctx):
+    st = workloads.demo3_frame()
+    L = 7
+    nl, q, eai = workloads.c2_cases(5, L, True)
+    ctx.upload(st, L, nl, q, eai)
+    ctx.assemble()
+    kval = ctx.download(obgpu.RES_KVAL, lk=L)
+    o = OracleProblem(st)
+    for c in range(L):
+        o.set_elem_EAI(eai[c])
+        o.assembleProblem(skip_subK=True)
+        assert relerr(kval[c], o.K_csc_upper()[2]) <= 1e-13
+
+
+def oracle_sparse_solve(st):
+    """Independent numerics: oracle's K (sparse) -> scipy splu on K_ff."""
+    o = OracleProblem(st).assembleProblem(skip_subK=True)
+    outer, inner, val = o.K_csc_upper()
+    n = len(outer) - 1
+    Ku = sp.csc_matrix((val, inner, outer), shape=(n, n))
+    K = (Ku + sp.triu(Ku, 1).T).tocsc()
+    f, b = o.free_dof_indices, o.bounded_dof_indices
+    U = spla.splu(K[f][:, f].tocsc()).solve(o.F_f)
+    return o, K, U, f, b
+
+
+@pytest.mark.parametrize("nx,ny", [(12, 10), (40, 35)])
+def test_pcg_grid(ctx, nx, ny):
+    st = workloads.grid_frame(nx, ny)
+    ctx.upload(st)
+    ctx.solve_static(method=obgpu.PCG_JACOBI, rtol=1e-13)
+    U, Fb, S = (ctx.download(w)[0] for w in (obgpu.RES_UF, obgpu.RES_FB, obgpu.RES_STRESS))
+    assert not ctx.download(obgpu.RES_INFO).any()
+    t = ctx.timings()
+    assert t["pcg_iters"] > 10
+    o, K, Uref, f, b = oracle_sparse_solve(st)
+    assert relerr(U, Uref) <= RTOL
+    if nx * ny <= 200:  # dense oracle end to end (reactions, stress)
+        od = OracleProblem(st).solveStatic().postProcCalcStress()
+        assert relerr(U, od.U_f) <= RTOL and relerr(Fb, od.F_b) <= RTOL and relerr(S, od.element_stress) <= RTOL
+    # equilibrium: sum of vertical reactions = total UDL; horizontal reactions balance the lateral loads
+    fb = Fb.reshape(-1, 3)
+    assert abs(fb[:, 1].sum() - 9810.0 * len(st.eload_q)) <= 1e-9 * np.abs(fb[:, 1]).sum()
+    assert abs(fb[:, 0].sum() + st.nload_val.sum()) <= 1e-9 * max(np.abs(fb[:, 0]).sum(), 1.0)
+
+
+def test_pcg_batch_of_grids(ctx):
+    """Config C5 shape: several large-ish structures in one batch, each solved by its own PCG."""
+    sts = [workloads.grid_frame(14, 11, seed_index=i, section=(2.1e11, workloads.IPE[5 + i][0], workloads.IPE[5 + i][1]))
+           for i in range(3)]
+    ctx.upload(sts)
+    ctx.solve_static(method=obgpu.PCG_JACOBI, rtol=1e-13)
+    U, Fb, S = (ctx.download(w)[0] for w in (obgpu.RES_UF, obgpu.RES_FB, obgpu.RES_STRESS))
+    fo, bo = ctx.offsets(obgpu.OFF_FREE), ctx.offsets(obgpu.OFF_BOUNDED)
+    eo = np.concatenate([[0], np.cumsum([s.n_elems for s in sts])])
+    for s, st in enumerate(sts):
+        od = OracleProblem(st).solveStatic().postProcCalcStress()
+        assert relerr(U[fo[s]:fo[s + 1]], od.U_f) <= RTOL
+        assert relerr(Fb[bo[s]:bo[s + 1]], od.F_b) <= RTOL
+        assert relerr(S[eo[s]:eo[s + 1]], od.element_stress) <= RTOL
+
+
+def test_pcg_matches_batched_ldlt(ctx):
+    sts = [workloads.c3_frame(i) for i in range(10)]
+    ctx.upload(sts)
+    ctx.solve_static()
+    U1, F1 = ctx.download(obgpu.RES_UF), ctx.download(obgpu.RES_FB)
+    ctx.solve_static(method=obgpu.PCG_JACOBI, rtol=1e-14, max_iter=20000)
+    U2, F2 = ctx.download(obgpu.RES_UF), ctx.download(obgpu.RES_FB)
+    assert relerr(U2, U1) <= RTOL and relerr(F2, F1) <= RTOL
+
+
+def test_pcg_not_converged_reported(ctx):
+    st = workloads.grid_frame(30, 30)
+    ctx.upload(st)
+    with pytest.raises(obgpu.ObgpuError) as e:
+        ctx.solve_static(method=obgpu.PCG_JACOBI, rtol=1e-13, max_iter=5)
+    assert e.value.status == obgpu.ENOTCONVERGED
