@@ -1,0 +1,234 @@
+// obhost.hpp — header-only C++ mirror of libopenbeam's static-solve interface over the C ABI (obgpu.h).
+//
+// Same method names, argument meaning and error behaviour as the reference (paths under
+// /root/reference/libopenbeam/include/openbeam/):
+//   BuildProblemInfo          CFiniteElementProblem.h:76-102
+//   StaticSolveProblemInfo    CFiniteElementProblem.h:105-123
+//   StaticSolverAlgorithm     CFiniteElementProblem.h:69-73    (+ GPU_* cases)
+//   StaticSolverOptions       CFiniteElementProblem.h:165-171
+//   StressInfo, FaceStress    CFiniteElementProblem.h:173-183, types.h:78-157
+//   assembleProblem / solveStatic / postProcCalcStress   CFiniteElementProblem.h:435,444-446,453-454
+// Errors: std::runtime_error with the reference's message for a non-positive-definite K_ff
+// (CFiniteElementProblem_solver_static.cpp:98-105).  No arithmetic happens in this header.
+#pragma once
+#include <array>
+#include <cstddef>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "obgpu.h"
+
+namespace obhost {
+
+using num_t = double;  // config.h:25
+
+enum class StaticSolverAlgorithm : uint8_t {
+  Dense_LLT = 0,   // reference CPU algorithms: refused here (libobgpu has no CPU fallback)
+  Sparse_LLT,
+  GPU_Batched_LDLT,
+  GPU_PCG_Jacobi,
+};
+
+struct StaticSolverOptions {
+  StaticSolverAlgorithm algorithm = StaticSolverAlgorithm::GPU_Batched_LDLT;
+  bool nonLinearIterative = false;
+  double pcg_rtol = 1e-12;
+  int pcg_max_iter = 0;
+};
+
+struct TDoFType {  // BuildProblemInfo::dof_types entries (assemble.cpp:83-97)
+  size_t bounded_index = std::string::npos, free_index = std::string::npos;
+};
+
+struct BuildProblemInfo {
+  std::vector<size_t> free_dof_indices, bounded_dof_indices;
+  std::vector<TDoFType> dof_types;
+  // K: upper triangle in Eigen's compressed column order (== CSR of the lower triangle)
+  std::vector<int32_t> K_outer, K_inner;
+  std::vector<num_t> K_values;
+  std::vector<num_t> U_b, F_f;
+};
+
+struct StaticSolveProblemInfo {
+  BuildProblemInfo build_info;
+  std::vector<num_t> U_f, F_b;
+};
+
+struct FaceStress {
+  num_t N = 0, Vy = 0, Vz = 0, Mx = 0, My = 0, Mz = 0;
+};
+using ElementStress = std::vector<FaceStress>;
+struct StressInfo {
+  std::vector<ElementStress> element_stress;
+};
+
+struct NodeDoF {  // CFiniteElementProblem.h:53-67
+  size_t nodeId;
+  uint8_t dof;
+};
+
+// One structure (2D beam elements RR/RA/AR/AA) bound to one GPU context.
+class CStructureProblem {
+ public:
+  explicit CStructureProblem(int device = 0) {
+    const int rc = obgpu_create(device, &ctx_);
+    if (rc != OBGPU_OK) throw std::runtime_error(std::string("obgpu_create: ") + obgpu_status_string(rc));
+  }
+  ~CStructureProblem() { obgpu_destroy(ctx_); }
+  CStructureProblem(const CStructureProblem&) = delete;
+  CStructureProblem& operator=(const CStructureProblem&) = delete;
+
+  // ---- model building (names follow CFiniteElementProblem.h:196-330) ----
+  size_t insertNode(num_t x, num_t y) {
+    node_xy_.push_back(x);
+    node_xy_.push_back(y);
+    dirty_ = true;
+    return node_xy_.size() / 2 - 1;
+  }
+  // type: OBGPU_BEAM2D_{RR,RA,AR,AA}; E, A, Iz as CBaseElementBeam
+  size_t insertElement(uint8_t type, size_t n0, size_t n1, num_t E, num_t A, num_t Iz) {
+    elem_nodes_.push_back(uint32_t(n0));
+    elem_nodes_.push_back(uint32_t(n1));
+    elem_type_.push_back(type);
+    elem_EAI_.insert(elem_EAI_.end(), {E, A, Iz});
+    dirty_ = true;
+    return elem_type_.size() - 1;
+  }
+  void insertConstraint(size_t node, uint8_t dof, num_t value = 0) {
+    con_node_.push_back(uint32_t(node)); con_dof_.push_back(dof); con_val_.push_back(value);
+    dirty_ = true;
+  }
+  void addLoadAtDOF(size_t node, uint8_t dof, num_t f) {
+    nl_node_.push_back(uint32_t(node)); nl_dof_.push_back(dof); nl_val_.push_back(f);
+    dirty_ = true;
+  }
+  // CLoadDistributedUniform(q, dir)
+  void addLoadAtBeam(size_t element, num_t q, num_t dx, num_t dy, num_t dz) {
+    el_elem_.push_back(uint32_t(element)); el_q_.push_back(q);
+    el_dir_.insert(el_dir_.end(), {dx, dy, dz});
+    dirty_ = true;
+  }
+  size_t getNumberOfNodes() const { return node_xy_.size() / 2; }
+  size_t getNumberOfElements() const { return elem_type_.size(); }
+
+  void updateAll() {
+    upload();
+    check(obgpu_symbolic(ctx_));
+  }
+  std::vector<NodeDoF> getProblemDoFs() {
+    updateAll();
+    const auto z = sizes();
+    std::vector<int32_t> nd(z[4]), id(z[4]);
+    check(obgpu_get_symbolic(ctx_, OBGPU_SYM_DOF_NODE, nd.data()));
+    check(obgpu_get_symbolic(ctx_, OBGPU_SYM_DOF_ID, id.data()));
+    std::vector<NodeDoF> out(z[4]);
+    for (size_t i = 0; i < out.size(); i++) out[i] = NodeDoF{size_t(nd[i]), uint8_t(id[i])};
+    return out;
+  }
+
+  // ---- the hot path ----
+  void assembleProblem(BuildProblemInfo& out) {
+    updateAll();
+    check(obgpu_assemble(ctx_));
+    fill_lists(out);
+    const auto z = sizes();
+    out.K_values.resize(z[8]);
+    check(obgpu_download(ctx_, OBGPU_RES_KVAL, out.K_values.data()));
+    out.U_b.resize(z[6]);
+    check(obgpu_download(ctx_, OBGPU_RES_UB, out.U_b.data()));
+    out.F_f.resize(z[5]);
+    check(obgpu_download(ctx_, OBGPU_RES_FF, out.F_f.data()));
+  }
+
+  void solveStatic(StaticSolveProblemInfo& out, const StaticSolverOptions& opts = StaticSolverOptions()) {
+    if (opts.algorithm == StaticSolverAlgorithm::Dense_LLT || opts.algorithm == StaticSolverAlgorithm::Sparse_LLT)
+      throw std::runtime_error("Dense_LLT/Sparse_LLT are the reference's CPU algorithms; libobgpu has no CPU fallback");
+    if (opts.nonLinearIterative) throw std::runtime_error("nonLinearIterative is outside the GPU path");
+    updateAll();
+    obgpu_solve_opts o;
+    o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI : OBGPU_BATCHED_LDLT;
+    o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.reserved = 0;
+    check(obgpu_solve_static(ctx_, &o));
+    const auto z = sizes();
+    std::vector<int32_t> info(z[0] * z[1]);
+    if (obgpu_download(ctx_, OBGPU_RES_INFO, info.data()) == OBGPU_ESINGULAR)
+      throw std::runtime_error(obgpu_status_string(OBGPU_ESINGULAR));  // solver_static.cpp:102-104
+    fill_lists(out.build_info);
+    out.build_info.U_b.resize(z[6]); out.build_info.F_f.resize(z[5]);
+    out.U_f.resize(z[5]); out.F_b.resize(z[6]);
+    check(obgpu_download(ctx_, OBGPU_RES_UB, out.build_info.U_b.data()));
+    check(obgpu_download(ctx_, OBGPU_RES_FF, out.build_info.F_f.data()));
+    check(obgpu_download(ctx_, OBGPU_RES_UF, out.U_f.data()));
+    check(obgpu_download(ctx_, OBGPU_RES_FB, out.F_b.data()));
+  }
+
+  void postProcCalcStress(StressInfo& out, const StaticSolveProblemInfo& /*solver_info*/) {
+    check(obgpu_stress(ctx_));
+    const size_t E = getNumberOfElements();
+    std::vector<num_t> s(E * 12);
+    check(obgpu_download(ctx_, OBGPU_RES_STRESS, s.data()));
+    out.element_stress.assign(E, ElementStress(2));
+    for (size_t e = 0; e < E; e++)
+      for (int f = 0; f < 2; f++) {
+        const num_t* v = &s[e * 12 + f * 6];
+        out.element_stress[e][f] = FaceStress{v[0], v[1], v[2], v[3], v[4], v[5]};
+      }
+  }
+
+  obgpu_ctx* ctx() { return ctx_; }
+
+ private:
+  void check(int rc) {
+    if (rc != OBGPU_OK) {
+      const char* m = obgpu_last_error(ctx_);
+      throw std::runtime_error((m && *m) ? m : obgpu_status_string(rc));
+    }
+  }
+  std::array<int64_t, OBGPU_NSIZES> sizes() {
+    std::array<int64_t, OBGPU_NSIZES> z{};
+    check(obgpu_get_sizes(ctx_, z.data()));
+    return z;
+  }
+  void upload() {
+    if (!dirty_) return;
+    const int64_t off_n[2] = {0, int64_t(getNumberOfNodes())}, off_e[2] = {0, int64_t(getNumberOfElements())};
+    const int64_t off_c[2] = {0, int64_t(con_node_.size())}, off_l[2] = {0, int64_t(nl_node_.size())};
+    const int64_t off_q[2] = {0, int64_t(el_elem_.size())};
+    obgpu_batch_desc d{};
+    d.n_structures = 1;
+    d.node_off = off_n; d.elem_off = off_e; d.con_off = off_c; d.nload_off = off_l; d.eload_off = off_q;
+    d.node_xy = node_xy_.data(); d.node_rotz = nullptr;
+    d.elem_nodes = elem_nodes_.data(); d.elem_type = elem_type_.data(); d.elem_EAI = elem_EAI_.data();
+    d.con_node = con_node_.data(); d.con_dof = con_dof_.data(); d.con_val = con_val_.data();
+    d.nload_node = nl_node_.data(); d.nload_dof = nl_dof_.data(); d.nload_val = nl_val_.data();
+    d.eload_elem = el_elem_.data(); d.eload_q = el_q_.data(); d.eload_dir = el_dir_.data();
+    d.n_cases = 1;
+    check(obgpu_batch_upload(ctx_, &d));
+    dirty_ = false;
+  }
+  void fill_lists(BuildProblemInfo& bi) {
+    const auto z = sizes();
+    std::vector<int32_t> f(z[5]), b(z[6]);
+    check(obgpu_get_symbolic(ctx_, OBGPU_SYM_FREE, f.data()));
+    check(obgpu_get_symbolic(ctx_, OBGPU_SYM_BOUNDED, b.data()));
+    bi.free_dof_indices.assign(f.begin(), f.end());
+    bi.bounded_dof_indices.assign(b.begin(), b.end());
+    bi.dof_types.assign(z[4], TDoFType());
+    for (size_t i = 0; i < f.size(); i++) bi.dof_types[f[i]].free_index = i;
+    for (size_t i = 0; i < b.size(); i++) bi.dof_types[b[i]].bounded_index = i;
+    bi.K_outer.resize(z[4] + 1);
+    bi.K_inner.resize(z[8]);
+    check(obgpu_get_symbolic(ctx_, OBGPU_SYM_K_ROWPTR, bi.K_outer.data()));
+    check(obgpu_get_symbolic(ctx_, OBGPU_SYM_K_COL, bi.K_inner.data()));
+  }
+
+  obgpu_ctx* ctx_ = nullptr;
+  bool dirty_ = true;
+  std::vector<double> node_xy_, elem_EAI_, con_val_, nl_val_, el_q_, el_dir_;
+  std::vector<uint32_t> elem_nodes_, con_node_, nl_node_, el_elem_;
+  std::vector<uint8_t> elem_type_, con_dof_, nl_dof_;
+};
+
+}  // namespace obhost

@@ -1,0 +1,38 @@
+"""The C++ host mirror (include/obhost.hpp) over the C ABI: compiles examples/ob_solve_demo3.cpp with g++ and runs
+it — symbolic-only on CPU, the full solve on the GPU box against SURVEY.md §4's closed-form-checked numbers."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def build(tmp_path):
+    exe = str(tmp_path / "ob_solve_demo3")
+    libdir = os.path.join(ROOT, "openbeam_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "ob_solve_demo3.cpp"), "-L" + libdir, "-lobgpu",
+                           "-Wl,-rpath," + libdir, "-o", exe])
+    return exe
+
+
+def test_cpp_mirror_symbolic(tmp_path):
+    out = subprocess.check_output([build(tmp_path), "-1"], text=True)
+    assert "nDOFs 12" in out
+    dofs = re.findall(r"dof (\d+) node (\d+) id (\d+)", out)
+    assert [(int(n), int(d)) for _, n, d in dofs] == [(n, d) for n in range(4) for d in (0, 1, 5)]
+
+
+@pytest.mark.gpu
+def test_cpp_mirror_solve(tmp_path):
+    out = subprocess.check_output([build(tmp_path), "0"], text=True)
+    U = np.array([float(x) for x in re.findall(r"U_f\[\d+\] (\S+)", out)])
+    F = np.array([float(x) for x in re.findall(r"F_b\[\d+\] (\S+)", out)])
+    assert np.allclose(U, [2.6013078134695e-5, -6.5563909774436e-5, -1.29984937854503e-3,
+                           -2.6013078134695e-5, -6.5563909774436e-5, 1.29984937854503e-3], rtol=1e-10)
+    assert np.allclose(F, [7784.41363180755, 19620, -5136.62044771133, -7784.41363180755, 19620, 5136.62044771133],
+                       rtol=1e-10)
+    assert re.search(r"stress e1 f0 N -7784\.41", out)
