@@ -157,7 +157,7 @@ def reference_arm(args, rank, world):
 def ours_arm(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
-    from openbeam_b200 import obgpu, workloads
+    from openbeam_b200 import obgpu, sharding, workloads
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — libobgpu has no CPU fallback")
@@ -171,7 +171,7 @@ def ours_arm(args, rank, local_rank, world):
     # pinned host buffers: this rank's cases [rank*L, (rank+1)*L)
     h_nl, h_q = obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 1))
     h_eai = obgpu.pinned_empty((L, 9)) if args.per_case_section else None
-    workloads.c2_cases(rank * L, L, args.per_case_section, h_nl, h_q, h_eai)
+    workloads.c2_cases(sharding.weak_range(L, rank)[0], L, args.per_case_section, h_nl, h_q, h_eai)
     h_U, h_Fb, h_S = obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 3, 2, 6))
     h_info = obgpu.pinned_empty((L,), np.int32)
 
@@ -190,7 +190,7 @@ def ours_arm(args, rank, local_rank, world):
         ctx.solve_static()                       # 1 fused kernel: K1+K2+K4+K5+K6+K10 per case
         ctx.summaries_device(summ.data_ptr())    # 1 kernel: per-case {max|U|, sum Fb_x, sum Fb_y, info}
         if world > 1:
-            dist.all_gather_into_tensor(gathered, summ)   # the only collective
+            sharding.gather_summaries(summ, gathered)     # the only collective
 
     with torch.cuda.stream(ext):
         for _ in range(W):
