@@ -79,16 +79,26 @@ __device__ __forceinline__ void elem_global_k(const ElemLocalK& k, const ElemGeo
   ke[18] = -s * k.q51; ke[19] = c * k.q51; ke[20] = k.q55;
 }
 
+// CLoadDistributedUniform.cpp:64-71: projections of the load direction on the beam axis and its normal
+// (case-invariant: depend on geometry and direction only)
+struct LoadProj {
+  double plong, pperp;
+};
+__device__ __forceinline__ LoadProj load_proj(const ElemGeom& g, double dx, double dy) {
+  LoadProj p;
+  p.plong = g.c * dx + g.s * dy;                 // Az = 0 in plane
+  const double cross_z = g.c * dy - g.s * dx;
+  p.pperp = sqrt(1.0 - p.plong * p.plong) * (cross_z < 0 ? 1.0 : -1.0);
+  return p;
+}
+
 // CLoadDistributedUniform.cpp:33-159.  Outputs:
 //   gl[6]  equivalent nodal loads in global axes (Fx,Fy,Mz at end 0; Fx,Fy,Mz at end 1)
 //   ex[6]  fixed-end stress to add in postProcCalcStress (N,Vy,Mz at face 0; N,Vy,Mz at face 1)
-__device__ __forceinline__ void uniform_load(int type, const ElemGeom& g, double q, double dx, double dy, double gl[6],
-                                             double ex[6]) {
+__device__ __forceinline__ void uniform_load_p(int type, const ElemGeom& g, double q, const LoadProj& pr, double gl[6],
+                                               double ex[6]) {
   const double L = g.L;
-  const double proy_long = g.c * dx + g.s * dy;                 // Az = 0 in plane
-  const double cross_z = g.c * dy - g.s * dx;
-  const double proy_perp = sqrt(1.0 - proy_long * proy_long) * (cross_z < 0 ? 1.0 : -1.0);
-  const double q_t = q * proy_long, q_n = q * proy_perp;
+  const double q_t = q * pr.plong, q_n = q * pr.pperp;
   const double fx = -q_t * L * 0.5;
   double f1y, f2y, m1, m2;
   if (type == OBGPU_BEAM2D_AA) {
@@ -104,6 +114,10 @@ __device__ __forceinline__ void uniform_load(int type, const ElemGeom& g, double
   ex[3] = fx;  ex[4] = f2y;  ex[5] = m2;
   gl[0] = -(g.c * fx - g.s * f1y); gl[1] = -(g.s * fx + g.c * f1y); gl[2] = -m1;
   gl[3] = -(g.c * fx - g.s * f2y); gl[4] = -(g.s * fx + g.c * f2y); gl[5] = -m2;
+}
+__device__ __forceinline__ void uniform_load(int type, const ElemGeom& g, double q, double dx, double dy, double gl[6],
+                                             double ex[6]) {
+  uniform_load_p(type, g, q, load_proj(g, dx, dy), gl, ex);
 }
 
 // postproc_stress.cpp:86-146 : raw end forces es = K_local * U_local (before the face-0 sign flip).

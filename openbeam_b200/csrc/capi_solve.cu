@@ -32,8 +32,8 @@ static int alloc_results(obgpu_ctx* c, int64_t L, bool stress) {
 static TinyArgs tiny_args(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai, double* Uf,
                           double* Fb, double* stress, double* Ff, int32_t* info) {
   TinyArgs a;
-  a.prog_i = c->d_prog_i.p;
-  a.prog_d = c->d_prog_d.p;
+  a.prog_i = c->prog.ints.data();
+  a.prog_d = c->prog.dbls.data();
   a.n_ints = int(c->prog.ints.size());
   a.n_dbls = int(c->prog.dbls.size());
   a.n_cases = L;

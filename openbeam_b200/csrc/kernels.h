@@ -5,7 +5,7 @@
 namespace obgpu {
 
 struct TinyArgs {
-  const int32_t* prog_i;
+  const int32_t* prog_i;   // HOST pointers: the topology program is copied into the kernel parameter (constant bank)
   const double* prog_d;
   int n_ints, n_dbls;
   int64_t n_cases;

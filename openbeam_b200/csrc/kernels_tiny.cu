@@ -1,133 +1,165 @@
 // kernels_tiny.cu — K1+K2+K4+K5+K6+K10 fused for batches of load cases over ONE small shared topology
-// (BASELINE config 2: demo3_frame x 1M cases).  One THREAD per system: at n_f <= 12 a CTA per
-// system would leave >90% of the lanes idle, and the whole pipeline is HBM-bound (440 B/case for
-// demo3_frame) — so each lane carries one case end to end:
-//   element stiffness (closed form, beam_math.cuh) -> scatter into its private packed K_ff in shared
-//   memory through the topology program (uniform indices: every lane of a warp follows the same
-//   program, so smem accesses are conflict-free [idx][lane] columns) -> equivalent nodal loads ->
-//   K_ff pulled into registers -> fully unrolled LDL^T + solves -> element end forces, reactions.
-// Sums follow the reference's element order (assemble.cpp:123-223), no atomics anywhere.
-// Replaces, per case, one full solveStatic()+postProcCalcStress() call of the reference.
+// (BASELINE config 2: demo3_frame x 1M cases).  One THREAD per system: at n_f <= 12 a CTA per system would
+// leave >90% of the lanes idle, and the pipeline moves only 440 B per case — so each lane
+// carries one case end to end:
+//   per CTA, once:  case-invariant geometry (orientation, L, 1/L: internals.cpp:30-123) of the E elements and
+//                   the projections of the element-load directions -> shared memory
+//   per case:       local stiffness from (E,A,Iz) -> rotation to global (closed form, beam_math.cuh) -> scatter
+//                   into the lane's private packed K_ff column in shared memory through the topology program
+//                   -> equivalent nodal loads -> K_ff pulled into registers -> fully unrolled LDL^T + solves
+//                   -> element end forces, reactions.
+// The topology "program" (integer indices produced by the host symbolic phase) rides in the kernel parameter,
+// i.e. the constant bank: every lane follows the same program, so index reads are uniform constant loads and
+// the skip-tests are uniform branches; shared memory holds only the per-lane columns [idx][lane] (conflict-free).
+// Sums follow the reference's element order (assemble.cpp:123-223); no atomics on the data path.
+#include <cstring>
+
 #include "beam_math.cuh"
 #include "kernels.h"
 #include "tiny_program.h"
 
 namespace obgpu {
 
+constexpr int TINY_BLOCK = 128;
+
+// fixed-capacity copy of the program, passed by value (constant bank)
+struct TinyParam {
+  int N, E, n, nb, NL, EL;
+  int8_t enode[2 * TINY_MAX_E];
+  int8_t etype[TINY_MAX_E];
+  int8_t udof[6 * TINY_MAX_E];       // -1 absent, k free, k|64 bounded
+  int8_t edst[ELEM_K * TINY_MAX_E];  // packed K_ff index or -1
+  int8_t elptr[TINY_MAX_E + 1];
+  int8_t elslot[TINY_MAX_EL];
+  int8_t nldst[TINY_MAX_NL];
+  int8_t freek[TINY_MAX_NF];
+  int8_t bndk[TINY_MAX_N];
+  double xy[2 * TINY_MAX_NODES];
+  double eai[3 * TINY_MAX_E];
+  double nlval[TINY_MAX_NL];
+  double elq[TINY_MAX_EL];
+  double eldir[2 * TINY_MAX_EL];
+};
+
 template <int NF>
-__device__ __forceinline__ int ldlt_solve_regs(double (&A)[NF * (NF + 1) / 2 + 1], double (&b)[NF + 1]) {
-  // A: packed lower, A[i*(i+1)/2+j].  In place: L (unit lower) below the diagonal, D on it.
+__device__ __forceinline__ int ldlt_solve_regs(double (&A)[NF + 1][NF + 1], double (&b)[NF + 1]) {
+  // A: lower triangle A[i][j], j <= i.  In place: L (unit lower) below the diagonal, D on it.
   int info = 0;
 #pragma unroll
   for (int j = 0; j < NF; j++) {
-    double dj = A[j * (j + 1) / 2 + j];
+    double dj = A[j][j];
 #pragma unroll
-    for (int k = 0; k < j; k++) {
-      const double l = A[j * (j + 1) / 2 + k];
-      dj -= l * l * A[k * (k + 1) / 2 + k];
-    }
+    for (int k = 0; k < NF; k++)
+      if (k < j) dj -= A[j][k] * A[j][k] * A[k][k];
     if (!(dj > 0.0) && info == 0) info = j + 1;  // Eigen LLT fails on x <= 0 (solver_static.cpp:97-105)
-    A[j * (j + 1) / 2 + j] = dj;
+    A[j][j] = dj;
     const double inv = 1.0 / dj;
 #pragma unroll
-    for (int i = j + 1; i < NF; i++) {
-      double v = A[i * (i + 1) / 2 + j];
+    for (int i = 0; i < NF; i++) {
+      if (i > j) {
+        double v = A[i][j];
 #pragma unroll
-      for (int k = 0; k < j; k++) v -= A[i * (i + 1) / 2 + k] * (A[j * (j + 1) / 2 + k] * A[k * (k + 1) / 2 + k]);
-      A[i * (i + 1) / 2 + j] = v * inv;
+        for (int k = 0; k < NF; k++)
+          if (k < j) v -= A[i][k] * (A[j][k] * A[k][k]);
+        A[i][j] = v * inv;
+      }
     }
   }
 #pragma unroll
   for (int i = 0; i < NF; i++) {  // L y = b
 #pragma unroll
-    for (int k = 0; k < i; k++) b[i] -= A[i * (i + 1) / 2 + k] * b[k];
+    for (int k = 0; k < NF; k++)
+      if (k < i) b[i] -= A[i][k] * b[k];
   }
 #pragma unroll
-  for (int i = 0; i < NF; i++) b[i] /= A[i * (i + 1) / 2 + i];
+  for (int i = 0; i < NF; i++) b[i] /= A[i][i];
 #pragma unroll
-  for (int ii = 0; ii < NF; ii++) {  // L^T x = z  (ascending counter so the loop unrolls)
+  for (int ii = 0; ii < NF; ii++) {  // L^T x = z
     const int i = NF - 1 - ii;
 #pragma unroll
-    for (int kk = 0; kk < ii; kk++) {
-      const int k = NF - 1 - kk;
-      b[i] -= A[k * (k + 1) / 2 + i] * b[k];
-    }
+    for (int k = 0; k < NF; k++)
+      if (k > i) b[i] -= A[k][i] * b[k];
   }
   return info;
 }
 
-template <int NF, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) k_tiny_fused(TinyArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  int32_t* PI = reinterpret_cast<int32_t*>(smem_raw);
-  double* PD = reinterpret_cast<double*>(smem_raw + size_t(a.n_ints) * 4);
-  double* scratch = PD + a.n_dbls;
-  for (int i = threadIdx.x; i < a.n_ints; i += BLOCK) PI[i] = a.prog_i[i];
-  for (int i = threadIdx.x; i < a.n_dbls; i += BLOCK) PD[i] = a.prog_d[i];
-  __syncthreads();
-  const int N = PI[0], E = PI[1], n = PI[2], nb = PI[4], NL = PI[5], EL = PI[6];
+template <int NF, int MINB>
+__global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_constant__ TinyParam P, TinyArgs a) {
+  constexpr int BLOCK = TINY_BLOCK;
   constexpr int NFP = NF * (NF + 1) / 2;
-  const TinyLayout lay(N, E, n, NF, nb, NL, EL);
-  // private columns: Kp[NFP] | F[n] | U[n], element [idx] of lane t at scratch[idx*BLOCK + t]
-  double* Kp = scratch + threadIdx.x;
-  double* F = Kp + size_t(NFP) * BLOCK;
-  double* U = F + size_t(n) * BLOCK;
+  extern __shared__ __align__(16) double smem[];
+  // shared: G[E][4] = c,s,L,1/L | LP[EL][2] | per-lane columns Kp[NFP][BLOCK], FU[n][BLOCK]
+  const int E = P.E, n = P.n, nb = P.nb, NL = P.NL, EL = P.EL;
+  double* G = smem;
+  double* LP = G + 4 * E;
+  double* Kp = LP + 2 * EL + threadIdx.x;
+  double* FU = Kp + size_t(NFP) * BLOCK;
+  if (threadIdx.x < E) {
+    const int e = threadIdx.x, na = P.enode[2 * e], nbn = P.enode[2 * e + 1];
+    const ElemGeom g = elem_geom(P.xy[2 * na], P.xy[2 * na + 1], P.xy[2 * nbn], P.xy[2 * nbn + 1]);
+    G[4 * e] = g.c; G[4 * e + 1] = g.s; G[4 * e + 2] = g.L; G[4 * e + 3] = g.invL;
+    for (int j = P.elptr[e]; j < P.elptr[e + 1]; j++) {
+      const int slot = P.elslot[j];
+      const LoadProj pr = load_proj(g, P.eldir[2 * slot], P.eldir[2 * slot + 1]);
+      LP[2 * slot] = pr.plong; LP[2 * slot + 1] = pr.pperp;
+    }
+  }
+  __syncthreads();
 
   for (int64_t cs = int64_t(blockIdx.x) * BLOCK + threadIdx.x; cs < a.n_cases; cs += int64_t(gridDim.x) * BLOCK) {
 #pragma unroll
     for (int i = 0; i < NFP; i++) Kp[i * BLOCK] = 0.0;
-    for (int i = 0; i < n; i++) {
-      F[i * BLOCK] = 0.0;
-      U[i * BLOCK] = 0.0;
-    }
+    for (int i = 0; i < n; i++) FU[i * BLOCK] = 0.0;
     // ---- nodal loads (assemble.cpp:326-341, free DOFs only) ----
     for (int i = 0; i < NL; i++) {
-      const int k = PI[lay.o_nldst + i];
-      const double v = a.case_nl ? __ldg(a.case_nl + cs * NL + i) : PD[lay.o_nlval + i];
-      if (k >= 0) F[k * BLOCK] += v;
+      const int k = P.nldst[i];
+      if (k >= 0) FU[k * BLOCK] += a.case_nl ? __ldg(a.case_nl + cs * NL + i) : P.nlval[i];
     }
     // ---- stage A: element stiffness + scatter, equivalent loads ----
     for (int e = 0; e < E; e++) {
-      const int na = PI[lay.o_enode + 2 * e], nbn = PI[lay.o_enode + 2 * e + 1], type = PI[lay.o_etype + e];
-      const ElemGeom g = elem_geom(PD[lay.o_xy + 2 * na], PD[lay.o_xy + 2 * na + 1], PD[lay.o_xy + 2 * nbn],
-                                   PD[lay.o_xy + 2 * nbn + 1]);
+      const int type = P.etype[e];
+      ElemGeom g;
+      g.c = G[4 * e]; g.s = G[4 * e + 1]; g.L = G[4 * e + 2]; g.invL = G[4 * e + 3];
       double Ee, Ae, Ie;
       if (a.case_eai) {
         const double* p = a.case_eai + (cs * E + e) * 3;
         Ee = __ldg(p); Ae = __ldg(p + 1); Ie = __ldg(p + 2);
       } else {
-        Ee = PD[lay.o_eai + 3 * e]; Ae = PD[lay.o_eai + 3 * e + 1]; Ie = PD[lay.o_eai + 3 * e + 2];
+        Ee = P.eai[3 * e]; Ae = P.eai[3 * e + 1]; Ie = P.eai[3 * e + 2];
       }
       const ElemLocalK lk = elem_local_k(type, Ee, Ae, Ie, g);
       if (NF > 0) {
         double ke[ELEM_K];
         elem_global_k(lk, g, ke);
-        const int32_t* dst = PI + lay.o_edst + ELEM_K * e;
 #pragma unroll
         for (int k = 0; k < ELEM_K; k++) {
-          const int d = dst[k];
+          const int d = P.edst[ELEM_K * e + k];
           if (d >= 0) Kp[d * BLOCK] += ke[k];
         }
       }
-      for (int j = PI[lay.o_elptr + e]; j < PI[lay.o_elptr + e + 1]; j++) {
-        const int slot = PI[lay.o_elslot + j];
-        const double q = a.case_q ? __ldg(a.case_q + cs * EL + slot) : PD[lay.o_elq + slot];
+      for (int j = P.elptr[e]; j < P.elptr[e + 1]; j++) {
+        const int slot = P.elslot[j];
+        const double q = a.case_q ? __ldg(a.case_q + cs * EL + slot) : P.elq[slot];
+        LoadProj pr;
+        pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
         double gl[6], ex[6];
-        uniform_load(type, g, q, PD[lay.o_eldir + 3 * slot], PD[lay.o_eldir + 3 * slot + 1], gl, ex);
-        const int32_t* ud = PI + lay.o_udof + 6 * e;
+        uniform_load_p(type, g, q, pr, gl, ex);
 #pragma unroll
         for (int k = 0; k < 6; k++) {
-          const int d = ud[k];
-          if (d >= 0) F[d * BLOCK] += gl[k];
+          const int d = P.udof[6 * e + k];
+          if (d >= 0) FU[(d & 63) * BLOCK] += gl[k];
         }
       }
     }
     // ---- K5/K6: gather K_ff, F_f into registers; LDL^T; solve ----
-    double A[NFP + 1], b[NF + 1];
+    double A[NF + 1][NF + 1], b[NF + 1];
 #pragma unroll
-    for (int i = 0; i < NFP; i++) A[i] = Kp[i * BLOCK];
+    for (int i = 0; i < NF; i++)
 #pragma unroll
-    for (int i = 0; i < NF; i++) b[i] = F[PI[lay.o_freek + i] * BLOCK];
+      for (int j = 0; j < NF; j++)
+        if (j <= i) A[i][j] = Kp[(i * (i + 1) / 2 + j) * BLOCK];
+#pragma unroll
+    for (int i = 0; i < NF; i++) b[i] = FU[P.freek[i] * BLOCK];
     if (a.F_f) {
 #pragma unroll
       for (int i = 0; i < NF; i++) a.F_f[cs * NF + i] = b[i];
@@ -137,44 +169,50 @@ __global__ void __launch_bounds__(BLOCK) k_tiny_fused(TinyArgs a) {
     if (info != 0) atomicOr(a.fail, 1);
 #pragma unroll
     for (int i = 0; i < NF; i++) {
-      U[PI[lay.o_freek + i] * BLOCK] = b[i];
+      FU[P.freek[i] * BLOCK] = b[i];
       a.U_f[cs * NF + i] = b[i];
     }
-    // reactions accumulate in F: bounded entries currently hold the equivalent loads (solver_static.cpp:208-218)
+    // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
     for (int i = 0; i < nb; i++) {
-      const int k = PI[lay.o_bndk + i];
-      F[k * BLOCK] = -F[k * BLOCK];
+      const int k = P.bndk[i];
+      FU[k * BLOCK] = -FU[k * BLOCK];
     }
     // ---- stage B: element end forces (K10) and reactions (K_bf*U_f == sum of element end forces) ----
     for (int e = 0; e < E; e++) {
-      const int na = PI[lay.o_enode + 2 * e], nbn = PI[lay.o_enode + 2 * e + 1], type = PI[lay.o_etype + e];
-      const ElemGeom g = elem_geom(PD[lay.o_xy + 2 * na], PD[lay.o_xy + 2 * na + 1], PD[lay.o_xy + 2 * nbn],
-                                   PD[lay.o_xy + 2 * nbn + 1]);
+      const int type = P.etype[e];
+      ElemGeom g;
+      g.c = G[4 * e]; g.s = G[4 * e + 1]; g.L = G[4 * e + 2]; g.invL = G[4 * e + 3];
       double Ee, Ae, Ie;
       if (a.case_eai) {
         const double* p = a.case_eai + (cs * E + e) * 3;
         Ee = __ldg(p); Ae = __ldg(p + 1); Ie = __ldg(p + 2);
       } else {
-        Ee = PD[lay.o_eai + 3 * e]; Ae = PD[lay.o_eai + 3 * e + 1]; Ie = PD[lay.o_eai + 3 * e + 2];
+        Ee = P.eai[3 * e]; Ae = P.eai[3 * e + 1]; Ie = P.eai[3 * e + 2];
       }
       const ElemLocalK lk = elem_local_k(type, Ee, Ae, Ie, g);
-      const int32_t* ud = PI + lay.o_udof + 6 * e;
       double ug[6], es[6];
 #pragma unroll
-      for (int k = 0; k < 6; k++) ug[k] = ud[k] >= 0 ? U[ud[k] * BLOCK] : 0.0;
+      for (int k = 0; k < 6; k++) {
+        const int d = P.udof[6 * e + k];
+        ug[k] = (d >= 0 && d < 64) ? FU[d * BLOCK] : 0.0;   // bounded DOFs: U_b = 0
+      }
       elem_end_forces(lk, g, ug, es);
       const double gf[6] = {g.c * es[0] - g.s * es[1], g.s * es[0] + g.c * es[1], es[2],
                             g.c * es[3] - g.s * es[4], g.s * es[3] + g.c * es[4], es[5]};
 #pragma unroll
-      for (int k = 0; k < 6; k++)
-        if (ud[k] >= 0) F[ud[k] * BLOCK] += gf[k];
+      for (int k = 0; k < 6; k++) {
+        const int d = P.udof[6 * e + k];
+        if (d >= 64) FU[(d & 63) * BLOCK] += gf[k];
+      }
       if (a.stress) {
         double ext[6] = {0, 0, 0, 0, 0, 0};
-        for (int j = PI[lay.o_elptr + e]; j < PI[lay.o_elptr + e + 1]; j++) {
-          const int slot = PI[lay.o_elslot + j];
-          const double q = a.case_q ? __ldg(a.case_q + cs * EL + slot) : PD[lay.o_elq + slot];
+        for (int j = P.elptr[e]; j < P.elptr[e + 1]; j++) {
+          const int slot = P.elslot[j];
+          const double q = a.case_q ? __ldg(a.case_q + cs * EL + slot) : P.elq[slot];
+          LoadProj pr;
+          pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
           double gl[6], ex[6];
-          uniform_load(type, g, q, PD[lay.o_eldir + 3 * slot], PD[lay.o_eldir + 3 * slot + 1], gl, ex);
+          uniform_load_p(type, g, q, pr, gl, ex);
 #pragma unroll
           for (int k = 0; k < 6; k++) ext[k] += ex[k];
         }
@@ -188,17 +226,42 @@ __global__ void __launch_bounds__(BLOCK) k_tiny_fused(TinyArgs a) {
         o[5] = make_double2(0.0, es[5] + ext[5]);
       }
     }
-    for (int i = 0; i < nb; i++) a.F_b[cs * nb + i] = F[PI[lay.o_bndk + i] * BLOCK];
+    for (int i = 0; i < nb; i++) a.F_b[cs * nb + i] = FU[P.bndk[i] * BLOCK];
   }
 }
 
-constexpr int TINY_BLOCK = 128;
+static void fill_param(TinyParam& P, const int32_t* I, const double* D) {
+  const int N = I[0], E = I[1], n = I[2], nf = I[3], nb = I[4], NL = I[5], EL = I[6];
+  const TinyLayout lay(N, E, n, nf, nb, NL, EL);
+  P.N = N; P.E = E; P.n = n; P.nb = nb; P.NL = NL; P.EL = EL;
+  for (int i = 0; i < 2 * E; i++) P.enode[i] = int8_t(I[lay.o_enode + i]);
+  for (int i = 0; i < E; i++) P.etype[i] = int8_t(I[lay.o_etype + i]);
+  for (int i = 0; i < 6 * E; i++) P.udof[i] = int8_t(I[lay.o_udof + i]);
+  for (int i = 0; i < ELEM_K * E; i++) P.edst[i] = int8_t(I[lay.o_edst + i]);
+  for (int i = 0; i <= E; i++) P.elptr[i] = int8_t(I[lay.o_elptr + i]);
+  for (int i = 0; i < EL; i++) P.elslot[i] = int8_t(I[lay.o_elslot + i]);
+  for (int i = 0; i < NL; i++) P.nldst[i] = int8_t(I[lay.o_nldst + i]);
+  for (int i = 0; i < nf; i++) P.freek[i] = int8_t(I[lay.o_freek + i]);
+  for (int i = 0; i < nb; i++) P.bndk[i] = int8_t(I[lay.o_bndk + i]);
+  for (int i = 0; i < 2 * N; i++) P.xy[i] = D[lay.o_xy + i];
+  for (int i = 0; i < 3 * E; i++) P.eai[i] = D[lay.o_eai + i];
+  for (int i = 0; i < NL; i++) P.nlval[i] = D[lay.o_nlval + i];
+  for (int i = 0; i < EL; i++) {
+    P.elq[i] = D[lay.o_elq + i];
+    P.eldir[2 * i] = D[lay.o_eldir + 3 * i];
+    P.eldir[2 * i + 1] = D[lay.o_eldir + 3 * i + 1];
+  }
+}
 
 template <int NF>
 static cudaError_t launch_nf(const TinyArgs& a, int n, int sm_count, cudaStream_t st) {
   constexpr int NFP = NF * (NF + 1) / 2;
-  const size_t smem = size_t(a.n_ints) * 4 + size_t(a.n_dbls) * 8 + size_t(NFP + 2 * n) * TINY_BLOCK * 8;
-  auto kern = k_tiny_fused<NF, TINY_BLOCK>;
+  constexpr int MINB = NF <= 6 ? 6 : NF <= 9 ? 3 : 2;  // register budget: K_ff (NFP doubles) lives in registers
+  TinyParam P;
+  std::memset(&P, 0, sizeof(P));
+  fill_param(P, a.prog_i, a.prog_d);
+  const size_t smem = size_t(4 * P.E + 2 * P.EL) * 8 + size_t(NFP + n) * TINY_BLOCK * 8;
+  auto kern = k_tiny_fused<NF, MINB>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (e != cudaSuccess) return e;
   int per_sm = 1;
@@ -206,11 +269,11 @@ static cudaError_t launch_nf(const TinyArgs& a, int n, int sm_count, cudaStream_
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
   const int64_t need = (a.n_cases + TINY_BLOCK - 1) / TINY_BLOCK;
-  // persistent-ish grid: a whole number of waves over the SMs, grid-stride over cases
+  // persistent-ish grid: a whole number of CTAs per SM, grid-stride over cases
   int64_t grid = int64_t(sm_count) * per_sm;
   if (need < grid) grid = need;
   if (grid < 1) grid = 1;
-  kern<<<unsigned(grid), TINY_BLOCK, smem, st>>>(a);
+  kern<<<unsigned(grid), TINY_BLOCK, smem, st>>>(P, a);
   return cudaGetLastError();
 }
 

@@ -21,6 +21,7 @@ constexpr int ELEM_K = 21;
 constexpr int TINY_MAX_NF = 12;   // thread-per-system kernel: K_ff lives in registers up to this size
 constexpr int TINY_MAX_N = 48;
 constexpr int TINY_MAX_E = 32;
+constexpr int TINY_MAX_NODES = 32, TINY_MAX_NL = 48, TINY_MAX_EL = 32;
 constexpr int32_t SLOT_NONE = INT32_MIN;  // DOF absent from the problem
 
 template <class T>

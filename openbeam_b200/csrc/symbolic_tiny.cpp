@@ -16,7 +16,8 @@ int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& pr
   }
   const int N = int(hb.Ntot()), E = int(hb.Etot()), n = int(sym.n_tot()), nf = int(sym.nf_tot()), nb = int(sym.nb_tot());
   const int NL = int(hb.NLtot()), EL = int(hb.ELtot());
-  if (nf > TINY_MAX_NF || n > TINY_MAX_N || E > TINY_MAX_E || hb.has_rotz) {
+  if (nf > TINY_MAX_NF || n > TINY_MAX_N || E > TINY_MAX_E || N > TINY_MAX_NODES || NL > TINY_MAX_NL ||
+      EL > TINY_MAX_EL || hb.has_rotz) {
     err = "structure too large for the thread-per-system kernel";
     return OBGPU_EUNSUPPORTED;
   }
@@ -47,7 +48,7 @@ int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& pr
     for (int f = 0; f < 2; f++)
       for (int a = 0; a < 3; a++) {
         const int k = sym.dof_index[6 * nd[f] + d3[a]];
-        I[lay.o_udof + 6 * e + 3 * f + a] = k;
+        I[lay.o_udof + 6 * e + 3 * f + a] = (k >= 0 && sym.dof_type[k] < 0) ? (k | 64) : k;  // bit 6: bounded
         fidx[f][a] = (k >= 0 && sym.dof_type[k] >= 0) ? sym.dof_type[k] : -1;
       }
     int* dst = &I[lay.o_edst + ELEM_K * e];
