@@ -20,7 +20,10 @@
 
 namespace obgpu {
 
-constexpr int TINY_BLOCK = 128;
+#ifndef TINY_BLOCK_SIZE
+#define TINY_BLOCK_SIZE 128
+#endif
+constexpr int TINY_BLOCK = TINY_BLOCK_SIZE;
 
 // fixed-capacity copy of the program, passed by value (constant bank)
 struct TinyParam {
@@ -83,17 +86,25 @@ __device__ __forceinline__ int ldlt_solve_regs(double (&A)[NF + 1][NF + 1], doub
   return info;
 }
 
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(uint32_t(__cvta_generic_to_shared(smem_dst))), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 template <int NF, int MINB>
 __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_constant__ TinyParam P, TinyArgs a) {
   constexpr int BLOCK = TINY_BLOCK;
+  constexpr int CS = TINY_BLOCK + 1;  // column stride (+1: conflict-light transposed reads in the coalesced stores)
   constexpr int NFP = NF * (NF + 1) / 2;
   extern __shared__ __align__(16) double smem[];
-  // shared: G[E][4] = c,s,L,1/L | LP[EL][2] | per-lane columns Kp[NFP][BLOCK], FU[n][BLOCK]
+  // shared: G[E][4] = c,s,L,1/L | LP[EL][2] | per-lane columns Kp[NFP][BLOCK], FU[n][BLOCK], SN[NL][BLOCK], SQ[2][EL][BLOCK]
   const int E = P.E, n = P.n, nb = P.nb, NL = P.NL, EL = P.EL;
   double* G = smem;
   double* LP = G + 4 * E;
   double* Kp = LP + 2 * EL + threadIdx.x;
-  double* FU = Kp + size_t(NFP) * BLOCK;
+  constexpr int KC = NFP > 12 ? NFP : 12;  // K columns double as the 12-wide staging record of the stress stores
+  double* FU = Kp + size_t(KC) * CS;
   if (threadIdx.x < E) {
     const int e = threadIdx.x, na = P.enode[2 * e], nbn = P.enode[2 * e + 1];
     const ElemGeom g = elem_geom(P.xy[2 * na], P.xy[2 * na + 1], P.xy[2 * nbn], P.xy[2 * nbn + 1]);
@@ -106,15 +117,40 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
   }
   __syncthreads();
 
-  for (int64_t cs = int64_t(blockIdx.x) * BLOCK + threadIdx.x; cs < a.n_cases; cs += int64_t(gridDim.x) * BLOCK) {
+  // Per-case inputs arrive by cp.async into the lane's staging columns one block of cases ahead of their use:
+  // SN[NL] (nodal-load values, consumed at the top of a case) and SQ[2][EL] (element-load q, double-buffered
+  // because it is still read at the end of the case), so global-load latency hides behind a whole case of compute.
+  double* SN = FU + size_t(n) * CS;
+  double* SQ = SN + (a.case_nl ? size_t(NL) * CS : 0);
+  const int64_t stride = int64_t(gridDim.x) * BLOCK;
+  const int64_t last = a.n_cases - 1;
+  auto prefetch = [&](int64_t b, int buf) {
+    const int64_t c = min(b + threadIdx.x, last);
+    if (a.case_nl)
+      for (int i = 0; i < NL; i++) cp_async8(SN + i * CS, a.case_nl + c * NL + i);
+    if (a.case_q)
+      for (int i = 0; i < EL; i++) cp_async8(SQ + (buf * EL + i) * CS, a.case_q + c * EL + i);
+    cp_async_commit();
+  };
+  int buf = 0;
+  int64_t base = int64_t(blockIdx.x) * BLOCK;
+  if (base < a.n_cases) prefetch(base, 0);
+  // CTA-uniform loop: lanes past the end recompute the last case and skip their stores, so the whole body is
+  // convergent (uniform program reads, uniform branches).
+  for (; base < a.n_cases; base += stride, buf ^= 1) {
+    const bool valid = base + threadIdx.x <= last;
+    const int64_t cs = min(base + threadIdx.x, last);
+    cp_async_wait_all();
 #pragma unroll
-    for (int i = 0; i < NFP; i++) Kp[i * BLOCK] = 0.0;
-    for (int i = 0; i < n; i++) FU[i * BLOCK] = 0.0;
+    for (int i = 0; i < NFP; i++) Kp[i * CS] = 0.0;
+    for (int i = 0; i < n; i++) FU[i * CS] = 0.0;
     // ---- nodal loads (assemble.cpp:326-341, free DOFs only) ----
     for (int i = 0; i < NL; i++) {
       const int k = P.nldst[i];
-      if (k >= 0) FU[k * BLOCK] += a.case_nl ? __ldg(a.case_nl + cs * NL + i) : P.nlval[i];
+      if (k >= 0) FU[k * CS] += a.case_nl ? SN[i * CS] : P.nlval[i];
     }
+    if (base + stride < a.n_cases) prefetch(base + stride, buf ^ 1);
+    const double* Q = SQ + size_t(buf) * EL * CS;
     // ---- stage A: element stiffness + scatter, equivalent loads ----
     for (int e = 0; e < E; e++) {
       const int type = P.etype[e];
@@ -134,12 +170,12 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
 #pragma unroll
         for (int k = 0; k < ELEM_K; k++) {
           const int d = P.edst[ELEM_K * e + k];
-          if (d >= 0) Kp[d * BLOCK] += ke[k];
+          if (d >= 0) Kp[d * CS] += ke[k];
         }
       }
       for (int j = P.elptr[e]; j < P.elptr[e + 1]; j++) {
         const int slot = P.elslot[j];
-        const double q = a.case_q ? __ldg(a.case_q + cs * EL + slot) : P.elq[slot];
+        const double q = a.case_q ? Q[slot * CS] : P.elq[slot];
         LoadProj pr;
         pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
         double gl[6], ex[6];
@@ -147,7 +183,7 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
 #pragma unroll
         for (int k = 0; k < 6; k++) {
           const int d = P.udof[6 * e + k];
-          if (d >= 0) FU[(d & 63) * BLOCK] += gl[k];
+          if (d >= 0) FU[(d & 63) * CS] += gl[k];
         }
       }
     }
@@ -157,25 +193,43 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
     for (int i = 0; i < NF; i++)
 #pragma unroll
       for (int j = 0; j < NF; j++)
-        if (j <= i) A[i][j] = Kp[(i * (i + 1) / 2 + j) * BLOCK];
+        if (j <= i) A[i][j] = Kp[(i * (i + 1) / 2 + j) * CS];
 #pragma unroll
-    for (int i = 0; i < NF; i++) b[i] = FU[P.freek[i] * BLOCK];
+    for (int i = 0; i < NF; i++) b[i] = FU[P.freek[i] * CS];
+    // Results leave through the warp's (now dead) K columns: each lane parks its values in its column, then the
+    // warp writes the 32 cases' contiguous output range with fully coalesced stores (a per-lane store of a
+    // 48..288-byte record would touch 32 different 128-byte lines per instruction and bind the kernel on L1 tags).
+    const int lane = threadIdx.x & 31, wl0 = threadIdx.x & ~31;
+    const int64_t c0 = base + wl0;                                   // first case of this warp
+    const int cnt = int(min(int64_t(32), a.n_cases - c0));           // valid cases in this warp (<= 0: none)
+    double* KW = Kp - threadIdx.x + wl0;                             // warp view of the K columns: KW[col*CS + t]
+    double* FW = FU - threadIdx.x + wl0;
     if (a.F_f) {
+      __syncwarp();
 #pragma unroll
-      for (int i = 0; i < NF; i++) a.F_f[cs * NF + i] = b[i];
+      for (int i = 0; i < NF; i++) Kp[i * CS] = b[i];
+      __syncwarp();
+      for (int j = lane; j < cnt * NF; j += 32) {
+        const int t = j / NF, i = j - t * NF;
+        a.F_f[c0 * NF + j] = KW[i * CS + t];
+      }
     }
     const int info = ldlt_solve_regs<NF>(A, b);
-    a.info[cs] = info;
-    if (info != 0) atomicOr(a.fail, 1);
+    if (valid) {
+      a.info[cs] = info;
+      if (info != 0) atomicOr(a.fail, 1);
+    }
 #pragma unroll
-    for (int i = 0; i < NF; i++) {
-      FU[P.freek[i] * BLOCK] = b[i];
-      a.U_f[cs * NF + i] = b[i];
+    for (int i = 0; i < NF; i++) FU[P.freek[i] * CS] = b[i];
+    __syncwarp();
+    for (int j = lane; j < cnt * NF; j += 32) {
+      const int t = j / NF, i = j - t * NF;
+      a.U_f[c0 * NF + j] = FW[P.freek[i] * CS + t];
     }
     // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
     for (int i = 0; i < nb; i++) {
       const int k = P.bndk[i];
-      FU[k * BLOCK] = -FU[k * BLOCK];
+      FU[k * CS] = -FU[k * CS];
     }
     // ---- stage B: element end forces (K10) and reactions (K_bf*U_f == sum of element end forces) ----
     for (int e = 0; e < E; e++) {
@@ -194,7 +248,7 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
 #pragma unroll
       for (int k = 0; k < 6; k++) {
         const int d = P.udof[6 * e + k];
-        ug[k] = (d >= 0 && d < 64) ? FU[d * BLOCK] : 0.0;   // bounded DOFs: U_b = 0
+        ug[k] = (d >= 0 && d < 64) ? FU[d * CS] : 0.0;   // bounded DOFs: U_b = 0
       }
       elem_end_forces(lk, g, ug, es);
       const double gf[6] = {g.c * es[0] - g.s * es[1], g.s * es[0] + g.c * es[1], es[2],
@@ -202,13 +256,13 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
 #pragma unroll
       for (int k = 0; k < 6; k++) {
         const int d = P.udof[6 * e + k];
-        if (d >= 64) FU[(d & 63) * BLOCK] += gf[k];
+        if (d >= 64) FU[(d & 63) * CS] += gf[k];
       }
       if (a.stress) {
         double ext[6] = {0, 0, 0, 0, 0, 0};
         for (int j = P.elptr[e]; j < P.elptr[e + 1]; j++) {
           const int slot = P.elslot[j];
-          const double q = a.case_q ? __ldg(a.case_q + cs * EL + slot) : P.elq[slot];
+          const double q = a.case_q ? Q[slot * CS] : P.elq[slot];
           LoadProj pr;
           pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
           double gl[6], ex[6];
@@ -217,16 +271,23 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
           for (int k = 0; k < 6; k++) ext[k] += ex[k];
         }
         // StressInfo::element_stress[e][face] = {N,Vy,Vz,Mx,My,Mz}; face 0 negated (postproc_stress.cpp:152-165)
-        double2* o = reinterpret_cast<double2*>(a.stress + (cs * E + e) * 12);
-        o[0] = make_double2(-es[0] + ext[0], -es[1] + ext[1]);
-        o[1] = make_double2(0.0, 0.0);
-        o[2] = make_double2(0.0, -es[2] + ext[2]);
-        o[3] = make_double2(es[3] + ext[3], es[4] + ext[4]);
-        o[4] = make_double2(0.0, 0.0);
-        o[5] = make_double2(0.0, es[5] + ext[5]);
+        __syncwarp();  // previous element's record has been read out
+        Kp[0 * CS] = -es[0] + ext[0]; Kp[1 * CS] = -es[1] + ext[1]; Kp[5 * CS] = -es[2] + ext[2];
+        Kp[6 * CS] = es[3] + ext[3];  Kp[7 * CS] = es[4] + ext[4];  Kp[11 * CS] = es[5] + ext[5];
+        __syncwarp();
+        for (int j = lane; j < cnt * 12; j += 32) {
+          const int t = j / 12, i = j - t * 12;
+          const bool zero = (0x71C >> i) & 1;  // Vz, Mx, My of both faces (components 2,3,4,8,9,10) are 0 in 2D
+          a.stress[((c0 + t) * E + e) * 12 + i] = zero ? 0.0 : KW[i * CS + t];
+        }
       }
     }
-    for (int i = 0; i < nb; i++) a.F_b[cs * nb + i] = FU[P.bndk[i] * BLOCK];
+    __syncwarp();
+    for (int j = lane; j < cnt * nb; j += 32) {
+      const int t = j / nb, i = j - t * nb;
+      a.F_b[c0 * nb + j] = FW[P.bndk[i] * CS + t];
+    }
+    __syncwarp();  // columns are zeroed again at the top of the next block of cases
   }
 }
 
@@ -256,11 +317,15 @@ static void fill_param(TinyParam& P, const int32_t* I, const double* D) {
 template <int NF>
 static cudaError_t launch_nf(const TinyArgs& a, int n, int sm_count, cudaStream_t st) {
   constexpr int NFP = NF * (NF + 1) / 2;
-  constexpr int MINB = NF <= 6 ? 6 : NF <= 9 ? 3 : 2;  // register budget: K_ff (NFP doubles) lives in registers
+#ifndef TINY_MINB_SMALL
+#define TINY_MINB_SMALL 6
+#endif
+  constexpr int MINB = NF <= 6 ? TINY_MINB_SMALL : NF <= 9 ? 3 : 2;  // register budget: K_ff (NFP doubles) lives in registers
   TinyParam P;
   std::memset(&P, 0, sizeof(P));
   fill_param(P, a.prog_i, a.prog_d);
-  const size_t smem = size_t(4 * P.E + 2 * P.EL) * 8 + size_t(NFP + n) * TINY_BLOCK * 8;
+  const size_t smem = size_t(4 * P.E + 2 * P.EL) * 8 +
+                      size_t((NFP > 12 ? NFP : 12) + n + (a.case_nl ? P.NL : 0) + (a.case_q ? 2 * P.EL : 0)) * (TINY_BLOCK + 1) * 8;
   auto kern = k_tiny_fused<NF, MINB>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (e != cudaSuccess) return e;

@@ -20,7 +20,7 @@ import numpy as np
 from .structure import Structure
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libobgpu.so")
+LIB_PATH = os.environ.get("OBGPU_LIB") or os.path.join(_HERE, "libobgpu.so")  # OBGPU_LIB: kernel-variant experiments
 
 OK, EINVAL, ECUDA, ESINGULAR, ENOTCONVERGED, EUNSUPPORTED, ESEQUENCE = range(7)
 BATCHED_LDLT, PCG_JACOBI, PCG_BJ3, PCG_IC0 = range(4)
