@@ -92,6 +92,25 @@ __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) 
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// Warp-cooperative store of a [32 cases][C] record block whose values sit in staging columns W[i*CS + t]
+// (component i, case-in-warp t): 32 consecutive doubles per instruction.  Full warps take the unrolled path
+// (compile-time trip count, division by the constant C becomes a multiply-high); the ragged last warp loops.
+template <int C, int CS>
+__device__ __forceinline__ void warp_store(double* __restrict__ g, const double* W, int lane, int cnt) {
+  if (cnt == 32) {
+#pragma unroll
+    for (int r = 0; r < C; r++) {
+      const int j = r * 32 + lane, t = j / C, i = j - t * C;
+      g[j] = W[i * CS + t];
+    }
+  } else {
+    for (int j = lane; j < cnt * C; j += 32) {
+      const int t = j / C, i = j - t * C;
+      g[j] = W[i * CS + t];
+    }
+  }
+}
+
 template <int NF, int MINB>
 __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_constant__ TinyParam P, TinyArgs a) {
   constexpr int BLOCK = TINY_BLOCK;
@@ -203,16 +222,13 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
     const int64_t c0 = base + wl0;                                   // first case of this warp
     const int cnt = int(min(int64_t(32), a.n_cases - c0));           // valid cases in this warp (<= 0: none)
     double* KW = Kp - threadIdx.x + wl0;                             // warp view of the K columns: KW[col*CS + t]
-    double* FW = FU - threadIdx.x + wl0;
     if (a.F_f) {
       __syncwarp();
 #pragma unroll
       for (int i = 0; i < NF; i++) Kp[i * CS] = b[i];
       __syncwarp();
-      for (int j = lane; j < cnt * NF; j += 32) {
-        const int t = j / NF, i = j - t * NF;
-        a.F_f[c0 * NF + j] = KW[i * CS + t];
-      }
+      if (NF > 0) warp_store<NF ? NF : 1, CS>(a.F_f + c0 * NF, KW, lane, cnt);
+      __syncwarp();
     }
     const int info = ldlt_solve_regs<NF>(A, b);
     if (valid) {
@@ -220,12 +236,12 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
       if (info != 0) atomicOr(a.fail, 1);
     }
 #pragma unroll
-    for (int i = 0; i < NF; i++) FU[P.freek[i] * CS] = b[i];
-    __syncwarp();
-    for (int j = lane; j < cnt * NF; j += 32) {
-      const int t = j / NF, i = j - t * NF;
-      a.U_f[c0 * NF + j] = FW[P.freek[i] * CS + t];
+    for (int i = 0; i < NF; i++) {
+      FU[P.freek[i] * CS] = b[i];
+      Kp[i * CS] = b[i];
     }
+    __syncwarp();
+    if (NF > 0) warp_store<NF ? NF : 1, CS>(a.U_f + c0 * NF, KW, lane, cnt);
     // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
     for (int i = 0; i < nb; i++) {
       const int k = P.bndk[i];
@@ -275,19 +291,34 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
         Kp[0 * CS] = -es[0] + ext[0]; Kp[1 * CS] = -es[1] + ext[1]; Kp[5 * CS] = -es[2] + ext[2];
         Kp[6 * CS] = es[3] + ext[3];  Kp[7 * CS] = es[4] + ext[4];  Kp[11 * CS] = es[5] + ext[5];
         __syncwarp();
-        for (int j = lane; j < cnt * 12; j += 32) {
-          const int t = j / 12, i = j - t * 12;
-          const bool zero = (0x71C >> i) & 1;  // Vz, Mx, My of both faces (components 2,3,4,8,9,10) are 0 in 2D
-          a.stress[((c0 + t) * E + e) * 12 + i] = zero ? 0.0 : KW[i * CS + t];
+        if (cnt == 32) {
+#pragma unroll
+          for (int r = 0; r < 12; r++) {
+            const int j = r * 32 + lane, t = j / 12, i = j - t * 12;
+            const bool zero = (0x71C >> i) & 1;  // Vz, Mx, My of both faces (components 2,3,4,8,9,10) are 0 in 2D
+            a.stress[((c0 + t) * E + e) * 12 + i] = zero ? 0.0 : KW[i * CS + t];
+          }
+        } else {
+          for (int j = lane; j < cnt * 12; j += 32) {
+            const int t = j / 12, i = j - t * 12;
+            const bool zero = (0x71C >> i) & 1;
+            a.stress[((c0 + t) * E + e) * 12 + i] = zero ? 0.0 : KW[i * CS + t];
+          }
         }
       }
     }
     __syncwarp();
-    for (int j = lane; j < cnt * nb; j += 32) {
-      const int t = j / nb, i = j - t * nb;
-      a.F_b[c0 * nb + j] = FW[P.bndk[i] * CS + t];
+    for (int i0 = 0; i0 < nb; i0 += KC) {  // reactions leave through the staging columns too, KC components at a time
+      const int w = min(KC, nb - i0);
+      for (int i = 0; i < w; i++) Kp[i * CS] = FU[P.bndk[i0 + i] * CS];
+      __syncwarp();
+      const float rw = 1.0f / float(w);
+      for (int j = lane; j < cnt * w; j += 32) {
+        const int t = int((float(j) + 0.5f) * rw), i = j - t * w;  // exact for j < 2^20
+        a.F_b[(c0 + t) * nb + i0 + i] = KW[i * CS + t];
+      }
+      __syncwarp();  // columns are zeroed again at the top of the next block of cases
     }
-    __syncwarp();  // columns are zeroed again at the top of the next block of cases
   }
 }
 
