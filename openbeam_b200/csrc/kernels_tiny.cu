@@ -12,6 +12,7 @@
 // i.e. the constant bank: every lane follows the same program, so index reads are uniform constant loads and
 // the skip-tests are uniform branches; shared memory holds only the per-lane columns [idx][lane] (conflict-free).
 // Sums follow the reference's element order (assemble.cpp:123-223); no atomics on the data path.
+#include <cstdlib>
 #include <cstring>
 
 #include "beam_math.cuh"
@@ -37,6 +38,7 @@ struct TinyParam {
   int8_t nldst[TINY_MAX_NL];
   int8_t freek[TINY_MAX_NF];
   int8_t bndk[TINY_MAX_N];
+  int8_t eblk[2 * TINY_MAX_E];       // node-blocked path: free node block of each element end, -1 = no free DOF
   double xy[2 * TINY_MAX_NODES];
   double eai[3 * TINY_MAX_E];
   double nlval[TINY_MAX_NL];
@@ -86,6 +88,54 @@ __device__ __forceinline__ int ldlt_solve_regs(double (&A)[NF + 1][NF + 1], doub
   return info;
 }
 
+// ---- node-blocked fast path -------------------------------------------------------------------------------------
+// When every element end is either entirely free with its three DOFs numbered consecutively from a multiple of 3
+// (free "node block" m: free indices 3m..3m+2) or has no free DOF at all (clamped supports: every frame of the
+// BASELINE configs), K_ff is a grid of 3x3 node blocks and the scatter of an element's K11/K22/K12 is a warp-uniform
+// choice of block position.  K_ff then lives in REGISTERS from its first touch to the end of the factorisation and
+// the displacement gather of stress recovery is a register select: no shared-memory round trips (the LSU data pipe
+// was the bound of the column-in-shared-memory version, profiles/README.md r01c).  Same adds in the same order.
+template <int NF>
+__device__ __forceinline__ void blk_add_diag(double (&A)[NF + 1][NF + 1], int m, const double* k6) {
+#pragma unroll
+  for (int I = 0; I < NF / 3; I++)
+    if (m == I) {  // k6 = upper triangle (0,0),(0,1),(0,2),(1,1),(1,2),(2,2) of a symmetric block
+      A[3 * I][3 * I] += k6[0];
+      A[3 * I + 1][3 * I] += k6[1];
+      A[3 * I + 1][3 * I + 1] += k6[3];
+      A[3 * I + 2][3 * I] += k6[2];
+      A[3 * I + 2][3 * I + 1] += k6[4];
+      A[3 * I + 2][3 * I + 2] += k6[5];
+    }
+}
+// k9 = K12 row-major (rows: end 0, columns: end 1); ma/mb = free node blocks of end 0 / end 1 (both >= 0, distinct)
+template <int NF>
+__device__ __forceinline__ void blk_add_off(double (&A)[NF + 1][NF + 1], int ma, int mb, const double* k9) {
+#pragma unroll
+  for (int I = 1; I < NF / 3; I++)
+#pragma unroll
+    for (int J = 0; J < I; J++) {
+      if (ma == I && mb == J) {
+#pragma unroll
+        for (int r = 0; r < 3; r++)
+#pragma unroll
+          for (int c = 0; c < 3; c++) A[3 * I + r][3 * J + c] += k9[3 * r + c];
+      } else if (mb == I && ma == J) {
+#pragma unroll
+        for (int r = 0; r < 3; r++)
+#pragma unroll
+          for (int c = 0; c < 3; c++) A[3 * I + r][3 * J + c] += k9[3 * c + r];
+      }
+    }
+}
+template <int NF>
+__device__ __forceinline__ void blk_get3(const double (&b)[NF + 1], int m, double* u) {
+  u[0] = u[1] = u[2] = 0.0;  // no free DOF at this end: U_b = 0
+#pragma unroll
+  for (int I = 0; I < NF / 3; I++)
+    if (m == I) { u[0] = b[3 * I]; u[1] = b[3 * I + 1]; u[2] = b[3 * I + 2]; }
+}
+
 __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(uint32_t(__cvta_generic_to_shared(smem_dst))), "l"(gsrc));
 }
@@ -111,7 +161,7 @@ __device__ __forceinline__ void warp_store(double* __restrict__ g, const double*
   }
 }
 
-template <int NF, int MINB>
+template <int NF, int MINB, bool BLK>
 __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_constant__ TinyParam P, TinyArgs a) {
   constexpr int BLOCK = TINY_BLOCK;
   constexpr int CS = TINY_BLOCK + 1;  // column stride (+1: conflict-light transposed reads in the coalesced stores)
@@ -122,7 +172,8 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
   double* G = smem;
   double* LP = G + 4 * E;
   double* Kp = LP + 2 * EL + threadIdx.x;
-  constexpr int KC = NFP > 12 ? NFP : 12;  // K columns double as the 12-wide staging record of the stress stores
+  // K columns (generic path) double as the 12-wide staging record of the stress stores
+  constexpr int KC = (!BLK && NFP > 12) ? NFP : 12;
   double* FU = Kp + size_t(KC) * CS;
   if (threadIdx.x < E) {
     const int e = threadIdx.x, na = P.enode[2 * e], nbn = P.enode[2 * e + 1];
@@ -160,8 +211,17 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
     const bool valid = base + threadIdx.x <= last;
     const int64_t cs = min(base + threadIdx.x, last);
     cp_async_wait_all();
+    double A[NF + 1][NF + 1], b[NF + 1];
+    if (BLK) {
 #pragma unroll
-    for (int i = 0; i < NFP; i++) Kp[i * CS] = 0.0;
+      for (int i = 0; i < NF; i++)
+#pragma unroll
+        for (int j = 0; j < NF; j++)
+          if (j <= i) A[i][j] = 0.0;
+    } else {
+#pragma unroll
+      for (int i = 0; i < NFP; i++) Kp[i * CS] = 0.0;
+    }
     for (int i = 0; i < n; i++) FU[i * CS] = 0.0;
     // ---- nodal loads (assemble.cpp:326-341, free DOFs only) ----
     for (int i = 0; i < NL; i++) {
@@ -186,10 +246,17 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
       if (NF > 0) {
         double ke[ELEM_K];
         elem_global_k(lk, g, ke);
+        if (BLK) {
+          const int ma = P.eblk[2 * e], mb = P.eblk[2 * e + 1];
+          blk_add_diag<NF>(A, ma, ke);
+          blk_add_diag<NF>(A, mb, ke + 6);
+          blk_add_off<NF>(A, ma, mb, ke + 12);
+        } else {
 #pragma unroll
-        for (int k = 0; k < ELEM_K; k++) {
-          const int d = P.edst[ELEM_K * e + k];
-          if (d >= 0) Kp[d * CS] += ke[k];
+          for (int k = 0; k < ELEM_K; k++) {
+            const int d = P.edst[ELEM_K * e + k];
+            if (d >= 0) Kp[d * CS] += ke[k];
+          }
         }
       }
       for (int j = P.elptr[e]; j < P.elptr[e + 1]; j++) {
@@ -207,12 +274,13 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
       }
     }
     // ---- K5/K6: gather K_ff, F_f into registers; LDL^T; solve ----
-    double A[NF + 1][NF + 1], b[NF + 1];
+    if (!BLK) {
 #pragma unroll
-    for (int i = 0; i < NF; i++)
+      for (int i = 0; i < NF; i++)
 #pragma unroll
-      for (int j = 0; j < NF; j++)
-        if (j <= i) A[i][j] = Kp[(i * (i + 1) / 2 + j) * CS];
+        for (int j = 0; j < NF; j++)
+          if (j <= i) A[i][j] = Kp[(i * (i + 1) / 2 + j) * CS];
+    }
 #pragma unroll
     for (int i = 0; i < NF; i++) b[i] = FU[P.freek[i] * CS];
     // Results leave through the warp's (now dead) K columns: each lane parks its values in its column, then the
@@ -237,7 +305,7 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
     }
 #pragma unroll
     for (int i = 0; i < NF; i++) {
-      FU[P.freek[i] * CS] = b[i];
+      if (!BLK) FU[P.freek[i] * CS] = b[i];
       Kp[i * CS] = b[i];
     }
     __syncwarp();
@@ -261,10 +329,15 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
       }
       const ElemLocalK lk = elem_local_k(type, Ee, Ae, Ie, g);
       double ug[6], es[6];
+      if (BLK) {
+        blk_get3<NF>(b, P.eblk[2 * e], ug);
+        blk_get3<NF>(b, P.eblk[2 * e + 1], ug + 3);
+      } else {
 #pragma unroll
-      for (int k = 0; k < 6; k++) {
-        const int d = P.udof[6 * e + k];
-        ug[k] = (d >= 0 && d < 64) ? FU[d * CS] : 0.0;   // bounded DOFs: U_b = 0
+        for (int k = 0; k < 6; k++) {
+          const int d = P.udof[6 * e + k];
+          ug[k] = (d >= 0 && d < 64) ? FU[d * CS] : 0.0;   // bounded DOFs: U_b = 0
+        }
       }
       elem_end_forces(lk, g, ug, es);
       const double gf[6] = {g.c * es[0] - g.s * es[1], g.s * es[0] + g.c * es[1], es[2],
@@ -322,7 +395,7 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
   }
 }
 
-static void fill_param(TinyParam& P, const int32_t* I, const double* D) {
+static bool fill_param(TinyParam& P, const int32_t* I, const double* D) {
   const int N = I[0], E = I[1], n = I[2], nf = I[3], nb = I[4], NL = I[5], EL = I[6];
   const TinyLayout lay(N, E, n, nf, nb, NL, EL);
   P.N = N; P.E = E; P.n = n; P.nb = nb; P.NL = NL; P.EL = EL;
@@ -343,21 +416,42 @@ static void fill_param(TinyParam& P, const int32_t* I, const double* D) {
     P.eldir[2 * i] = D[lay.o_eldir + 3 * i];
     P.eldir[2 * i + 1] = D[lay.o_eldir + 3 * i + 1];
   }
+  // node-blocked? every element end: three free DOFs at free indices 3m,3m+1,3m+2, or no free DOF at all
+  int finv[64];
+  for (int i = 0; i < 64; i++) finv[i] = -1;
+  for (int i = 0; i < nf; i++) finv[P.freek[i]] = i;
+  bool blocked = nf % 3 == 0 && nf > 0;
+  for (int e = 0; e < E && blocked; e++)
+    for (int end = 0; end < 2; end++) {
+      int f[3];
+      for (int k = 0; k < 3; k++) {
+        const int d = P.udof[6 * e + 3 * end + k];
+        f[k] = (d >= 0 && d < 64) ? finv[d] : -1;
+      }
+      if (f[0] < 0 && f[1] < 0 && f[2] < 0) P.eblk[2 * e + end] = -1;
+      else if (f[0] >= 0 && f[0] % 3 == 0 && f[1] == f[0] + 1 && f[2] == f[0] + 2) P.eblk[2 * e + end] = int8_t(f[0] / 3);
+      else blocked = false;
+    }
+  for (int e = 0; e < E && blocked; e++)  // an element between two ends of the same node block would alias K11/K22/K12
+    if (P.eblk[2 * e] >= 0 && P.eblk[2 * e] == P.eblk[2 * e + 1]) blocked = false;
+  return blocked;
 }
 
-template <int NF>
-static cudaError_t launch_nf(const TinyArgs& a, int n, int sm_count, cudaStream_t st) {
+template <int NF, bool BLK>
+static cudaError_t launch_nf(const TinyParam& P, const TinyArgs& a, int n, int sm_count, cudaStream_t st) {
   constexpr int NFP = NF * (NF + 1) / 2;
 #ifndef TINY_MINB_SMALL
 #define TINY_MINB_SMALL 6
 #endif
-  constexpr int MINB = NF <= 6 ? TINY_MINB_SMALL : NF <= 9 ? 3 : 2;  // register budget: K_ff (NFP doubles) lives in registers
-  TinyParam P;
-  std::memset(&P, 0, sizeof(P));
-  fill_param(P, a.prog_i, a.prog_d);
+#ifndef TINY_MINB_BLK
+#define TINY_MINB_BLK 4
+#endif
+  // the node-blocked path keeps K_ff, F_f and the element blocks live together: 120 registers without spills (4 CTAs/SM
+  // measured fastest: 140 us vs 150 us at 5 and 163 us at 6 CTAs/SM with spills)
+  constexpr int MINB = NF <= 6 ? (BLK ? TINY_MINB_BLK : TINY_MINB_SMALL) : NF <= 9 ? 3 : 2;  // register budget: K_ff (NFP doubles) lives in registers
   const size_t smem = size_t(4 * P.E + 2 * P.EL) * 8 +
-                      size_t((NFP > 12 ? NFP : 12) + n + (a.case_nl ? P.NL : 0) + (a.case_q ? 2 * P.EL : 0)) * (TINY_BLOCK + 1) * 8;
-  auto kern = k_tiny_fused<NF, MINB>;
+                      size_t(((!BLK && NFP > 12) ? NFP : 12) + n + (a.case_nl ? P.NL : 0) + (a.case_q ? 2 * P.EL : 0)) * (TINY_BLOCK + 1) * 8;
+  auto kern = k_tiny_fused<NF, MINB, BLK>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (e != cudaSuccess) return e;
   int per_sm = 1;
@@ -374,8 +468,16 @@ static cudaError_t launch_nf(const TinyArgs& a, int n, int sm_count, cudaStream_
 }
 
 cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st) {
+  TinyParam P;
+  std::memset(&P, 0, sizeof(P));
+  const bool blocked = fill_param(P, a.prog_i, a.prog_d) && !getenv("OBGPU_TINY_GENERIC");
+  if (blocked) switch (nf) {
+#define OB_CASE(K) case K: return launch_nf<K, true>(P, a, n, sm_count, st);
+    OB_CASE(3) OB_CASE(6) OB_CASE(9) OB_CASE(12)
+#undef OB_CASE
+  }
   switch (nf) {
-#define OB_CASE(K) case K: return launch_nf<K>(a, n, sm_count, st);
+#define OB_CASE(K) case K: return launch_nf<K, false>(P, a, n, sm_count, st);
     OB_CASE(0) OB_CASE(1) OB_CASE(2) OB_CASE(3) OB_CASE(4) OB_CASE(5) OB_CASE(6)
     OB_CASE(7) OB_CASE(8) OB_CASE(9) OB_CASE(10) OB_CASE(11) OB_CASE(12)
 #undef OB_CASE
