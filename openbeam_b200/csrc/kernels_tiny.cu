@@ -48,27 +48,35 @@ struct TinyParam {
 
 template <int NF>
 __device__ __forceinline__ int ldlt_solve_regs(double (&A)[NF + 1][NF + 1], double (&b)[NF + 1]) {
-  // A: lower triangle A[i][j], j <= i.  In place: L (unit lower) below the diagonal, D on it.
+  // A: lower triangle A[i][j], j <= i.  In place: L (unit lower) below the diagonal, 1/D on it.
+  // Rows below the current column stay unnormalised (V = L D) until their own column is reached, so the only
+  // divisions are the NF reciprocals of the pivots (an FP64 division is ~15 instructions).
   int info = 0;
 #pragma unroll
   for (int j = 0; j < NF; j++) {
+    double w[NF + 1];
     double dj = A[j][j];
 #pragma unroll
     for (int k = 0; k < NF; k++)
-      if (k < j) dj -= A[j][k] * A[j][k] * A[k][k];
+      if (k < j) {
+        w[k] = A[j][k] * A[k][k];  // L(j,k) = V(j,k) / D(k)
+        dj -= A[j][k] * w[k];
+      }
     if (!(dj > 0.0) && info == 0) info = j + 1;  // Eigen LLT fails on x <= 0 (solver_static.cpp:97-105)
-    A[j][j] = dj;
-    const double inv = 1.0 / dj;
+    A[j][j] = 1.0 / dj;
 #pragma unroll
     for (int i = 0; i < NF; i++) {
       if (i > j) {
         double v = A[i][j];
 #pragma unroll
         for (int k = 0; k < NF; k++)
-          if (k < j) v -= A[i][k] * (A[j][k] * A[k][k]);
-        A[i][j] = v * inv;
+          if (k < j) v -= A[i][k] * w[k];
+        A[i][j] = v;
       }
     }
+#pragma unroll
+    for (int k = 0; k < NF; k++)
+      if (k < j) A[j][k] = w[k];
   }
 #pragma unroll
   for (int i = 0; i < NF; i++) {  // L y = b
@@ -77,7 +85,7 @@ __device__ __forceinline__ int ldlt_solve_regs(double (&A)[NF + 1][NF + 1], doub
       if (k < i) b[i] -= A[i][k] * b[k];
   }
 #pragma unroll
-  for (int i = 0; i < NF; i++) b[i] /= A[i][i];
+  for (int i = 0; i < NF; i++) b[i] *= A[i][i];
 #pragma unroll
   for (int ii = 0; ii < NF; ii++) {  // L^T x = z
     const int i = NF - 1 - ii;
@@ -143,23 +151,36 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // Warp-cooperative store of a [32 cases][C] record block whose values sit in staging columns W[i*CS + t]
-// (component i, case-in-warp t): 32 consecutive doubles per instruction.  Full warps take the unrolled path
-// (compile-time trip count, division by the constant C becomes a multiply-high); the ragged last warp loops.
+// (component i, case-in-warp t): 32 consecutive doubles per instruction.  Element j = r*32 + lane of the block is
+// component i = j % C of case t = j / C; both repeat with period PER = C/gcd(C,32) in r (t advancing by
+// TSTEP = 32/gcd(C,32)), so the PER lane-dependent staging offsets are computed ONCE per thread, outside the case
+// loop, and every other round is an immediate offset away.  (The divisions cost 26 instructions per store in v4:
+// 29 % of all instructions issued, profiles/README.md r01d.)
+__host__ __device__ constexpr int gcd32(int c) { return (c % 32 == 0) ? 32 : (c % 16 == 0) ? 16 : (c % 8 == 0) ? 8 : (c % 4 == 0) ? 4 : (c % 2 == 0) ? 2 : 1; }
 template <int C, int CS>
-__device__ __forceinline__ void warp_store(double* __restrict__ g, const double* W, int lane, int cnt) {
-  if (cnt == 32) {
+struct StoreMap {
+  static constexpr int G = gcd32(C), PER = C / G, TSTEP = 32 / G;
+  int so[PER];
+  __device__ __forceinline__ void init(int lane) {
 #pragma unroll
-    for (int r = 0; r < C; r++) {
-      const int j = r * 32 + lane, t = j / C, i = j - t * C;
-      g[j] = W[i * CS + t];
-    }
-  } else {
-    for (int j = lane; j < cnt * C; j += 32) {
-      const int t = j / C, i = j - t * C;
-      g[j] = W[i * CS + t];
+    for (int r0 = 0; r0 < PER; r0++) {
+      const int j = r0 * 32 + lane, t = j / C, i = j - t * C;
+      so[r0] = i * CS + t;
     }
   }
-}
+  // contiguous destination g[0 .. cnt*C)
+  __device__ __forceinline__ void store(double* __restrict__ g, const double* W, int lane, int cnt) const {
+    if (cnt == 32) {
+#pragma unroll
+      for (int r = 0; r < C; r++) g[r * 32 + lane] = W[so[r % PER] + (r / PER) * TSTEP];
+    } else {
+      for (int j = lane; j < cnt * C; j += 32) {
+        const int t = j / C, i = j - t * C;
+        g[j] = W[i * CS + t];
+      }
+    }
+  }
+};
 
 template <int NF, int MINB, bool BLK>
 __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_constant__ TinyParam P, TinyArgs a) {
@@ -172,9 +193,30 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
   double* G = smem;
   double* LP = G + 4 * E;
   double* Kp = LP + 2 * EL + threadIdx.x;
-  // K columns (generic path) double as the 12-wide staging record of the stress stores
-  constexpr int KC = (!BLK && NFP > 12) ? NFP : 12;
+  // Staging columns of the coalesced result stores: SS = the 12-wide element_stress record, whose Vz,Mx,My
+  // components (2,3,4,8,9,10: zero in 2D) are plain zero columns; SX = U_f / F_f / F_b records, XW wide.  The
+  // node-blocked path gives SS its own columns (zeroed once per CTA); the generic path overlays both on its K columns.
+  constexpr int XW = BLK ? (NF > 6 ? NF : 6) : (NFP > 12 ? NFP : 12);
+  constexpr int KC = BLK ? 12 + XW : XW;
+  double* SX = BLK ? Kp + 12 * CS : Kp;
   double* FU = Kp + size_t(KC) * CS;
+  const int lane = threadIdx.x & 31, wl0 = threadIdx.x & ~31;
+  const double* SSW = Kp - threadIdx.x + wl0;  // warp views of the staging columns: [col*CS + case-in-warp]
+  const double* SXW = SX - threadIdx.x + wl0;
+  StoreMap<12, CS> map12;
+  StoreMap<(NF ? NF : 1), CS> mapNF;
+  map12.init(lane);
+  mapNF.init(lane);
+  int go12[3];  // global offsets of the stress record rounds: case t, component i -> t*E*12 + i
+#pragma unroll
+  for (int r0 = 0; r0 < 3; r0++) {
+    const int j = r0 * 32 + lane, t = j / 12, i = j - t * 12;
+    go12[r0] = t * P.E * 12 + i;
+  }
+  if (BLK) {
+    Kp[2 * CS] = 0.0; Kp[3 * CS] = 0.0; Kp[4 * CS] = 0.0;
+    Kp[8 * CS] = 0.0; Kp[9 * CS] = 0.0; Kp[10 * CS] = 0.0;
+  }
   if (threadIdx.x < E) {
     const int e = threadIdx.x, na = P.enode[2 * e], nbn = P.enode[2 * e + 1];
     const ElemGeom g = elem_geom(P.xy[2 * na], P.xy[2 * na + 1], P.xy[2 * nbn], P.xy[2 * nbn + 1]);
@@ -286,16 +328,14 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
     // Results leave through the warp's (now dead) K columns: each lane parks its values in its column, then the
     // warp writes the 32 cases' contiguous output range with fully coalesced stores (a per-lane store of a
     // 48..288-byte record would touch 32 different 128-byte lines per instruction and bind the kernel on L1 tags).
-    const int lane = threadIdx.x & 31, wl0 = threadIdx.x & ~31;
     const int64_t c0 = base + wl0;                                   // first case of this warp
     const int cnt = int(min(int64_t(32), a.n_cases - c0));           // valid cases in this warp (<= 0: none)
-    double* KW = Kp - threadIdx.x + wl0;                             // warp view of the K columns: KW[col*CS + t]
     if (a.F_f) {
       __syncwarp();
 #pragma unroll
-      for (int i = 0; i < NF; i++) Kp[i * CS] = b[i];
+      for (int i = 0; i < NF; i++) SX[i * CS] = b[i];
       __syncwarp();
-      if (NF > 0) warp_store<NF ? NF : 1, CS>(a.F_f + c0 * NF, KW, lane, cnt);
+      if (NF > 0) mapNF.store(a.F_f + c0 * NF, SXW, lane, cnt);
       __syncwarp();
     }
     const int info = ldlt_solve_regs<NF>(A, b);
@@ -306,10 +346,15 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
 #pragma unroll
     for (int i = 0; i < NF; i++) {
       if (!BLK) FU[P.freek[i] * CS] = b[i];
-      Kp[i * CS] = b[i];
+      SX[i * CS] = b[i];
     }
     __syncwarp();
-    if (NF > 0) warp_store<NF ? NF : 1, CS>(a.U_f + c0 * NF, KW, lane, cnt);
+    if (NF > 0) mapNF.store(a.U_f + c0 * NF, SXW, lane, cnt);
+    if (!BLK) {  // the K columns become the stress record: its Vz,Mx,My columns must read zero
+      __syncwarp();
+      Kp[2 * CS] = 0.0; Kp[3 * CS] = 0.0; Kp[4 * CS] = 0.0;
+      Kp[8 * CS] = 0.0; Kp[9 * CS] = 0.0; Kp[10 * CS] = 0.0;
+    }
     // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
     for (int i = 0; i < nb; i++) {
       const int k = P.bndk[i];
@@ -364,33 +409,38 @@ __global__ void __launch_bounds__(TINY_BLOCK, MINB) k_tiny_fused(const __grid_co
         Kp[0 * CS] = -es[0] + ext[0]; Kp[1 * CS] = -es[1] + ext[1]; Kp[5 * CS] = -es[2] + ext[2];
         Kp[6 * CS] = es[3] + ext[3];  Kp[7 * CS] = es[4] + ext[4];  Kp[11 * CS] = es[5] + ext[5];
         __syncwarp();
+        double* gs = a.stress + (c0 * E + e) * 12;
         if (cnt == 32) {
 #pragma unroll
-          for (int r = 0; r < 12; r++) {
-            const int j = r * 32 + lane, t = j / 12, i = j - t * 12;
-            const bool zero = (0x71C >> i) & 1;  // Vz, Mx, My of both faces (components 2,3,4,8,9,10) are 0 in 2D
-            a.stress[((c0 + t) * E + e) * 12 + i] = zero ? 0.0 : KW[i * CS + t];
-          }
+          for (int r = 0; r < 12; r++)  // round r = r0 + 3k: case t0 + 8k, same component (96 = 8 * 12)
+            gs[go12[r % 3] + (r / 3) * 96 * E] = SSW[map12.so[r % 3] + (r / 3) * 8];
         } else {
           for (int j = lane; j < cnt * 12; j += 32) {
             const int t = j / 12, i = j - t * 12;
-            const bool zero = (0x71C >> i) & 1;
-            a.stress[((c0 + t) * E + e) * 12 + i] = zero ? 0.0 : KW[i * CS + t];
+            gs[t * E * 12 + i] = SSW[i * CS + t];
           }
         }
       }
     }
     __syncwarp();
-    for (int i0 = 0; i0 < nb; i0 += KC) {  // reactions leave through the staging columns too, KC components at a time
-      const int w = min(KC, nb - i0);
-      for (int i = 0; i < w; i++) Kp[i * CS] = FU[P.bndk[i0 + i] * CS];
+    if (NF > 0 && nb == NF) {  // same record width as U_f: reuse its hoisted store map
+#pragma unroll
+      for (int i = 0; i < NF; i++) SX[i * CS] = FU[P.bndk[i] * CS];
       __syncwarp();
-      const float rw = 1.0f / float(w);
-      for (int j = lane; j < cnt * w; j += 32) {
-        const int t = int((float(j) + 0.5f) * rw), i = j - t * w;  // exact for j < 2^20
-        a.F_b[(c0 + t) * nb + i0 + i] = KW[i * CS + t];
+      mapNF.store(a.F_b + c0 * NF, SXW, lane, cnt);
+      __syncwarp();
+    } else {
+      for (int i0 = 0; i0 < nb; i0 += XW) {  // reactions leave through the staging columns too, XW components at a time
+        const int w = min(XW, nb - i0);
+        for (int i = 0; i < w; i++) SX[i * CS] = FU[P.bndk[i0 + i] * CS];
+        __syncwarp();
+        const float rw = 1.0f / float(w);
+        for (int j = lane; j < cnt * w; j += 32) {
+          const int t = int((float(j) + 0.5f) * rw), i = j - t * w;  // exact for j < 2^20
+          a.F_b[(c0 + t) * nb + i0 + i] = SXW[i * CS + t];
+        }
+        __syncwarp();  // columns are rewritten at the top of the next block of cases
       }
-      __syncwarp();  // columns are zeroed again at the top of the next block of cases
     }
   }
 }
@@ -444,13 +494,13 @@ static cudaError_t launch_nf(const TinyParam& P, const TinyArgs& a, int n, int s
 #define TINY_MINB_SMALL 6
 #endif
 #ifndef TINY_MINB_BLK
-#define TINY_MINB_BLK 4
+#define TINY_MINB_BLK 5
 #endif
-  // the node-blocked path keeps K_ff, F_f and the element blocks live together: 120 registers without spills (4 CTAs/SM
-  // measured fastest: 140 us vs 150 us at 5 and 163 us at 6 CTAs/SM with spills)
+  // the node-blocked path keeps K_ff, F_f and the element blocks live together: measured (v5, 1M cases) 115 us at
+  // 5 CTAs/SM (96 registers), 123 us at 4 (118 registers, no spills), 140 us at 6 (80 registers, spills)
   constexpr int MINB = NF <= 6 ? (BLK ? TINY_MINB_BLK : TINY_MINB_SMALL) : NF <= 9 ? 3 : 2;  // register budget: K_ff (NFP doubles) lives in registers
   const size_t smem = size_t(4 * P.E + 2 * P.EL) * 8 +
-                      size_t(((!BLK && NFP > 12) ? NFP : 12) + n + (a.case_nl ? P.NL : 0) + (a.case_q ? 2 * P.EL : 0)) * (TINY_BLOCK + 1) * 8;
+                      size_t((BLK ? 12 + (NF > 6 ? NF : 6) : (NFP > 12 ? NFP : 12)) + n + (a.case_nl ? P.NL : 0) + (a.case_q ? 2 * P.EL : 0)) * (TINY_BLOCK + 1) * 8;
   auto kern = k_tiny_fused<NF, MINB, BLK>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (e != cudaSuccess) return e;
