@@ -44,13 +44,46 @@ int ensure_device_batch(obgpu_ctx* c) {
     c->max_nb = std::max(c->max_nb, m.nb);
   }
   OB_CUDA(c, c->d_meta.upload(meta, st));
-  OB_CUDA(c, cudaStreamSynchronize(st));  // meta is a stack vector
+  // Size classes: per-warp shared memory is sized for the largest structure a launch serves, so structures are
+  // bucketed by their need (band + vectors, in doubles) and every class gets its own launch and occupancy.
+  static const int64_t kClassLimit[] = {256, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2560, 3072, 4096, 6144, 8192,
+                                        12288, 16384, 24576, INT64_MAX};
+  constexpr int NCLS = int(sizeof(kClassLimit) / sizeof(kClassLimit[0]));
+  auto cls_of = [&](const FrameMeta& m) {
+    const int64_t need = int64_t(m.hb + 1) * m.nf + 2 * int64_t(m.nf) + 2 * int64_t(m.nb);
+    int k = 0;
+    while (need > kClassLimit[k]) k++;
+    return k;
+  };
+  std::vector<int64_t> cnt(NCLS + 1, 0);
+  for (int64_t s = 0; s < hb.S; s++) cnt[cls_of(meta[s]) + 1]++;
+  for (int k = 0; k < NCLS; k++) cnt[k + 1] += cnt[k];
+  std::vector<int32_t> order(hb.S);
+  c->frame_classes.clear();
+  {
+    std::vector<int64_t> pos(cnt.begin(), cnt.end() - 1);
+    for (int64_t s = 0; s < hb.S; s++) order[pos[cls_of(meta[s])]++] = int32_t(s);
+    for (int k = 0; k < NCLS; k++) {
+      if (cnt[k + 1] == cnt[k]) continue;
+      obgpu_ctx::FrameClass fc{cnt[k], cnt[k + 1], 0, 0, 0, 0};
+      for (int64_t i = cnt[k]; i < cnt[k + 1]; i++) {
+        const FrameMeta& m = meta[order[i]];
+        fc.max_band = std::max<int64_t>(fc.max_band, int64_t(m.hb + 1) * m.nf);
+        fc.max_nf = std::max(fc.max_nf, m.nf);
+        fc.max_nb = std::max(fc.max_nb, m.nb);
+        fc.max_hb = std::max(fc.max_hb, m.hb);
+      }
+      c->frame_classes.push_back(fc);
+    }
+  }
+  OB_CUDA(c, c->d_frame_order.upload(order, st));
+  OB_CUDA(c, cudaStreamSynchronize(st));  // meta, order are stack vectors
   c->dev_batch = true;
   return OBGPU_OK;
 }
 
 static bool frame_kernel_fits(const obgpu_ctx* c) {
-  return frame_smem_per_warp(c->max_band, c->max_nf, c->max_nb) * 4 <= size_t(227) * 1024;
+  return frame_smem_per_warp(c->max_band, c->max_nf, c->max_nb) * FRAME_WARPS <= size_t(227) * 1024;
 }
 
 int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
@@ -90,12 +123,17 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   a.U_f = c->d_Uf.p; a.F_b = c->d_Fb.p; a.F_f = c->d_Ff.p;
   a.stress = o.with_stress ? c->d_stress.p : nullptr;
   a.info = c->d_info.p; a.fail = c->d_fail.p;
-  a.max_band = c->max_band; a.max_nf = c->max_nf; a.max_nb = c->max_nb;
+  a.order = c->d_frame_order.p;
   OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-  OB_CUDA(c, launch_frame_fused(a, c->sm_count, c->stream));
+  for (auto it = c->frame_classes.rbegin(); it != c->frame_classes.rend(); ++it) {  // largest structures first
+    const obgpu_ctx::FrameClass& fc = *it;
+    a.o0 = fc.o0; a.o1 = fc.o1;
+    a.max_band = fc.max_band; a.max_nf = fc.max_nf; a.max_nb = fc.max_nb; a.max_hb = fc.max_hb;
+    OB_CUDA(c, launch_frame_fused(a, c->sm_count, c->stream));
+  }
   OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
   c->t_have[1] = true;
-  c->launches = 1;
+  c->launches = double(c->frame_classes.size());
   c->pcg_iters = 0;
   c->solved = true;
   c->have_stress = o.with_stress != 0;

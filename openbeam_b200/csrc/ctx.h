@@ -1,5 +1,7 @@
 // ctx.h — the opaque obgpu_ctx.
 #pragma once
+#include <vector>
+
 #include "kernels.h"
 
 struct obgpu_ctx {
@@ -35,6 +37,13 @@ struct obgpu_ctx {
   obgpu::DevBuf<int32_t> d_node_slot, d_nload_slot, d_el_ptr, d_el_order;
   obgpu::DevBuf<obgpu::FrameMeta> d_meta;
   int max_band = 0, max_nf = 0, max_nb = 0;
+  // size classes of the warp-per-structure kernel: structures sorted by shared-memory need
+  struct FrameClass {
+    int64_t o0, o1;
+    int max_band, max_nf, max_nb, max_hb;
+  };
+  std::vector<FrameClass> frame_classes;
+  obgpu::DevBuf<int32_t> d_frame_order;
   // sparse route (capi_sparse.cu)
   obgpu::SparsePlan plan;
   bool dev_plan = false, assembled = false;

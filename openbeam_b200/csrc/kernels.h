@@ -54,11 +54,16 @@ struct FrameArgs {
   double* stress;               // [L][Etot][12] or null
   int32_t* info;                // [L][S]
   int32_t* fail;                // [1]
-  int max_band;                 // max over structures of (hb+1)*nf   (doubles)
-  int max_nf, max_nb;
+  // size class served by this launch: structures order[o0 .. o1), whose banded K_ff, n_f, n_b and half bandwidth
+  // are bounded by the class maxima below (shared memory per warp is sized from them)
+  const int32_t* order;         // [S] structure ids sorted by size class
+  int64_t o0, o1;
+  int max_band;                 // max over the class of (hb+1)*nf   (doubles)
+  int max_nf, max_nb, max_hb;
 };
 cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st);
 size_t frame_smem_per_warp(int max_band, int max_nf, int max_nb);
+constexpr int FRAME_WARPS = 4;  // warps per CTA of k_frame_fused
 
 // Device view of the sparse route (global indices over the batch).
 struct SparseDev {

@@ -1,29 +1,33 @@
 // kernels_frame.cu — K1+K2+K4+K5+K6+K10 fused for batches of DIFFERENT small structures (BASELINE config 3:
 // random 2D frames, 10-60 elements, n_f up to ~180).  One WARP per system (structure s, load case c):
-//   stage A  lane = element: orientation, local stiffness, rotation to global (beam_math.cuh), summed
-//            equivalent nodal loads of the element's DISTRIB_UNIFORM loads -> shared-memory staging;
-//            then the 32 staged elements are scattered ONE ELEMENT AT A TIME (lanes = the 21 compact
-//            entries + 6 load entries) into the banded K_ff / F_f in shared memory.  Entries of one element
-//            never collide, elements are applied in the reference's order (assemble.cpp:123-223), so the sums
-//            are deterministic and need no atomics.  Bounded rows/columns are dropped on the fly
-//            (BC elimination as a gather through the per-node slots, assemble.cpp:249-341).
-//   stage B  banded LDL^T in shared memory (lanes over the trailing band block), forward/back substitution
-//            with warp-shuffle dot products.  Non-positive pivot -> info = row+1 (solver_static.cpp:97-105).
+//   stage A  lane = element (chunks of 16): orientation, local stiffness, rotation to global (beam_math.cuh),
+//            summed equivalent nodal loads of the element's DISTRIB_UNIFORM loads -> shared-memory staging;
+//            the staged elements are then scattered ONE ELEMENT AT A TIME (lanes = the 21 compact entries + 6
+//            load entries) into the banded K_ff / F_f in shared memory.  Entries of one element never collide,
+//            elements are applied in the reference's order (assemble.cpp:123-223), so the sums are
+//            deterministic and need no atomics.  Bounded rows/columns are dropped on the fly (BC elimination as
+//            a gather through the per-node slots, assemble.cpp:249-341).
+//   stage B  banded LDL^T in shared memory on the unscaled factor V = L D, the trailing triangle of every column
+//            flattened over the 32 lanes; L y = b fused into the column loop; L^T x = D^-1 y as a column sweep.
+//            Non-positive pivot -> info = row+1 (solver_static.cpp:97-105).
 //   stage C  lane = element: end forces (postproc_stress.cpp:86-165) staged and written coalesced; global end
-//            forces scattered element by element into the bounded DOFs = K_bf*U_f (solver_static.cpp:196-218).
+//            forces of the elements that touch a support scattered into the bounded DOFs = K_bf*U_f
+//            (solver_static.cpp:196-218).
+// Structures are served in SIZE CLASSES (host: capi_general.cu): shared memory per warp is sized by the class
+// maxima, so small frames run at high occupancy, and the kernel is instantiated per number of update rounds.
 #include "beam_math.cuh"
 #include "kernels.h"
 
 namespace obgpu {
 
-constexpr int FRAME_WARPS = 4;       // warps per CTA
-constexpr int STAGE_D = 27;          // doubles staged per element: 21 stiffness + 6 equivalent loads
+constexpr int STAGE_D = 27;  // doubles staged per element: 21 stiffness + 6 equivalent loads
+constexpr int CHUNK = 16;    // elements staged at a time
 
-// per-warp shared memory: band[max_band] | Ff[max_nf] | R[max_nb] | Eq[max_nb] | stage[32*STAGE_D] | slots[32*6] (int)
-// (stage C reuses stage[] as [32][12] stress + [32][6] global end forces)
+// per-warp shared memory: band[max_band] | Ff[max_nf] | R[max_nb] | Eq[max_nb] | Dinv[max_nf] | stage[CHUNK*STAGE_D]
+// | slots[CHUNK*6] (int).  Stage C reuses stage[] as [CHUNK][12] stress + [CHUNK][6] global end forces.
 size_t frame_smem_per_warp(int max_band, int max_nf, int max_nb) {
-  size_t d = size_t(max_band) + max_nf + 2 * size_t(max_nb) + 32 * STAGE_D;
-  return d * 8 + 32 * 6 * 4;
+  size_t d = size_t(max_band) + 2 * size_t(max_nf) + 2 * size_t(max_nb) + CHUNK * STAGE_D;
+  return d * 8 + CHUNK * 6 * 4;
 }
 
 // compact entry cid (0..20) -> the two compact DOF positions (0..5 = end0 {x,y,rz}, end1 {x,y,rz})
@@ -42,12 +46,60 @@ __device__ __forceinline__ void cid_pair(int cid, int& a, int& b) {
   }
 }
 
-__device__ __forceinline__ double warp_sum(double v) {
+// Flattened trailing triangle of one column step (see stage B): entry e = r*32 + lane is (p, q), 1 <= q <= p, rows p
+// in order, i.e. the entries of rows p <= m are exactly e < m(m+1)/2.  Byte offsets from the pivot (j, j):
+//   V(j+p, j+q) at (p*(W-1) + q)*8,   V(j+p, j) at p*(W-1)*8,   V(j+q, j) at q*(W-1)*8.
+// (p, q) depend on (round, lane) only, so the map is built once per structure.
+template <int MAXR>
+struct TriMap {
+  int v[MAXR > 0 ? MAXR : 1], p[MAXR > 0 ? MAXR : 1], q[MAXR > 0 ? MAXR : 1];
+  __device__ __forceinline__ void init(int lane, int W) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
+    for (int r = 0; r < MAXR; r++) {
+      const int e = r * 32 + lane;
+      int pp = int((sqrtf(8.0f * float(e) + 1.0f) + 1.0f) * 0.5f);
+      while (pp * (pp - 1) / 2 > e) pp--;
+      while (pp * (pp + 1) / 2 <= e) pp++;
+      const int qq = e - pp * (pp - 1) / 2 + 1;
+      v[r] = (pp * (W - 1) + qq) * 8;
+      p[r] = pp * (W - 1) * 8;
+      q[r] = qq * (W - 1) * 8;
+    }
+  }
+};
+
+// One column step of the factorisation for bands narrower than 32 (TriMap rounds), returns nothing: updates the
+// trailing triangle of column j.  Rounds are entered through a switch so that rounds beyond R_j cost nothing (real
+// branches: an `if (r < R_j)` guard is if-converted by the compiler and every round would issue, predicated off).
+template <int MAXR>
+__device__ __forceinline__ void trailing_update(char* bj, const TriMap<MAXR>& tm, double inv, int tri_j, int lane) {
+  const int R_j = (tri_j + 31) >> 5;
+  const int rem = tri_j - lane;  // entry (r, lane) is inside the triangle iff rem > 32 r
+  double v[MAXR > 0 ? MAXR : 1];
+#define OB_LD(r)                                                                                   \
+  case r + 1:                                                                                      \
+    if (MAXR > r && rem > 32 * r)                                                                  \
+      v[r < MAXR ? r : 0] = *reinterpret_cast<double*>(bj + tm.v[r < MAXR ? r : 0]) -              \
+                            *reinterpret_cast<double*>(bj + tm.p[r < MAXR ? r : 0]) *              \
+                                (*reinterpret_cast<double*>(bj + tm.q[r < MAXR ? r : 0]) * inv);
+#define OB_ST(r)                                                                                   \
+  case r + 1:                                                                                      \
+    if (MAXR > r && rem > 32 * r) *reinterpret_cast<double*>(bj + tm.v[r < MAXR ? r : 0]) = v[r < MAXR ? r : 0];
+  switch (R_j) {
+    OB_LD(15) OB_LD(14) OB_LD(13) OB_LD(12) OB_LD(11) OB_LD(10) OB_LD(9) OB_LD(8)
+    OB_LD(7) OB_LD(6) OB_LD(5) OB_LD(4) OB_LD(3) OB_LD(2) OB_LD(1) OB_LD(0)
+    default: break;
+  }
+  switch (R_j) {
+    OB_ST(15) OB_ST(14) OB_ST(13) OB_ST(12) OB_ST(11) OB_ST(10) OB_ST(9) OB_ST(8)
+    OB_ST(7) OB_ST(6) OB_ST(5) OB_ST(4) OB_ST(3) OB_ST(2) OB_ST(1) OB_ST(0)
+    default: break;
+  }
+#undef OB_LD
+#undef OB_ST
 }
 
+template <int MAXR>
 __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, int doubles_per_warp) {
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -55,12 +107,20 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
   double* Ff = band + a.max_band;
   double* R = Ff + a.max_nf;
   double* Eq = R + a.max_nb;
-  double* stage = Eq + a.max_nb;                                   // [32][STAGE_D] (stage A) / [32][12]+[32][6] (stage C)
-  int32_t* slots = reinterpret_cast<int32_t*>(stage + 32 * STAGE_D);  // [32][6]
-  const int64_t n_sys = a.S * a.L;
+  double* Dinv = Eq + a.max_nb;                                        // reciprocal pivots
+  double* stage = Dinv + a.max_nf;                                     // [CHUNK][STAGE_D] (A) / [CHUNK][12]+[CHUNK][6] (C)
+  int32_t* slots = reinterpret_cast<int32_t*>(stage + CHUNK * STAGE_D);  // [CHUNK][6]
+  const int64_t n_cls = a.o1 - a.o0;
+  const int64_t n_sys = n_cls * a.L;
   const int64_t wstride = int64_t(gridDim.x) * FRAME_WARPS;
-  for (int64_t sys = int64_t(blockIdx.x) * FRAME_WARPS + warp; sys < n_sys; sys += wstride) {
-    const int64_t c = sys / a.S, s = sys - c * a.S;
+  int pa = 0, pb = 0;  // scatter role of this lane: compact entry (pa, pb) or load component pa
+  if (lane < ELEM_K) cid_pair(lane, pa, pb);
+  else if (lane < STAGE_D) pa = lane - ELEM_K;
+  const int offF = int(Ff - band), offEq = int(Eq - band);
+  for (int64_t it = int64_t(blockIdx.x) * FRAME_WARPS + warp; it < n_sys; it += wstride) {
+    const int64_t c = it / n_cls;
+    const int64_t s = a.order[a.o0 + (it - c * n_cls)];
+    const int64_t sys = c * a.S + s;
     const FrameMeta m = a.meta[s];
     const int nf = m.nf, nb = m.nb, hb = m.hb, W = hb + 1;
     for (int i = lane; i < W * nf; i += 32) band[i] = 0.0;
@@ -79,8 +139,8 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
     const double* eai_base = a.case_eai ? a.case_eai + c * 3 * a.Etot : a.elem_EAI;
     const double* q_base = a.case_q ? a.case_q + c * a.ELtot : a.eload_q;
     // ---- stage A ----
-    for (int eb = 0; eb < m.E; eb += 32) {
-      const int cnt = min(32, m.E - eb);
+    for (int eb = 0; eb < m.E; eb += CHUNK) {
+      const int cnt = min(CHUNK, m.E - eb);
       if (lane < cnt) {
         const int64_t e = m.e0 + eb + lane;
         const uint2 nd = a.elem_nodes[e];
@@ -110,67 +170,95 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
         }
       }
       __syncwarp();
-      int pa = 0, pb = 0;
-      if (lane < ELEM_K) cid_pair(lane, pa, pb);
-      for (int ee = 0; ee < cnt; ee++) {
+      // Scatter, one element per step in the reference's order.  band | Ff | R | Eq are one contiguous block, so a
+      // lane's target is a single offset from `band`; the next element's offset and value are fetched while the
+      // current read-modify-write is in flight (the RMW chain is the only serial dependency left).
+      auto fetch = [&](int ee, int& off, double& v) {
         const int32_t* sl = slots + ee * 6;
-        if (lane < ELEM_K) {
-          const int32_t fi = sl[pa], fj = sl[pb];
-          if (fi >= 0 && fj >= 0) {
-            const int i = max(fi, fj), j = min(fi, fj);
-            band[i * W + (j - i + hb)] += stage[ee * STAGE_D + lane];
-          }
-        } else if (lane < STAGE_D) {
-          const int32_t t = sl[lane - ELEM_K];
-          const double v = stage[ee * STAGE_D + lane];
-          if (t >= 0) Ff[t] += v;
-          else if (t != SLOT_NONE) Eq[-t - 1] += v;
+        off = -1;
+        v = 0.0;
+        if (lane < STAGE_D) {
+          v = stage[ee * STAGE_D + lane];
+          const int32_t fi = sl[pa];
+          if (lane < ELEM_K) {
+            const int32_t fj = sl[pb];
+            if (fi >= 0 && fj >= 0) {
+              const int i = max(fi, fj), j = min(fi, fj);
+              off = i * W + (j - i + hb);
+            }
+          } else if (fi >= 0) off = offF + fi;
+          else if (fi != SLOT_NONE) off = offEq + (-fi - 1);
         }
+      };
+      int off_n;
+      double v_n;
+      fetch(0, off_n, v_n);
+      for (int ee = 0; ee < cnt; ee++) {
+        const int off = off_n;
+        const double v = v_n;
+        if (ee + 1 < cnt) fetch(ee + 1, off_n, v_n);
+        if (off >= 0) band[off] += v;
         __syncwarp();
       }
     }
     if (a.F_f)
       for (int i = lane; i < nf; i += 32) a.F_f[c * a.nf_tot + m.f0 + i] = Ff[i];
     // ---- stage B: banded LDL^T (row i holds columns i-hb..i at band[i*W + (j-i+hb)]) ----
+    // Right-looking, one column j per step, on the UNSCALED factor V = L D (V(i,j) = L(i,j) D(j)): the column is
+    // never rewritten, the only division is the reciprocal pivot (kept in Dinv), and L y = b rides along
+    // (F(j+q) -= V(j+q,j) * y(j)/D(j)).  The trailing update V(j+p,j+q) -= V(j+p,j) V(j+q,j) / D(j), 1 <= q <= p <= m,
+    // is a triangle of m(m+1)/2 independent entries, flattened over the 32 lanes in rounds (TriMap): a round costs
+    // 3 loads + 2 FP64 ops + 1 store and all lanes work; all loads of a column are issued ahead of its stores.
     int info = 0;
-    for (int j = 0; j < nf; j++) {
-      const double d = band[j * W + hb];
-      if (!(d > 0.0)) {  // Eigen LLT stops at the first x <= 0 (solver_static.cpp:97-105)
-        info = j + 1;
-        break;
+    const int q = lane + 1;
+    if (MAXR > 0) {
+      TriMap<MAXR> tm;
+      tm.init(lane, W);
+      const int tri_full = hb * (hb + 1) / 2;
+      for (int j = 0; j < nf; j++) {
+        double* bj = band + j * W + hb;  // (j, j)
+        const double d = *bj;
+        if (!(d > 0.0)) {  // Eigen LLT stops at the first x <= 0 (solver_static.cpp:97-105)
+          info = j + 1;
+          break;
+        }
+        const double inv = 1.0 / d;
+        const double tj = Ff[j] * inv;
+        const int mrows = min(hb, nf - 1 - j);
+        if (lane == 0) Dinv[j] = inv;
+        if (q <= mrows) Ff[j + q] -= bj[q * (W - 1)] * tj;
+        trailing_update<MAXR>(reinterpret_cast<char*>(bj), tm, inv, mrows == hb ? tri_full : mrows * (mrows + 1) / 2, lane);
+        __syncwarp();
       }
-      const double inv = 1.0 / d;
-      const int imax = min(j + hb, nf - 1);
-      // trailing update with the still-unscaled column j: B(i,k) -= B(i,j)*B(k,j)/d, j < k <= i
-      for (int i = j + 1; i <= imax; i++) {
-        const double lij = band[i * W + (j - i + hb)] * inv;
-        for (int k = j + 1 + lane; k <= i; k += 32) band[i * W + (k - i + hb)] -= lij * band[k * W + (j - k + hb)];
+    } else {  // wide bands (hb >= 32: more than 10 nodes per storey): lanes stride over the columns of each row
+      for (int j = 0; j < nf; j++) {
+        const double d = band[j * W + hb];
+        if (!(d > 0.0)) {
+          info = j + 1;
+          break;
+        }
+        const double inv = 1.0 / d;
+        const double tj = Ff[j] * inv;
+        const int mrows = min(hb, nf - 1 - j);
+        for (int i = j + 1; i <= j + mrows; i++) {
+          const double lij = band[i * W + (j - i + hb)] * inv;
+          for (int k = j + 1 + lane; k <= i; k += 32) band[i * W + (k - i + hb)] -= lij * band[k * W + (j - k + hb)];
+        }
+        for (int i = j + 1 + lane; i <= j + mrows; i += 32) Ff[i] -= band[i * W + (j - i + hb)] * tj;
+        if (lane == 0) Dinv[j] = inv;
+        __syncwarp();
       }
-      __syncwarp();
-      for (int i = j + 1 + lane; i <= imax; i += 32) band[i * W + (j - i + hb)] *= inv;  // store L
-      __syncwarp();
     }
     if (info == 0) {
-      // L y = b
-      for (int i = 1; i < nf; i++) {
-        const int k0 = max(0, i - hb);
-        double acc = 0.0;
-        for (int k = k0 + lane; k < i; k += 32) acc += band[i * W + (k - i + hb)] * Ff[k];
-        acc = warp_sum(acc);
-        if (lane == 0) Ff[i] -= acc;
+      // L^T x = D^-1 y as a column sweep from the last row up: x(j) = Dinv(j) * (y(j) - sum_k V(k,j) x(k)); row j of
+      // V is contiguous in the band
+      for (int j = nf - 1; j >= 0; j--) {
+        const double xj = Ff[j] * Dinv[j];
+        for (int qq = q; qq <= min(hb, j); qq += 32) Ff[j - qq] -= band[j * W + hb - qq] * xj;
         __syncwarp();
+        if (lane == 0) Ff[j] = xj;
       }
-      for (int i = lane; i < nf; i += 32) Ff[i] /= band[i * W + hb];
       __syncwarp();
-      // L^T x = z
-      for (int i = nf - 2; i >= 0; i--) {
-        const int k1 = min(nf - 1, i + hb);
-        double acc = 0.0;
-        for (int k = i + 1 + lane; k <= k1; k += 32) acc += band[k * W + (i - k + hb)] * Ff[k];
-        acc = warp_sum(acc);
-        if (lane == 0) Ff[i] -= acc;
-        __syncwarp();
-      }
     }
     if (lane == 0) {
       a.info[sys] = info;
@@ -178,10 +266,11 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
     }
     for (int i = lane; i < nf; i += 32) a.U_f[c * a.nf_tot + m.f0 + i] = Ff[i];
     // ---- stage C: element end forces, reactions ----
-    double* sst = stage;               // [32][12] stress staging
-    double* sgf = stage + 32 * 12;     // [32][6]  global end forces
-    for (int eb = 0; eb < m.E; eb += 32) {
-      const int cnt = min(32, m.E - eb);
+    double* sst = stage;                  // [CHUNK][12] stress staging
+    double* sgf = stage + CHUNK * 12;     // [CHUNK][6]  global end forces
+    for (int eb = 0; eb < m.E; eb += CHUNK) {
+      const int cnt = min(CHUNK, m.E - eb);
+      bool hasb = false;
       if (lane < cnt) {
         const int64_t e = m.e0 + eb + lane;
         const uint2 nd = a.elem_nodes[e];
@@ -195,6 +284,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
           const int32_t t0 = a.node_slot[3 * (m.n0 + nd.x) + k], t1 = a.node_slot[3 * (m.n0 + nd.y) + k];
           slots[lane * 6 + k] = t0;
           slots[lane * 6 + 3 + k] = t1;
+          hasb |= (t0 < 0 && t0 != SLOT_NONE) || (t1 < 0 && t1 != SLOT_NONE);
           ug[k] = t0 >= 0 ? Ff[t0] : 0.0;
           ug[3 + k] = t1 >= 0 ? Ff[t1] : 0.0;
         }
@@ -224,7 +314,10 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
         double* o = a.stress + (c * a.Etot + m.e0 + eb) * 12;
         for (int i = lane; i < cnt * 12; i += 32) o[i] = sst[i];
       }
-      for (int ee = 0; ee < cnt; ee++) {
+      unsigned todo = __ballot_sync(0xffffffffu, hasb);  // elements touching a support, still in element order
+      while (todo) {
+        const int ee = __ffs(todo) - 1;
+        todo &= todo - 1;
         if (lane < 6) {
           const int32_t t = slots[ee * 6 + lane];
           if (t < 0 && t != SLOT_NONE) R[-t - 1] += sgf[ee * 6 + lane];
@@ -238,23 +331,37 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
   }
 }
 
-cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st) {
+template <int MAXR>
+static cudaError_t launch_frame_r(const FrameArgs& a, int sm_count, cudaStream_t st) {
   const size_t per_warp = frame_smem_per_warp(a.max_band, a.max_nf, a.max_nb);
   const size_t smem = per_warp * FRAME_WARPS;
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-  cudaError_t e = cudaFuncSetAttribute(k_frame_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+  auto kern = k_frame_fused<MAXR>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (e != cudaSuccess) return e;
   int per_sm = 1;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_frame_fused, FRAME_WARPS * 32, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FRAME_WARPS * 32, smem);
   if (e != cudaSuccess) return e;
   if (per_sm < 1) per_sm = 1;
-  const int64_t n_sys = a.S * a.L;
-  int64_t grid = int64_t(sm_count) * per_sm;
+  const int64_t n_sys = (a.o1 - a.o0) * a.L;
+  int64_t grid = int64_t(sm_count) * per_sm;  // persistent: a whole number of CTAs per SM, warps stride over systems
   const int64_t need = (n_sys + FRAME_WARPS - 1) / FRAME_WARPS;
   if (grid > need) grid = need;
   if (grid < 1) grid = 1;
-  k_frame_fused<<<unsigned(grid), FRAME_WARPS * 32, smem, st>>>(a, int(per_warp / 8));
+  kern<<<unsigned(grid), FRAME_WARPS * 32, smem, st>>>(a, int(per_warp / 8));
   return cudaGetLastError();
+}
+
+cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st) {
+  if (a.o1 <= a.o0) return cudaSuccess;
+  if (a.max_hb >= 32) return launch_frame_r<0>(a, sm_count, st);
+  const int rounds = (a.max_hb * (a.max_hb + 1) / 2 + 31) / 32;  // update rounds of the widest band in the class
+  if (rounds <= 2) return launch_frame_r<2>(a, sm_count, st);
+  if (rounds <= 4) return launch_frame_r<4>(a, sm_count, st);
+  if (rounds <= 6) return launch_frame_r<6>(a, sm_count, st);
+  if (rounds <= 8) return launch_frame_r<8>(a, sm_count, st);
+  if (rounds <= 12) return launch_frame_r<12>(a, sm_count, st);
+  return launch_frame_r<16>(a, sm_count, st);
 }
 
 }  // namespace obgpu
