@@ -100,7 +100,7 @@ __device__ __forceinline__ void trailing_update(char* bj, const TriMap<MAXR>& tm
 }
 
 template <int MAXR>
-__global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, int doubles_per_warp) {
+__global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_fused(FrameArgs a, int doubles_per_warp) {
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* band = smem + size_t(warp) * doubles_per_warp;
@@ -215,19 +215,28 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
       TriMap<MAXR> tm;
       tm.init(lane, W);
       const int tri_full = hb * (hb + 1) / 2;
+      // The pivot chain (load d, reciprocal, scale, update, store, sync) is the serial latency of a column; the
+      // NEXT pivot V(j+1,j+1) - V(j+1,j)^2/D(j) is therefore formed (bit-identically to the trailing update) and
+      // inverted at the top of step j, so its reciprocal overlaps the update of column j.
+      double d = nf > 0 ? band[hb] : 1.0;
+      double inv = 1.0 / d;
       for (int j = 0; j < nf; j++) {
         double* bj = band + j * W + hb;  // (j, j)
-        const double d = *bj;
         if (!(d > 0.0)) {  // Eigen LLT stops at the first x <= 0 (solver_static.cpp:97-105)
           info = j + 1;
           break;
         }
-        const double inv = 1.0 / d;
-        const double tj = Ff[j] * inv;
+        const double inv_j = inv;
         const int mrows = min(hb, nf - 1 - j);
-        if (lane == 0) Dinv[j] = inv;
+        if (j + 1 < nf) {
+          const double c1 = mrows > 0 ? bj[W - 1] : 0.0;
+          d = bj[W] - c1 * (c1 * inv_j);
+          inv = 1.0 / d;
+        }
+        const double tj = Ff[j] * inv_j;
+        if (lane == 0) Dinv[j] = inv_j;
         if (q <= mrows) Ff[j + q] -= bj[q * (W - 1)] * tj;
-        trailing_update<MAXR>(reinterpret_cast<char*>(bj), tm, inv, mrows == hb ? tri_full : mrows * (mrows + 1) / 2, lane);
+        trailing_update<MAXR>(reinterpret_cast<char*>(bj), tm, inv_j, mrows == hb ? tri_full : mrows * (mrows + 1) / 2, lane);
         __syncwarp();
       }
     } else {  // wide bands (hb >= 32: more than 10 nodes per storey): lanes stride over the columns of each row
@@ -249,9 +258,27 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32) k_frame_fused(FrameArgs a, i
         __syncwarp();
       }
     }
-    if (info == 0) {
-      // L^T x = D^-1 y as a column sweep from the last row up: x(j) = Dinv(j) * (y(j) - sum_k V(k,j) x(k)); row j of
-      // V is contiguous in the band
+    if (info == 0 && MAXR > 0) {
+      // L^T x = D^-1 y as a column sweep from the last row up: x(j) = Dinv(j) * (y(j) - sum_k V(k,j) x(k)).  The
+      // running sums live in REGISTERS: row i is carried by lane i%32 from the step it first receives a term
+      // (j = i + hb) to its own step (hb < 32, so the rows in flight sit in distinct lanes); x(j) reaches the
+      // other lanes by shuffle, so the serial chain of a step is shuffle + 2 FP64 ops with no shared-memory
+      // round trip or barrier.
+      int myrow = (nf - 1) - ((nf - 1 - lane) & 31);
+      double acc = myrow >= 0 ? Ff[myrow] : 0.0;
+      for (int j = nf - 1; j >= 0; j--) {
+        const double vj = (myrow >= 0 && myrow < j && j - myrow <= hb) ? band[j * W + hb - (j - myrow)] : 0.0;
+        const double xj = __shfl_sync(0xffffffffu, acc, j & 31) * Dinv[j];
+        if (lane == (j & 31)) {
+          Ff[j] = xj;
+          myrow -= 32;
+          acc = myrow >= 0 ? Ff[myrow] : 0.0;
+        } else {
+          acc -= vj * xj;
+        }
+      }
+      __syncwarp();
+    } else if (info == 0) {
       for (int j = nf - 1; j >= 0; j--) {
         const double xj = Ff[j] * Dinv[j];
         for (int qq = q; qq <= min(hb, j); qq += 32) Ff[j - qq] -= band[j * W + hb - qq] * xj;
