@@ -1,6 +1,7 @@
 // capi_sparse.cu — global K assembly (K1+K4), BC gather (K5) and the PCG route (K7-K9, K10) for large structures.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "ctx.h"
@@ -36,7 +37,7 @@ static int ensure_plan(obgpu_ctx* c) {
   OB_CUDA(c, c->d_eload_elem_g.upload(eg, st));
   OB_CUDA(c, c->d_seg_ptr.upload(P.seg_ptr, st));
   OB_CUDA(c, c->d_seg_src.upload(P.seg_src, st));
-  OB_CUDA(c, c->d_ff_rowptr.upload(P.ff_rowptr, st));
+  OB_CUDA(c, c->d_sl_ptr.upload(P.sl_ptr, st));
   OB_CUDA(c, c->d_ff_col.upload(P.ff_col, st));
   OB_CUDA(c, c->d_ff_src.upload(P.ff_src, st));
   OB_CUDA(c, c->d_ff_diag.upload(P.ff_diag, st));
@@ -64,7 +65,7 @@ static SparseDev sparse_dev(obgpu_ctx* c, int64_t k /* K copy */) {
   d.node_slot = c->d_node_slot.p; d.el_ptr = c->d_el_ptr.p; d.el_order = c->d_el_order.p;
   d.eload_elem_g = c->d_eload_elem_g.p; d.eload_dir = c->d_eload_dir.p;
   d.seg_ptr = c->d_seg_ptr.p; d.seg_src = c->d_seg_src.p;
-  d.ff_rowptr = c->d_ff_rowptr.p; d.ff_col = c->d_ff_col.p; d.ff_src = c->d_ff_src.p; d.ff_diag = c->d_ff_diag.p;
+  d.sl_ptr = c->d_sl_ptr.p; d.ff_col = c->d_ff_col.p; d.ff_src = c->d_ff_src.p; d.ff_diag = c->d_ff_diag.p;
   d.bf_rowptr = c->d_bf_rowptr.p; d.bf_col = c->d_bf_col.p; d.bf_src = c->d_bf_src.p;
   d.fseg_ptr = c->d_fseg_ptr.p; d.fseg_src = c->d_fseg_src.p;
   d.elem_k = c->d_elem_k.p + size_t(k) * d.Etot * ELEM_K;
@@ -122,7 +123,39 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   OB_CUDA(c, c->d_info.reserve(size_t(L) * S));
   OB_CUDA(c, c->d_fail.reserve(1));
   if (o.with_stress) OB_CUDA(c, c->d_stress.reserve(size_t(L) * Etot * 12));
-  for (auto* b : {&c->d_minv, &c->d_r, &c->d_z, &c->d_p, &c->d_ap}) OB_CUDA(c, b->reserve(std::max<int64_t>(nf, 1)));
+  // PCG work vectors in one slab (p | ap | r | z | minv).  The matrix (360 MB at C4) streams through the 126 MB L2
+  // once per iteration and would evict them; an access-policy window marks the slab persisting (everything else on
+  // the stream is treated as streaming), so the three vector kernels and the gathers of the SpMV run out of L2.
+  const size_t nfp = (size_t(std::max<int64_t>(nf, 1)) + 31) & ~size_t(31);
+  OB_CUDA(c, c->d_pcgvec.reserve(5 * nfp));
+  double* const v_p = c->d_pcgvec.p;
+  double* const v_ap = v_p + nfp;
+  double* const v_r = v_ap + nfp;
+  double* const v_z = v_r + nfp;
+  double* const v_minv = v_z + nfp;
+  bool l2_window = false;
+  {
+    static const bool want = !(getenv("OBGPU_L2_PERSIST") && atoi(getenv("OBGPU_L2_PERSIST")) == 0);
+    int max_persist = 0, max_window = 0;
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, c->device);
+    cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
+    const size_t slab = 5 * nfp * sizeof(double);
+    if (want && max_persist > 0 && max_window > 0 && slab > (8u << 20)) {
+      const size_t win = std::min(slab, size_t(max_window));
+      const size_t carve = std::min(win, size_t(max_persist));
+      if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve) == cudaSuccess) {
+        cudaStreamAttrValue av;
+        std::memset(&av, 0, sizeof(av));
+        av.accessPolicyWindow.base_ptr = v_p;
+        av.accessPolicyWindow.num_bytes = win;
+        av.accessPolicyWindow.hitRatio = float(double(carve) / double(win));
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        l2_window = cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
+      }
+      cudaGetLastError();  // the window is an optimisation: never fail the solve over it
+    }
+  }
   OB_CUDA(c, c->d_scal.reserve(16));
   OB_CUDA(c, c->d_partial.reserve(size_t(2) * c->sm_count * 8));
   OB_CUDA(c, c->d_counter.reserve(1));
@@ -141,7 +174,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     SparseDev d = sparse_dev(c, k);
     if (cs == 0 || c->has_case_eai) {  // K5: BC elimination as gathers, Jacobi diagonal
       OB_CUDA(c, launch_bc_gather(d, c->stream));
-      OB_CUDA(c, launch_inv_diag(nf, d.ff_diag, d.ff_val, c->d_minv.p, c->stream));
+      OB_CUDA(c, launch_inv_diag(nf, d.ff_diag, d.ff_val, v_minv, c->stream));
       launches += 3;
     }
     const double* nl = c->has_case_nl ? c->d_case_nl.p + size_t(cs) * c->hb.NLtot() : c->d_nload_val.p;
@@ -155,10 +188,10 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
       PcgArgs a;
       a.r0 = int32_t(sy.free_off[s]); a.r1 = int32_t(sy.free_off[s + 1]);
       if (a.r1 == a.r0) continue;
-      a.rowptr = d.ff_rowptr; a.col = d.ff_col; a.val = d.ff_val; a.minv = c->d_minv.p;
+      a.slptr = d.sl_ptr; a.col = d.ff_col; a.val = d.ff_val; a.minv = v_minv;
       a.b = c->d_Ff.p + size_t(cs) * nf;
       a.x = c->d_Uf.p + size_t(cs) * nf;
-      a.r = c->d_r.p; a.z = c->d_z.p; a.p = c->d_p.p; a.ap = c->d_ap.p;
+      a.r = v_r; a.z = v_z; a.p = v_p; a.ap = v_ap;
       a.scal = c->d_scal.p; a.partial = c->d_partial.p; a.counter = c->d_counter.p;
       OB_CUDA(c, launch_pcg_init(a, c->sm_count, c->stream));
       launches += 1;
@@ -199,6 +232,13 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     OB_CUDA(c, cudaMemcpyAsync(c->d_info.p, h_info.data(), h_info.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
   OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
   OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (l2_window) {
+    cudaStreamAttrValue av;
+    std::memset(&av, 0, sizeof(av));
+    cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+    cudaCtxResetPersistingL2Cache();
+    cudaGetLastError();
+  }
   c->t_have[1] = true;
   c->launches = launches;
   c->pcg_iters = iters_total;

@@ -48,9 +48,10 @@ struct obgpu_ctx {
   obgpu::SparsePlan plan;
   bool dev_plan = false, assembled = false;
   int64_t LK = 1;  // number of assembled K copies (L when sections vary per case, else 1)
-  obgpu::DevBuf<int32_t> d_seg_ptr, d_seg_src, d_ff_rowptr, d_ff_col, d_ff_src, d_ff_diag, d_bf_rowptr, d_bf_col, d_bf_src,
+  obgpu::DevBuf<int32_t> d_seg_ptr, d_seg_src, d_sl_ptr, d_ff_col, d_ff_src, d_ff_diag, d_bf_rowptr, d_bf_col, d_bf_src,
       d_fseg_ptr, d_fseg_src, d_elem_node0, d_elem_f0, d_eload_elem_g;
-  obgpu::DevBuf<double> d_elem_k, d_kval, d_ff_val, d_bf_val, d_eload_g, d_Eq, d_minv, d_r, d_z, d_p, d_ap, d_scal, d_partial;
+  obgpu::DevBuf<double> d_elem_k, d_kval, d_ff_val, d_bf_val, d_eload_g, d_Eq, d_scal, d_partial;
+  obgpu::DevBuf<double> d_pcgvec;  // p | ap | r | z | minv in one slab: the L2 persistence window of the PCG loop
   obgpu::DevBuf<unsigned int> d_counter;
   double* h_scal = nullptr;  // pinned [8]
   double pcg_relres = 0;

@@ -74,7 +74,7 @@ struct SparseDev {
   const int32_t* node_slot; const int32_t* el_ptr; const int32_t* el_order;
   const int32_t* eload_elem_g; // [ELtot] global element of each element load (caller slot order)
   const double* eload_dir;
-  const int32_t *seg_ptr, *seg_src, *ff_rowptr, *ff_col, *ff_src, *ff_diag, *bf_rowptr, *bf_col, *bf_src, *fseg_ptr, *fseg_src;
+  const int32_t *seg_ptr, *seg_src, *sl_ptr, *ff_col, *ff_src, *ff_diag, *bf_rowptr, *bf_col, *bf_src, *fseg_ptr, *fseg_src;
   double *elem_k, *kval, *ff_val, *bf_val, *eload_g, *Eq;
 };
 cudaError_t launch_elem_stiff(const SparseDev& d, const double* eai, cudaStream_t st);
@@ -87,7 +87,7 @@ cudaError_t launch_stress(const SparseDev& d, const double* eai, const double* q
 // Jacobi-PCG on rows [r0, r1) of the K_ff CSR (one structure).  Device scalars live in `scal` (16 doubles).
 struct PcgArgs {
   int32_t r0, r1;
-  const int32_t *rowptr, *col;
+  const int32_t *slptr, *col;  // K_ff in SELL-32 (SparsePlan): slice offsets, column of every stored entry
   const double* val;
   const double* minv;   // [nf] inverse diagonal
   const double* b;      // rhs (F_f)

@@ -2,12 +2,13 @@
 // solveStatic, solver_static.cpp:110-129): memory-bound CSR SpMV fused with the p.Ap dot, and fused
 // axpy / preconditioner / dot kernels.  Dots finish in-kernel (last-block pattern, fixed summation order), the
 // step lengths alpha/beta are computed on the device from `scal`, so an iteration is 3 launches with no host sync.
+#include <cstdlib>
+
 #include "kernels.h"
 
 namespace obgpu {
 
 constexpr int PCG_BLOCK = 256;
-constexpr int LPR = 8;  // lanes per CSR row (K_ff of a frame grid has ~15 entries per row)
 
 __device__ __forceinline__ double block_sum(double v, double* sh) {
 #pragma unroll
@@ -70,22 +71,41 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_init(PcgArgs a) {
   if (blockIdx.x == 0 && threadIdx.x == 0) a.scal[1] = 0.0;
 }
 
-// ap = A p on rows [r0, r1); scal[2] = p.Ap
+// ap = A p on rows [r0, r1); scal[2] = p.Ap.  K_ff is in SELL-32 (symbolic_sparse.cpp): one warp per slice of 32
+// rows, lane = row; step k reads 32 consecutive values and columns (fully coalesced) and gathers p.  The k loop is
+// unrolled by 4 with all matrix loads issued ahead of the gathers.  The matrix streams through once per
+// iteration (360 MB at C4, 3x the L2): evict-first loads keep the 16 MB vectors resident in the 126 MB L2.
+template <bool STREAM>
 __global__ void __launch_bounds__(PCG_BLOCK) k_spmv_dot(PcgArgs a) {
   __shared__ double sh[PCG_BLOCK / 32];
-  const int sub = threadIdx.x % LPR;
-  const int64_t groups = int64_t(gridDim.x) * (PCG_BLOCK / LPR);
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = int64_t(gridDim.x) * (PCG_BLOCK / 32);
+  const int64_t s1 = (int64_t(a.r1) + 31) >> 5;
   double v[1] = {0.0};
-  for (int64_t base = a.r0 + int64_t(blockIdx.x) * (PCG_BLOCK / LPR); base < a.r1; base += groups) {
-    const int64_t row = base + threadIdx.x / LPR;
+  for (int64_t sl = (a.r0 >> 5) + int64_t(blockIdx.x) * (PCG_BLOCK / 32) + (threadIdx.x >> 5); sl < s1; sl += nwarps) {
+    const int32_t base = a.slptr[sl], w = (a.slptr[sl + 1] - base) >> 5;
+    const double* __restrict__ pv = a.val + base + lane;
+    const int32_t* __restrict__ pc = a.col + base + lane;
     double sum = 0.0;
-    if (row < a.r1) {
-      const int32_t k1 = a.rowptr[row + 1];
-      for (int32_t k = a.rowptr[row] + sub; k < k1; k += LPR) sum += a.val[k] * a.p[a.col[k]];
-    }
+    int k = 0;
+    for (; k + 4 <= w; k += 4) {
+      int32_t c[4];
+      double m[4];
 #pragma unroll
-    for (int o = LPR / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-    if (sub == 0 && row < a.r1) {
+      for (int u = 0; u < 4; u++) {
+        c[u] = STREAM ? __ldcs(pc + 32 * (k + u)) : pc[32 * (k + u)];
+        m[u] = STREAM ? __ldcs(pv + 32 * (k + u)) : pv[32 * (k + u)];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) sum += m[u] * a.p[c[u]];
+    }
+    for (; k < w; k++) {
+      const int32_t c = STREAM ? __ldcs(pc + 32 * k) : pc[32 * k];
+      const double m = STREAM ? __ldcs(pv + 32 * k) : pv[32 * k];
+      sum += m * a.p[c];
+    }
+    const int64_t row = sl * 32 + lane;
+    if (row >= a.r0 && row < a.r1) {
       a.ap[row] = sum;
       v[0] += sum * a.p[row];
     }
@@ -121,9 +141,9 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_dir(PcgArgs a, int cur) {
     a.p[i] = a.z[i] + beta * a.p[i];
 }
 
-static unsigned pcg_grid(int64_t work_items, int sm_count) {
+static unsigned pcg_grid(int64_t work_items, int sm_count, int ctas_per_sm = 8) {
   int64_t g = (work_items + PCG_BLOCK - 1) / PCG_BLOCK;
-  const int64_t cap = int64_t(sm_count) * 8;  // persistent-ish: a whole number of CTAs per SM, grid-stride inside
+  const int64_t cap = int64_t(sm_count) * ctas_per_sm;  // persistent-ish: a whole number of CTAs per SM, grid-stride inside
   if (g > cap) g = cap;
   return unsigned(g < 1 ? 1 : g);
 }
@@ -136,7 +156,12 @@ cudaError_t launch_pcg_init(const PcgArgs& a, int sm_count, cudaStream_t st) {
 cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t st) {
   const int64_t n = a.r1 - a.r0;
   const int cur = it & 1;
-  k_spmv_dot<<<pcg_grid(n * LPR, sm_count), PCG_BLOCK, 0, st>>>(a);
+  static const bool stream = getenv("OBGPU_SPMV_STREAM") ? atoi(getenv("OBGPU_SPMV_STREAM")) != 0 : false;
+  static const int cps = getenv("OBGPU_PCG_CTAS") ? atoi(getenv("OBGPU_PCG_CTAS")) : 8;
+  const int64_t slices = ((int64_t(a.r1) + 31) >> 5) - (a.r0 >> 5);
+  const unsigned g = pcg_grid(slices * 32, sm_count, cps);  // one warp per slice, grid-stride
+  if (stream) k_spmv_dot<true><<<g, PCG_BLOCK, 0, st>>>(a);
+  else k_spmv_dot<false><<<g, PCG_BLOCK, 0, st>>>(a);
   k_pcg_update<<<pcg_grid(n, sm_count), PCG_BLOCK, 0, st>>>(a, cur);
   k_pcg_dir<<<pcg_grid(n, sm_count), PCG_BLOCK, 0, st>>>(a, cur);
   return cudaGetLastError();

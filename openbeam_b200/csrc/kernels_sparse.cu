@@ -68,7 +68,10 @@ __global__ void __launch_bounds__(256) k_assemble_seg(int64_t nnz, const int32_t
 __global__ void __launch_bounds__(256) k_gather(int64_t n, const int32_t* __restrict__ src, const double* __restrict__ in,
                                                 double* __restrict__ out) {
   const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = in[src[i]];
+  if (i < n) {
+    const int32_t s = src[i];
+    out[i] = s >= 0 ? in[s] : 0.0;  // -1: padding entry of the SELL layout
+  }
 }
 
 __global__ void __launch_bounds__(256) k_load_vector(int64_t nf, int64_t nb, const int32_t* __restrict__ fseg_ptr,

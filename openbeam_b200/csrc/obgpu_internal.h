@@ -109,8 +109,11 @@ struct TinyProgram {
 struct SparsePlan {
   bool valid = false;
   std::vector<int32_t> seg_ptr, seg_src;      // [nnz_tot+1], [T_tot]: K slot <- ELEM_K entries (elem*21+cid, -1 = zero)
-  std::vector<int32_t> ff_rowptr, ff_col, ff_src;  // K_ff, full symmetric CSR over global free indices; src = K slot
+  // K_ff, full symmetric over global free indices, in SELL-32 order (see build_sparse_plan): sl_ptr[nf_tot/32 + 1]
+  // slice offsets, ff_col / ff_src (K slot, -1 = padding) per stored entry; ff_rowptr is scratch of the builder
+  std::vector<int32_t> ff_rowptr, ff_col, ff_src, sl_ptr;
   std::vector<int32_t> ff_diag;               // [nf_tot] position of the diagonal entry inside ff_col/ff_src
+  int64_t ff_nnz = 0;                         // structural entries of K_ff (without padding)
   std::vector<int32_t> bf_rowptr, bf_col, bf_src;  // K_bf: rows = global bounded index, cols = global free index
   // load vector gather: target t < nf_tot -> F_f[t]; t >= nf_tot -> Eq[t - nf_tot] (equivalent loads on bounded DOFs)
   // src >= 0: ELOAD_G entry (multimap position*6 + k); src < 0: nodal load -(l+1)

@@ -91,6 +91,48 @@ int build_sparse_plan(const HostBatch& hb, const Symbolic& sym, SparsePlan& P, s
       err = "free DOF without a diagonal entry in K";
       return OBGPU_EINVAL;
     }
+  // ---- K_ff for SpMV: SELL-32 (sliced ELLPACK).  Slice = 32 consecutive rows, entries column-major inside the
+  // slice (entry k of row r at sl_ptr[r/32] + 32 k + r%32) and padded to the slice's longest row with
+  // (col = own row, value 0): one warp per slice reads 256 contiguous bytes of values per step and the k loop has
+  // no row-pointer dependency, so all of a row's loads are in flight together.  Order inside a row = CSR order.
+  {
+    const int64_t nsl = (nf + 31) / 32;
+    P.sl_ptr.assign(nsl + 1, 0);
+    for (int64_t sl = 0; sl < nsl; sl++) {
+      int32_t w = 0;
+      for (int64_t r = sl * 32; r < std::min<int64_t>(nf, sl * 32 + 32); r++) w = std::max(w, P.ff_rowptr[r + 1] - P.ff_rowptr[r]);
+      const int64_t next = int64_t(P.sl_ptr[sl]) + int64_t(w) * 32;
+      if (next >= INT32_MAX) {
+        err = "K_ff too large for 32-bit SELL offsets";
+        return OBGPU_EUNSUPPORTED;
+      }
+      P.sl_ptr[sl + 1] = int32_t(next);
+    }
+    std::vector<int32_t> col(P.sl_ptr[nsl]), src(P.sl_ptr[nsl], -1), diag(nf, -1);
+    for (int64_t sl = 0; sl < nsl; sl++) {
+      const int32_t base = P.sl_ptr[sl], w = (P.sl_ptr[sl + 1] - base) / 32;
+      for (int l = 0; l < 32; l++) {
+        const int64_t r = sl * 32 + l;
+        const int32_t a0 = r < nf ? P.ff_rowptr[r] : 0, len = r < nf ? P.ff_rowptr[r + 1] - a0 : 0;
+        for (int32_t k = 0; k < w; k++) {
+          const int32_t q = base + 32 * k + l;
+          if (k < len) {
+            col[q] = P.ff_col[a0 + k];
+            src[q] = P.ff_src[a0 + k];
+            if (a0 + k == P.ff_diag[r]) diag[r] = q;
+          } else {
+            col[q] = int32_t(std::min<int64_t>(r, nf - 1));
+          }
+        }
+      }
+    }
+    P.ff_nnz = int64_t(P.ff_col.size());
+    P.ff_col.swap(col);
+    P.ff_src.swap(src);
+    P.ff_diag.swap(diag);
+    P.ff_rowptr.clear();
+    P.ff_rowptr.shrink_to_fit();
+  }
   // ---- load vector gather lists ----
   const int64_t nt = nf + nb;
   std::vector<int32_t> cnt(nt + 1, 0);
