@@ -245,7 +245,9 @@ def ours_arm(args, rank, local_rank, world):
             "dtype": "f64", "data": "synthetic", "config": config_dict(args, world),
             "dof_per_s": value * N_DOF,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": TRAFFIC_BYTES_PER_LAUNCH, "kernel": "k_tiny_fused<6,128>",
+                         "traffic": None if TRAFFIC_BYTES_PER_CASE is None else TRAFFIC_BYTES_PER_CASE * L,
+                         "traffic_source": TRAFFIC_SOURCE,
+                         "kernel": "k_tiny_fused<NF=6, 5 CTAs/SM, node-blocked> (128 threads/CTA, thread per case)",
                          "kernel_ms": kern_avg_ms, "algorithmic_bytes_per_launch": ALG_BYTES_PER_CASE * L,
                          "peak_source": peak_src},
             "e2e": {"value": world * L * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes,
@@ -272,9 +274,10 @@ def ours_arm(args, rank, local_rank, world):
     return 0
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_tiny_fused launch at 1M cases, from the committed
-# `ncu --set full` capture (profiles/); None until a capture exists
-TRAFFIC_BYTES_PER_LAUNCH = None
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_tiny_fused launch, per case, from the committed
+# `ncu --set full` capture of the current kernel at 1M cases (56.06 MB read + 382.85 MB written)
+TRAFFIC_BYTES_PER_CASE = 438.9
+TRAFFIC_SOURCE = "profiles/r01e_ncu_full_k_tiny_fused_v5_summary.txt (1M-case launch, scaled per case)"
 
 
 def main():

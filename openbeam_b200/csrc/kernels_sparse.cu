@@ -19,18 +19,27 @@ __global__ void __launch_bounds__(256) k_elem_stiff(int64_t Etot, const uint2* _
                                                     const uint8_t* __restrict__ elem_type, const double* __restrict__ eai,
                                                     const double2* __restrict__ node_xy, const int32_t* __restrict__ elem_node0,
                                                     double* __restrict__ elem_k) {
+  // a lane's 21 values are a 168-byte record: staged per warp in shared memory (odd stride: conflict-free) and
+  // written as 32 consecutive doubles per instruction instead of 32 scattered 8-byte stores
+  __shared__ double stg[8][32 * ELEM_K];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (e >= Etot) return;
-  const uint2 nd = elem_nodes[e];
-  const int64_t n0 = elem_node0[e];
-  const double2 p0 = node_xy[n0 + nd.x], p1 = node_xy[n0 + nd.y];
-  const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
-  const ElemLocalK lk = elem_local_k(elem_type[e], eai[3 * e], eai[3 * e + 1], eai[3 * e + 2], g);
-  double ke[ELEM_K];
-  elem_global_k(lk, g, ke);
-  double* o = elem_k + e * ELEM_K;
+  if (e < Etot) {
+    const uint2 nd = elem_nodes[e];
+    const int64_t n0 = elem_node0[e];
+    const double2 p0 = node_xy[n0 + nd.x], p1 = node_xy[n0 + nd.y];
+    const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
+    const ElemLocalK lk = elem_local_k(elem_type[e], eai[3 * e], eai[3 * e + 1], eai[3 * e + 2], g);
+    double ke[ELEM_K];
+    elem_global_k(lk, g, ke);
 #pragma unroll
-  for (int k = 0; k < ELEM_K; k++) o[k] = ke[k];
+    for (int k = 0; k < ELEM_K; k++) stg[warp][lane * ELEM_K + k] = ke[k];
+  }
+  __syncwarp();
+  const int64_t e0 = e - lane;  // first element of this warp
+  const int cnt = int(min(int64_t(32), Etot - e0));
+  double* o = elem_k + e0 * ELEM_K;
+  for (int i = lane; i < cnt * ELEM_K; i += 32) o[i] = stg[warp][i];
 }
 
 __global__ void __launch_bounds__(256) k_elem_loads(int64_t ELtot, const int32_t* __restrict__ el_order,
@@ -96,8 +105,10 @@ __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __res
                                                 const int32_t* __restrict__ el_ptr, const int32_t* __restrict__ el_order,
                                                 const double* __restrict__ q, const double* __restrict__ dir,
                                                 const double* __restrict__ U_f, double* __restrict__ stress) {
+  __shared__ double stg[8][32 * 13];  // [lane][12] records, stride 13: conflict-free staging for coalesced stores
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (e >= Etot) return;
+  if (e < Etot) {
   const uint2 nd = elem_nodes[e];
   const int64_t n0 = elem_node0[e];
   const int type = elem_type[e];
@@ -121,13 +132,15 @@ __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __res
 #pragma unroll
     for (int k = 0; k < 6; k++) ext[k] += ex[k];
   }
-  double2* o = reinterpret_cast<double2*>(stress + e * 12);
-  o[0] = make_double2(-es[0] + ext[0], -es[1] + ext[1]);
-  o[1] = make_double2(0.0, 0.0);
-  o[2] = make_double2(0.0, -es[2] + ext[2]);
-  o[3] = make_double2(es[3] + ext[3], es[4] + ext[4]);
-  o[4] = make_double2(0.0, 0.0);
-  o[5] = make_double2(0.0, es[5] + ext[5]);
+  double* o = stg[warp] + lane * 13;
+  o[0] = -es[0] + ext[0]; o[1] = -es[1] + ext[1]; o[2] = 0.0; o[3] = 0.0; o[4] = 0.0; o[5] = -es[2] + ext[2];
+  o[6] = es[3] + ext[3];  o[7] = es[4] + ext[4];  o[8] = 0.0; o[9] = 0.0; o[10] = 0.0; o[11] = es[5] + ext[5];
+  }
+  __syncwarp();
+  const int64_t e0 = e - lane;
+  const int cnt = int(min(int64_t(32), Etot - e0));
+  double* g = stress + e0 * 12;
+  for (int i = lane; i < cnt * 12; i += 32) g[i] = stg[warp][(i / 12) * 13 + i % 12];
 }
 
 static inline unsigned nblk(int64_t n, int b = 256) { return unsigned((n + b - 1) / b); }
