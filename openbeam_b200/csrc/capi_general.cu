@@ -15,6 +15,7 @@ int ensure_device_batch(obgpu_ctx* c) {
   const Symbolic& sy = c->sym;
   cudaStream_t st = c->stream;
   OB_CUDA(c, c->d_node_xy.upload(hb.node_xy, st));
+  if (hb.has_rotz) OB_CUDA(c, c->d_node_rot.upload(hb.node_rotz, st));
   OB_CUDA(c, c->d_elem_nodes.upload(hb.elem_nodes, st));
   OB_CUDA(c, c->d_elem_type.upload(hb.elem_type, st));
   OB_CUDA(c, c->d_elem_EAI.upload(hb.elem_EAI, st));
@@ -89,13 +90,13 @@ static bool frame_kernel_fits(const obgpu_ctx* c) {
 int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   int rc = ensure_device_batch(c);
   if (rc != OBGPU_OK) return rc;
-  for (double v : c->sym.U_b)
-    if (v != 0.0)
-      return fail(c, OBGPU_EUNSUPPORTED, "non-zero prescribed displacements are not implemented on the GPU path yet");
-  if (c->hb.has_rotz) return fail(c, OBGPU_EUNSUPPORTED, "nodal rotated frames are not implemented on the GPU path yet");
+  bool any_ub = false;
+  for (double v : c->sym.U_b) any_ub |= v != 0.0;
   if (o.method != OBGPU_BATCHED_LDLT || !frame_kernel_fits(c)) {
     if (o.method == OBGPU_BATCHED_LDLT)
       return fail(c, OBGPU_EUNSUPPORTED, "structure too large for the batched LDLt kernel: use a PCG method");
+    if (any_ub)
+      return fail(c, OBGPU_EUNSUPPORTED, "non-zero prescribed displacements are not implemented on the PCG route yet");
     return solve_sparse(c, o);
   }
   const Symbolic& sy = c->sym;
@@ -117,6 +118,8 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   a.elem_type = c->d_elem_type.p; a.elem_EAI = c->d_elem_EAI.p;
   a.node_slot = c->d_node_slot.p; a.nload_slot = c->d_nload_slot.p; a.nload_val = c->d_nload_val.p;
   a.el_ptr = c->d_el_ptr.p; a.el_order = c->d_el_order.p; a.eload_q = c->d_eload_q.p; a.eload_dir = c->d_eload_dir.p;
+  a.U_b = any_ub ? c->d_Ub.p : nullptr;
+  a.node_rot = c->hb.has_rotz ? c->d_node_rot.p : nullptr;
   a.case_nl = c->has_case_nl ? c->d_case_nl.p : nullptr;
   a.case_q = c->has_case_q ? c->d_case_q.p : nullptr;
   a.case_eai = c->has_case_eai ? c->d_case_eai.p : nullptr;

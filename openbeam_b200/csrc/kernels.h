@@ -45,6 +45,8 @@ struct FrameArgs {
   const int32_t* el_order;      // [ELtot]
   const double* eload_q;        // [ELtot]
   const double* eload_dir;      // [3*ELtot]
+  const double* U_b;            // [nb_tot] prescribed displacements (nodal frames), or null when all are zero
+  const double* node_rot;       // [Ntot] nodal frame yaw (radians), or null when every node frame is the identity
   const double* case_nl;        // [L][NLtot] or null
   const double* case_q;         // [L][ELtot] or null
   const double* case_eai;       // [L][3*Etot] or null

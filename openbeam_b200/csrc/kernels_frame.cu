@@ -46,6 +46,51 @@ __device__ __forceinline__ void cid_pair(int cid, int& a, int& b) {
   }
 }
 
+// ---- general path: nodal rotated frames and non-zero prescribed displacements ----------------------
+// Compact element block -> full symmetric 6x6 over (end0 x,y,rz, end1 x,y,rz).
+__device__ __forceinline__ double ke_at(const double* ke, int a, int b) {
+  if (a > b) { const int t = a; a = b; b = t; }
+  if (b < 3) return ke[a == 0 ? b : a == 1 ? 2 + b : 5];
+  if (a >= 3) return ke[6 + (a == 3 ? b - 3 : a == 4 ? b - 1 : 5)];
+  return ke[12 + 3 * a + (b - 3)];
+}
+// assemble.cpp:144-179: K_ij <- T_i^T K_ij T_j on every 3x3 sub-block, T = nodal frame (a rotation about z by the
+// node's yaw: Q = [[c,-s,0],[s,c,0],[0,0,1]] on (x,y,rz)).  (ci,si)/(cj,sj) = cos/sin of end 0 / end 1.
+__device__ __forceinline__ void rotate_nodal(double* ke, double ci, double si, double cj, double sj) {
+  double B[3][3][3];  // [block K11,K22,K12][r][c]
+#pragma unroll
+  for (int r = 0; r < 3; r++)
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      B[0][r][c] = ke_at(ke, r, c);
+      B[1][r][c] = ke_at(ke, 3 + r, 3 + c);
+      B[2][r][c] = ke_at(ke, r, 3 + c);
+    }
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const double cl = k == 1 ? cj : ci, sl = k == 1 ? sj : si;  // left factor: node of the block's rows
+    const double cr = k == 0 ? ci : cj, sr = k == 0 ? si : sj;  // right factor: node of the block's columns
+#pragma unroll
+    for (int c = 0; c < 3; c++) {  // Q_l^T B
+      const double b0 = B[k][0][c], b1 = B[k][1][c];
+      B[k][0][c] = cl * b0 + sl * b1;
+      B[k][1][c] = -sl * b0 + cl * b1;
+    }
+#pragma unroll
+    for (int r = 0; r < 3; r++) {  // B Q_r
+      const double b0 = B[k][r][0], b1 = B[k][r][1];
+      B[k][r][0] = cr * b0 + sr * b1;
+      B[k][r][1] = -sr * b0 + cr * b1;
+    }
+  }
+  ke[0] = B[0][0][0]; ke[1] = B[0][0][1]; ke[2] = B[0][0][2]; ke[3] = B[0][1][1]; ke[4] = B[0][1][2]; ke[5] = B[0][2][2];
+  ke[6] = B[1][0][0]; ke[7] = B[1][0][1]; ke[8] = B[1][0][2]; ke[9] = B[1][1][1]; ke[10] = B[1][1][2]; ke[11] = B[1][2][2];
+#pragma unroll
+  for (int r = 0; r < 3; r++)
+#pragma unroll
+    for (int c = 0; c < 3; c++) ke[12 + 3 * r + c] = B[2][r][c];
+}
+
 // Flattened trailing triangle of one column step (see stage B): entry e = r*32 + lane is (p, q), 1 <= q <= p, rows p
 // in order, i.e. the entries of rows p <= m are exactly e < m(m+1)/2.  Byte offsets from the pivot (j, j):
 //   V(j+p, j+q) at (p*(W-1) + q)*8,   V(j+p, j) at p*(W-1)*8,   V(j+q, j) at q*(W-1)*8.
@@ -99,7 +144,9 @@ __device__ __forceinline__ void trailing_update(char* bj, const TriMap<MAXR>& tm
 #undef OB_ST
 }
 
-template <int MAXR>
+// GEN: the general path (nodal rotated frames and/or non-zero prescribed displacements) is a separate
+// instantiation so that its extra state never costs the common kernel a register.
+template <int MAXR, bool GEN>
 __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_fused(FrameArgs a, int doubles_per_warp) {
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -138,7 +185,10 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
     __syncwarp();
     const double* eai_base = a.case_eai ? a.case_eai + c * 3 * a.Etot : a.elem_EAI;
     const double* q_base = a.case_q ? a.case_q + c * a.ELtot : a.eload_q;
-    // ---- stage A ----
+    // ---- stage A ----  (pass 1 only with prescribed displacements: F_f -= K_fb U_b, solver_static.cpp:37-43)
+    const double* Ub = GEN && a.U_b ? a.U_b + m.b0 : nullptr;
+    const double* node_rot = GEN ? a.node_rot : nullptr;
+    for (int pass = 0; pass < (Ub ? 2 : 1); pass++) {
     for (int eb = 0; eb < m.E; eb += CHUNK) {
       const int cnt = min(CHUNK, m.E - eb);
       if (lane < cnt) {
@@ -150,23 +200,44 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
         const ElemLocalK lk = elem_local_k(type, eai_base[3 * e], eai_base[3 * e + 1], eai_base[3 * e + 2], g);
         double ke[ELEM_K];
         elem_global_k(lk, g, ke);
-        double* st = stage + lane * STAGE_D;
-#pragma unroll
-        for (int k = 0; k < ELEM_K; k++) st[k] = ke[k];
-        double gsum[6] = {0, 0, 0, 0, 0, 0};
-        for (int j = a.el_ptr[e]; j < a.el_ptr[e + 1]; j++) {
-          const int sl = a.el_order[j];
-          double gl[6], ex[6];
-          uniform_load(type, g, q_base[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
-#pragma unroll
-          for (int k = 0; k < 6; k++) gsum[k] += gl[k];
+        if (node_rot) {
+          const double r0 = node_rot[m.n0 + nd.x], r1 = node_rot[m.n0 + nd.y];
+          if (r0 != 0.0 || r1 != 0.0) rotate_nodal(ke, cos(r0), sin(r0), cos(r1), sin(r1));
         }
-#pragma unroll
-        for (int k = 0; k < 6; k++) st[ELEM_K + k] = gsum[k];
+        double* st = stage + lane * STAGE_D;
+        int32_t sl6[6];
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-          slots[lane * 6 + k] = a.node_slot[3 * (m.n0 + nd.x) + k];
-          slots[lane * 6 + 3 + k] = a.node_slot[3 * (m.n0 + nd.y) + k];
+          sl6[k] = a.node_slot[3 * (m.n0 + nd.x) + k];
+          sl6[3 + k] = a.node_slot[3 * (m.n0 + nd.y) + k];
+        }
+        double gsum[6] = {0, 0, 0, 0, 0, 0};
+        if (pass == 0) {
+#pragma unroll
+          for (int k = 0; k < ELEM_K; k++) st[k] = ke[k];
+          for (int j = a.el_ptr[e]; j < a.el_ptr[e + 1]; j++) {
+            const int sl = a.el_order[j];
+            double gl[6], ex[6];
+            uniform_load(type, g, q_base[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
+#pragma unroll
+            for (int k = 0; k < 6; k++) gsum[k] += gl[k];
+          }
+        } else {  // free rows of the element: -sum over its bounded DOFs of K(a,b) U_b(b)
+#pragma unroll
+          for (int b = 0; b < 6; b++) {
+            const int32_t tb = sl6[b];
+            if (tb < 0 && tb != SLOT_NONE) {
+              const double ub = Ub[-tb - 1];
+#pragma unroll
+              for (int r = 0; r < 6; r++)
+                if (sl6[r] >= 0) gsum[r] -= ke_at(ke, r, b) * ub;
+            }
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+          st[ELEM_K + k] = gsum[k];
+          slots[lane * 6 + k] = sl6[k];
         }
       }
       __syncwarp();
@@ -177,7 +248,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
         const int32_t* sl = slots + ee * 6;
         off = -1;
         v = 0.0;
-        if (lane < STAGE_D) {
+        if (lane < STAGE_D && (pass == 0 || lane >= ELEM_K)) {
           v = stage[ee * STAGE_D + lane];
           const int32_t fi = sl[pa];
           if (lane < ELEM_K) {
@@ -201,8 +272,24 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
         __syncwarp();
       }
     }
-    if (a.F_f)
-      for (int i = lane; i < nf; i += 32) a.F_f[c * a.nf_tot + m.f0 + i] = Ff[i];
+    if (pass == 0) {
+      if (node_rot) {  // assemble.cpp:349-435: (Fx,Fy) of a rotated node's FREE DOFs -> nodal frame (bounded ones count as 0)
+        for (int n = lane; n < m.N; n += 32) {
+          const double r = node_rot[m.n0 + n];
+          if (r != 0.0) {
+            const int32_t sx = a.node_slot[3 * (m.n0 + n)], sy = a.node_slot[3 * (m.n0 + n) + 1];
+            const double fx = sx >= 0 ? Ff[sx] : 0.0, fy = sy >= 0 ? Ff[sy] : 0.0;
+            const double cr = cos(r), sr = sin(r);
+            if (sx >= 0) Ff[sx] = cr * fx + sr * fy;
+            if (sy >= 0) Ff[sy] = -sr * fx + cr * fy;
+          }
+        }
+        __syncwarp();
+      }
+      if (a.F_f)
+        for (int i = lane; i < nf; i += 32) a.F_f[c * a.nf_tot + m.f0 + i] = Ff[i];
+    }
+    }  // pass
     // ---- stage B: banded LDL^T (row i holds columns i-hb..i at band[i*W + (j-i+hb)]) ----
     // Right-looking, one column j per step, on the UNSCALED factor V = L D (V(i,j) = L(i,j) D(j)): the column is
     // never rewritten, the only division is the reciprocal pivot (kept in Dinv), and L y = b rides along
@@ -306,22 +393,53 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
         const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
         const ElemLocalK lk = elem_local_k(type, eai_base[3 * e], eai_base[3 * e + 1], eai_base[3 * e + 2], g);
         double ug[6], es[6];
+        int32_t sl6[6];
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-          const int32_t t0 = a.node_slot[3 * (m.n0 + nd.x) + k], t1 = a.node_slot[3 * (m.n0 + nd.y) + k];
-          slots[lane * 6 + k] = t0;
-          slots[lane * 6 + 3 + k] = t1;
-          hasb |= (t0 < 0 && t0 != SLOT_NONE) || (t1 < 0 && t1 != SLOT_NONE);
-          ug[k] = t0 >= 0 ? Ff[t0] : 0.0;
-          ug[3 + k] = t1 >= 0 ? Ff[t1] : 0.0;
+          sl6[k] = a.node_slot[3 * (m.n0 + nd.x) + k];
+          sl6[3 + k] = a.node_slot[3 * (m.n0 + nd.y) + k];
+        }
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+          const int32_t t = sl6[k];
+          slots[lane * 6 + k] = t;
+          hasb |= t < 0 && t != SLOT_NONE;
+          // postproc_stress.cpp:86-119: U as solved (nodal frames are NOT undone there, quirk Q6), U_b on bounded DOFs
+          ug[k] = t >= 0 ? Ff[t] : (Ub && t != SLOT_NONE) ? Ub[-t - 1] : 0.0;
         }
         elem_end_forces(lk, g, ug, es);
-        sgf[lane * 6 + 0] = g.c * es[0] - g.s * es[1];
-        sgf[lane * 6 + 1] = g.s * es[0] + g.c * es[1];
-        sgf[lane * 6 + 2] = es[2];
-        sgf[lane * 6 + 3] = g.c * es[3] - g.s * es[4];
-        sgf[lane * 6 + 4] = g.s * es[3] + g.c * es[4];
-        sgf[lane * 6 + 5] = es[5];
+        if (!Ub && !node_rot) {  // K_bf U_f of this element = its global end forces (U_b = 0, identity node frames)
+          sgf[lane * 6 + 0] = g.c * es[0] - g.s * es[1];
+          sgf[lane * 6 + 1] = g.s * es[0] + g.c * es[1];
+          sgf[lane * 6 + 2] = es[2];
+          sgf[lane * 6 + 3] = g.c * es[3] - g.s * es[4];
+          sgf[lane * 6 + 4] = g.s * es[3] + g.c * es[4];
+          sgf[lane * 6 + 5] = es[5];
+        } else {
+          // general reactions, solver_static.cpp:196-200: bounded row r of K_bf U_f + K_bb U_b with the element's
+          // block in nodal frames; K_bb holds only its upper triangle in the reference and is multiplied as a
+          // general matrix, so a bounded column c contributes to row r only when c >= r
+          double ke[ELEM_K];
+          elem_global_k(lk, g, ke);
+          if (node_rot) {
+            const double r0 = node_rot[m.n0 + nd.x], r1 = node_rot[m.n0 + nd.y];
+            if (r0 != 0.0 || r1 != 0.0) rotate_nodal(ke, cos(r0), sin(r0), cos(r1), sin(r1));
+          }
+#pragma unroll
+          for (int r = 0; r < 6; r++) {
+            double acc = 0.0;
+            const int32_t tr = sl6[r];
+            if (tr < 0 && tr != SLOT_NONE) {
+#pragma unroll
+              for (int b = 0; b < 6; b++) {
+                const int32_t tb = sl6[b];
+                if (tb >= 0) acc += ke_at(ke, r, b) * Ff[tb];
+                else if (Ub && tb != SLOT_NONE && -tb >= -tr) acc += ke_at(ke, r, b) * Ub[-tb - 1];
+              }
+            }
+            sgf[lane * 6 + r] = acc;
+          }
+        }
         if (a.stress) {
           double ext[6] = {0, 0, 0, 0, 0, 0};
           for (int j = a.el_ptr[e]; j < a.el_ptr[e + 1]; j++) {
@@ -358,12 +476,12 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
   }
 }
 
-template <int MAXR>
-static cudaError_t launch_frame_r(const FrameArgs& a, int sm_count, cudaStream_t st) {
+template <int MAXR, bool GEN>
+static cudaError_t launch_frame_rg(const FrameArgs& a, int sm_count, cudaStream_t st) {
   const size_t per_warp = frame_smem_per_warp(a.max_band, a.max_nf, a.max_nb);
   const size_t smem = per_warp * FRAME_WARPS;
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-  auto kern = k_frame_fused<MAXR>;
+  auto kern = k_frame_fused<MAXR, GEN>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
   if (e != cudaSuccess) return e;
   int per_sm = 1;
@@ -377,6 +495,12 @@ static cudaError_t launch_frame_r(const FrameArgs& a, int sm_count, cudaStream_t
   if (grid < 1) grid = 1;
   kern<<<unsigned(grid), FRAME_WARPS * 32, smem, st>>>(a, int(per_warp / 8));
   return cudaGetLastError();
+}
+
+template <int MAXR>
+static cudaError_t launch_frame_r(const FrameArgs& a, int sm_count, cudaStream_t st) {
+  if (a.U_b || a.node_rot) return launch_frame_rg<MAXR, true>(a, sm_count, st);
+  return launch_frame_rg<MAXR, false>(a, sm_count, st);
 }
 
 cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st) {

@@ -178,6 +178,22 @@ int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want
         const int32_t k = sym.dof_index[6 * (n0 + hb.nload_node[l]) + hb.nload_dof[l]];
         sym.nload_slot[l] = k < 0 ? SLOT_NONE : sym.dof_type[k0 + k];
       }
+      // assemble.cpp:349-435: prescribed displacements of a node with a rotated frame go to nodal coordinates,
+      // U' = R^T (Ux, Uy, .) with only the BOUNDED components taken (free ones count as 0).  Input preparation of
+      // BuildProblemInfo::U_b, once per topology, a handful of supports.
+      if (hb.has_rotz)
+        for (int64_t i = 0; i < N; i++) {
+          const double r = hb.node_rotz[n0 + i];
+          if (r == 0.0) continue;
+          const int32_t tx = sym.node_slot[3 * (n0 + i)], ty = sym.node_slot[3 * (n0 + i) + 1];
+          const bool bx = tx < 0 && tx != SLOT_NONE, by = ty < 0 && ty != SLOT_NONE;
+          if (!bx && !by) continue;
+          const size_t ub0 = size_t(sym.bnd_off[s]);
+          const double ux = bx ? sym.U_b[ub0 + (-tx - 1)] : 0.0, uy = by ? sym.U_b[ub0 + (-ty - 1)] : 0.0;
+          const double cr = std::cos(r), sr = std::sin(r);
+          if (bx) sym.U_b[ub0 + (-tx - 1)] = cr * ux + sr * uy;
+          if (by) sym.U_b[ub0 + (-ty - 1)] = -sr * ux + cr * uy;
+        }
       const int64_t l0 = hb.eload_off[s], EL = hb.eload_off[s + 1] - l0;
       order.resize(EL);
       for (int64_t i = 0; i < EL; i++) order[i] = int32_t(i);

@@ -52,6 +52,45 @@ def test_fixture_batch(ctx):
     assert ctx.timings()["launches"] == 1
 
 
+def settlement_cases():
+    """Non-zero prescribed displacements (support settlement / imposed rotation), with and without nodal rotated
+    frames, incl. a support whose DOFs are only partly constrained (K_bb upper-triangle quirk Q1 is exercised by
+    nodes with several prescribed DOFs)."""
+    from openbeam_b200.structure import build_structure
+    sec = fixtures.IPE200
+    L, H = 4.0, 2.0
+    el = [("BEAM2D_RR", 0, 1, "IPE200"), ("BEAM2D_RR", 1, 2, "IPE200"), ("BEAM2D_RR", 2, 3, "IPE200")]
+    out = []
+    for rot in (None, 30.0, -20.0):
+        n3 = (L, 0) if rot is None else (L, 0, rot)
+        nodes = [(0, 0), (0, H), (L, H), n3]
+        cons = [(0, "DX", 1e-3), (0, "DY", -2e-3), (0, "RZ", 5e-4), (3, "DX", 0.0), (3, "DY", -5e-3), (3, "RZ", -1e-3)]
+        out.append(build_structure(nodes, el, sec, cons, [(1, "DX", 5e3)], [(1, 9810.0, fixtures.DOWN)]))
+        cons = [(0, "DXDYRZ"), (3, "DY", -4e-3)]  # slider with a settlement
+        out.append(build_structure(nodes, el, sec, cons, [(2, "DY", -1e4)], [(1, 9810.0, fixtures.DOWN)]))
+    # propped cantilever, prescribed end rotation and a mid support settlement
+    nodes = [(0, 0), (2.0, 0), (4.5, 0, 15.0)]
+    el = [("BEAM2D_RR", 0, 1, "IPE200"), ("BEAM2D_RA", 1, 2, "IPE200")]
+    cons = [(0, "DXDYRZ"), (1, "DY", -3e-3), (2, "DY", 1e-3)]
+    out.append(build_structure(nodes, el, sec, cons, [], [(0, 5e3, fixtures.DOWN), (1, 5e3, fixtures.DOWN)]))
+    return out
+
+
+def test_rotated_frames_and_settlements(ctx):
+    """nodal rotated frames (assemble.cpp:144-179,349-435) and U_b != 0 (solver_static.cpp:37-43,196-198)
+    on the GPU, against the oracle; the tilted reference fixtures ride in the same batch as plain ones."""
+    sts = [fixtures.ALL[k]() for k in fixtures.ALL] + settlement_cases()
+    check_batch(ctx, sts)
+    # U_b as BuildProblemInfo holds it (nodal coordinates)
+    Ub = ctx.download(obgpu.RES_UB)
+    bo = ctx.offsets(obgpu.OFF_BOUNDED)
+    for s, st in enumerate(sts):
+        o = OracleProblem(st).solveStatic()
+        assert relerr(Ub[bo[s]:bo[s + 1]], o.U_b) <= 1e-15
+    # a single structure with U_b != 0 must not take the thread-per-case kernel's U_b = 0 shortcut
+    check_batch(ctx, [settlement_cases()[0]])
+
+
 def test_random_frames(ctx):
     """Config C3 sample: 300 random frames (10-60 elements, mixed RR/RA/AR/AA beams)."""
     check_batch(ctx, [workloads.c3_frame(i) for i in range(300)])
