@@ -34,6 +34,9 @@ enum {
 
 /* element types: CElementBeam_2D_{RR,RA,AR,AA}.cpp */
 enum { OBGPU_BEAM2D_RR = 0, OBGPU_BEAM2D_RA = 1, OBGPU_BEAM2D_AR = 2, OBGPU_BEAM2D_AA = 3 };
+/* element loads (libopenbeam/include/openbeam/loads.h): CLoadDistributedUniform, CLoadDistributedTriangular (RR only),
+ * CLoadConcentratedForce (RR only, perpendicular to the beam), CLoadConstTemperature */
+enum { OBGPU_LOAD_UNIFORM = 0, OBGPU_LOAD_TRIANGULAR = 1, OBGPU_LOAD_CONCENTRATED = 2, OBGPU_LOAD_TEMPERATURE = 3 };
 /* DoF_index, CFiniteElementProblem.h:53-67 */
 enum { OBGPU_DX = 0, OBGPU_DY = 1, OBGPU_DZ = 2, OBGPU_RX = 3, OBGPU_RY = 4, OBGPU_RZ = 5 };
 
@@ -60,14 +63,17 @@ typedef struct obgpu_batch_desc {
   const uint32_t* nload_node; /* [NLtot] */
   const uint8_t* nload_dof;   /* [NLtot] */
   const double* nload_val;    /* [NLtot] addLoadAtDOF values (m_loads_at_each_dof)                */
-  const uint32_t* eload_elem; /* [ELtot] element index (local) carrying a DISTRIB_UNIFORM load    */
-  const double* eload_q;      /* [ELtot] q (N/m)                                                  */
-  const double* eload_dir;    /* [3*ELtot] unit direction (CLoadDistributedUniform::dir)          */
+  const uint32_t* eload_elem; /* [ELtot] element index (local) carrying the load (m_loads_on_beams) */
+  const double* eload_q;      /* [ELtot] first parameter: q (N/m) | q_ini | P (N) | temperature increment */
+  const double* eload_dir;    /* [3*ELtot] unit direction (CLoadDistributedUniform::dir); unused for TEMPERATURE */
   /* load cases: case-major overrides of the value arrays above (NULL = use the base values) */
   int64_t n_cases;              /* L >= 1 */
   const double* case_nload_val; /* NULL or [L][NLtot] */
   const double* case_eload_q;   /* NULL or [L][ELtot] */
   const double* case_elem_EAI;  /* NULL or [L][3*Etot] per-case section sweep */
+  /* element-load kinds other than DISTRIB_UNIFORM (both NULL = every load is uniform) */
+  const uint8_t* eload_type;    /* NULL or [ELtot] OBGPU_LOAD_*                                          */
+  const double* eload_q2;       /* NULL or [ELtot] second parameter: q_end (TRIANGULAR), dist (CONCENTRATED) */
 } obgpu_batch_desc;
 
 enum { OBGPU_BATCHED_LDLT = 0, OBGPU_PCG_JACOBI = 1, OBGPU_PCG_BJ3 = 2, OBGPU_PCG_IC0 = 3 };

@@ -120,6 +120,58 @@ __device__ __forceinline__ void uniform_load(int type, const ElemGeom& g, double
   uniform_load_p(type, g, q, load_proj(g, dx, dy), gl, ex);
 }
 
+// Every element load the reference has, same outputs as uniform_load_p:
+//   OBGPU_LOAD_UNIFORM      p1 = q                       CLoadDistributedUniform.cpp:33-159 (all four beam types)
+//   OBGPU_LOAD_TRIANGULAR   p1 = q_ini, p2 = q_end       CLoadDistributedTriangular.cpp:31-169 (RR only)
+//   OBGPU_LOAD_CONCENTRATED p1 = P, p2 = distance from end 0   CLoadConcentratedForce.cpp:31-154 (RR, perpendicular only)
+//   OBGPU_LOAD_TEMPERATURE  p1 = temperature increment   CLoadConstTemperature.cpp:31-93 (alpha = 12e-6 hard-wired there)
+// EA = E*A of the element (temperature only).  Unsupported (load, element) pairs are refused by the host at upload,
+// like the reference throws.
+__device__ __forceinline__ void elem_load_p(int ltype, int etype, const ElemGeom& g, double p1, double p2, const LoadProj& pr,
+                                            double EA, double gl[6], double ex[6]) {
+  if (ltype == OBGPU_LOAD_UNIFORM) {
+    uniform_load_p(etype, g, p1, pr, gl, ex);
+    return;
+  }
+  const double L = g.L;
+  double f1x = 0.0, f2x = 0.0, f1y = 0.0, f2y = 0.0, m1 = 0.0, m2 = 0.0;
+  if (ltype == OBGPU_LOAD_TEMPERATURE) {
+    const double N = EA * 12e-6 * p1;  // stress N = -N at both faces; loads -N*axis at end 0, +N*axis at end 1
+    ex[0] = -N; ex[1] = 0.0; ex[2] = 0.0;
+    ex[3] = -N; ex[4] = 0.0; ex[5] = 0.0;
+    gl[0] = -N * g.c; gl[1] = -N * g.s; gl[2] = 0.0;
+    gl[3] = N * g.c;  gl[4] = N * g.s;  gl[5] = 0.0;
+    return;
+  }
+  if (ltype == OBGPU_LOAD_TRIANGULAR) {
+    const double q0_t = p1 * pr.plong, q1_t = p2 * pr.plong, q0_n = p1 * pr.pperp, q1_n = p2 * pr.pperp;
+    f1y = L * (q0_n * 0.5 + (q1_n - q0_n) * 3. / 20.);
+    m1 = +L * L * (q0_n * 1. / 12. + (q1_n - q0_n) * 1. / 30.);
+    f2y = L * (q0_n * 0.5 + (q1_n - q0_n) * 7. / 20.);
+    m2 = -L * L * (q0_n * 1. / 12. + (q1_n - q0_n) * 1. / 20.);
+    f1x = -0.5 * L * (q0_t + (q1_t - q0_t) / 3.0);
+    f2x = -0.5 * L * (q0_t + 2.0 * (q1_t - q0_t) / 3.0);
+  } else {  // OBGPU_LOAD_CONCENTRATED
+    const double P_n = p1 * pr.pperp;
+    const double a = p2, b = L - a, a2 = a * a, b2 = b * b, L2 = L * L, L3 = L * L2;
+    f1y = P_n * (b2 / L3) * (3 * a + b);
+    m1 = P_n * a * b2 / L2;
+    f2y = P_n * (a2 / L3) * (a + 3 * b);
+    m2 = -P_n * a2 * b / L2;
+  }
+  ex[0] = -f1x; ex[1] = -f1y; ex[2] = -m1;
+  ex[3] = f2x;  ex[4] = f2y;  ex[5] = m2;
+  gl[0] = -(g.c * f1x - g.s * f1y); gl[1] = -(g.s * f1x + g.c * f1y); gl[2] = -m1;
+  gl[3] = -(g.c * f2x - g.s * f2y); gl[4] = -(g.s * f2x + g.c * f2y); gl[5] = -m2;
+}
+__device__ __forceinline__ void elem_load(int ltype, int etype, const ElemGeom& g, double p1, double p2, double dx, double dy,
+                                          double EA, double gl[6], double ex[6]) {
+  LoadProj pr;
+  pr.plong = 0.0; pr.pperp = 0.0;
+  if (ltype != OBGPU_LOAD_TEMPERATURE) pr = load_proj(g, dx, dy);
+  elem_load_p(ltype, etype, g, p1, p2, pr, EA, gl, ex);
+}
+
 // postproc_stress.cpp:86-146 : raw end forces es = K_local * U_local (before the face-0 sign flip).
 // ug = global (ux,uy,rz) of end 0 then end 1.  es = (N,Vy,Mz) at end 0 then end 1.
 __device__ __forceinline__ void elem_end_forces(const ElemLocalK& k, const ElemGeom& g, const double ug[6], double es[6]) {

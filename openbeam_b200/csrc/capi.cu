@@ -1,5 +1,6 @@
 // capi.cu — extern "C" surface of libobgpu (include/obgpu.h): context, upload, symbolic, solve, download.
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 
@@ -152,7 +153,16 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   if (NL) { copy_vec(hb.nload_node, d->nload_node, NL); copy_vec(hb.nload_dof, d->nload_dof, NL); copy_vec(hb.nload_val, d->nload_val, NL); }
   if (EL) {
     copy_vec(hb.eload_elem, d->eload_elem, EL); copy_vec(hb.eload_q, d->eload_q, EL); copy_vec(hb.eload_dir, d->eload_dir, 3 * EL);
-    for (int64_t i = 0; i < EL; i++) {  // ASSERT_NEAR_(|dir|^2, 1, 1e-6), CLoadDistributedUniform.cpp:37-38
+    hb.eload_type.assign(EL, OBGPU_LOAD_UNIFORM);
+    hb.eload_q2.assign(EL, 0.0);
+    if (d->eload_type) copy_vec(hb.eload_type, d->eload_type, EL);
+    if (d->eload_q2) copy_vec(hb.eload_q2, d->eload_q2, EL);
+    for (int64_t i = 0; i < EL; i++) {
+      const int lt = hb.eload_type[i];
+      if (lt > OBGPU_LOAD_TEMPERATURE) return fail(c, OBGPU_EINVAL, "unknown element load type");
+      if (lt != OBGPU_LOAD_UNIFORM) hb.has_load_kinds = true;
+      if (lt == OBGPU_LOAD_TEMPERATURE) continue;  // no direction (CLoadConstTemperature.cpp)
+      // ASSERT_NEAR_(|dir|^2, 1, 1e-6), CLoadDistributedUniform.cpp:37-38
       const double* v = &hb.eload_dir[3 * i];
       const double n2 = v[0] * v[0] + v[1] * v[1] + v[2] * v[2];
       if (!(n2 > 1 - 1e-6 && n2 < 1 + 1e-6)) return fail(c, OBGPU_EINVAL, "element load direction is not a unit vector");
@@ -163,6 +173,30 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
       if (hb.elem_EAI[3 * e + k] == 1.7976931348623157e308) return fail(c, OBGPU_EINVAL, "Uninitialized parameter E/A/Iz");
     if (hb.elem_type[e] > OBGPU_BEAM2D_AA) return fail(c, OBGPU_EINVAL, "unknown element type");
   }
+  // (load, element) pairs the reference throws on (CLoadDistributedTriangular.cpp:93-125,
+  // CLoadConcentratedForce.cpp:77-84,114-116): refused here, at upload
+  if (hb.has_load_kinds)
+    for (int64_t s = 0; s < S; s++)
+      for (int64_t l = hb.eload_off[s]; l < hb.eload_off[s + 1]; l++) {
+        const int lt = hb.eload_type[l];
+        if (lt != OBGPU_LOAD_TRIANGULAR && lt != OBGPU_LOAD_CONCENTRATED) continue;
+        const int64_t e = hb.elem_off[s] + hb.eload_elem[l];
+        if (hb.eload_elem[l] >= uint32_t(hb.elem_off[s + 1] - hb.elem_off[s])) continue;  // reported by the symbolic phase
+        if (hb.elem_type[e] != OBGPU_BEAM2D_RR)
+          return fail(c, OBGPU_EINVAL, lt == OBGPU_LOAD_TRIANGULAR
+                                           ? "Unsupported element type for load 'CLoadDistributedTriangular'"
+                                           : "Unsupported element type for load 'CLoadConcentratedForce'");
+        if (lt == OBGPU_LOAD_CONCENTRATED) {
+          const int64_t n0 = hb.node_off[s];
+          const double* p0 = &hb.node_xy[2 * (n0 + hb.elem_nodes[2 * e])];
+          const double* p1 = &hb.node_xy[2 * (n0 + hb.elem_nodes[2 * e + 1])];
+          const double ax = p1[0] - p0[0], ay = p1[1] - p0[1], len = std::sqrt(ax * ax + ay * ay);
+          const double plong = (ax * hb.eload_dir[3 * l] + ay * hb.eload_dir[3 * l + 1]) / len;
+          if (std::fabs(plong) > 1e-5) return fail(c, OBGPU_EINVAL, "Only perpendicular forces supported by now!");
+          if (hb.eload_q2[l] < 0 || len - hb.eload_q2[l] < 0)
+            return fail(c, OBGPU_EINVAL, "Error: Point of application is out of the beam!");
+        }
+      }
   hb.L = d->n_cases < 1 ? 1 : d->n_cases;
   c->uploaded = true;
   c->sym = Symbolic();

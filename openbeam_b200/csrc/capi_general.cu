@@ -16,6 +16,10 @@ int ensure_device_batch(obgpu_ctx* c) {
   cudaStream_t st = c->stream;
   OB_CUDA(c, c->d_node_xy.upload(hb.node_xy, st));
   if (hb.has_rotz) OB_CUDA(c, c->d_node_rot.upload(hb.node_rotz, st));
+  if (hb.has_load_kinds) {
+    OB_CUDA(c, c->d_eload_type.upload(hb.eload_type, st));
+    OB_CUDA(c, c->d_eload_q2.upload(hb.eload_q2, st));
+  }
   OB_CUDA(c, c->d_elem_nodes.upload(hb.elem_nodes, st));
   OB_CUDA(c, c->d_elem_type.upload(hb.elem_type, st));
   OB_CUDA(c, c->d_elem_EAI.upload(hb.elem_EAI, st));
@@ -118,6 +122,8 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   a.elem_type = c->d_elem_type.p; a.elem_EAI = c->d_elem_EAI.p;
   a.node_slot = c->d_node_slot.p; a.nload_slot = c->d_nload_slot.p; a.nload_val = c->d_nload_val.p;
   a.el_ptr = c->d_el_ptr.p; a.el_order = c->d_el_order.p; a.eload_q = c->d_eload_q.p; a.eload_dir = c->d_eload_dir.p;
+  a.eload_type = c->hb.has_load_kinds ? c->d_eload_type.p : nullptr;
+  a.eload_q2 = c->hb.has_load_kinds ? c->d_eload_q2.p : nullptr;
   a.U_b = any_ub ? c->d_Ub.p : nullptr;
   a.node_rot = c->hb.has_rotz ? c->d_node_rot.p : nullptr;
   a.case_nl = c->has_case_nl ? c->d_case_nl.p : nullptr;

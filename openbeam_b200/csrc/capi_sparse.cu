@@ -64,6 +64,8 @@ static SparseDev sparse_dev(obgpu_ctx* c, int64_t k /* K copy */) {
   d.elem_node0 = c->d_elem_node0.p; d.elem_f0 = c->d_elem_f0.p;
   d.node_slot = c->d_node_slot.p; d.el_ptr = c->d_el_ptr.p; d.el_order = c->d_el_order.p;
   d.eload_elem_g = c->d_eload_elem_g.p; d.eload_dir = c->d_eload_dir.p;
+  d.eload_type = c->hb.has_load_kinds ? c->d_eload_type.p : nullptr;
+  d.eload_q2 = c->hb.has_load_kinds ? c->d_eload_q2.p : nullptr;
   d.seg_ptr = c->d_seg_ptr.p; d.seg_src = c->d_seg_src.p;
   d.sl_ptr = c->d_sl_ptr.p; d.ff_col = c->d_ff_col.p; d.ff_src = c->d_ff_src.p; d.ff_diag = c->d_ff_diag.p;
   d.bf_rowptr = c->d_bf_rowptr.p; d.bf_col = c->d_bf_col.p; d.bf_src = c->d_bf_src.p;
@@ -100,7 +102,8 @@ int assemble_general(obgpu_ctx* c) {
     SparseDev d = sparse_dev(c, 0);
     const double* nl = c->has_case_nl ? c->d_case_nl.p + size_t(cs) * c->hb.NLtot() : c->d_nload_val.p;
     const double* q = c->has_case_q ? c->d_case_q.p + size_t(cs) * c->hb.ELtot() : c->d_eload_q.p;
-    OB_CUDA(c, launch_load_vector(d, nl, q, c->d_Ff.p + size_t(cs) * nf, c->stream));
+    const double* eai_cs = c->has_case_eai ? c->d_case_eai.p + size_t(cs) * 3 * Etot : c->d_elem_EAI.p;
+    OB_CUDA(c, launch_load_vector(d, nl, q, eai_cs, c->d_Ff.p + size_t(cs) * nf, c->stream));
     launches += d.ELtot ? 2 : 1;
   }
   OB_CUDA(c, cudaEventRecord(c->ev[7], c->stream));
@@ -181,7 +184,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     const double* q = c->has_case_q ? c->d_case_q.p + size_t(cs) * c->hb.ELtot() : c->d_eload_q.p;
     const double* eai = c->has_case_eai ? c->d_case_eai.p + size_t(cs) * 3 * Etot : c->d_elem_EAI.p;
     if (L > 1) {  // Eq (equivalent loads on bounded DOFs) of THIS case; F_f was filled by assemble_general
-      OB_CUDA(c, launch_load_vector(d, nl, q, c->d_Ff.p + size_t(cs) * nf, c->stream));
+      OB_CUDA(c, launch_load_vector(d, nl, q, eai, c->d_Ff.p + size_t(cs) * nf, c->stream));
       launches += 2;
     }
     for (int64_t s = 0; s < S; s++) {

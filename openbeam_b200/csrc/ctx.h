@@ -31,7 +31,8 @@ struct obgpu_ctx {
   bool solved = false, have_stress = false;
   // general path: the batch arrays + symbolic slots on the device
   bool dev_batch = false;
-  obgpu::DevBuf<double> d_node_rot;
+  obgpu::DevBuf<double> d_node_rot, d_eload_q2;
+  obgpu::DevBuf<uint8_t> d_eload_type;
   obgpu::DevBuf<double> d_node_xy, d_elem_EAI, d_nload_val, d_eload_q, d_eload_dir;
   obgpu::DevBuf<uint32_t> d_elem_nodes;
   obgpu::DevBuf<uint8_t> d_elem_type;

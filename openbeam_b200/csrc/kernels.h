@@ -45,6 +45,8 @@ struct FrameArgs {
   const int32_t* el_order;      // [ELtot]
   const double* eload_q;        // [ELtot]
   const double* eload_dir;      // [3*ELtot]
+  const uint8_t* eload_type;    // [ELtot] OBGPU_LOAD_*, or null when every load is DISTRIB_UNIFORM
+  const double* eload_q2;       // [ELtot] second load parameter (with eload_type)
   const double* U_b;            // [nb_tot] prescribed displacements (nodal frames), or null when all are zero
   const double* node_rot;       // [Ntot] nodal frame yaw (radians), or null when every node frame is the identity
   const double* case_nl;        // [L][NLtot] or null
@@ -76,13 +78,16 @@ struct SparseDev {
   const int32_t* node_slot; const int32_t* el_ptr; const int32_t* el_order;
   const int32_t* eload_elem_g; // [ELtot] global element of each element load (caller slot order)
   const double* eload_dir;
+  const uint8_t* eload_type;   // null when every load is DISTRIB_UNIFORM
+  const double* eload_q2;
   const int32_t *seg_ptr, *seg_src, *sl_ptr, *ff_col, *ff_src, *ff_diag, *bf_rowptr, *bf_col, *bf_src, *fseg_ptr, *fseg_src;
   double *elem_k, *kval, *ff_val, *bf_val, *eload_g, *Eq;
 };
 cudaError_t launch_elem_stiff(const SparseDev& d, const double* eai, cudaStream_t st);
 cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st);
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st);
-cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, double* F_f, cudaStream_t st);
+cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, const double* eai, double* F_f,
+                               cudaStream_t st);
 cudaError_t launch_stress(const SparseDev& d, const double* eai, const double* q, const double* U_f, double* stress,
                           cudaStream_t st);
 

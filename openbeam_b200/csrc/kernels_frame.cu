@@ -218,7 +218,11 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
           for (int j = a.el_ptr[e]; j < a.el_ptr[e + 1]; j++) {
             const int sl = a.el_order[j];
             double gl[6], ex[6];
-            uniform_load(type, g, q_base[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
+            if (a.eload_type)
+              elem_load(a.eload_type[sl], type, g, q_base[sl], a.eload_q2[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1],
+                        eai_base[3 * e] * eai_base[3 * e + 1], gl, ex);
+            else
+              uniform_load(type, g, q_base[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
 #pragma unroll
             for (int k = 0; k < 6; k++) gsum[k] += gl[k];
           }
@@ -445,7 +449,11 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
           for (int j = a.el_ptr[e]; j < a.el_ptr[e + 1]; j++) {
             const int sl = a.el_order[j];
             double gl[6], ex[6];
-            uniform_load(type, g, q_base[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
+            if (a.eload_type)
+              elem_load(a.eload_type[sl], type, g, q_base[sl], a.eload_q2[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1],
+                        eai_base[3 * e] * eai_base[3 * e + 1], gl, ex);
+            else
+              uniform_load(type, g, q_base[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
 #pragma unroll
             for (int k = 0; k < 6; k++) ext[k] += ex[k];
           }

@@ -46,7 +46,9 @@ __global__ void __launch_bounds__(256) k_elem_loads(int64_t ELtot, const int32_t
                                                     const int32_t* __restrict__ eload_elem_g, const double* __restrict__ q,
                                                     const double* __restrict__ dir, const uint2* __restrict__ elem_nodes,
                                                     const uint8_t* __restrict__ elem_type, const double2* __restrict__ node_xy,
-                                                    const int32_t* __restrict__ elem_node0, double* __restrict__ eload_g) {
+                                                    const int32_t* __restrict__ elem_node0, const uint8_t* __restrict__ eload_type,
+                                                    const double* __restrict__ eload_q2, const double* __restrict__ eai,
+                                                    double* __restrict__ eload_g) {
   const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   if (j >= ELtot) return;
   const int sl = el_order[j];
@@ -56,7 +58,10 @@ __global__ void __launch_bounds__(256) k_elem_loads(int64_t ELtot, const int32_t
   const double2 p0 = node_xy[n0 + nd.x], p1 = node_xy[n0 + nd.y];
   const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
   double gl[6], ex[6];
-  uniform_load(elem_type[e], g, q[sl], dir[3 * sl], dir[3 * sl + 1], gl, ex);
+  if (eload_type)
+    elem_load(eload_type[sl], elem_type[e], g, q[sl], eload_q2[sl], dir[3 * sl], dir[3 * sl + 1], eai[3 * e] * eai[3 * e + 1], gl, ex);
+  else
+    uniform_load(elem_type[e], g, q[sl], dir[3 * sl], dir[3 * sl + 1], gl, ex);
 #pragma unroll
   for (int k = 0; k < 6; k++) eload_g[j * 6 + k] = gl[k];
 }
@@ -104,6 +109,7 @@ __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __res
                                                 const int32_t* __restrict__ elem_f0, const int32_t* __restrict__ node_slot,
                                                 const int32_t* __restrict__ el_ptr, const int32_t* __restrict__ el_order,
                                                 const double* __restrict__ q, const double* __restrict__ dir,
+                                                const uint8_t* __restrict__ eload_type, const double* __restrict__ eload_q2,
                                                 const double* __restrict__ U_f, double* __restrict__ stress) {
   __shared__ double stg[8][32 * 13];  // [lane][12] records, stride 13: conflict-free staging for coalesced stores
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -128,7 +134,10 @@ __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __res
   for (int j = el_ptr[e]; j < el_ptr[e + 1]; j++) {
     const int sl = el_order[j];
     double gl[6], ex[6];
-    uniform_load(type, g, q[sl], dir[3 * sl], dir[3 * sl + 1], gl, ex);
+    if (eload_type)
+      elem_load(eload_type[sl], type, g, q[sl], eload_q2[sl], dir[3 * sl], dir[3 * sl + 1], eai[3 * e] * eai[3 * e + 1], gl, ex);
+    else
+      uniform_load(type, g, q[sl], dir[3 * sl], dir[3 * sl + 1], gl, ex);
 #pragma unroll
     for (int k = 0; k < 6; k++) ext[k] += ex[k];
   }
@@ -158,17 +167,18 @@ cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st) {
   if (d.nnz_bf) k_gather<<<nblk(d.nnz_bf), 256, 0, st>>>(d.nnz_bf, d.bf_src, d.kval, d.bf_val);
   return cudaGetLastError();
 }
-cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, double* F_f, cudaStream_t st) {
+cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, const double* eai, double* F_f,
+                               cudaStream_t st) {
   if (d.ELtot)
     k_elem_loads<<<nblk(d.ELtot), 256, 0, st>>>(d.ELtot, d.el_order, d.eload_elem_g, q, d.eload_dir, d.elem_nodes,
-                                                 d.elem_type, d.node_xy, d.elem_node0, d.eload_g);
+                                                 d.elem_type, d.node_xy, d.elem_node0, d.eload_type, d.eload_q2, eai, d.eload_g);
   k_load_vector<<<nblk(d.nf + d.nb), 256, 0, st>>>(d.nf, d.nb, d.fseg_ptr, d.fseg_src, nload_val, d.eload_g, F_f, d.Eq);
   return cudaGetLastError();
 }
 cudaError_t launch_stress(const SparseDev& d, const double* eai, const double* q, const double* U_f, double* stress,
                           cudaStream_t st) {
   k_stress<<<nblk(d.Etot), 256, 0, st>>>(d.Etot, d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.elem_f0,
-                                         d.node_slot, d.el_ptr, d.el_order, q, d.eload_dir, U_f, stress);
+                                         d.node_slot, d.el_ptr, d.el_order, q, d.eload_dir, d.eload_type, d.eload_q2, U_f, stress);
   return cudaGetLastError();
 }
 

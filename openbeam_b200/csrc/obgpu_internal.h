@@ -55,6 +55,9 @@ struct HostBatch {
   int64_t S = 0, L = 1;
   std::vector<int64_t> node_off, elem_off, con_off, nload_off, eload_off;
   std::vector<double> node_xy, node_rotz, elem_EAI, con_val, nload_val, eload_q, eload_dir;
+  std::vector<double> eload_q2;      // [ELtot] second load parameter (zeros when every load is uniform)
+  std::vector<uint8_t> eload_type;   // [ELtot] OBGPU_LOAD_*
+  bool has_load_kinds = false;       // any load other than DISTRIB_UNIFORM
   std::vector<uint32_t> elem_nodes, con_node, nload_node, eload_elem;
   std::vector<uint8_t> elem_type, con_dof, nload_dof;
   bool has_rotz = false;

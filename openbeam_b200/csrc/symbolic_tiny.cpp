@@ -17,7 +17,7 @@ int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& pr
   const int N = int(hb.Ntot()), E = int(hb.Etot()), n = int(sym.n_tot()), nf = int(sym.nf_tot()), nb = int(sym.nb_tot());
   const int NL = int(hb.NLtot()), EL = int(hb.ELtot());
   if (nf > TINY_MAX_NF || n > TINY_MAX_N || E > TINY_MAX_E || N > TINY_MAX_NODES || NL > TINY_MAX_NL ||
-      EL > TINY_MAX_EL || hb.has_rotz) {
+      EL > TINY_MAX_EL || hb.has_rotz || hb.has_load_kinds) {
     err = "structure too large for the thread-per-system kernel";
     return OBGPU_EUNSUPPORTED;
   }

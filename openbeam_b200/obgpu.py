@@ -51,6 +51,7 @@ class BatchDesc(C.Structure):
         ("eload_elem", C.c_void_p), ("eload_q", C.c_void_p), ("eload_dir", C.c_void_p),
         ("n_cases", C.c_int64),
         ("case_nload_val", C.c_void_p), ("case_eload_q", C.c_void_p), ("case_elem_EAI", C.c_void_p),
+        ("eload_type", C.c_void_p), ("eload_q2", C.c_void_p),
     ]
 
 
@@ -161,8 +162,13 @@ def pack_batch(structures):
         eload_elem=cat([s.eload_elem for s in structures], np.uint32),
         eload_q=cat([s.eload_q for s in structures], np.float64),
         eload_dir=cat([s.eload_dir for s in structures], np.float64),
-        node_rotz=None,
+        node_rotz=None, eload_type=None, eload_q2=None,
     )
+    if any(s.eload_type is not None for s in structures):
+        b["eload_type"] = cat([s.eload_type if s.eload_type is not None else np.zeros(len(s.eload_elem), np.uint8)
+                               for s in structures], np.uint8)
+        b["eload_q2"] = cat([s.eload_q2 if s.eload_q2 is not None else np.zeros(len(s.eload_elem))
+                             for s in structures], np.float64)
     if any(s.node_rotz is not None for s in structures):
         b["node_rotz"] = cat([s.node_rotz if s.node_rotz is not None else np.zeros(s.n_nodes) for s in structures],
                              np.float64)
@@ -203,7 +209,7 @@ class Context:
         d.n_structures = batch["S"]
         for k in ("node_off", "elem_off", "con_off", "nload_off", "eload_off", "node_xy", "node_rotz", "elem_nodes",
                   "elem_type", "elem_EAI", "con_node", "con_dof", "con_val", "nload_node", "nload_dof", "nload_val",
-                  "eload_elem", "eload_q", "eload_dir"):
+                  "eload_elem", "eload_q", "eload_dir", "eload_type", "eload_q2"):
             a = batch.get(k)
             setattr(d, k, None if a is None or a.size == 0 else a.ctypes.data)
         d.n_cases = n_cases

@@ -13,6 +13,10 @@ import numpy as np
 # element types (CElementBeam_2D_{RR,RA,AR,AA}); values match include/obgpu.h
 RR, RA, AR, AA = 0, 1, 2, 3
 ELEM_TYPE_NAMES = {"BEAM2D_RR": RR, "BEAM2D_RA": RA, "BEAM2D_AR": AR, "BEAM2D_AA": AA}
+# element loads (include/obgpu.h OBGPU_LOAD_*; reference classes in libopenbeam/include/openbeam/loads.h)
+LOAD_UNIFORM, LOAD_TRIANGULAR, LOAD_CONCENTRATED, LOAD_TEMPERATURE = 0, 1, 2, 3
+LOAD_TYPE_NAMES = {"DISTRIB_UNIFORM": LOAD_UNIFORM, "UNIFORM": LOAD_UNIFORM, "TRIANGULAR": LOAD_TRIANGULAR,
+                   "CONCENTRATED": LOAD_CONCENTRATED, "TEMPERATURE": LOAD_TEMPERATURE}
 # DoF_index (CFiniteElementProblem.h:53-67)
 DX, DY, DZ, RX, RY, RZ = range(6)
 # constraint / load DOF names as accepted by the parser (parse_file.cpp listDofNames)
@@ -48,6 +52,8 @@ class Structure:
     eload_q: np.ndarray = field(default_factory=lambda: np.zeros(0, np.float64))
     eload_dir: np.ndarray = field(default_factory=lambda: np.zeros((0, 3), np.float64))
     node_rotz: np.ndarray | None = None      # [N] f64 radians (nodal rotated frames), None = all zero
+    eload_type: np.ndarray | None = None     # [EL] u8 LOAD_* (None = all DISTRIB_UNIFORM)
+    eload_q2: np.ndarray | None = None       # [EL] f64 second load parameter (q_end / dist)
 
     def __post_init__(self):
         self.node_xy = _a(self.node_xy, np.float64, (-1, 2))
@@ -63,6 +69,11 @@ class Structure:
         self.eload_elem = _a(self.eload_elem, np.uint32)
         self.eload_q = _a(self.eload_q, np.float64)
         self.eload_dir = _a(self.eload_dir, np.float64, (-1, 3))
+        if self.eload_type is not None:
+            self.eload_type = _a(self.eload_type, np.uint8)
+            self.eload_q2 = _a(self.eload_q2 if self.eload_q2 is not None else np.zeros(len(self.eload_type)), np.float64)
+            if not np.any(self.eload_type):
+                self.eload_type = self.eload_q2 = None
         if self.node_rotz is not None:
             self.node_rotz = _a(self.node_rotz, np.float64)
             if not np.any(self.node_rotz):
@@ -82,7 +93,9 @@ def build_structure(nodes, elements, sections, constraints, node_loads=(), eleme
     (docs/structure-definition-format.rst): ``nodes`` = [(x, y[, rot_z_deg])],
     ``elements`` = [(type_name, n0, n1, section_name)], ``sections`` = {name: (E, A, Iz)},
     ``constraints`` = [(node, dof_name[, value])], ``node_loads`` = [(node, dof_name, value)],
-    ``element_loads`` = [(element, q, (dx, dy, dz))]  (DISTRIB_UNIFORM only)."""
+    ``element_loads`` = [(element, q, (dx, dy, dz))] for DISTRIB_UNIFORM, or
+    (element, "TRIANGULAR", q_ini, q_end, dir) / (element, "CONCENTRATED", P, dist, dir) /
+    (element, "TEMPERATURE", deltaT)  (parse_file.cpp element-load section)."""
     xy = [(n[0], n[1]) for n in nodes]
     # parse_file.cpp:463-468: rot_z given in degrees -> DEG2RAD
     rotz = [np.deg2rad(n[2]) if len(n) > 2 else 0.0 for n in nodes]
@@ -97,8 +110,15 @@ def build_structure(nodes, elements, sections, constraints, node_loads=(), eleme
     for l in node_loads:
         for d in DOF_NAMES[l[1]]:
             ln.append(l[0]); ld.append(d); lv.append(l[2])
-    ee = [l[0] for l in element_loads]
-    eq = [l[1] for l in element_loads]
-    ed = [l[2] for l in element_loads]
+    ee, eq, ed, ety, eq2 = [], [], [], [], []
+    for l in element_loads:
+        ee.append(l[0])
+        if isinstance(l[1], str):
+            kind = LOAD_TYPE_NAMES[l[1]]
+            ety.append(kind); eq.append(l[2])
+            eq2.append(l[3] if kind in (LOAD_TRIANGULAR, LOAD_CONCENTRATED) else 0.0)
+            ed.append((1.0, 0.0, 0.0) if kind == LOAD_TEMPERATURE else l[4])
+        else:
+            ety.append(LOAD_UNIFORM); eq.append(l[1]); eq2.append(0.0); ed.append(l[2])
     return Structure(xy, en, et, eai, cn, cd, cv, ln, ld, lv, ee, eq,
-                     np.asarray(ed, np.float64).reshape(-1, 3), rotz)
+                     np.asarray(ed, np.float64).reshape(-1, 3), rotz, ety if any(ety) else None, eq2 if any(ety) else None)

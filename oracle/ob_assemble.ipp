@@ -125,6 +125,109 @@ static void uniformLoad_computeStressAndEquivalentLoads(const ElemLoad& ld, cons
   loads[1] = {F2[0], F2[1], F2[2], 0, 0, -m2};
 }
 
+// src/CLoadDistributedTriangular.cpp:31-169, src/CLoadConcentratedForce.cpp:31-154 (both: RR beams only)
+static void triOrPointLoad_computeStressAndEquivalentLoads(const ElemLoad& ld, const CElement* el, ElementStress& stress,
+                                                           std::vector<array6>& loads) {
+  const num_t* dir = ld.dir;
+  if (!(std::abs(1 - (dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2])) < 1e-6))
+    throw std::runtime_error("ASSERT_(|1 - |dir|^2| < 1e-6)");
+  const TRotationTrans3D& node0 = el->m_parent->getNodePose(el->conected_nodes_ids[0]);
+  const TRotationTrans3D& node1 = el->m_parent->getNodePose(el->conected_nodes_ids[1]);
+  num_t Ax = node1.t[0] - node0.t[0];
+  num_t Ay = node1.t[1] - node0.t[1];
+  num_t Az = node1.t[2] - node0.t[2];
+  const num_t L2 = Ax * Ax + Ay * Ay + Az * Az;
+  const num_t L = std::sqrt(L2);
+  if (!(L > 0)) throw std::runtime_error("ASSERT_(L > 0)");
+  const num_t _1_L = 1 / L;
+  Ax *= _1_L;
+  Ay *= _1_L;
+  Az *= _1_L;
+  const num_t cross_prod[3] = {Ay * dir[2] - Az * dir[1], -Ax * dir[2] + Az * dir[0], Ax * dir[1] - Ay * dir[0]};
+  const num_t proy_long = (Ax * dir[0] + Ay * dir[1] + Az * dir[2]);
+  const num_t proy_perp = std::sqrt(1 - proy_long * proy_long) * (cross_prod[2] < 0 ? +1. : -1.);
+  num_t f1[3] = {0, 0, 0}, f2[3] = {0, 0, 0};
+  num_t m1, m2;
+  if (ld.kind == OBO_LOAD_TRIANGULAR) {  // CLoadDistributedTriangular.cpp:72-130
+    const num_t q_ini = ld.q, q_end = ld.q2;
+    const num_t q0_t = q_ini * proy_long, q1_t = q_end * proy_long;
+    const num_t q0_n = q_ini * proy_perp, q1_n = q_end * proy_perp;
+    if (el->type == OBO_RR) {
+      f1[1] = L * (q0_n * 0.5 + (q1_n - q0_n) * 3. / 20.);
+      m1 = +L * L * (q0_n * 1. / 12. + (q1_n - q0_n) * 1. / 30.);
+      f2[1] = L * (q0_n * 0.5 + (q1_n - q0_n) * 7. / 20.);
+      m2 = -L * L * (q0_n * 1. / 12. + (q1_n - q0_n) * 1. / 20.);
+    } else if (el->type == OBO_AA || el->type == OBO_RA || el->type == OBO_AR) {
+      throw std::runtime_error("TODO");
+    } else {
+      throw std::runtime_error("Unsupported element type for load 'CLoadDistributedTriangular'");
+    }
+    f1[0] = -0.5 * L * (q0_t + (q1_t - q0_t) / 3.0);
+    f2[0] = -0.5 * L * (q0_t + 2.0 * (q1_t - q0_t) / 3.0);
+  } else {  // CLoadConcentratedForce.cpp:72-116
+    const num_t P_n = ld.q * proy_perp;
+    if (std::abs(proy_long) > 1e-5) throw std::runtime_error("Only perpendicular forces supported by now!");
+    const num_t a = ld.q2;
+    const num_t b = L - a;
+    if (a < 0 || b < 0) throw std::runtime_error("Error: Point of application is out of the beam!");
+    const num_t a2 = a * a;
+    const num_t b2 = b * b;
+    const num_t L3 = L * L2;
+    if (el->type == OBO_RR) {
+      f1[0] = 0;
+      f1[1] = P_n * (b2 / L3) * (3 * a + b);
+      m1 = P_n * a * b2 / L2;
+      f2[0] = 0;
+      f2[1] = P_n * (a2 / L3) * (a + 3 * b);
+      m2 = -P_n * a2 * b / L2;
+    } else {
+      throw std::runtime_error("Unsupported element type for load 'CLoadConstTemperature'");  // sic (:114-116)
+    }
+  }
+  stress.assign(2, FaceStress());
+  stress[0].N = -f1[0]; stress[0].Vy = -f1[1]; stress[0].Mz = -m1;
+  stress[1].N = f2[0];  stress[1].Vy = f2[1];  stress[1].Mz = m2;
+  const Matrix33& R = el->m_global_orientation.rot;
+  num_t F1[3], F2[3];
+  for (int r = 0; r < 3; r++) {  // F = -R * f
+    num_t a = (-R(r, 0)) * f1[0]; a += (-R(r, 1)) * f1[1]; a += (-R(r, 2)) * f1[2];
+    num_t b = (-R(r, 0)) * f2[0]; b += (-R(r, 1)) * f2[1]; b += (-R(r, 2)) * f2[2];
+    F1[r] = a; F2[r] = b;
+  }
+  loads.resize(2);
+  loads[0] = {F1[0], F1[1], F1[2], 0, 0, -m1};
+  loads[1] = {F2[0], F2[1], F2[2], 0, 0, -m2};
+}
+
+// src/CLoadConstTemperature.cpp:31-93 (alpha = 12e-6 is hard-wired there)
+static void temperatureLoad_computeStressAndEquivalentLoads(const ElemLoad& ld, const CElement* el, ElementStress& stress,
+                                                            std::vector<array6>& loads) {
+  const num_t E = el->E, A = el->A, alpha = 12e-6;
+  const num_t N = E * A * alpha * ld.q;
+  stress.assign(2, FaceStress());
+  stress[0].N = -N;
+  stress[1].N = -N;
+  loads.resize(2);
+  for (int i = 0; i < 6; i++) {
+    loads[0][i] = 0;
+    loads[1][i] = 0;
+  }
+  const TRotationTrans3D& node0 = el->m_parent->getNodePose(el->conected_nodes_ids[0]);
+  const TRotationTrans3D& node1 = el->m_parent->getNodePose(el->conected_nodes_ids[1]);
+  num_t Ax = node1.t[0] - node0.t[0];
+  num_t Ay = node1.t[1] - node0.t[1];
+  num_t Az = node1.t[2] - node0.t[2];
+  const num_t L2 = Ax * Ax + Ay * Ay + Az * Az;
+  const num_t L = std::sqrt(L2);
+  if (!(L > 0)) throw std::runtime_error("ASSERT_(L > 0)");
+  const num_t _1_L = 1 / L;
+  Ax *= _1_L;
+  Ay *= _1_L;
+  Az *= _1_L;
+  loads[0][0] = -N * Ax; loads[0][1] = -N * Ay; loads[0][2] = -N * Az;
+  loads[1][0] = N * Ax;  loads[1][1] = N * Ay;  loads[1][2] = N * Az;
+}
+
 // src/CStructureProblem.cpp:59-113
 void Problem::internalComputeStressAndEquivalentLoads() {
   m_loads_at_each_dof_equivs.clear();
@@ -133,7 +236,10 @@ void Problem::internalComputeStressAndEquivalentLoads() {
     auto el = m_elements.at(elIdxLoadPair.first);
     ElementStress stress;
     std::vector<array6> loads;
-    uniformLoad_computeStressAndEquivalentLoads(elIdxLoadPair.second, el.get(), stress, loads);
+    const ElemLoad& ld = elIdxLoadPair.second;  // virtual CLoadOnBeam::computeStressAndEquivalentLoads
+    if (ld.kind == OBO_LOAD_UNIFORM) uniformLoad_computeStressAndEquivalentLoads(ld, el.get(), stress, loads);
+    else if (ld.kind == OBO_LOAD_TEMPERATURE) temperatureLoad_computeStressAndEquivalentLoads(ld, el.get(), stress, loads);
+    else triOrPointLoad_computeStressAndEquivalentLoads(ld, el.get(), stress, loads);
     for (size_t p = 0; p < loads.size(); p++) {
       const size_t idx_node = el->conected_nodes_ids[p];
       for (int d = 0; d < 6; d++) {

@@ -68,6 +68,23 @@ obo_problem* obo_create(int64_t n_nodes, const double* node_xy, const double* no
 
 void obo_destroy(obo_problem* h) { delete h; }
 
+int obo_set_eload_kinds(obo_problem* h, const uint8_t* kind, const double* q2) {
+  obo::Problem& P = *h->p;
+  if (P.raw_eload_elem.empty()) return 0;
+  // multimap iteration order = stable sort of insertion order by element index
+  std::vector<size_t> order(P.raw_eload_elem.size());
+  for (size_t i = 0; i < order.size(); i++) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return P.raw_eload_elem[a] < P.raw_eload_elem[b]; });
+  size_t k = 0;
+  for (auto& kv : P.m_loads_on_beams) {
+    const size_t i = order[k++];
+    if (kind[i] > 3) return -1;
+    kv.second.kind = kind[i];
+    kv.second.q2 = q2 ? q2[i] : 0.0;
+  }
+  return 0;
+}
+
 static void set_loads(obo::Problem& P, const double* nl_val, const double* el_q) {
   if (nl_val)
     for (size_t i = 0; i < P.raw_nloads_val.size(); i++) P.raw_nloads_val[i] = nl_val[i];

@@ -166,9 +166,14 @@ struct CElement {
   void lengths(num_t& L, num_t& L2, num_t& L3) const;
 };
 
-struct ElemLoad {  // CLoadDistributedUniform (loads.h) : q + unit direction
+// loads.h: CLoadDistributedUniform (q, dir) | CLoadDistributedTriangular (q_ini = q, q_end = q2, dir) |
+// CLoadConcentratedForce (P = q, dist = q2, dir) | CLoadConstTemperature (m_incr_temp = q)
+enum { OBO_LOAD_UNIFORM = 0, OBO_LOAD_TRIANGULAR = 1, OBO_LOAD_CONCENTRATED = 2, OBO_LOAD_TEMPERATURE = 3 };
+struct ElemLoad {
   num_t q;
   num_t dir[3];
+  int kind = OBO_LOAD_UNIFORM;
+  num_t q2 = 0;
 };
 
 struct TDoFType {

@@ -59,6 +59,9 @@ obo_problem* obo_create(int64_t n_nodes, const double* node_xy, const double* no
                         int64_t n_nloads, const uint32_t* nl_node, const uint8_t* nl_dof, const double* nl_val,
                         int64_t n_eloads, const uint32_t* el_elem, const double* el_q, const double* el_dir);
 void obo_destroy(obo_problem*);
+/* element-load kinds (call right after obo_create; default = every load DISTRIB_UNIFORM):
+ * kind[i] in {0 uniform, 1 triangular (q=q_ini, q2=q_end), 2 concentrated (q=P, q2=dist), 3 temperature (q=dT)} */
+int obo_set_eload_kinds(obo_problem*, const uint8_t* kind, const double* q2);
 /* replace load values in place (same slots): node-load values and element-load q */
 int obo_set_load_values(obo_problem*, const double* nl_val, const double* el_q);
 /* replace every element's (E,A,Iz) */

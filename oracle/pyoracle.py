@@ -37,6 +37,7 @@ def lib():
         L.obo_create.argtypes = [i64, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp]
         L.obo_destroy.argtypes = [vp]
         L.obo_set_load_values.argtypes = [vp, dp, dp]
+        L.obo_set_eload_kinds.argtypes = [vp, dp, dp]
         L.obo_set_elem_EAI.argtypes = [vp, dp]
         L.obo_assemble.argtypes = [vp, C.c_int]
         L.obo_solve_static.argtypes = [vp, C.c_int]
@@ -76,6 +77,9 @@ class OracleProblem:
             len(st.eload_elem), _p(st.eload_elem), _p(st.eload_q), _p(st.eload_dir))
         if not self.h:
             raise OracleError("obo_create failed (bad element type?)")
+        if getattr(st, "eload_type", None) is not None:
+            if L.obo_set_eload_kinds(self.h, _p(st.eload_type), _p(st.eload_q2)) != 0:
+                raise OracleError("obo_set_eload_kinds failed (bad load type?)")
 
     def __del__(self):
         if getattr(self, "h", None):

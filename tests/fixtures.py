@@ -104,6 +104,25 @@ def inclined_mixed():
                            [(1, 8000.0, DOWN), (0, 3000.0, tuple(d)), (5, 1200.0, DOWN)])
 
 
+def load_kinds():
+    """Every element-load class of the reference on one frame: DISTRIB_UNIFORM, TRIANGULAR and
+    CONCENTRATED (RR beams only, the latter perpendicular to the member) and TEMPERATURE (any beam type, here also
+    an inclined RA member and an AA bar)."""
+    nodes = [(0, 0), (0, 3.0), (4.0, 3.0), (4.0, 0), (7.0, 3.0), (7.0, 0.5)]
+    elements = [("BEAM2D_RR", 0, 1, "IPE200"), ("BEAM2D_RR", 1, 2, "IPE200"), ("BEAM2D_RR", 2, 3, "IPE200"),
+                ("BEAM2D_RA", 2, 4, "IPE200"), ("BEAM2D_AA", 4, 5, "IPE200"), ("BEAM2D_RR", 3, 5, "IPE200")]
+    cons = [(0, "DXDYRZ"), (3, "DXDY"), (5, "DY")]
+    d = (3.0 - 0.5, 3.0, 0.0)   # perpendicular to member 5 (nodes 3 -> 5: axis (3, 0.5))... see below
+    ax = np.array([7.0 - 4.0, 0.5 - 0.0])
+    perp = np.array([-ax[1], ax[0]]) / np.hypot(*ax)
+    eloads = [(1, "TRIANGULAR", 2000.0, 9000.0, DOWN), (1, 1500.0, DOWN), (0, "CONCENTRATED", 4000.0, 1.2, (1.0, 0.0, 0.0)),
+              (5, "CONCENTRATED", -2500.0, 0.9, (float(perp[0]), float(perp[1]), 0.0)),
+              (3, "TEMPERATURE", 35.0), (4, "TEMPERATURE", -20.0), (2, "TEMPERATURE", 15.0),
+              (2, "TRIANGULAR", 500.0, 0.0, (1.0, 0.0, 0.0))]
+    del d
+    return build_structure(nodes, elements, IPE200, cons, [(1, "DX", 1000.0)], eloads)
+
+
 def mechanism():
     """demo1 without the DY support at node 1 -> singular K_ff (the reference throws
     'Ill-conditioned matrix. Too few restrictions?', solver_static.cpp:98-105)."""
@@ -128,6 +147,7 @@ ALL = {
     "propped_cantilever_udl": propped_cantilever_udl,
     "simply_supported_udl": simply_supported_udl,
     "inclined_mixed": inclined_mixed,
+    "load_kinds": load_kinds,
 }
 # fixtures without nodal rotated frames (U_b = 0, identity node frames): the round-1 GPU scope
 PLAIN = [k for k in ALL if "tilted" not in k and "tilded" not in k]
