@@ -33,7 +33,11 @@ enum {
 };
 
 /* element types: CElementBeam_2D_{RR,RA,AR,AA}.cpp */
-enum { OBGPU_BEAM2D_RR = 0, OBGPU_BEAM2D_RA = 1, OBGPU_BEAM2D_AR = 2, OBGPU_BEAM2D_AA = 3 };
+enum { OBGPU_BEAM2D_RR = 0, OBGPU_BEAM2D_RA = 1, OBGPU_BEAM2D_AR = 2, OBGPU_BEAM2D_AA = 3,
+       /* CElementBeam_2D_RD.cpp, CElementSpring.cpp, CElementSpringXY.cpp, CElementSpringDXDYRZ.cpp (with its K11(5,5)
+        * assignment slip, reproduced), CElementTorsionSpring.cpp.  Their constants ride in elem_EAI:
+        * RD (E, A, Iz) | SPRING_1D (K, -, -) | SPRING_XY (Kx, Ky, -) | SPRING_DXDYRZ (Kx, Ky, KRz) | SPRING_TORSION (K, -, -) */
+       OBGPU_BEAM2D_RD = 4, OBGPU_SPRING_1D = 5, OBGPU_SPRING_XY = 6, OBGPU_SPRING_DXDYRZ = 7, OBGPU_SPRING_TORSION = 8 };
 /* element loads (libopenbeam/include/openbeam/loads.h): CLoadDistributedUniform, CLoadDistributedTriangular (RR only),
  * CLoadConcentratedForce (RR only, perpendicular to the beam), CLoadConstTemperature */
 enum { OBGPU_LOAD_UNIFORM = 0, OBGPU_LOAD_TRIANGULAR = 1, OBGPU_LOAD_CONCENTRATED = 2, OBGPU_LOAD_TEMPERATURE = 3 };
@@ -55,8 +59,8 @@ typedef struct obgpu_batch_desc {
   const double* node_xy;      /* [2*Ntot] x,y  (m_node_poses[i].t, z = 0)                         */
   const double* node_rotz;    /* NULL or [Ntot] nodal frame yaw in radians (parse_file.cpp:467)   */
   const uint32_t* elem_nodes; /* [2*Etot] conected_nodes_ids[0..1]                                */
-  const uint8_t* elem_type;   /* [Etot]   OBGPU_BEAM2D_*                                          */
-  const double* elem_EAI;     /* [3*Etot] E, A, Iz  (G = J = 0 as CBaseElementBeam.h:45-46)       */
+  const uint8_t* elem_type;   /* [Etot]   OBGPU_BEAM2D_* / OBGPU_SPRING_*                                */
+  const double* elem_EAI;     /* [3*Etot] E, A, Iz  (G = J = 0 as CBaseElementBeam.h:45-46); spring constants */
   const uint32_t* con_node;   /* [Ctot] */
   const uint8_t* con_dof;     /* [Ctot] OBGPU_DX..RZ */
   const double* con_val;      /* [Ctot] prescribed displacement (m_DoF_constraints)               */

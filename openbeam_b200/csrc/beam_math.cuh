@@ -23,6 +23,10 @@ __device__ __forceinline__ ElemGeom elem_geom(double x0, double y0, double x1, d
   const double dx = x1 - x0, dy = y1 - y0;
   const double L2 = dx * dx + dy * dy;
   g.L = sqrt(L2);
+  if (L2 == 0.0) {  // internals.cpp:100-104: coincident nodes (springs) -> identity orientation
+    g.invL = 0.0; g.c = 1.0; g.s = 0.0;
+    return g;
+  }
   g.invL = 1.0 / g.L;
   g.c = dx * g.invL;
   g.s = dy * g.invL;
@@ -61,8 +65,26 @@ __device__ __forceinline__ ElemLocalK elem_local_k(int type, double E, double A,
     k.p22 = -3.0 * EI_L2;
     k.r22 = 3.0 * EI_L;
     k.q15 = -k.p22;
-  } else {  // AA, CElementBeam_2D_AA.cpp:86-94
+  } else if (type == OBGPU_BEAM2D_AA) {  // CElementBeam_2D_AA.cpp:86-94
     k.b = 0.0;
+  } else if (type == OBGPU_BEAM2D_RD) {  // CElementBeam_2D_RD.cpp:96-112
+    k.b = 0.0;
+    k.r11 = k.r22 = EI_L;
+    k.q55 = -EI_L;
+  } else {  // springs: (E, A, Iz) carry (K | Kx, Ky, KRz)
+    k.a = k.b = 0.0;
+    if (type == OBGPU_SPRING_1D) {  // CElementSpring.cpp:56-66
+      k.a = E;
+    } else if (type == OBGPU_SPRING_XY) {  // CElementSpringXY.cpp:47-59
+      k.a = E; k.b = A;
+    } else if (type == OBGPU_SPRING_DXDYRZ) {
+      // CElementSpringDXDYRZ.cpp:47-62: the last line there assigns K11(5,5) = -KRz (not K12): K11(5,5) = -KRz,
+      // K22(5,5) = +KRz (copied before), K12(5,5) = 0.  Reproduced as is.
+      k.a = E; k.b = A; k.r11 = -Iz; k.r22 = Iz;
+    } else {  // OBGPU_SPRING_TORSION, CElementTorsionSpring.cpp:57-67
+      k.r11 = k.r22 = E;
+      k.q55 = -E;
+    }
   }
   return k;
 }

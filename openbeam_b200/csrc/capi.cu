@@ -171,17 +171,21 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   for (int64_t e = 0; e < E; e++) {  // UNINITIALIZED_VALUE checks, CElementBeam_2D_RR.cpp:64-91
     for (int k = 0; k < 3; k++)
       if (hb.elem_EAI[3 * e + k] == 1.7976931348623157e308) return fail(c, OBGPU_EINVAL, "Uninitialized parameter E/A/Iz");
-    if (hb.elem_type[e] > OBGPU_BEAM2D_AA) return fail(c, OBGPU_EINVAL, "unknown element type");
+    if (hb.elem_type[e] > OBGPU_SPRING_TORSION) return fail(c, OBGPU_EINVAL, "unknown element type");
   }
   // (load, element) pairs the reference throws on (CLoadDistributedTriangular.cpp:93-125,
   // CLoadConcentratedForce.cpp:77-84,114-116): refused here, at upload
-  if (hb.has_load_kinds)
+  if (EL)
     for (int64_t s = 0; s < S; s++)
       for (int64_t l = hb.eload_off[s]; l < hb.eload_off[s + 1]; l++) {
         const int lt = hb.eload_type[l];
-        if (lt != OBGPU_LOAD_TRIANGULAR && lt != OBGPU_LOAD_CONCENTRATED) continue;
         const int64_t e = hb.elem_off[s] + hb.eload_elem[l];
         if (hb.eload_elem[l] >= uint32_t(hb.elem_off[s + 1] - hb.elem_off[s])) continue;  // reported by the symbolic phase
+        if (lt == OBGPU_LOAD_UNIFORM && hb.elem_type[e] > OBGPU_BEAM2D_AA)   // CLoadDistributedUniform.cpp:85-125
+          return fail(c, OBGPU_EINVAL, "Unsupported element type for load 'CLoadDistributedUniform'");
+        if (lt == OBGPU_LOAD_TEMPERATURE && hb.elem_type[e] > OBGPU_BEAM2D_RD)  // CBaseElementBeam only (:40-49)
+          return fail(c, OBGPU_EINVAL, "Unsupported element type for load 'CLoadConstTemperature'");
+        if (lt != OBGPU_LOAD_TRIANGULAR && lt != OBGPU_LOAD_CONCENTRATED) continue;
         if (hb.elem_type[e] != OBGPU_BEAM2D_RR)
           return fail(c, OBGPU_EINVAL, lt == OBGPU_LOAD_TRIANGULAR
                                            ? "Unsupported element type for load 'CLoadDistributedTriangular'"
@@ -226,9 +230,10 @@ int obgpu_symbolic(obgpu_ctx* c) {
   // the K pattern costs O(T log T) host work: built eagerly for moderate batches, on demand otherwise
   int rc = run_symbolic(c->hb, c->sym, err, c->hb.Etot() <= (int64_t(1) << 22));
   if (rc != OBGPU_OK) return fail(c, rc, err);
-  // ASSERT_(L > 0), CElementBeam_2D_RR.cpp:63
+  // ASSERT_(L > 0), CElementBeam_2D_RR.cpp:63 (beams; springs may join coincident nodes: identity orientation)
   for (int64_t s = 0; s < c->hb.S; s++)
     for (int64_t e = c->hb.elem_off[s]; e < c->hb.elem_off[s + 1]; e++) {
+      if (c->hb.elem_type[e] > OBGPU_BEAM2D_RD) continue;
       const double* p0 = &c->hb.node_xy[2 * (c->hb.node_off[s] + c->hb.elem_nodes[2 * e])];
       const double* p1 = &c->hb.node_xy[2 * (c->hb.node_off[s] + c->hb.elem_nodes[2 * e + 1])];
       if (!((p1[0] - p0[0]) * (p1[0] - p0[0]) + (p1[1] - p0[1]) * (p1[1] - p0[1]) > 0))

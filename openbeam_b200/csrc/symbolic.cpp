@@ -30,7 +30,7 @@ static inline int elemk_cid(int j, int r, int c) {
 // Global DOF masks of the two element ends (bit d = DOF d used), CElement.cpp:192-247 specialised to
 // the four beam types' local masks (getLocalDoFs: RR.cpp:129-139, RA.cpp:110-119, AR.cpp:110-119, AA.cpp:97-106).
 // Orientation as internals.cpp:30-123 with z = 0: X = p12 * (1/len), Z = (0,0,1), Y = Z x X.
-static bool element_end_masks(const double* p1, const double* p2, int type, unsigned& m0, unsigned& m1) {
+static bool element_end_masks(const double* p1, const double* p2, int type, const double* par, unsigned& m0, unsigned& m1) {
   const double dx = p2[0] - p1[0], dy = p2[1] - p1[1], dz = 0.0;
   const double len = std::sqrt(dx * dx + dy * dy + dz * dz);
   double R[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
@@ -67,6 +67,13 @@ static bool element_end_masks(const double* p1, const double* p2, int type, unsi
     case OBGPU_BEAM2D_RA: l0 = R_; l1 = A2; break;
     case OBGPU_BEAM2D_AR: l0 = A2; l1 = R_; break;
     case OBGPU_BEAM2D_AA: l0 = A1; l1 = A1; break;
+    case OBGPU_BEAM2D_RD: l0 = R_; l1 = 0x21; break;                                     // RD.cpp:114-125
+    case OBGPU_SPRING_1D: l0 = l1 = A1; break;                                           // CElementSpring.cpp:69-75
+    case OBGPU_SPRING_XY: l0 = l1 = (par[0] != 0 ? 1u : 0u) | (par[1] != 0 ? 2u : 0u); break;  // SpringXY.cpp:62-66
+    case OBGPU_SPRING_DXDYRZ:
+      l0 = l1 = (par[0] != 0 ? 1u : 0u) | (par[1] != 0 ? 2u : 0u) | (par[2] != 0 ? 0x20u : 0u);
+      break;                                                                             // SpringDXDYRZ.cpp:65-70
+    case OBGPU_SPRING_TORSION: l0 = l1 = 0x20; break;                                    // TorsionSpring.cpp:70-75
     default: return false;
   }
   m0 = glob(l0);
@@ -107,7 +114,7 @@ int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want
         return OBGPU_EINVAL;
       }
       unsigned m0, m1;
-      if (!element_end_masks(&hb.node_xy[2 * (n0 + a)], &hb.node_xy[2 * (n0 + b)], hb.elem_type[e0 + e], m0, m1)) {
+      if (!element_end_masks(&hb.node_xy[2 * (n0 + a)], &hb.node_xy[2 * (n0 + b)], hb.elem_type[e0 + e], &hb.elem_EAI[3 * (e0 + e)], m0, m1)) {
         err = "unknown element type";
         return OBGPU_EINVAL;
       }

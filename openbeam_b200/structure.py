@@ -12,7 +12,10 @@ import numpy as np
 
 # element types (CElementBeam_2D_{RR,RA,AR,AA}); values match include/obgpu.h
 RR, RA, AR, AA = 0, 1, 2, 3
-ELEM_TYPE_NAMES = {"BEAM2D_RR": RR, "BEAM2D_RA": RA, "BEAM2D_AR": AR, "BEAM2D_AA": AA}
+RD, SPRING_1D, SPRING_XY, SPRING_DXDYRZ, SPRING_TORSION = 4, 5, 6, 7, 8   # constants ride in the (E, A, Iz) triple
+ELEM_TYPE_NAMES = {"BEAM2D_RR": RR, "BEAM2D_RA": RA, "BEAM2D_AR": AR, "BEAM2D_AA": AA, "BEAM2D_RD": RD,
+                   "SPRING_1D": SPRING_1D, "SPRING_XY": SPRING_XY, "SPRING_DXDYRZ": SPRING_DXDYRZ,
+                   "SPRING_TORSION": SPRING_TORSION}
 # element loads (include/obgpu.h OBGPU_LOAD_*; reference classes in libopenbeam/include/openbeam/loads.h)
 LOAD_UNIFORM, LOAD_TRIANGULAR, LOAD_CONCENTRATED, LOAD_TEMPERATURE = 0, 1, 2, 3
 LOAD_TYPE_NAMES = {"DISTRIB_UNIFORM": LOAD_UNIFORM, "UNIFORM": LOAD_UNIFORM, "TRIANGULAR": LOAD_TRIANGULAR,

@@ -202,6 +202,8 @@ static void triOrPointLoad_computeStressAndEquivalentLoads(const ElemLoad& ld, c
 // src/CLoadConstTemperature.cpp:31-93 (alpha = 12e-6 is hard-wired there)
 static void temperatureLoad_computeStressAndEquivalentLoads(const ElemLoad& ld, const CElement* el, ElementStress& stress,
                                                             std::vector<array6>& loads) {
+  if (el->type > OBO_RD)  // dynamic_cast<const CBaseElementBeam*> fails for the springs (:40-49)
+    throw std::runtime_error("Unsupported element type for load 'CLoadConstTemperature'");
   const num_t E = el->E, A = el->A, alpha = 12e-6;
   const num_t N = E * A * alpha * ld.q;
   stress.assign(2, FaceStress());

@@ -428,12 +428,100 @@ struct CElementBeam_2D_AA : CElement {  // src/CElementBeam_2D_AA.cpp:41-106
   }
   std::shared_ptr<CElement> clone() const override { return std::make_shared<CElementBeam_2D_AA>(*this); }
 };
+struct CElementBeam_2D_RD : CElement {  // src/CElementBeam_2D_RD.cpp:41-125 (rigid end - slider end)
+  void getLocalStiffnessMatrices(std::vector<TStiffnessSubmatrix>& o) const override {
+    initSub(o);
+    num_t L, L2, L3;
+    lengths(L, L2, L3);
+    checkInit(this, "CElementBeam_2D_RD", true);
+    Matrix66 &K11 = o[0].matrix, &K22 = o[1].matrix, &K12 = o[2].matrix;
+    K11(0, 0) = E * A / L;
+    K11(5, 5) = E * Iz / L;
+    K22(0, 0) = K11(0, 0);
+    K22(5, 5) = K11(5, 5);
+    K12(0, 0) = -K11(0, 0);
+    K12(5, 5) = -K11(5, 5);
+  }
+  void getLocalDoFs(std::vector<used_DoFs_t>& d) const override {
+    d.resize(2);
+    d[0] = used_DoFs_t{true, true, false, false, false, true};
+    d[1] = used_DoFs_t{true, false, false, false, false, true};
+  }
+  std::shared_ptr<CElement> clone() const override { return std::make_shared<CElementBeam_2D_RD>(*this); }
+};
+// The spring elements keep their constants in the generic parameter triple: E = K | Kx, A = Ky, Iz = KRz.
+struct CElementSpring : CElement {  // src/CElementSpring.cpp:41-80 (SPRING_1D: along the element's local x)
+  void getLocalStiffnessMatrices(std::vector<TStiffnessSubmatrix>& o) const override {
+    initSub(o);
+    if (E == UNINITIALIZED_VALUE) throw std::runtime_error("CElementSpring: Uninitialized parameter K");
+    o[0].matrix(0, 0) = E;
+    o[1].matrix = o[0].matrix;
+    o[2].matrix(0, 0) = -E;
+  }
+  void getLocalDoFs(std::vector<used_DoFs_t>& d) const override {
+    d.resize(2);
+    d[0] = d[1] = used_DoFs_t{true, false, false, false, false, false};
+  }
+  std::shared_ptr<CElement> clone() const override { return std::make_shared<CElementSpring>(*this); }
+};
+struct CElementSpringXY : CElement {  // src/CElementSpringXY.cpp:31-66
+  void getLocalStiffnessMatrices(std::vector<TStiffnessSubmatrix>& o) const override {
+    initSub(o);
+    o[0].matrix(0, 0) = E;
+    o[0].matrix(1, 1) = A;
+    o[1].matrix = o[0].matrix;
+    o[2].matrix(0, 0) = -E;
+    o[2].matrix(1, 1) = -A;
+  }
+  void getLocalDoFs(std::vector<used_DoFs_t>& d) const override {
+    d.resize(2);
+    d[0] = d[1] = used_DoFs_t{E != 0, A != 0, false, false, false, false};
+  }
+  std::shared_ptr<CElement> clone() const override { return std::make_shared<CElementSpringXY>(*this); }
+};
+struct CElementSpringDXDYRZ : CElement {  // src/CElementSpringDXDYRZ.cpp:31-70
+  void getLocalStiffnessMatrices(std::vector<TStiffnessSubmatrix>& o) const override {
+    initSub(o);
+    Matrix66 &K11 = o[0].matrix, &K22 = o[1].matrix, &K12 = o[2].matrix;
+    K11(0, 0) = E;
+    K11(1, 1) = A;
+    K11(5, 5) = Iz;
+    K22 = K11;
+    K12(0, 0) = -E;
+    K12(1, 1) = -A;
+    K11(5, 5) = -Iz;  // sic (:62): the reference assigns K11 here, not K12 -> K11(5,5) = -KRz, K12(5,5) stays 0
+  }
+  void getLocalDoFs(std::vector<used_DoFs_t>& d) const override {
+    d.resize(2);
+    d[0] = d[1] = used_DoFs_t{E != 0, A != 0, false, false, false, Iz != 0};
+  }
+  std::shared_ptr<CElement> clone() const override { return std::make_shared<CElementSpringDXDYRZ>(*this); }
+};
+struct CElementTorsionSpring : CElement {  // src/CElementTorsionSpring.cpp:41-75
+  void getLocalStiffnessMatrices(std::vector<TStiffnessSubmatrix>& o) const override {
+    initSub(o);
+    if (E == UNINITIALIZED_VALUE) throw std::runtime_error("CElementTorsionSpring: Uninitialized parameter K");
+    o[0].matrix(5, 5) = E;
+    o[1].matrix = o[0].matrix;
+    o[2].matrix(5, 5) = -E;
+  }
+  void getLocalDoFs(std::vector<used_DoFs_t>& d) const override {
+    d.resize(2);
+    d[0] = d[1] = used_DoFs_t{false, false, false, false, false, true};
+  }
+  std::shared_ptr<CElement> clone() const override { return std::make_shared<CElementTorsionSpring>(*this); }
+};
 static std::shared_ptr<CElement> createElementByType(int t) {
   switch (t) {
     case OBO_RR: return std::make_shared<CElementBeam_2D_RR>();
     case OBO_RA: return std::make_shared<CElementBeam_2D_RA>();
     case OBO_AR: return std::make_shared<CElementBeam_2D_AR>();
     case OBO_AA: return std::make_shared<CElementBeam_2D_AA>();
+    case OBO_RD: return std::make_shared<CElementBeam_2D_RD>();
+    case OBO_SPRING_1D: return std::make_shared<CElementSpring>();
+    case OBO_SPRING_XY: return std::make_shared<CElementSpringXY>();
+    case OBO_SPRING_DXDYRZ: return std::make_shared<CElementSpringDXDYRZ>();
+    case OBO_SPRING_TORSION: return std::make_shared<CElementTorsionSpring>();
   }
   return nullptr;
 }

@@ -22,7 +22,10 @@ extern "C" {
 typedef struct obo_problem obo_problem;
 
 /* element types: CElementBeam_2D_{RR,RA,AR,AA} */
-enum { OBO_RR = 0, OBO_RA = 1, OBO_AR = 2, OBO_AA = 3 };
+enum { OBO_RR = 0, OBO_RA = 1, OBO_AR = 2, OBO_AA = 3,
+       /* SURVEY 8f N4; constants ride in elem_EAI: (E,A,Iz) for RD, (K,-,-) SPRING_1D / SPRING_TORSION,
+        * (Kx,Ky,-) SPRING_XY, (Kx,Ky,KRz) SPRING_DXDYRZ */
+       OBO_RD = 4, OBO_SPRING_1D = 5, OBO_SPRING_XY = 6, OBO_SPRING_DXDYRZ = 7, OBO_SPRING_TORSION = 8 };
 /* solver algorithm: StaticSolverAlgorithm (CFiniteElementProblem.h:69-73) */
 enum { OBO_DENSE_LLT = 0, OBO_SPARSE_SKIP_SUBK = 1 };
 

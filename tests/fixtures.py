@@ -123,6 +123,21 @@ def load_kinds():
     return build_structure(nodes, elements, IPE200, cons, [(1, "DX", 1000.0)], eloads)
 
 
+def springs_and_slider():
+    """The remaining element classes of the reference: BEAM2D_RD (rigid end + slider end), SPRING_1D
+    (along its own axis, here vertical), SPRING_XY (vertical member: local x = global -y), SPRING_DXDYRZ between two
+    coincident nodes (identity orientation; carries the reference's K11(5,5) = -KRz slip) and SPRING_TORSION.
+    Spring constants ride in the section triple (K|Kx, Ky, KRz)."""
+    sec = dict(IPE200)
+    sec.update(S1=(2e6, 0.0, 0.0), SXY=(1e6, 3e6, 0.0), SXYR=(5e5, 0.0, 2e5), ST=(1e5, 0.0, 0.0))
+    nodes = [(0, 0), (3.0, 0), (6.0, 0), (3.0, -1.0), (6.0, -1.5), (6.0, 0), (3.0, 1.0)]
+    elements = [("BEAM2D_RR", 0, 1, "IPE200"), ("BEAM2D_RD", 1, 2, "IPE200"), ("SPRING_1D", 1, 3, "S1"),
+                ("SPRING_XY", 2, 4, "SXY"), ("SPRING_DXDYRZ", 2, 5, "SXYR"), ("SPRING_TORSION", 1, 6, "ST")]
+    cons = [(0, "DXDYRZ"), (3, "DXDY"), (4, "DXDY"), (5, "DXDYRZ"), (6, "RZ")]
+    return build_structure(nodes, elements, sec, cons, [(1, "DY", -5e3), (2, "DX", 2e3), (2, "DY", -1.5e3)],
+                           [(0, 4000.0, DOWN), (1, "TEMPERATURE", 25.0)])
+
+
 def mechanism():
     """demo1 without the DY support at node 1 -> singular K_ff (the reference throws
     'Ill-conditioned matrix. Too few restrictions?', solver_static.cpp:98-105)."""
@@ -148,6 +163,7 @@ ALL = {
     "simply_supported_udl": simply_supported_udl,
     "inclined_mixed": inclined_mixed,
     "load_kinds": load_kinds,
+    "springs_and_slider": springs_and_slider,
 }
 # fixtures without nodal rotated frames (U_b = 0, identity node frames): the round-1 GPU scope
 PLAIN = [k for k in ALL if "tilted" not in k and "tilded" not in k]
