@@ -165,6 +165,10 @@ def ours_arm(args, rank, local_rank, world):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # NCCL writes its banner ("NCCL version ...") to STDOUT when NCCL_DEBUG is VERSION or higher; stdout carries
+        # exactly one JSON line, so its log goes to stderr
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "") or "NCCL_DEBUG_FILE" not in os.environ:
+            os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
         dist.init_process_group("nccl", device_id=dev)
     L, K, W = args.cases, args.steps, args.warmup
     ctx = obgpu.Context(local_rank)

@@ -37,6 +37,11 @@ static int ensure_plan(obgpu_ctx* c) {
   OB_CUDA(c, c->d_eload_elem_g.upload(eg, st));
   OB_CUDA(c, c->d_seg_ptr.upload(P.seg_ptr, st));
   OB_CUDA(c, c->d_seg_src.upload(P.seg_src, st));
+  if (P.asm_max_loc > 0) {
+    OB_CUDA(c, c->d_blk_elem_ptr.upload(P.blk_elem_ptr, st));
+    OB_CUDA(c, c->d_blk_elems.upload(P.blk_elems, st));
+    OB_CUDA(c, c->d_seg_loc.upload(P.seg_loc, st));
+  }
   OB_CUDA(c, c->d_sl_ptr.upload(P.sl_ptr, st));
   OB_CUDA(c, c->d_ff_col.upload(P.ff_col, st));
   OB_CUDA(c, c->d_ff_src.upload(P.ff_src, st));
@@ -67,6 +72,9 @@ static SparseDev sparse_dev(obgpu_ctx* c, int64_t k /* K copy */) {
   d.eload_type = c->hb.has_load_kinds ? c->d_eload_type.p : nullptr;
   d.eload_q2 = c->hb.has_load_kinds ? c->d_eload_q2.p : nullptr;
   d.seg_ptr = c->d_seg_ptr.p; d.seg_src = c->d_seg_src.p;
+  static const bool fused_ok = !(getenv("OBGPU_ASM_FUSED") && atoi(getenv("OBGPU_ASM_FUSED")) == 0);
+  d.asm_max_loc = fused_ok ? c->plan.asm_max_loc : 0;
+  d.blk_elem_ptr = c->d_blk_elem_ptr.p; d.blk_elems = c->d_blk_elems.p; d.seg_loc = c->d_seg_loc.p;
   d.sl_ptr = c->d_sl_ptr.p; d.ff_col = c->d_ff_col.p; d.ff_src = c->d_ff_src.p; d.ff_diag = c->d_ff_diag.p;
   d.bf_rowptr = c->d_bf_rowptr.p; d.bf_col = c->d_bf_col.p; d.bf_src = c->d_bf_src.p;
   d.fseg_ptr = c->d_fseg_ptr.p; d.fseg_src = c->d_fseg_src.p;
@@ -84,7 +92,9 @@ int assemble_general(obgpu_ctx* c) {
   const int64_t L = c->L, LK = c->has_case_eai ? L : 1;
   c->LK = LK;
   const int64_t Etot = c->hb.Etot(), nnz = c->sym.nnz_tot(), nf = c->sym.nf_tot();
-  OB_CUDA(c, c->d_elem_k.reserve(size_t(LK) * Etot * ELEM_K));
+  const bool fused = sparse_dev(c, 0).asm_max_loc > 0;
+  if (!fused) OB_CUDA(c, c->d_elem_k.reserve(size_t(LK) * Etot * ELEM_K));
+  c->elem_k_valid = !fused;
   OB_CUDA(c, c->d_kval.reserve(size_t(LK) * std::max<int64_t>(nnz, 1)));
   OB_CUDA(c, c->d_ff_val.reserve(std::max<size_t>(c->plan.ff_col.size(), 1)));
   OB_CUDA(c, c->d_bf_val.reserve(std::max<size_t>(c->plan.bf_col.size(), 1)));
@@ -94,9 +104,14 @@ int assemble_general(obgpu_ctx* c) {
   for (int64_t k = 0; k < LK; k++) {
     SparseDev d = sparse_dev(c, k);
     const double* eai = c->has_case_eai ? c->d_case_eai.p + size_t(k) * 3 * Etot : c->d_elem_EAI.p;
-    OB_CUDA(c, launch_elem_stiff(d, eai, c->stream));
-    OB_CUDA(c, launch_assemble(d, c->stream));
-    launches += 2;
+    if (fused) {  // K1 fused into K4: no element-block array in HBM
+      OB_CUDA(c, launch_assemble_fused(d, eai, c->stream));
+      launches += 1;
+    } else {
+      OB_CUDA(c, launch_elem_stiff(d, eai, c->stream));
+      OB_CUDA(c, launch_assemble(d, c->stream));
+      launches += 2;
+    }
   }
   for (int64_t cs = 0; cs < L; cs++) {
     SparseDev d = sparse_dev(c, 0);
@@ -261,7 +276,18 @@ int download_general(obgpu_ctx* c, int which, void* out, bool& handled) {
   const void* src;
   size_t bytes;
   if (which == OBGPU_RES_KVAL) { src = c->d_kval.p; bytes = size_t(c->LK) * c->sym.nnz_tot() * 8; }
-  else if (which == OBGPU_RES_ELEM_K) { src = c->d_elem_k.p; bytes = size_t(c->LK) * c->hb.Etot() * ELEM_K * 8; }
+  else if (which == OBGPU_RES_ELEM_K) {
+    if (!c->elem_k_valid) {  // the fused assembly never materialises the element blocks: produce them on demand
+      OB_CUDA(c, c->d_elem_k.reserve(size_t(c->LK) * c->hb.Etot() * ELEM_K));
+      for (int64_t k = 0; k < c->LK; k++) {
+        SparseDev d = sparse_dev(c, k);
+        const double* eai = c->has_case_eai ? c->d_case_eai.p + size_t(k) * 3 * c->hb.Etot() : c->d_elem_EAI.p;
+        OB_CUDA(c, launch_elem_stiff(d, eai, c->stream));
+      }
+      c->elem_k_valid = true;
+    }
+    src = c->d_elem_k.p; bytes = size_t(c->LK) * c->hb.Etot() * ELEM_K * 8;
+  }
   else { src = c->d_Ff.p; bytes = size_t(c->L) * c->sym.nf_tot() * 8; }
   if (bytes) OB_CUDA(c, cudaMemcpyAsync(out, src, bytes, cudaMemcpyDeviceToHost, c->stream));
   OB_CUDA(c, cudaStreamSynchronize(c->stream));

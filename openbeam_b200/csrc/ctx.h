@@ -55,6 +55,9 @@ struct obgpu_ctx {
   obgpu::DevBuf<double> d_elem_k, d_kval, d_ff_val, d_bf_val, d_eload_g, d_Eq, d_scal, d_partial;
   obgpu::DevBuf<double> d_pcgvec;  // p | ap | r | z | minv in one slab: the L2 persistence window of the PCG loop
   obgpu::DevBuf<unsigned int> d_counter;
+  obgpu::DevBuf<int32_t> d_blk_elem_ptr, d_blk_elems;
+  obgpu::DevBuf<uint16_t> d_seg_loc;
+  bool elem_k_valid = false;  // d_elem_k holds the element blocks of the current batch (only the two-kernel path fills it)
   double* h_scal = nullptr;  // pinned [8]
   double pcg_relres = 0;
 

@@ -80,11 +80,15 @@ struct SparseDev {
   const double* eload_dir;
   const uint8_t* eload_type;   // null when every load is DISTRIB_UNIFORM
   const double* eload_q2;
+  const int32_t *blk_elem_ptr, *blk_elems;  // fused assembly plan (null: two-kernel K1 + K4)
+  const uint16_t* seg_loc;
+  int asm_max_loc;
   const int32_t *seg_ptr, *seg_src, *sl_ptr, *ff_col, *ff_src, *ff_diag, *bf_rowptr, *bf_col, *bf_src, *fseg_ptr, *fseg_src;
   double *elem_k, *kval, *ff_val, *bf_val, *eload_g, *Eq;
 };
 cudaError_t launch_elem_stiff(const SparseDev& d, const double* eai, cudaStream_t st);
 cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st);
+cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStream_t st);
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st);
 cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, const double* eai, double* F_f,
                                cudaStream_t st);

@@ -79,6 +79,75 @@ __global__ void __launch_bounds__(256) k_assemble_seg(int64_t nnz, const int32_t
   kval[g] = acc;
 }
 
+// K1 fused into K4.  One CTA owns ASM_SLOTS consecutive K slots; the host plan lists the elements those slots draw
+// from (a slot block of a node-ordered mesh is a compact patch: ~60 elements per 1024 slots on a grid frame).  The CTA
+// computes their global blocks into shared memory (lane = element, records at an odd stride) and every thread then
+// sums its slots from there in the reference's triplet order.  HBM sees the element inputs, 4 B per slot of segment
+// pointers, 2 B per triplet of block-local sources and the K values once: no 168-byte element records are written
+// and gathered back 8 bytes at a time (400 MB of reads at C4 in the two-kernel version).
+constexpr int ASM_SLOTS = SparsePlan::ASM_SLOTS;
+constexpr int ASM_SPT = 4;                        // consecutive slots per thread
+constexpr int ASM_THREADS = ASM_SLOTS / ASM_SPT;  // 128 threads per CTA: short element phase, 16 CTAs/SM to overlap it
+__global__ void __launch_bounds__(ASM_THREADS) k_assemble_fused(int64_t nnz, const int32_t* __restrict__ seg_ptr,
+                                                        const uint16_t* __restrict__ seg_loc,
+                                                        const int32_t* __restrict__ blk_elem_ptr, const int32_t* __restrict__ blk_elems,
+                                                        const uint2* __restrict__ elem_nodes, const uint8_t* __restrict__ elem_type,
+                                                        const double* __restrict__ eai, const double2* __restrict__ node_xy,
+                                                        const int32_t* __restrict__ elem_node0, double* __restrict__ kval) {
+  extern __shared__ double kes[];  // [nloc][ELEM_K]
+  constexpr int SPT = ASM_SPT;
+  const int64_t g = int64_t(blockIdx.x) * ASM_SLOTS + SPT * threadIdx.x;
+  int32_t p[SPT + 1];  // segment pointers first: their latency overlaps the element phase
+#pragma unroll
+  for (int r = 0; r <= SPT; r++) p[r] = seg_ptr[min(g + r, nnz)];
+  const int32_t b0 = blk_elem_ptr[blockIdx.x], nloc = blk_elem_ptr[blockIdx.x + 1] - b0;
+  for (int i = threadIdx.x; i < nloc; i += blockDim.x) {
+    const int64_t e = blk_elems[b0 + i];
+    const uint2 nd = elem_nodes[e];
+    const int64_t n0 = elem_node0[e];
+    const double2 p0 = node_xy[n0 + nd.x], p1 = node_xy[n0 + nd.y];
+    const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
+    const ElemLocalK lk = elem_local_k(elem_type[e], eai[3 * e], eai[3 * e + 1], eai[3 * e + 2], g);
+    double ke[ELEM_K];
+    elem_global_k(lk, g, ke);
+#pragma unroll
+    for (int k = 0; k < ELEM_K; k++) kes[i * ELEM_K + k] = ke[k];
+  }
+  __syncthreads();
+  // each thread owns 4 CONSECUTIVE slots: one read of 5 consecutive segment pointers, one contiguous run of
+  // block-local sources, 32 contiguous bytes of K values (two dependent global round trips in all)
+  if (g >= nnz) return;
+  double acc[SPT];
+  // a slot sums 1-4 element entries on a frame (more only where many members meet): the first four sources of every
+  // slot are loaded together (16 independent loads per thread in flight), the rest in a loop.  Order = triplet order;
+  // structural zeros of the triplet list (0xFFFF) add +0 like the reference.
+  unsigned src[SPT][4];
+#pragma unroll
+  for (int r = 0; r < SPT; r++)
+#pragma unroll
+    for (int i = 0; i < 4; i++) src[r][i] = p[r] + i < p[r + 1] ? unsigned(seg_loc[p[r] + i]) : 0xFFFFu;
+#pragma unroll
+  for (int r = 0; r < SPT; r++) {
+    acc[r] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+      if (p[r] + i < p[r + 1]) acc[r] += src[r][i] != 0xFFFFu ? kes[src[r][i]] : 0.0;
+    for (int32_t t = p[r] + 4; t < p[r + 1]; t++) {
+      const unsigned s2 = seg_loc[t];
+      acc[r] += s2 != 0xFFFFu ? kes[s2] : 0.0;
+    }
+  }
+  if (g + SPT <= nnz && (reinterpret_cast<uintptr_t>(kval + g) & 15) == 0) {
+    double2* o = reinterpret_cast<double2*>(kval + g);
+#pragma unroll
+    for (int r = 0; r < SPT; r += 2) o[r / 2] = make_double2(acc[r], acc[r + 1]);
+  } else {
+#pragma unroll
+    for (int r = 0; r < SPT; r++)
+      if (g + r < nnz) kval[g + r] = acc[r];
+  }
+}
+
 __global__ void __launch_bounds__(256) k_gather(int64_t n, const int32_t* __restrict__ src, const double* __restrict__ in,
                                                 double* __restrict__ out) {
   const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -160,6 +229,18 @@ cudaError_t launch_elem_stiff(const SparseDev& d, const double* eai, cudaStream_
 }
 cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st) {
   k_assemble_seg<<<nblk(d.nnz), 256, 0, st>>>(d.nnz, d.seg_ptr, d.seg_src, d.elem_k, d.kval);
+  return cudaGetLastError();
+}
+cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStream_t st) {
+  const size_t smem = size_t(d.asm_max_loc) * ELEM_K * sizeof(double);
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaError_t e = cudaFuncSetAttribute(k_assemble_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return e;
+    configured = smem;
+  }
+  k_assemble_fused<<<nblk(d.nnz, ASM_SLOTS), ASM_THREADS, smem, st>>>(d.nnz, d.seg_ptr, d.seg_loc, d.blk_elem_ptr, d.blk_elems,
+                                                              d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.kval);
   return cudaGetLastError();
 }
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st) {

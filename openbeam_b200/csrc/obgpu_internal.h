@@ -112,6 +112,15 @@ struct TinyProgram {
 struct SparsePlan {
   bool valid = false;
   std::vector<int32_t> seg_ptr, seg_src;      // [nnz_tot+1], [T_tot]: K slot <- ELEM_K entries (elem*21+cid, -1 = zero)
+  // fused K1+K4 (k_assemble_fused): K slots in blocks of ASM_SLOTS; per block the elements its slots draw from
+  // (blk_elems[blk_elem_ptr[b] ..]) and per triplet the block-local source (local element * 21 + cid, 0xFFFF = zero)
+  #ifndef OBGPU_ASM_SLOTS
+#define OBGPU_ASM_SLOTS 512
+#endif
+  static constexpr int ASM_SLOTS = OBGPU_ASM_SLOTS;
+  std::vector<int32_t> blk_elem_ptr, blk_elems;
+  std::vector<uint16_t> seg_loc;
+  int asm_max_loc = 0;                        // largest element list of a block; 0 = fused assembly not available
   // K_ff, full symmetric over global free indices, in SELL-32 order (see build_sparse_plan): sl_ptr[nf_tot/32 + 1]
   // slice offsets, ff_col / ff_src (K slot, -1 = padding) per stored entry; ff_rowptr is scratch of the builder
   std::vector<int32_t> ff_rowptr, ff_col, ff_src, sl_ptr;

@@ -24,6 +24,39 @@ int build_sparse_plan(const HostBatch& hb, const Symbolic& sym, SparsePlan& P, s
   P.seg_src.resize(T);
   for (int64_t i = 0; i <= nnz; i++) P.seg_ptr[i] = int32_t(sym.seg_ptr[i]);
   for (int64_t i = 0; i < T; i++) P.seg_src[i] = int32_t(sym.seg_src[i]);
+  // ---- fused assembly plan: block-local element lists ----
+  {
+    const int64_t nblk = (nnz + SparsePlan::ASM_SLOTS - 1) / SparsePlan::ASM_SLOTS;
+    std::vector<int32_t> stamp(hb.Etot(), -1), local(hb.Etot(), 0);
+    P.blk_elem_ptr.assign(nblk + 1, 0);
+    P.seg_loc.resize(T);
+    bool ok = true;
+    for (int64_t b = 0; b < nblk && ok; b++) {
+      const int64_t g0 = b * SparsePlan::ASM_SLOTS, g1 = std::min<int64_t>(nnz, g0 + SparsePlan::ASM_SLOTS);
+      int32_t nloc = 0;
+      for (int64_t t = P.seg_ptr[g0]; t < P.seg_ptr[g1]; t++) {
+        const int32_t src = P.seg_src[t];
+        if (src < 0) {
+          P.seg_loc[t] = 0xFFFF;
+          continue;
+        }
+        const int32_t e = src / ELEM_K, cid = src - e * ELEM_K;
+        if (stamp[e] != int32_t(b)) {
+          stamp[e] = int32_t(b);
+          local[e] = nloc++;
+          P.blk_elems.push_back(e);
+        }
+        if (local[e] * ELEM_K + cid >= 0xFFFF) ok = false;
+        P.seg_loc[t] = uint16_t(local[e] * ELEM_K + cid);
+      }
+      P.blk_elem_ptr[b + 1] = int32_t(P.blk_elems.size());
+      P.asm_max_loc = std::max(P.asm_max_loc, nloc);
+    }
+    if (!ok || size_t(P.asm_max_loc) * ELEM_K * sizeof(double) > size_t(200) * 1024) {  // irregular: two-kernel path
+      P.asm_max_loc = 0;
+      P.blk_elem_ptr.clear(); P.blk_elems.clear(); P.seg_loc.clear();
+    }
+  }
   // ---- K_ff (full symmetric) and K_bf ----
   std::vector<int32_t> lowc(nf, 0), upc(nf, 0), blow(nb, 0), bup(nb, 0);
   auto for_each_entry = [&](auto&& fn) {
