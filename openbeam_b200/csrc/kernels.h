@@ -20,6 +20,7 @@ struct TinyArgs {
   int32_t* fail;           // [1] set to 1 when any system has info != 0
 };
 cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st);
+cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStream_t st);  // tiny_jit.cu
 
 // Per-structure record of the batched kernels (one 64-byte line per structure).
 struct __align__(16) FrameMeta {

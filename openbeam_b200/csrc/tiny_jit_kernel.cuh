@@ -1,0 +1,275 @@
+// tiny_jit_kernel.cuh — the thread-per-case kernel SPECIALISED TO ONE TOPOLOGY (compiled at run time by NVRTC, see
+// tiny_jit.cpp).  Same pipeline and same arithmetic as k_tiny_fused (kernels_tiny.cu): per case the element
+// stiffnesses are formed, rotated, assembled, factored (LDL^T) and solved, then end forces and reactions — nothing is
+// hoisted out of the case loop.  What changes is that the integer topology program (DOF maps, element->K_ff slots,
+// load slots) is a set of compile-time constants (the generated prelude `TJ_*`), so
+//   * every loop over elements / loads / DOFs unrolls and every index is an immediate,
+//   * K_ff, F and U are plain register arrays from first touch to last use: no shared-memory read-modify-write, no
+//     dispatch on block positions, no per-entry skip tests (entries that leave K_ff simply generate no code),
+//   * it serves ANY topology within the tiny limits, not only the node-blocked ones.
+// Shared memory only stages the per-case inputs (cp.async, one block of cases ahead) and the coalesced result stores.
+// The floating-point inputs (coordinates, sections, base load values) stay run-time kernel parameters.
+//
+// The prelude must define:  TJ_N, TJ_E, TJ_n, TJ_NF, TJ_NB, TJ_NL, TJ_EL, TJ_MINB and the constexpr arrays
+//   TJ_enode[2E], TJ_etype[E], TJ_udof[6E] (-1 absent, k free, k|64 bounded), TJ_edst[21E] (packed K_ff index or -1),
+//   TJ_elptr[E+1], TJ_elslot[EL], TJ_nldst[NL], TJ_freek[NF], TJ_bndk[NB]
+// (arrays padded to at least one entry), then include this file after beam_math.cuh.
+#pragma once
+
+namespace obgpu {
+
+struct TinyJitVals {  // run-time values of the shared topology (kernel parameter -> constant bank)
+  double xy[2 * TJ_N];
+  double eai[3 * TJ_E];
+  double nlval[TJ_NL > 0 ? TJ_NL : 1];
+  double elq[TJ_EL > 0 ? TJ_EL : 1];
+  double eldir[TJ_EL > 0 ? 2 * TJ_EL : 1];
+};
+
+__host__ __device__ constexpr int tj_row(int d) {
+  int i = 0;
+  while ((i + 1) * (i + 2) / 2 <= d) i++;
+  return i;
+}
+__host__ __device__ constexpr int tj_gcd32(int c) {
+  return (c % 32 == 0) ? 32 : (c % 16 == 0) ? 16 : (c % 8 == 0) ? 8 : (c % 4 == 0) ? 4 : (c % 2 == 0) ? 2 : 1;
+}
+
+__device__ __forceinline__ void tj_cp_async8(double* smem_dst, const double* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(unsigned(__cvta_generic_to_shared(smem_dst))), "l"(gsrc));
+}
+
+// Coalesced store of a [32 cases][C] record block staged as W[i*CS + t] (see StoreMap in kernels_tiny.cu).
+template <int C, int CS>
+struct TjStoreMap {
+  static constexpr int G = tj_gcd32(C), PER = C / G, TSTEP = 32 / G;
+  int so[PER];
+  __device__ __forceinline__ void init(int lane) {
+#pragma unroll
+    for (int r0 = 0; r0 < PER; r0++) {
+      const int j = r0 * 32 + lane, t = j / C, i = j - t * C;
+      so[r0] = i * CS + t;
+    }
+  }
+  __device__ __forceinline__ void store(double* __restrict__ g, const double* W, int lane, int cnt) const {
+    if (cnt == 32) {
+#pragma unroll
+      for (int r = 0; r < C; r++) g[r * 32 + lane] = W[so[r % PER] + (r / PER) * TSTEP];
+    } else {
+      for (int j = lane; j < cnt * C; j += 32) {
+        const int t = j / C, i = j - t * C;
+        g[j] = W[i * CS + t];
+      }
+    }
+  }
+};
+
+constexpr int TJ_BLOCK = 128;
+constexpr int TJ_CS = TJ_BLOCK + 3;  // column stride = 3 (mod 16 doubles): fewest bank conflicts of the transposed reads
+constexpr int TJ_XW = TJ_NF > TJ_NB ? (TJ_NF > 0 ? TJ_NF : 1) : (TJ_NB > 0 ? TJ_NB : 1);  // widest U_f / F_f / F_b record
+
+extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const __grid_constant__ TinyJitVals V, TinyArgs a) {
+  constexpr int E = TJ_E, n = TJ_n, NF = TJ_NF, NB = TJ_NB, NL = TJ_NL, EL = TJ_EL, CS = TJ_CS;
+  extern __shared__ __align__(16) double smem[];
+  // shared: G[E][4] = c,s,L,1/L | LP[EL][2] | staging columns SS[12] (stress record, zero columns 2,3,4,8,9,10) |
+  // SX[XW] (U_f/F_f/F_b records) | SN[NL] | SQ[2][EL]   (columns are [CS] wide, one entry per thread)
+  double* G = smem;
+  double* LP = G + 4 * E;
+  double* SS = LP + 2 * (EL > 0 ? EL : 1) + threadIdx.x;
+  double* SX = SS + 12 * CS;
+  double* SN = SX + TJ_XW * CS;
+  double* SQ = SN + (a.case_nl ? NL * CS : 0);
+  const int lane = threadIdx.x & 31, wl0 = threadIdx.x & ~31;
+  const double* SSW = SS - threadIdx.x + wl0;
+  const double* SXW = SX - threadIdx.x + wl0;
+  if (threadIdx.x < E) {
+    const int e = threadIdx.x, na = TJ_enode[2 * e], nbn = TJ_enode[2 * e + 1];
+    const ElemGeom g = elem_geom(V.xy[2 * na], V.xy[2 * na + 1], V.xy[2 * nbn], V.xy[2 * nbn + 1]);
+    G[4 * e] = g.c; G[4 * e + 1] = g.s; G[4 * e + 2] = g.L; G[4 * e + 3] = g.invL;
+    for (int j = TJ_elptr[e]; j < TJ_elptr[e + 1]; j++) {
+      const int slot = TJ_elslot[j];
+      const LoadProj pr = load_proj(g, V.eldir[2 * slot], V.eldir[2 * slot + 1]);
+      LP[2 * slot] = pr.plong; LP[2 * slot + 1] = pr.pperp;
+    }
+  }
+  SS[2 * CS] = 0.0; SS[3 * CS] = 0.0; SS[4 * CS] = 0.0;
+  SS[8 * CS] = 0.0; SS[9 * CS] = 0.0; SS[10 * CS] = 0.0;
+  TjStoreMap<12, CS> map12;
+  TjStoreMap<(NF > 0 ? NF : 1), CS> mapNF;
+  TjStoreMap<(NB > 0 ? NB : 1), CS> mapNB;
+  map12.init(lane);
+  mapNF.init(lane);
+  mapNB.init(lane);
+  int go12[3];
+#pragma unroll
+  for (int r0 = 0; r0 < 3; r0++) {
+    const int j = r0 * 32 + lane, t = j / 12, i = j - t * 12;
+    go12[r0] = t * E * 12 + i;
+  }
+  __syncthreads();
+
+  const long long stride = (long long)gridDim.x * TJ_BLOCK;
+  const long long last = a.n_cases - 1;
+  auto prefetch = [&](long long b, int buf) {
+    const long long c = min(b + (long long)threadIdx.x, last);
+    if (a.case_nl)
+#pragma unroll
+      for (int i = 0; i < NL; i++) tj_cp_async8(SN + i * CS, a.case_nl + c * NL + i);
+    if (a.case_q)
+#pragma unroll
+      for (int i = 0; i < EL; i++) tj_cp_async8(SQ + (buf * EL + i) * CS, a.case_q + c * EL + i);
+    asm volatile("cp.async.commit_group;");
+  };
+  int buf = 0;
+  long long base = (long long)blockIdx.x * TJ_BLOCK;
+  if (base < a.n_cases) prefetch(base, 0);
+  for (; base < a.n_cases; base += stride, buf ^= 1) {
+    const bool valid = base + threadIdx.x <= last;
+    const long long cs = min(base + (long long)threadIdx.x, last);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    // ---- registers: lower triangle of K_ff, F/U over all problem DOFs ----
+    double A[NF + 1][NF + 1], fu[n + 1], b[NF + 1];
+#pragma unroll
+    for (int i = 0; i < NF; i++)
+#pragma unroll
+      for (int j = 0; j <= i; j++) A[i][j] = 0.0;
+#pragma unroll
+    for (int i = 0; i < n; i++) fu[i] = 0.0;
+    // nodal loads (assemble.cpp:326-341, free DOFs only)
+#pragma unroll
+    for (int i = 0; i < NL; i++)
+      if (TJ_nldst[i] >= 0) fu[TJ_nldst[i] >= 0 ? TJ_nldst[i] : 0] += a.case_nl ? SN[i * CS] : V.nlval[i];
+    if (base + stride < a.n_cases) prefetch(base + stride, buf ^ 1);
+    const double* Q = SQ + buf * EL * CS;
+    // ---- stage A: element stiffness -> K_ff registers, equivalent loads -> F registers ----
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+      constexpr int dummy = 0;
+      (void)dummy;
+      const int type = TJ_etype[e];
+      ElemGeom g;
+      g.c = G[4 * e]; g.s = G[4 * e + 1]; g.L = G[4 * e + 2]; g.invL = G[4 * e + 3];
+      double Ee, Ae, Ie;
+      if (a.case_eai) {
+        const double* p = a.case_eai + (cs * E + e) * 3;
+        Ee = __ldg(p); Ae = __ldg(p + 1); Ie = __ldg(p + 2);
+      } else {
+        Ee = V.eai[3 * e]; Ae = V.eai[3 * e + 1]; Ie = V.eai[3 * e + 2];
+      }
+      const ElemLocalK lk = elem_local_k(type, Ee, Ae, Ie, g);
+      double ke[ELEM_K];
+      elem_global_k(lk, g, ke);
+#pragma unroll
+      for (int k = 0; k < ELEM_K; k++) {
+        const int d = TJ_edst[ELEM_K * e + k];
+        if (d >= 0) A[tj_row(d >= 0 ? d : 0)][(d >= 0 ? d : 0) - tj_row(d >= 0 ? d : 0) * (tj_row(d >= 0 ? d : 0) + 1) / 2] += ke[k];
+      }
+#pragma unroll
+      for (int j = TJ_elptr[e]; j < TJ_elptr[e + 1]; j++) {
+        const int slot = TJ_elslot[j];
+        const double q = a.case_q ? Q[slot * CS] : V.elq[slot];
+        LoadProj pr;
+        pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
+        double gl[6], ex[6];
+        uniform_load_p(type, g, q, pr, gl, ex);
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+          const int d = TJ_udof[6 * e + k];
+          if (d >= 0) fu[(d >= 0 ? d : 0) & 63] += gl[k];
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NF; i++) b[i] = fu[TJ_freek[i]];
+    const long long c0 = base + wl0;
+    const int cnt = int(min(32LL, a.n_cases - c0));
+    if (a.F_f) {
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < NF; i++) SX[i * CS] = b[i];
+      __syncwarp();
+      if (NF > 0) mapNF.store(a.F_f + c0 * NF, SXW, lane, cnt);
+      __syncwarp();
+    }
+    const int info = ldlt_solve_regs<NF>(A, b);
+    if (valid) {
+      a.info[cs] = info;
+      if (info != 0) atomicOr(a.fail, 1);
+    }
+#pragma unroll
+    for (int i = 0; i < NF; i++) {
+      fu[TJ_freek[i]] = b[i];
+      SX[i * CS] = b[i];
+    }
+    __syncwarp();
+    if (NF > 0) mapNF.store(a.U_f + c0 * NF, SXW, lane, cnt);
+    // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
+#pragma unroll
+    for (int i = 0; i < NB; i++) fu[TJ_bndk[i]] = -fu[TJ_bndk[i]];
+    // ---- stage B: element end forces (K10), reactions (K_bf U_f = sum of element end forces, U_b = 0) ----
+#pragma unroll
+    for (int e = 0; e < E; e++) {
+      const int type = TJ_etype[e];
+      ElemGeom g;
+      g.c = G[4 * e]; g.s = G[4 * e + 1]; g.L = G[4 * e + 2]; g.invL = G[4 * e + 3];
+      double Ee, Ae, Ie;
+      if (a.case_eai) {
+        const double* p = a.case_eai + (cs * E + e) * 3;
+        Ee = __ldg(p); Ae = __ldg(p + 1); Ie = __ldg(p + 2);
+      } else {
+        Ee = V.eai[3 * e]; Ae = V.eai[3 * e + 1]; Ie = V.eai[3 * e + 2];
+      }
+      const ElemLocalK lk = elem_local_k(type, Ee, Ae, Ie, g);
+      double ug[6], es[6];
+#pragma unroll
+      for (int k = 0; k < 6; k++) {
+        const int d = TJ_udof[6 * e + k];
+        ug[k] = (d >= 0 && d < 64) ? fu[(d >= 0 && d < 64) ? d : 0] : 0.0;
+      }
+      elem_end_forces(lk, g, ug, es);
+      const double gf[6] = {g.c * es[0] - g.s * es[1], g.s * es[0] + g.c * es[1], es[2],
+                            g.c * es[3] - g.s * es[4], g.s * es[3] + g.c * es[4], es[5]};
+#pragma unroll
+      for (int k = 0; k < 6; k++) {
+        const int d = TJ_udof[6 * e + k];
+        if (d >= 64) fu[(d >= 64 ? d : 64) & 63] += gf[k];
+      }
+      if (a.stress) {
+        double ext[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int j = TJ_elptr[e]; j < TJ_elptr[e + 1]; j++) {
+          const int slot = TJ_elslot[j];
+          const double q = a.case_q ? Q[slot * CS] : V.elq[slot];
+          LoadProj pr;
+          pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
+          double gl[6], ex[6];
+          uniform_load_p(type, g, q, pr, gl, ex);
+#pragma unroll
+          for (int k = 0; k < 6; k++) ext[k] += ex[k];
+        }
+        __syncwarp();
+        SS[0 * CS] = -es[0] + ext[0]; SS[1 * CS] = -es[1] + ext[1]; SS[5 * CS] = -es[2] + ext[2];
+        SS[6 * CS] = es[3] + ext[3];  SS[7 * CS] = es[4] + ext[4];  SS[11 * CS] = es[5] + ext[5];
+        __syncwarp();
+        double* gs = a.stress + (c0 * E + e) * 12;
+        if (cnt == 32) {
+#pragma unroll
+          for (int r = 0; r < 12; r++) gs[go12[r % 3] + (r / 3) * 96 * E] = SSW[map12.so[r % 3] + (r / 3) * 8];
+        } else {
+          for (int j = lane; j < cnt * 12; j += 32) {
+            const int t = j / 12, i = j - t * 12;
+            gs[t * E * 12 + i] = SSW[i * CS + t];
+          }
+        }
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < NB; i++) SX[i * CS] = fu[TJ_bndk[i]];
+    __syncwarp();
+    if (NB > 0) mapNB.store(a.F_b + c0 * NB, SXW, lane, cnt);
+    __syncwarp();
+  }
+}
+
+}  // namespace obgpu
