@@ -86,8 +86,11 @@ typedef struct obgpu_solve_opts {
   int with_stress;   /* fuse postProcCalcStress into the solve kernel (default 1) */
   double rtol;       /* PCG: ||r||_2 <= rtol*||b||_2 (default 1e-12)             */
   int max_iter;      /* PCG: default 20*sqrt(n_f)+1000                            */
-  int reserved;
+  int flags;         /* OBGPU_SOLVE_* bits (default 0)                            */
 } obgpu_solve_opts;
+/* OBGPU_SOLVE_SKIP_FF: do not keep BuildProblemInfo::F_f (the assembled free-DOF load vector is an intermediate of the
+ * fused kernel; storing it costs 8*n_f bytes per case of HBM writes).  OBGPU_RES_FF is then unavailable after the solve. */
+enum { OBGPU_SOLVE_SKIP_FF = 1 };
 
 /* sizes: obgpu_get_sizes fills out[0..11] with
  * S, L, Ntot, Etot, n_tot, nf_tot, nb_tot, T_tot (triplets), nnz_tot (K upper), Ctot, NLtot, ELtot */

@@ -149,7 +149,7 @@ class CStructureProblem {
     updateAll();
     obgpu_solve_opts o;
     o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI : OBGPU_BATCHED_LDLT;
-    o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.reserved = 0;
+    o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.flags = 0;
     check(obgpu_solve_static(ctx_, &o));
     const auto z = sizes();
     std::vector<int32_t> info(z[0] * z[1]);

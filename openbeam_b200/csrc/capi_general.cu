@@ -145,6 +145,7 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   c->launches = double(c->frame_classes.size());
   c->pcg_iters = 0;
   c->solved = true;
+  c->have_ff = true;
   c->have_stress = o.with_stress != 0;
   return OBGPU_OK;
 }

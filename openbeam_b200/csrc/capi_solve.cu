@@ -51,7 +51,7 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
   int rc = ensure_symbolic(c);
   if (rc != OBGPU_OK) return rc;
   obgpu_solve_opts o;
-  o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.reserved = 0;
+  o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.flags = 0;
   if (opts) o = *opts;
   if (o.method == OBGPU_BATCHED_LDLT && c->prog.valid) {
     rc = alloc_results(c, c->L, o.with_stress != 0);
@@ -59,7 +59,9 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
     OB_CUDA(c, cudaMemsetAsync(c->d_fail.p, 0, sizeof(int32_t), c->stream));
     TinyArgs a = tiny_args(c, c->L, c->has_case_nl ? c->d_case_nl.p : nullptr, c->has_case_q ? c->d_case_q.p : nullptr,
                            c->has_case_eai ? c->d_case_eai.p : nullptr, c->d_Uf.p, c->d_Fb.p,
-                           o.with_stress ? c->d_stress.p : nullptr, c->d_Ff.p, c->d_info.p);
+                           o.with_stress ? c->d_stress.p : nullptr,
+                           (o.flags & OBGPU_SOLVE_SKIP_FF) ? nullptr : c->d_Ff.p, c->d_info.p);
+    c->have_ff = !(o.flags & OBGPU_SOLVE_SKIP_FF);
     OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream));
     OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
@@ -86,7 +88,7 @@ int obgpu_stress(obgpu_ctx* c) {
   if (!c->solved) return fail(c, OBGPU_ESEQUENCE, "obgpu_stress before obgpu_solve_static");
   if (c->have_stress) return OBGPU_OK;
   obgpu_solve_opts o;
-  o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.reserved = 0;
+  o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.flags = 0;
   return obgpu_solve_static(c, &o);  // the fused kernels recompute; cheap relative to a second pass over HBM
 }
 
@@ -98,7 +100,9 @@ int obgpu_device_ptr(obgpu_ctx* c, int which, void** p) {
     case OBGPU_RES_FB: *p = c->d_Fb.p; break;
     case OBGPU_RES_STRESS: *p = c->d_stress.p; break;
     case OBGPU_RES_INFO: *p = c->d_info.p; break;
-    case OBGPU_RES_FF: *p = c->d_Ff.p; break;
+    case OBGPU_RES_FF:
+      if (!c->have_ff) return fail(c, OBGPU_ESEQUENCE, "F_f was not kept (OBGPU_SOLVE_SKIP_FF)");
+      *p = c->d_Ff.p; break;
     case OBGPU_RES_UB: *p = c->d_Ub.p; break;
     default: return OBGPU_EINVAL;
   }
@@ -117,7 +121,9 @@ int obgpu_download(obgpu_ctx* c, int which, void* out) {
   size_t bytes = 0;
   switch (which) {
     case OBGPU_RES_UF: src = c->d_Uf.p; bytes = size_t(c->L) * s.nf_tot() * 8; break;
-    case OBGPU_RES_FF: src = c->d_Ff.p; bytes = size_t(c->L) * s.nf_tot() * 8; break;
+    case OBGPU_RES_FF:
+      if (!c->have_ff) return fail(c, OBGPU_ESEQUENCE, "F_f was not kept (OBGPU_SOLVE_SKIP_FF)");
+      src = c->d_Ff.p; bytes = size_t(c->L) * s.nf_tot() * 8; break;
     case OBGPU_RES_FB: src = c->d_Fb.p; bytes = size_t(c->L) * s.nb_tot() * 8; break;
     case OBGPU_RES_UB: src = c->d_Ub.p; bytes = size_t(s.nb_tot()) * 8; break;
     case OBGPU_RES_STRESS:

@@ -28,7 +28,7 @@ struct obgpu_ctx {
   obgpu::DevBuf<int64_t> d_free_off, d_bnd_off;  // [S+1]
   obgpu::DevBuf<uint8_t> d_bnd_dofid;            // [nb_tot]
   obgpu::DevBuf<int32_t> d_fail;  // [1] OR of per-system failures of the last solve
-  bool solved = false, have_stress = false;
+  bool solved = false, have_stress = false, have_ff = true;
   // general path: the batch arrays + symbolic slots on the device
   bool dev_batch = false;
   obgpu::DevBuf<double> d_node_rot, d_eload_q2;

@@ -102,7 +102,7 @@ void arr(std::string& s, const char* name, const int32_t* v, int cnt) {
   s += "};\n";
 }
 
-constexpr int JIT_BLOCK = 128, JIT_CS = JIT_BLOCK + 3;
+constexpr int JIT_BLOCK = 128, JIT_CS = JIT_BLOCK, JIT_RS = JIT_BLOCK + 16;  // = TJ_BLOCK, TJ_CS, TJ_RS of the kernel
 
 }  // namespace
 
@@ -126,13 +126,23 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
   static std::map<std::string, Compiled> cache;
   std::string key(reinterpret_cast<const char*>(I), size_t(a.n_ints) * sizeof(int32_t));
   key += char('0' + device);
+  key += a.F_f ? 'F' : '-';  // the kernel is also specialised on whether F_f is kept (staging rows, occupancy)
   std::lock_guard<std::mutex> lock(mu);
   Compiled& c = cache[key];
   if (c.failed) return cudaErrorNotSupported;
   if (!c.fn) {
     const int nfp = nf * (nf + 1) / 2;
-    const int minb = nfp + n <= 40 ? 5 : nfp + n <= 64 ? 3 : 2;  // register budget: K_ff + F/U live in registers
+    int minb = nfp + n <= 40 ? 5 : nfp + n <= 64 ? 3 : 2;  // register budget: K_ff + F/U live in registers
+    if (getenv("OBGPU_TINY_JIT_MINB")) minb = atoi(getenv("OBGPU_TINY_JIT_MINB"));  // tuning experiments
+    // result records through the bulk-copy engine when a CTA's staging rows (final layout, 4 warps x 32 cases) stay small
+    const size_t bulk_bytes = size_t(JIT_BLOCK / 32) * (size_t(32) * (12 * E + (a.F_f ? 2 : 1) * nf + nb) + 16) * 8;
+    bool bulk = bulk_bytes <= 56 * 1024;
+    if (const char* ev = getenv("OBGPU_TINY_JIT_BULK")) bulk = bulk && atoi(ev) != 0;
     std::string src;
+    src += std::string("#define TJ_BULK ") + (bulk ? "1\n" : "0\n");
+    src += std::string("#define TJ_FF ") + (a.F_f ? "1\n" : "0\n");
+    const char* ef = getenv("OBGPU_TINY_JIT_EVICT_FIRST");
+    src += std::string("#define TJ_EVICT_FIRST ") + (ef && atoi(ef) == 0 ? "0\n" : "1\n");
     src += "#define TJ_N " + std::to_string(N) + "\n#define TJ_E " + std::to_string(E) + "\n#define TJ_n " + std::to_string(n) +
            "\n#define TJ_NF " + std::to_string(nf) + "\n#define TJ_NB " + std::to_string(nb) + "\n#define TJ_NL " +
            std::to_string(NL) + "\n#define TJ_EL " + std::to_string(EL) + "\n#define TJ_MINB " + std::to_string(minb) + "\n";
@@ -145,7 +155,16 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     arr(src, "TJ_nldst", I + lay.o_nldst, NL);
     arr(src, "TJ_freek", I + lay.o_freek, nf);
     arr(src, "TJ_bndk", I + lay.o_bndk, nb);
+    if (const char* abl = getenv("OBGPU_TINY_JIT_ABL")) {  // ablation experiments (scripts/), never set in production
+      if (atoi(abl) & 1) src += "#define TJ_ABL_NOSTORE 1\n";
+      if (atoi(abl) & 2) src += "#define TJ_ABL_NOSOLVE 1\n";
+    }
     src += kTinyJitSource;
+    if (const char* dump = getenv("OBGPU_TINY_JIT_DUMP"))  // the generated translation unit, for offline nvcc/cuobjdump study
+      if (FILE* f = fopen(dump, "w")) {
+        fwrite(src.data(), 1, src.size(), f);
+        fclose(f);
+      }
     nvrtcProgram prog = nullptr;
     const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "-lineinfo", "-default-device"};
     bool ok = A.nvrtcCreateProgram(&prog, src.c_str(), "k_tiny_jit.cu", 0, nullptr, nullptr) == 0;
@@ -177,7 +196,7 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
       return cudaErrorNotSupported;
     }
     const int xw = std::max(std::max(nf, nb), 1);
-    c.smem_base = size_t(4 * E + 2 * std::max(EL, 1)) * 8 + size_t(12 + xw) * JIT_CS * 8;
+    c.smem_base = size_t(4 * E + 2 * std::max(EL, 1)) * 8 + (bulk ? bulk_bytes : size_t(12 + xw) * JIT_RS * 8);
     c.smem_nl = size_t(NL) * JIT_CS * 8;
     c.smem_q = size_t(2 * EL) * JIT_CS * 8;
     const size_t smem_max = c.smem_base + c.smem_nl + c.smem_q;
@@ -202,7 +221,9 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     V.push_back(0.0);
   const size_t smem = c.smem_base + (a.case_nl ? c.smem_nl : 0) + (a.case_q ? c.smem_q : 0);
   const int64_t need = (a.n_cases + JIT_BLOCK - 1) / JIT_BLOCK;
-  int64_t grid = int64_t(sm_count) * c.per_sm;  // persistent: a whole number of CTAs per SM, grid-stride over cases
+  int per_sm = c.per_sm;
+  if (getenv("OBGPU_TINY_JIT_CTAS")) per_sm = std::max(1, std::min(per_sm, atoi(getenv("OBGPU_TINY_JIT_CTAS"))));  // tuning experiments
+  int64_t grid = int64_t(sm_count) * per_sm;  // persistent: a whole number of CTAs per SM, grid-stride over cases
   if (need < grid) grid = need;
   if (grid < 1) grid = 1;
   TinyArgs args = a;

@@ -12,6 +12,7 @@
 //
 // The prelude must define:  TJ_N, TJ_E, TJ_n, TJ_NF, TJ_NB, TJ_NL, TJ_EL, TJ_MINB and the constexpr arrays
 //   TJ_enode[2E], TJ_etype[E], TJ_udof[6E] (-1 absent, k free, k|64 bounded), TJ_edst[21E] (packed K_ff index or -1),
+//   TJ_BULK (records through the bulk-copy engine), TJ_FF (F_f is kept), TJ_EVICT_FIRST,
 //   TJ_elptr[E+1], TJ_elslot[EL], TJ_nldst[NL], TJ_freek[NF], TJ_bndk[NB]
 // (arrays padded to at least one entry), then include this file after beam_math.cuh.
 #pragma once
@@ -39,8 +40,25 @@ __device__ __forceinline__ void tj_cp_async8(double* smem_dst, const double* gsr
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(unsigned(__cvta_generic_to_shared(smem_dst))), "l"(gsrc));
 }
 
-// Coalesced store of a [32 cases][C] record block staged as W[i*CS + t] (see StoreMap in kernels_tiny.cu).
-template <int C, int CS>
+// Staging columns of a [cases][C] record: column i starts at i*TJ_RS + sigma_C(i) doubles, one entry per thread after
+// that.  The thread-per-case writes are trivially conflict-free; the transposed reads of the coalesced store (lane ->
+// flat index j = C*t + i of the 32-case block) touch bank pair (sigma_C(i) + t) mod 16, and sigma is chosen so that this
+// is a BIJECTION on every aligned run of 16 flat indices (one 64-bit half-warp access):
+//   C = 2^a q (q odd), i = 2^a u + v:  sigma = (16 / 2^a) v + q^{-1} u  (mod 16)   [2^a >= 16: sigma = i]
+// since with J = q t + u (j = 2^a J + v) the bank is (16/2^a) v + q^{-1} J, distinct over 16/2^a consecutive J and all v.
+__host__ __device__ constexpr int tj_sigma(int C, int i) {
+  int p2 = 1, q = C;
+  while (q % 2 == 0 && p2 < 16) { q /= 2; p2 *= 2; }
+  if (p2 >= 16) return i % 16;
+  int qi = 1;
+  while ((qi * (q % 16)) % 16 != 1) qi += 2;
+  return ((16 / p2) * (i % p2) + qi * (i / p2)) % 16;
+}
+constexpr int TJ_RS = 128 + 16;  // column pitch of the record staging (room for the bank offset)
+__host__ __device__ constexpr int tj_col(int C, int i) { return i * TJ_RS + tj_sigma(C, i); }
+
+// Coalesced store of a [32 cases][C] record block staged in tj_col columns (see StoreMap in kernels_tiny.cu).
+template <int C>
 struct TjStoreMap {
   static constexpr int G = tj_gcd32(C), PER = C / G, TSTEP = 32 / G;
   int so[PER];
@@ -48,7 +66,7 @@ struct TjStoreMap {
 #pragma unroll
     for (int r0 = 0; r0 < PER; r0++) {
       const int j = r0 * 32 + lane, t = j / C, i = j - t * C;
-      so[r0] = i * CS + t;
+      so[r0] = tj_col(C, i) + t;
     }
   }
   __device__ __forceinline__ void store(double* __restrict__ g, const double* W, int lane, int cnt) const {
@@ -58,30 +76,87 @@ struct TjStoreMap {
     } else {
       for (int j = lane; j < cnt * C; j += 32) {
         const int t = j / C, i = j - t * C;
-        g[j] = W[i * CS + t];
+        g[j] = W[tj_col(C, i) + t];
       }
     }
   }
 };
 
+// ---- TJ_BULK: result records leave through the TMA (cp.async.bulk shared -> global) ----
+// Each warp keeps its 32 cases' records in shared memory in the FINAL global layout ([case][record], every thread writes
+// its own row), then one lane hands the whole contiguous block to the bulk-copy engine and the warp goes on computing:
+// the stores no longer sit in the warps' instruction streams, so a saturated memory system cannot stall the arithmetic
+// of the other warps behind a queue of STGs (measured: compute 45 us + stores 65 us ran back to back as 98 us).
+// The staging rows are reused one iteration later, after cp.async.bulk.wait_group.read.
+__device__ __forceinline__ void tj_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tj_bulk_wait_read(int lane) {
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  __syncwarp();
+}
+// All lanes call this after their row writes + tj_fence_async() + __syncwarp().  rec_bytes is a multiple of 4.
+__device__ __forceinline__ void tj_bulk_store(void* g, const void* s, int rec_bytes, int cnt, int lane) {
+  if (cnt <= 0) return;
+  const int bytes = cnt * rec_bytes;
+  if (((unsigned long long)(g) & 15ULL) == 0 && (bytes & 15) == 0) {
+    if (lane == 0) {
+#if TJ_EVICT_FIRST  // results are written once and not read again by this kernel: do not let them displace the inputs in L2
+      unsigned long long pol;
+      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(g),
+                   "r"(unsigned(__cvta_generic_to_shared(s))), "r"(bytes), "l"(pol)
+                   : "memory");
+#else
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(g),
+                   "r"(unsigned(__cvta_generic_to_shared(s))), "r"(bytes)
+                   : "memory");
+#endif
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+  } else {  // ragged tail / unaligned destination: plain stores
+    for (int j = lane; j < bytes / 4; j += 32) static_cast<int*>(g)[j] = static_cast<const int*>(s)[j];
+  }
+}
+
 constexpr int TJ_BLOCK = 128;
-constexpr int TJ_CS = TJ_BLOCK + 3;  // column stride = 3 (mod 16 doubles): fewest bank conflicts of the transposed reads
+constexpr int TJ_CS = TJ_BLOCK;  // pitch of the per-case input columns (read back by the owning thread only)
 constexpr int TJ_XW = TJ_NF > TJ_NB ? (TJ_NF > 0 ? TJ_NF : 1) : (TJ_NB > 0 ? TJ_NB : 1);  // widest U_f / F_f / F_b record
 
 extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const __grid_constant__ TinyJitVals V, TinyArgs a) {
   constexpr int E = TJ_E, n = TJ_n, NF = TJ_NF, NB = TJ_NB, NL = TJ_NL, EL = TJ_EL, CS = TJ_CS;
   extern __shared__ __align__(16) double smem[];
   // shared: G[E][4] = c,s,L,1/L | LP[EL][2] | staging columns SS[12] (stress record, zero columns 2,3,4,8,9,10) |
-  // SX[XW] (U_f/F_f/F_b records) | SN[NL] | SQ[2][EL]   (columns are [CS] wide, one entry per thread)
+  // SX[XW] (U_f/F_f/F_b records) | SN[NL] | SQ[2][EL]   (record columns: tj_col; input columns: [CS] wide)
   double* G = smem;
   double* LP = G + 4 * E;
-  double* SS = LP + 2 * (EL > 0 ? EL : 1) + threadIdx.x;
-  double* SX = SS + 12 * CS;
-  double* SN = SX + TJ_XW * CS;
-  double* SQ = SN + (a.case_nl ? NL * CS : 0);
   const int lane = threadIdx.x & 31, wl0 = threadIdx.x & ~31;
+#if TJ_BULK
+  // per warp: RS[32][12E] stress | RU[32][NF] U_f | RF[32][NF] F_f | RB[32][NB] F_b | RI[32] info   (final layouts)
+  constexpr int WR = 32 * (12 * E + (TJ_FF ? 2 : 1) * NF + NB) + 16;  // doubles per warp
+  double* RS = LP + 2 * (EL > 0 ? EL : 1) + (threadIdx.x >> 5) * WR;
+  double* RU = RS + 32 * 12 * E;
+  double* RF = RU + 32 * NF;
+  double* RB = RF + (TJ_FF ? 32 * NF : 0);
+  int* RI = reinterpret_cast<int*>(RB + 32 * NB);
+  double* SN = LP + 2 * (EL > 0 ? EL : 1) + (TJ_BLOCK / 32) * WR + threadIdx.x;
+  double* SQ = SN + (a.case_nl ? NL * CS : 0);
+  double* rs = RS + lane * 12 * E;
+#pragma unroll
+  for (int i = 0; i < 12 * E; i++) rs[i] = 0.0;  // the structural zeros of the stress records stay in place
+#else
+  double* SS = LP + 2 * (EL > 0 ? EL : 1) + threadIdx.x;
+  double* SX = SS + 12 * TJ_RS;
+  double* SN = SX + TJ_XW * TJ_RS;
+  double* SQ = SN + (a.case_nl ? NL * CS : 0);
+#endif
+#ifdef TJ_ABL_NOSTORE  // ablation experiment (OBGPU_TINY_JIT_ABL=1): everything computed, no global result stores
+  const bool st_on = a.fail == nullptr;
+#else
+  constexpr bool st_on = true;
+#endif
+#if !TJ_BULK
   const double* SSW = SS - threadIdx.x + wl0;
   const double* SXW = SX - threadIdx.x + wl0;
+#endif
   if (threadIdx.x < E) {
     const int e = threadIdx.x, na = TJ_enode[2 * e], nbn = TJ_enode[2 * e + 1];
     const ElemGeom g = elem_geom(V.xy[2 * na], V.xy[2 * na + 1], V.xy[2 * nbn], V.xy[2 * nbn + 1]);
@@ -92,11 +167,13 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
       LP[2 * slot] = pr.plong; LP[2 * slot + 1] = pr.pperp;
     }
   }
-  SS[2 * CS] = 0.0; SS[3 * CS] = 0.0; SS[4 * CS] = 0.0;
-  SS[8 * CS] = 0.0; SS[9 * CS] = 0.0; SS[10 * CS] = 0.0;
-  TjStoreMap<12, CS> map12;
-  TjStoreMap<(NF > 0 ? NF : 1), CS> mapNF;
-  TjStoreMap<(NB > 0 ? NB : 1), CS> mapNB;
+#if !TJ_BULK
+  constexpr int NFC = NF > 0 ? NF : 1, NBC = NB > 0 ? NB : 1;
+  SS[tj_col(12, 2)] = 0.0; SS[tj_col(12, 3)] = 0.0; SS[tj_col(12, 4)] = 0.0;
+  SS[tj_col(12, 8)] = 0.0; SS[tj_col(12, 9)] = 0.0; SS[tj_col(12, 10)] = 0.0;
+  TjStoreMap<12> map12;
+  TjStoreMap<NFC> mapNF;
+  TjStoreMap<NBC> mapNB;
   map12.init(lane);
   mapNF.init(lane);
   mapNB.init(lane);
@@ -106,6 +183,7 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     const int j = r0 * 32 + lane, t = j / 12, i = j - t * 12;
     go12[r0] = t * E * 12 + i;
   }
+#endif
   __syncthreads();
 
   const long long stride = (long long)gridDim.x * TJ_BLOCK;
@@ -183,26 +261,65 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     for (int i = 0; i < NF; i++) b[i] = fu[TJ_freek[i]];
     const long long c0 = base + wl0;
     const int cnt = int(min(32LL, a.n_cases - c0));
+#if TJ_BULK
+    tj_bulk_wait_read(lane);  // last iteration's records have left the staging rows
+    if (TJ_FF && a.F_f && NF > 0) {
+#pragma unroll
+      for (int i = 0; i < NF; i++) RF[lane * NF + i] = b[i];
+      tj_fence_async();
+      __syncwarp();
+      if (st_on) tj_bulk_store(a.F_f + c0 * NF, RF, NF * 8, cnt, lane);
+    }
+#else
     if (a.F_f) {
       __syncwarp();
 #pragma unroll
-      for (int i = 0; i < NF; i++) SX[i * CS] = b[i];
+      for (int i = 0; i < NF; i++) SX[tj_col(NFC, i)] = b[i];
       __syncwarp();
-      if (NF > 0) mapNF.store(a.F_f + c0 * NF, SXW, lane, cnt);
+      if (NF > 0 && st_on) mapNF.store(a.F_f + c0 * NF, SXW, lane, cnt);
       __syncwarp();
     }
+#endif
+#ifdef TJ_ABL_NOSOLVE  // ablation experiment (OBGPU_TINY_JIT_ABL=2): K_ff assembled but not factored
+    int info = 0;
+#pragma unroll
+    for (int i = 0; i < NF; i++)
+#pragma unroll
+      for (int j = 0; j <= i; j++) b[i] += A[i][j];
+#else
     const int info = ldlt_solve_regs<NF>(A, b);
-    if (valid) {
+#endif
+#if TJ_BULK
+    if (valid && info != 0) atomicOr(a.fail, 1);
+    RI[lane] = info;
+#pragma unroll
+    for (int i = 0; i < NF; i++) {
+      fu[TJ_freek[i]] = b[i];
+      if (NF % 2 == 0) {
+        if (i % 2 == 1) reinterpret_cast<double2*>(RU + lane * NF)[i / 2] = make_double2(b[i - 1], b[i]);
+      } else {
+        RU[lane * NF + i] = b[i];
+      }
+    }
+    tj_fence_async();
+    __syncwarp();
+    if (st_on) {
+      tj_bulk_store(a.info + c0, RI, 4, cnt, lane);
+      if (NF > 0) tj_bulk_store(a.U_f + c0 * NF, RU, NF * 8, cnt, lane);
+    }
+#else
+    if (valid && st_on) {
       a.info[cs] = info;
       if (info != 0) atomicOr(a.fail, 1);
     }
 #pragma unroll
     for (int i = 0; i < NF; i++) {
       fu[TJ_freek[i]] = b[i];
-      SX[i * CS] = b[i];
+      SX[tj_col(NFC, i)] = b[i];
     }
     __syncwarp();
-    if (NF > 0) mapNF.store(a.U_f + c0 * NF, SXW, lane, cnt);
+    if (NF > 0 && st_on) mapNF.store(a.U_f + c0 * NF, SXW, lane, cnt);
+#endif
     // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
 #pragma unroll
     for (int i = 0; i < NB; i++) fu[TJ_bndk[i]] = -fu[TJ_bndk[i]];
@@ -247,29 +364,52 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
 #pragma unroll
           for (int k = 0; k < 6; k++) ext[k] += ex[k];
         }
+#if TJ_BULK
+        reinterpret_cast<double2*>(rs + 12 * e)[0] = make_double2(-es[0] + ext[0], -es[1] + ext[1]);
+        rs[12 * e + 5] = -es[2] + ext[2];
+        reinterpret_cast<double2*>(rs + 12 * e)[3] = make_double2(es[3] + ext[3], es[4] + ext[4]);
+        rs[12 * e + 11] = es[5] + ext[5];
+#else
         __syncwarp();
-        SS[0 * CS] = -es[0] + ext[0]; SS[1 * CS] = -es[1] + ext[1]; SS[5 * CS] = -es[2] + ext[2];
-        SS[6 * CS] = es[3] + ext[3];  SS[7 * CS] = es[4] + ext[4];  SS[11 * CS] = es[5] + ext[5];
+        SS[tj_col(12, 0)] = -es[0] + ext[0]; SS[tj_col(12, 1)] = -es[1] + ext[1]; SS[tj_col(12, 5)] = -es[2] + ext[2];
+        SS[tj_col(12, 6)] = es[3] + ext[3];  SS[tj_col(12, 7)] = es[4] + ext[4];  SS[tj_col(12, 11)] = es[5] + ext[5];
         __syncwarp();
         double* gs = a.stress + (c0 * E + e) * 12;
-        if (cnt == 32) {
+        if (!st_on) {
+        } else if (cnt == 32) {
 #pragma unroll
           for (int r = 0; r < 12; r++) gs[go12[r % 3] + (r / 3) * 96 * E] = SSW[map12.so[r % 3] + (r / 3) * 8];
         } else {
           for (int j = lane; j < cnt * 12; j += 32) {
             const int t = j / 12, i = j - t * 12;
-            gs[t * E * 12 + i] = SSW[i * CS + t];
+            gs[t * E * 12 + i] = SSW[tj_col(12, i) + t];
           }
         }
+#endif
       }
     }
+#if TJ_BULK
+#pragma unroll
+    for (int i = 0; i < NB; i++) RB[lane * NB + i] = fu[TJ_bndk[i]];
+    tj_fence_async();
+    __syncwarp();
+    if (st_on) {
+      if (a.stress) tj_bulk_store(a.stress + c0 * E * 12, RS, E * 96, cnt, lane);
+      if (NB > 0) tj_bulk_store(a.F_b + c0 * NB, RB, NB * 8, cnt, lane);
+    }
+#else
     __syncwarp();
 #pragma unroll
-    for (int i = 0; i < NB; i++) SX[i * CS] = fu[TJ_bndk[i]];
+    for (int i = 0; i < NB; i++) SX[tj_col(NBC, i)] = fu[TJ_bndk[i]];
     __syncwarp();
-    if (NB > 0) mapNB.store(a.F_b + c0 * NB, SXW, lane, cnt);
+    if (NB > 0 && st_on) mapNB.store(a.F_b + c0 * NB, SXW, lane, cnt);
     __syncwarp();
+#endif
   }
+#if TJ_BULK
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // staging rows stay valid until read
+  __syncwarp();
+#endif
 }
 
 }  // namespace obgpu

@@ -24,6 +24,7 @@ LIB_PATH = os.environ.get("OBGPU_LIB") or os.path.join(_HERE, "libobgpu.so")  # 
 
 OK, EINVAL, ECUDA, ESINGULAR, ENOTCONVERGED, EUNSUPPORTED, ESEQUENCE = range(7)
 BATCHED_LDLT, PCG_JACOBI, PCG_BJ3, PCG_IC0 = range(4)
+SOLVE_SKIP_FF = 1  # obgpu_solve_opts.flags
 (RES_UF, RES_FB, RES_STRESS, RES_INFO, RES_FF, RES_UB, RES_KVAL, RES_ELEM_K) = range(8)
 (SYM_DOF_NODE, SYM_DOF_ID, SYM_FREE, SYM_BOUNDED, SYM_DOF_INDEX, SYM_K_ROWPTR, SYM_K_COL, SYM_TRI_NNZ) = range(8)
 OFF_DOF, OFF_FREE, OFF_BOUNDED, OFF_NNZ, OFF_TRIPLET = range(5)
@@ -57,7 +58,7 @@ class BatchDesc(C.Structure):
 
 class SolveOpts(C.Structure):
     _fields_ = [("method", C.c_int), ("with_stress", C.c_int), ("rtol", C.c_double), ("max_iter", C.c_int),
-                ("reserved", C.c_int)]
+                ("flags", C.c_int)]
 
 
 class ObgpuError(RuntimeError):
@@ -233,8 +234,8 @@ class Context:
     def assemble(self):
         self._chk(lib().obgpu_assemble(self.h))
 
-    def solve_static(self, method=BATCHED_LDLT, with_stress=True, rtol=1e-12, max_iter=0):
-        o = SolveOpts(method, int(with_stress), rtol, max_iter, 0)
+    def solve_static(self, method=BATCHED_LDLT, with_stress=True, rtol=1e-12, max_iter=0, keep_Ff=True):
+        o = SolveOpts(method, int(with_stress), rtol, max_iter, 0 if keep_Ff else SOLVE_SKIP_FF)
         self._chk(lib().obgpu_solve_static(self.h, C.byref(o)))
 
     def stress(self):
