@@ -166,12 +166,20 @@ int obgpu_solve_cases_host(obgpu_ctx*, int64_t n_cases, const double* case_nload
 /* per-structure summaries {max|U_f|, sum F_b over DX dofs, sum F_b over DY dofs, info} = 4 doubles per system,
  * written to a caller-provided DEVICE buffer [L*S*4] (e.g. a torch tensor that is then NCCL-gathered) */
 int obgpu_summaries_device(obgpu_ctx*, double* d_out);
+/* Binds a device buffer [L][S][4] (32-byte aligned, NULL to unbind): later obgpu_solve_static calls leave the summaries
+ * there as part of the solve (the thread-per-case kernel writes them from registers instead of a second pass over
+ * U_f / F_b), and obgpu_summaries_device(ctx, same pointer) then returns at once.  Routes without the fused form
+ * still produce them with the separate kernel at obgpu_summaries_device time. */
+int obgpu_bind_summaries(obgpu_ctx*, double* d_out);
 
 /* timings of the last call of each phase, in ms, measured with CUDA events on the ctx stream; section
  * names follow the reference's CTimeLogger entries (assemble.cpp:39-346, solver_static.cpp:53-121):
  * out[0] symbolic (host), [1] assembleProblem, [2] solveStatic.2_solve, [3] postProcCalcStress, [4] H2D, [5] D2H,
  * [6] kernel launches in the last solve/assemble call (count), [7] PCG iterations of the last solve */
 int obgpu_get_timings(const obgpu_ctx*, double out[8]);
+/* diagnostic: which kernel carried the last solve (the run-time specialised one, or the precompiled fallback when
+ * NVRTC / the driver library could not be loaded); benchmark reports cite it.  Never NULL. */
+const char* obgpu_kernel_info(const obgpu_ctx*);
 /* the CUDA stream the ctx launches on (a cudaStream_t), so callers can record their own events on it */
 int obgpu_get_stream(obgpu_ctx*, void** stream);
 

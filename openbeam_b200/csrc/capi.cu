@@ -254,6 +254,7 @@ int obgpu_symbolic(obgpu_ctx* c) {
       for (int64_t i = c->sym.bnd_off[st]; i < c->sym.bnd_off[st + 1]; i++)
         bdof[i] = uint8_t(c->sym.dof_id[c->sym.dof_off[st] + c->sym.bnd_idx[i]]);
     OB_CUDA(c, c->d_bnd_dofid.upload(bdof, c->stream));
+    c->h_bnd_dofid = bdof;
     OB_CUDA(c, c->d_free_off.upload(c->sym.free_off, c->stream));
     OB_CUDA(c, c->d_bnd_off.upload(c->sym.bnd_off, c->stream));
     OB_CUDA(c, c->d_Ub.upload(c->sym.U_b, c->stream));

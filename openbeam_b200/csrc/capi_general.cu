@@ -146,6 +146,7 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   c->pcg_iters = 0;
   c->solved = true;
   c->have_ff = true;
+  c->kernel_info = "k_frame_fused (warp per structure, banded LDLt in shared memory)";
   c->have_stress = o.with_stress != 0;
   return OBGPU_OK;
 }
@@ -157,10 +158,8 @@ extern "C" int obgpu_summaries_device(obgpu_ctx* c, double* d_out) {
   OB_NEED_DEVICE(c);
   if (!c->solved) return obgpu::fail(c, OBGPU_ESEQUENCE, "obgpu_summaries_device before obgpu_solve_static");
   if (reinterpret_cast<uintptr_t>(d_out) % 32) return obgpu::fail(c, OBGPU_EINVAL, "summary buffer must be 32-byte aligned");
-  obgpu::SummaryArgs a;
-  a.L = c->L; a.S = c->hb.S; a.nf_tot = c->sym.nf_tot(); a.nb_tot = c->sym.nb_tot();
-  a.free_off = c->d_free_off.p; a.bnd_off = c->d_bnd_off.p; a.bnd_dofid = c->d_bnd_dofid.p;
-  a.U_f = c->d_Uf.p; a.F_b = c->d_Fb.p; a.info = c->d_info.p; a.out = d_out;
+  if (c->summ_written == d_out) return OBGPU_OK;  // bound buffer: the solve's own kernel already wrote them
+  const obgpu::SummaryArgs a = obgpu::summary_args(c, d_out);
   OB_CUDA(c, obgpu::launch_summaries(a, c->sm_count, c->stream));
   c->launches += 1;
   return OBGPU_OK;

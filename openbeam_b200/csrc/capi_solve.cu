@@ -29,6 +29,14 @@ static int alloc_results(obgpu_ctx* c, int64_t L, bool stress) {
   return OBGPU_OK;
 }
 
+SummaryArgs obgpu::summary_args(obgpu_ctx* c, double* d_out) {
+  SummaryArgs a;
+  a.L = c->L; a.S = c->hb.S; a.nf_tot = c->sym.nf_tot(); a.nb_tot = c->sym.nb_tot();
+  a.free_off = c->d_free_off.p; a.bnd_off = c->d_bnd_off.p; a.bnd_dofid = c->d_bnd_dofid.p;
+  a.U_f = c->d_Uf.p; a.F_b = c->d_Fb.p; a.info = c->d_info.p; a.out = d_out;
+  return a;
+}
+
 static TinyArgs tiny_args(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai, double* Uf,
                           double* Fb, double* stress, double* Ff, int32_t* info) {
   TinyArgs a;
@@ -40,6 +48,7 @@ static TinyArgs tiny_args(obgpu_ctx* c, int64_t L, const double* nl, const doubl
   a.case_nl = nl; a.case_q = q; a.case_eai = eai;
   a.U_f = Uf; a.F_b = Fb; a.stress = stress; a.F_f = Ff; a.info = info;
   a.fail = c->d_fail.p;
+  a.summ = nullptr; a.bnd_dofid = nullptr; a.summ_fallback = nullptr;
   return a;
 }
 
@@ -53,6 +62,7 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
   obgpu_solve_opts o;
   o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.flags = 0;
   if (opts) o = *opts;
+  c->summ_written = nullptr;
   if (o.method == OBGPU_BATCHED_LDLT && c->prog.valid) {
     rc = alloc_results(c, c->L, o.with_stress != 0);
     if (rc != OBGPU_OK) return rc;
@@ -62,17 +72,33 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
                            o.with_stress ? c->d_stress.p : nullptr,
                            (o.flags & OBGPU_SOLVE_SKIP_FF) ? nullptr : c->d_Ff.p, c->d_info.p);
     c->have_ff = !(o.flags & OBGPU_SOLVE_SKIP_FF);
+    SummaryArgs sa;
+    if (c->d_summ) {  // bound summaries: written by the solve kernel itself (or by k_summaries right behind it)
+      sa = summary_args(c, c->d_summ);
+      a.summ = c->d_summ; a.bnd_dofid = c->h_bnd_dofid.data(); a.summ_fallback = &sa;
+    }
     OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream));
+    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream, &c->kernel_info));
     OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     c->t_have[1] = true;
-    c->launches = 1;
+    c->summ_written = c->d_summ;
+    c->launches = (c->d_summ && std::strncmp(c->kernel_info, "k_tiny_jit", 10) != 0) ? 2 : 1;
     c->pcg_iters = 0;
     c->solved = true;
     c->have_stress = o.with_stress != 0;
     return OBGPU_OK;
   }
   return solve_general(c, o);
+}
+
+const char* obgpu_kernel_info(const obgpu_ctx* c) { return c ? c->kernel_info : ""; }
+
+int obgpu_bind_summaries(obgpu_ctx* c, double* d_out) {
+  if (!c) return OBGPU_EINVAL;
+  if (reinterpret_cast<uintptr_t>(d_out) % 32) return fail(c, OBGPU_EINVAL, "summary buffer must be 32-byte aligned");
+  c->d_summ = d_out;
+  c->summ_written = nullptr;
+  return OBGPU_OK;
 }
 
 int obgpu_assemble(obgpu_ctx* c) {
@@ -201,7 +227,7 @@ int obgpu_solve_cases_host(obgpu_ctx* c, int64_t L, const double* nl, const doub
     if (eai) OB_CUDA(c, cudaMemcpyAsync(sl.eai.p, eai + c0 * 3 * E, size_t(n) * 3 * E * 8, cudaMemcpyHostToDevice, st));
     TinyArgs a = tiny_args(c, n, nl ? sl.nl.p : nullptr, q ? sl.q.p : nullptr, eai ? sl.eai.p : nullptr, sl.Uf.p, sl.Fb.p,
                            stress ? sl.stress.p : nullptr, nullptr, sl.info.p);
-    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st));
+    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st, &c->kernel_info));
     launches++;
     if (U_f && nf) OB_CUDA(c, cudaMemcpyAsync(U_f + c0 * nf, sl.Uf.p, size_t(n) * nf * 8, cudaMemcpyDeviceToHost, st));
     if (F_b && nb) OB_CUDA(c, cudaMemcpyAsync(F_b + c0 * nb, sl.Fb.p, size_t(n) * nb * 8, cudaMemcpyDeviceToHost, st));

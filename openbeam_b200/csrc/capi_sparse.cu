@@ -263,6 +263,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   c->pcg_relres = worst_rel;
   c->solved = true;
   c->have_ff = true;
+  c->kernel_info = "k_spmv_dot (SELL-32 SpMV of the Jacobi-PCG iteration)";
   c->have_stress = o.with_stress != 0;
   if (!all_converged) return fail(c, OBGPU_ENOTCONVERGED, "PCG did not converge (or broke down: K_ff not positive definite?)");
   return OBGPU_OK;

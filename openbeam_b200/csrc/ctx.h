@@ -29,6 +29,10 @@ struct obgpu_ctx {
   obgpu::DevBuf<uint8_t> d_bnd_dofid;            // [nb_tot]
   obgpu::DevBuf<int32_t> d_fail;  // [1] OR of per-system failures of the last solve
   bool solved = false, have_stress = false, have_ff = true;
+  std::vector<uint8_t> h_bnd_dofid;               // host copy of d_bnd_dofid
+  double* d_summ = nullptr;                       // obgpu_bind_summaries target (caller's device buffer) or null
+  const double* summ_written = nullptr;           // where the last solve's own kernel left the summaries, if it did
+  const char* kernel_info = "";  // dominant kernel of the last solve (obgpu_kernel_info)
   // general path: the batch arrays + symbolic slots on the device
   bool dev_batch = false;
   obgpu::DevBuf<double> d_node_rot, d_eload_q2;
@@ -75,6 +79,7 @@ struct obgpu_ctx {
 namespace obgpu {
 int fail(obgpu_ctx* c, int code, const std::string& msg);
 int cuda_fail(obgpu_ctx* c, cudaError_t e, const char* where);
+SummaryArgs summary_args(obgpu_ctx* c, double* d_out);  // capi_solve.cu
 }  // namespace obgpu
 
 #define OB_CUDA(c, call)                                             \

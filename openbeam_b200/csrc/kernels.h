@@ -18,9 +18,12 @@ struct TinyArgs {
   double* F_f;             // [L][nf] or null
   int32_t* info;           // [L]
   int32_t* fail;           // [1] set to 1 when any system has info != 0
+  double* summ;            // [L][4] or null: per-case summaries written by the same kernel (obgpu_bind_summaries)
+  const uint8_t* bnd_dofid;                 // HOST [nb]: DoF_index of each bounded DOF (used with summ)
+  const struct SummaryArgs* summ_fallback;  // HOST: arguments of the separate k_summaries launch for kernels without it
 };
-cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st);
-cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStream_t st);  // tiny_jit.cu
+cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st, const char** which = nullptr);
+cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStream_t st, const char** which = nullptr);  // tiny_jit.cu
 
 // Per-structure record of the batched kernels (one 64-byte line per structure).
 struct __align__(16) FrameMeta {

@@ -468,15 +468,26 @@ static cudaError_t launch_nf(const TinyParam& P, const TinyArgs& a, int n, int s
   return cudaGetLastError();
 }
 
-cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st) {
+static cudaError_t launch_tiny_precompiled(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st);
+
+cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st, const char** which) {
   // first choice: the kernel specialised to this topology at run time (tiny_jit.cu); the precompiled interpreter
   // below serves when NVRTC or the driver library is not available
   {
     int dev = 0;
     cudaGetDevice(&dev);
-    const cudaError_t je = launch_tiny_jit(dev, a, sm_count, st);
+    const cudaError_t je = launch_tiny_jit(dev, a, sm_count, st, which);
     if (je != cudaErrorNotSupported) return je;
   }
+  if (which) *which = "k_tiny_fused (precompiled, thread per case, 128 threads/CTA)";
+  if (a.summ && a.summ_fallback) {  // the precompiled kernels do not write summaries: separate pass over U_f / F_b
+    const cudaError_t e = launch_tiny_precompiled(nf, n, a, sm_count, st);
+    return e != cudaSuccess ? e : launch_summaries(*a.summ_fallback, sm_count, st);
+  }
+  return launch_tiny_precompiled(nf, n, a, sm_count, st);
+}
+
+cudaError_t launch_tiny_precompiled(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st) {
   TinyParam P;
   std::memset(&P, 0, sizeof(P));
   const bool blocked = fill_param(P, a.prog_i, a.prog_d) && !getenv("OBGPU_TINY_GENERIC");

@@ -87,6 +87,7 @@ Api& api() {
 struct Compiled {
   CUfunction fn = nullptr;
   int per_sm = 1;
+  bool bulk = false;
   size_t smem_nl = 0, smem_q = 0, smem_base = 0;  // dynamic shared memory = base + (case_nl ? nl : 0) + (case_q ? q : 0)
   bool failed = false;
 };
@@ -108,7 +109,7 @@ constexpr int JIT_BLOCK = 128, JIT_CS = JIT_BLOCK, JIT_RS = JIT_BLOCK + 16;  // 
 
 // Returns cudaSuccess after a launch; cudaErrorNotSupported when the specialised kernel is unavailable (caller falls
 // back to the precompiled kernel).
-cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStream_t st) {
+cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStream_t st, const char** which) {
   static const bool enabled = !(getenv("OBGPU_TINY_JIT") && atoi(getenv("OBGPU_TINY_JIT")) == 0);
   if (!enabled) return cudaErrorNotSupported;
   Api& A = api();
@@ -126,7 +127,9 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
   static std::map<std::string, Compiled> cache;
   std::string key(reinterpret_cast<const char*>(I), size_t(a.n_ints) * sizeof(int32_t));
   key += char('0' + device);
-  key += a.F_f ? 'F' : '-';  // the kernel is also specialised on whether F_f is kept (staging rows, occupancy)
+  key += a.F_f ? 'F' : '-';
+  key += a.summ ? 'S' : '-';
+  if (a.summ) key.append(reinterpret_cast<const char*>(a.bnd_dofid), size_t(nb));  // the kernel is also specialised on whether F_f is kept (staging rows, occupancy)
   std::lock_guard<std::mutex> lock(mu);
   Compiled& c = cache[key];
   if (c.failed) return cudaErrorNotSupported;
@@ -135,8 +138,9 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     int minb = nfp + n <= 40 ? 5 : nfp + n <= 64 ? 3 : 2;  // register budget: K_ff + F/U live in registers
     if (getenv("OBGPU_TINY_JIT_MINB")) minb = atoi(getenv("OBGPU_TINY_JIT_MINB"));  // tuning experiments
     // result records through the bulk-copy engine when a CTA's staging rows (final layout, 4 warps x 32 cases) stay small
-    const size_t bulk_bytes = size_t(JIT_BLOCK / 32) * (size_t(32) * (12 * E + (a.F_f ? 2 : 1) * nf + nb) + 16) * 8;
-    bool bulk = bulk_bytes <= 56 * 1024;
+    const size_t bulk_bytes = size_t(JIT_BLOCK / 32) * (size_t(32) * (12 * E + (a.F_f ? 2 : 1) * nf + nb + (a.summ ? 4 : 0)) + 16) * 8;
+    bool& bulk = c.bulk;
+    bulk = bulk_bytes <= 60 * 1024;
     if (const char* ev = getenv("OBGPU_TINY_JIT_BULK")) bulk = bulk && atoi(ev) != 0;
     std::string src;
     src += std::string("#define TJ_BULK ") + (bulk ? "1\n" : "0\n");
@@ -155,6 +159,12 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     arr(src, "TJ_nldst", I + lay.o_nldst, NL);
     arr(src, "TJ_freek", I + lay.o_freek, nf);
     arr(src, "TJ_bndk", I + lay.o_bndk, nb);
+    {
+      std::vector<int32_t> bd(size_t(std::max(nb, 1)), 0);
+      for (int i = 0; i < nb && a.summ; i++) bd[size_t(i)] = a.bnd_dofid[i];
+      arr(src, "TJ_bnddof", bd.data(), nb);
+      src += std::string("#define TJ_SUMM ") + (a.summ ? "1\n" : "0\n");
+    }
     if (const char* abl = getenv("OBGPU_TINY_JIT_ABL")) {  // ablation experiments (scripts/), never set in production
       if (atoi(abl) & 1) src += "#define TJ_ABL_NOSTORE 1\n";
       if (atoi(abl) & 2) src += "#define TJ_ABL_NOSOLVE 1\n";
@@ -231,6 +241,9 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
   if (A.cuLaunchKernel(c.fn, unsigned(grid), 1, 1, JIT_BLOCK, 1, 1, unsigned(smem), reinterpret_cast<CUstream>(st), params,
                        nullptr) != 0)
     return cudaErrorLaunchFailure;
+  if (which)
+    *which = c.bulk ? "k_tiny_jit (NVRTC, specialised to the topology; thread per case, 128 threads/CTA, records stored by cp.async.bulk)"
+                    : "k_tiny_jit (NVRTC, specialised to the topology; thread per case, 128 threads/CTA, staged coalesced stores)";
   return cudaSuccess;
 }
 

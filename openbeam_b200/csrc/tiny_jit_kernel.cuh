@@ -12,6 +12,7 @@
 //
 // The prelude must define:  TJ_N, TJ_E, TJ_n, TJ_NF, TJ_NB, TJ_NL, TJ_EL, TJ_MINB and the constexpr arrays
 //   TJ_enode[2E], TJ_etype[E], TJ_udof[6E] (-1 absent, k free, k|64 bounded), TJ_edst[21E] (packed K_ff index or -1),
+//   TJ_SUMM + TJ_bnddof[NB] (per-case summaries written by this kernel; DoF_index of each bounded DOF),
 //   TJ_BULK (records through the bulk-copy engine), TJ_FF (F_f is kept), TJ_EVICT_FIRST,
 //   TJ_elptr[E+1], TJ_elslot[EL], TJ_nldst[NL], TJ_freek[NF], TJ_bndk[NB]
 // (arrays padded to at least one entry), then include this file after beam_math.cuh.
@@ -130,13 +131,15 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
   double* LP = G + 4 * E;
   const int lane = threadIdx.x & 31, wl0 = threadIdx.x & ~31;
 #if TJ_BULK
-  // per warp: RS[32][12E] stress | RU[32][NF] U_f | RF[32][NF] F_f | RB[32][NB] F_b | RI[32] info   (final layouts)
-  constexpr int WR = 32 * (12 * E + (TJ_FF ? 2 : 1) * NF + NB) + 16;  // doubles per warp
+  // per warp: RS[32][12E] stress | RU[32][NF] U_f | RF[32][NF] F_f | RB[32][NB] F_b | RM[32][4] summaries | RI[32] info
+  // (final layouts)
+  constexpr int WR = 32 * (12 * E + (TJ_FF ? 2 : 1) * NF + NB + (TJ_SUMM ? 4 : 0)) + 16;  // doubles per warp
   double* RS = LP + 2 * (EL > 0 ? EL : 1) + (threadIdx.x >> 5) * WR;
   double* RU = RS + 32 * 12 * E;
   double* RF = RU + 32 * NF;
   double* RB = RF + (TJ_FF ? 32 * NF : 0);
-  int* RI = reinterpret_cast<int*>(RB + 32 * NB);
+  double* RM = RB + 32 * NB;  // [32][4] summaries
+  int* RI = reinterpret_cast<int*>(RM + (TJ_SUMM ? 32 * 4 : 0));
   double* SN = LP + 2 * (EL > 0 ? EL : 1) + (TJ_BLOCK / 32) * WR + threadIdx.x;
   double* SQ = SN + (a.case_nl ? NL * CS : 0);
   double* rs = RS + lane * 12 * E;
@@ -218,6 +221,11 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     for (int i = 0; i < NL; i++)
       if (TJ_nldst[i] >= 0) fu[TJ_nldst[i] >= 0 ? TJ_nldst[i] : 0] += a.case_nl ? SN[i * CS] : V.nlval[i];
     if (base + stride < a.n_cases) prefetch(base + stride, buf ^ 1);
+    if (a.case_eai && base + stride < a.n_cases) {  // next block's section rows: pull them into L2 ahead of the __ldg reads
+      const char* p = reinterpret_cast<const char*>(a.case_eai + min(base + stride + (long long)threadIdx.x, last) * (3 * E));
+#pragma unroll
+      for (int o = 0; o < 3 * E * 8; o += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + o));
+    }
     const double* Q = SQ + buf * EL * CS;
     // ---- stage A: element stiffness -> K_ff registers, equivalent loads -> F registers ----
 #pragma unroll
@@ -320,6 +328,11 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     __syncwarp();
     if (NF > 0 && st_on) mapNF.store(a.U_f + c0 * NF, SXW, lane, cnt);
 #endif
+#if TJ_SUMM
+    double umax = 0.0;  // k_summaries' max |U_f| (kernels_misc.cu), same order of operations
+#pragma unroll
+    for (int i = 0; i < NF; i++) umax = fmax(umax, fabs(b[i]));
+#endif
     // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
 #pragma unroll
     for (int i = 0; i < NB; i++) fu[TJ_bndk[i]] = -fu[TJ_bndk[i]];
@@ -388,6 +401,22 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
 #endif
       }
     }
+#if TJ_SUMM
+    {
+      double fx = 0.0, fy = 0.0;
+#pragma unroll
+      for (int i = 0; i < NB; i++) {
+        if (TJ_bnddof[i] == 0) fx += fu[TJ_bndk[i]];  // OBGPU_DX
+        if (TJ_bnddof[i] == 1) fy += fu[TJ_bndk[i]];  // OBGPU_DY
+      }
+#if TJ_BULK
+      reinterpret_cast<double2*>(RM + lane * 4)[0] = make_double2(umax, fx);
+      reinterpret_cast<double2*>(RM + lane * 4)[1] = make_double2(fy, double(info));
+#else
+      if (valid && st_on) reinterpret_cast<double4*>(a.summ)[cs] = make_double4(umax, fx, fy, double(info));
+#endif
+    }
+#endif
 #if TJ_BULK
 #pragma unroll
     for (int i = 0; i < NB; i++) RB[lane * NB + i] = fu[TJ_bndk[i]];
@@ -396,6 +425,7 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     if (st_on) {
       if (a.stress) tj_bulk_store(a.stress + c0 * E * 12, RS, E * 96, cnt, lane);
       if (NB > 0) tj_bulk_store(a.F_b + c0 * NB, RB, NB * 8, cnt, lane);
+      if (TJ_SUMM) tj_bulk_store(a.summ + c0 * 4, RM, 32, cnt, lane);
     }
 #else
     __syncwarp();

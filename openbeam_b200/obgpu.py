@@ -36,7 +36,7 @@ ABI_SYMBOLS = (
     "obgpu_host_free", "obgpu_batch_upload", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
     "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host",
-    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_get_stream",
+    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries",
 )
 
 
@@ -81,6 +81,8 @@ def lib():
         L.obgpu_create.argtypes = [C.c_int, C.POINTER(vp)]
         L.obgpu_destroy.argtypes = [vp]
         L.obgpu_destroy.restype = None
+        L.obgpu_kernel_info.argtypes = [vp]
+        L.obgpu_kernel_info.restype = C.c_char_p
         L.obgpu_last_error.argtypes = [vp]
         L.obgpu_last_error.restype = C.c_char_p
         L.obgpu_status_string.argtypes = [C.c_int]
@@ -99,6 +101,7 @@ def lib():
         L.obgpu_device_ptr.argtypes = [vp, C.c_int, C.POINTER(vp)]
         L.obgpu_solve_cases_host.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp]
         L.obgpu_summaries_device.argtypes = [vp, vp]
+        L.obgpu_bind_summaries.argtypes = [vp, vp]
         L.obgpu_get_timings.argtypes = [vp, vp]
         L.obgpu_get_stream.argtypes = [vp, C.POINTER(vp)]
         _LIB = L
@@ -233,6 +236,12 @@ class Context:
 
     def assemble(self):
         self._chk(lib().obgpu_assemble(self.h))
+
+    def bind_summaries(self, ptr):
+        self._chk(lib().obgpu_bind_summaries(self.h, _p(int(ptr)) if ptr else None))
+
+    def kernel_info(self):
+        return lib().obgpu_kernel_info(self.h).decode()
 
     def solve_static(self, method=BATCHED_LDLT, with_stress=True, rtol=1e-12, max_iter=0, keep_Ff=True):
         o = SolveOpts(method, int(with_stress), rtol, max_iter, 0 if keep_Ff else SOLVE_SKIP_FF)

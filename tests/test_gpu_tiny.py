@@ -102,6 +102,62 @@ def test_c2_sample_parity(ctx, per_case_section):
     assert Ff.shape == U.shape
 
 
+@pytest.mark.parametrize("L", [1, 31, 33, 1003, 10007])
+def test_ragged_case_counts_and_skip_ff(ctx, L):
+    """Case counts that are not a multiple of the warp / CTA width (the bulk-copy record stores fall back to plain
+    stores for a ragged tail), and OBGPU_SOLVE_SKIP_FF: same bits for every other result, F_f unavailable."""
+    st = workloads.demo3_frame()
+    nl, q, _ = workloads.c2_cases(777, L)
+    _, oU, oF, oS = OracleProblem(st).run_cases(L, nl, q, None, n_threads=2)
+    ctx.upload(st, L, nl, q)
+    ctx.solve_static()
+    U, Fb, S, Ff = (ctx.download(w) for w in (obgpu.RES_UF, obgpu.RES_FB, obgpu.RES_STRESS, obgpu.RES_FF))
+    assert not ctx.download(obgpu.RES_INFO).any()
+    assert relerr(U, oU) <= RTOL and relerr(Fb, oF) <= RTOL and relerr(S, oS) <= RTOL
+    # F_f by linearity from the oracle's base problem (zero nodal loads, q = 9810): the six nodal-load slots are the
+    # free DOFs of nodes 1 and 2 in order
+    base = OracleProblem(st).solveStatic()
+    assert relerr(Ff, nl + (q / 9810.0) * np.asarray(base.F_f)[None, :]) <= RTOL
+    ctx.solve_static(keep_Ff=False)
+    assert np.array_equal(U, ctx.download(obgpu.RES_UF)) and np.array_equal(Fb, ctx.download(obgpu.RES_FB))
+    assert np.array_equal(S, ctx.download(obgpu.RES_STRESS))
+    with pytest.raises(obgpu.ObgpuError, match="F_f was not kept"):
+        ctx.download(obgpu.RES_FF)
+
+
+def test_bound_summaries_match_separate_kernel(ctx):
+    """obgpu_bind_summaries: the summaries the solve kernel writes from registers are bit-identical to the separate
+    k_summaries pass, and a later unbound solve leaves the bound buffer alone."""
+    import torch
+    st = workloads.demo3_frame()
+    L = 5003
+    nl, q, _ = workloads.c2_cases(4242, L)
+    ctx.upload(st, L, nl, q)
+    ctx.solve_static()
+    ref = torch.empty((L, 4), dtype=torch.float64, device="cuda:0")
+    ctx.summaries_device(ref.data_ptr())
+    ctx.synchronize()
+    fused = torch.full((L, 4), -1.0, dtype=torch.float64, device="cuda:0")
+    ctx.bind_summaries(fused.data_ptr())
+    try:
+        ctx.solve_static(keep_Ff=False)
+        assert ctx.timings()["launches"] == (1 if ctx.kernel_info().startswith("k_tiny_jit") else 2)
+        ctx.summaries_device(fused.data_ptr())
+        ctx.synchronize()
+        assert torch.equal(ref, fused)
+        U, Fb = ctx.download(obgpu.RES_UF), ctx.download(obgpu.RES_FB)
+        h = fused.cpu().numpy()
+        assert np.array_equal(h[:, 0], np.abs(U).max(axis=1))
+        assert np.array_equal(h[:, 1], Fb[:, 0] + Fb[:, 3]) and np.array_equal(h[:, 2], Fb[:, 1] + Fb[:, 4])
+        assert not h[:, 3].any()
+    finally:
+        ctx.bind_summaries(0)
+    fused.fill_(-2.0)
+    ctx.solve_static()
+    ctx.synchronize()
+    assert bool((fused == -2.0).all())
+
+
 def test_c2_full_size_equilibrium(ctx):
     """All 10^6 cases: global equilibrium  sum(F_b) + sum(F_ext) = 0  per case (size-independent property),
     and linearity: solution of (a + b) = solution(a) + solution(b)."""
