@@ -5,7 +5,8 @@ Workload at N=1 (BASELINE.json configs[1]): demo3_frame.yaml x 1,000,000 randomi
 pass over the whole batch: per case the full  assembleProblem -> solveStatic -> postProcCalcStress  pipeline
 (element stiffness, assembly, BC elimination, LDL^T factor + solve, reactions, element end forces), i.e. what
 one ob-solve run does per structure.  Weak scaling: every rank owns its own 1M cases (case index offset by
-rank), no data-path collective; one NCCL all-gather of per-case summaries ends each step when N > 1.
+rank), no data-path collective; the job's one exchange is the final all-gather of the per-case summaries (N > 1):
+the last step's kernel stores them into every rank's gathered array over NVLink (symmetric memory), else NCCL.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--cases L]
 
@@ -54,8 +55,10 @@ def config_dict(args, world):
                     "each case = full assembleProblem+solveStatic(LDLt)+postProcCalcStress" %
                     (args.cases, "; per-case section sweep" if args.per_case_section else ""),
         "cases_per_gpu": args.cases, "n_dof": N_DOF, "n_free": 6, "n_bounded": 6, "elements": 3,
-        "parallelism": "independent load cases sharded over %d GPU(s), no data-path collective; one final NCCL "
-                       "all-gather of the 32-byte per-case summaries after the last step, inside the timed region" % world,
+        "parallelism": "independent load cases sharded over %d GPU(s), no data-path collective; one final "
+                       "all-gather of the 32-byte per-case summaries inside the timed region (peer stores of the last "
+                       "step's kernel over NVLink + device barrier; NCCL all-gather when symmetric memory is "
+                       "unavailable)" % world,
         "l2_policy": "no flush: per-step inputs+outputs (%.0f MB) exceed the 126 MB L2" %
                      (args.cases * (ALG_BYTES_PER_CASE + 48 + 36) / 1e6),
     }
@@ -151,8 +154,25 @@ def reference_arm(args, rank, world):
         "gpu_launches": 0,
         "note": "reference unbuildable here (needs MRPT>=2.4 + Eigen): this is the oracle port in faithful mode",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
+
+
+def bind_to_gpu_numa_node(index):
+    """Pins this process to the CPUs NVML reports as local to GPU `index`, so that the pinned host buffers of the e2e
+    leg land on the memory node next to the GPU's PCIe root (one process per GPU: without this all ranks allocate on
+    whatever node they were started on and share one socket's memory and PCIe path).  Best effort."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:  # noqa: BLE001
+        pass
 
 
 def ours_arm(args, rank, local_rank, world):
@@ -171,6 +191,7 @@ def ours_arm(args, rank, local_rank, world):
             os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
         dist.init_process_group("nccl", device_id=dev)
     L, K, W = args.cases, args.steps, args.warmup
+    bind_to_gpu_numa_node(local_rank)   # before the pinned buffers are allocated (first touch decides their node)
     ctx = obgpu.Context(local_rank)
     st = workloads.demo3_frame()
     # pinned host buffers: this rank's cases [rank*L, (rank+1)*L)
@@ -185,6 +206,12 @@ def ours_arm(args, rank, local_rank, world):
     ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
     summ = torch.empty((L, 4), dtype=torch.float64, device=dev)
     gathered = torch.empty((world * L, 4), dtype=torch.float64, device=dev) if world > 1 else None
+    peer = None
+    if world > 1 and not os.environ.get("OBGPU_BENCH_NCCL_GATHER"):
+        try:   # symmetric memory: the last step's kernel stores its summaries straight into every rank's gathered array
+            peer = sharding.PeerGather(L, dev)
+        except Exception as e:  # noqa: BLE001 - any failure here means "use the NCCL all-gather"
+            print("symmetric memory unavailable (%s): final gather through NCCL" % e, file=sys.stderr)
     ctx.bind_summaries(summ.data_ptr())      # the solve kernel writes the per-case summaries itself
 
     def barrier():
@@ -203,17 +230,42 @@ def ours_arm(args, rank, local_rank, world):
         if world > 1:
             sharding.gather_summaries(summ, gathered)
 
-    with torch.cuda.stream(ext):
-        for _ in range(W):
+    def run_steps(n):
+        """n steps and the job's one exchange.  With symmetric memory the LAST step's kernel also stores its summaries
+        into every rank's gathered array (peer stores over NVLink overlapped with its own arithmetic), followed by a
+        device-side barrier; otherwise one NCCL all-gather after the last step."""
+        if peer is None:
+            for _ in range(n):
+                step()
+            final_gather()
+            return
+        for _ in range(n - 1):
             step()
-        final_gather()
+        ctx.bind_summary_peers(peer.slots)
+        step()
+        ctx.bind_summary_peers([])
+        peer.fence()
+
+    with torch.cuda.stream(ext):
+        run_steps(W)
+        if peer is not None:   # self-check outside the timed region: peer stores == NCCL all-gather
+            torch.cuda.synchronize(dev)
+            final_gather()
+            torch.cuda.synchronize(dev)
+            if not torch.equal(gathered, peer.buf):
+                raise RuntimeError("peer-store gather differs from the NCCL all-gather")
         barrier()
         sampler = ClockSampler(local_rank) if rank == 0 else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            # the host barrier above releases the ranks a few hundred microseconds apart; a device-side barrier on the
+            # timed stream lines the GPUs up so that the start skew is not billed to the final exchange
+            if peer is not None:
+                peer.fence()
+            else:
+                dist.all_reduce(torch.zeros(1, device=dev))
         e0.record(ext)
-        for _ in range(K):
-            step()
-        final_gather()
+        run_steps(K)
         e1.record(ext)
         barrier()
         ms_total = e0.elapsed_time(e1)
@@ -287,7 +339,7 @@ def ours_arm(args, rank, local_rank, world):
                 "sample": "%d cases of the same workload on %d host threads (and %d cases on 1 thread): oracle port "
                           "of the reference's solveStatic+postProcCalcStress, one call per case"
                           % (sample, cores, min(sample, 200_000))}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
@@ -300,8 +352,27 @@ TRAFFIC_BYTES_PER_CASE = 438.9
 TRAFFIC_SOURCE = "profiles/r01e_ncu_full_k_tiny_fused_v5_summary.txt (1M-case launch, scaled per case)"
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The one JSON line, on the process's ORIGINAL stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    global _JSON_FD
     args = parse_args()
+    # stdout carries exactly one JSON line: native libraries (the NCCL banner, NVRTC) write to fd 1 behind Python's back,
+    # so fd 1 is pointed at stderr for the life of the process and the line goes to a saved copy of the real stdout
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

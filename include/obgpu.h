@@ -171,6 +171,13 @@ int obgpu_summaries_device(obgpu_ctx*, double* d_out);
  * U_f / F_b), and obgpu_summaries_device(ctx, same pointer) then returns at once.  Routes without the fused form
  * still produce them with the separate kernel at obgpu_summaries_device time. */
 int obgpu_bind_summaries(obgpu_ctx*, double* d_out);
+/* The all-gather of the summaries as part of the solve (the job's only inter-GPU exchange): bufs[0..n)
+ * (n <= 8, 32-byte aligned) are device pointers valid in THIS process to the destination blocks [L][S][4] in other
+ * GPUs' memory (peer / symmetric-memory mappings, already offset to this rank's slot).  Later solves store their summary
+ * block into each of them as well, from the solve kernel itself over NVLink while it computes (bulk copies; plain
+ * device-to-device copies behind the kernels on routes without the fused form).  The caller orders the ranks
+ * afterwards (stream sync + barrier).  n = 0 unbinds; needs obgpu_bind_summaries first. */
+int obgpu_bind_summary_peers(obgpu_ctx*, int n, double* const* bufs);
 
 /* timings of the last call of each phase, in ms, measured with CUDA events on the ctx stream; section
  * names follow the reference's CTimeLogger entries (assemble.cpp:39-346, solver_static.cpp:53-121):

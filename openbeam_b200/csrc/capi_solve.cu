@@ -48,7 +48,8 @@ static TinyArgs tiny_args(obgpu_ctx* c, int64_t L, const double* nl, const doubl
   a.case_nl = nl; a.case_q = q; a.case_eai = eai;
   a.U_f = Uf; a.F_b = Fb; a.stress = stress; a.F_f = Ff; a.info = info;
   a.fail = c->d_fail.p;
-  a.summ = nullptr; a.bnd_dofid = nullptr; a.summ_fallback = nullptr;
+  a.summ = nullptr; a.bnd_dofid = nullptr; a.summ_fallback = nullptr; a.n_summ_peer = 0;
+  for (double*& p : a.summ_peer) p = nullptr;
   return a;
 }
 
@@ -76,13 +77,15 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
     if (c->d_summ) {  // bound summaries: written by the solve kernel itself (or by k_summaries right behind it)
       sa = summary_args(c, c->d_summ);
       a.summ = c->d_summ; a.bnd_dofid = c->h_bnd_dofid.data(); a.summ_fallback = &sa;
+      a.n_summ_peer = c->n_summ_peer;
+      for (int p = 0; p < c->n_summ_peer; p++) a.summ_peer[p] = c->summ_peer[p];
     }
     OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
     OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream, &c->kernel_info));
     OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     c->t_have[1] = true;
     c->summ_written = c->d_summ;
-    c->launches = (c->d_summ && std::strncmp(c->kernel_info, "k_tiny_jit", 10) != 0) ? 2 : 1;
+    c->launches = (c->d_summ && std::strncmp(c->kernel_info, "k_tiny_jit", 10) != 0) ? 2 + c->n_summ_peer : 1;
     c->pcg_iters = 0;
     c->solved = true;
     c->have_stress = o.with_stress != 0;
@@ -93,11 +96,22 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
 
 const char* obgpu_kernel_info(const obgpu_ctx* c) { return c ? c->kernel_info : ""; }
 
+int obgpu_bind_summary_peers(obgpu_ctx* c, int n, double* const* bufs) {
+  if (!c || n < 0 || n > 8 || (n > 0 && !bufs)) return OBGPU_EINVAL;
+  for (int i = 0; i < n; i++)
+    if (!bufs[i] || reinterpret_cast<uintptr_t>(bufs[i]) % 32) return fail(c, OBGPU_EINVAL, "peer summary buffers must be non-null and 32-byte aligned");
+  if (n > 0 && !c->d_summ) return fail(c, OBGPU_ESEQUENCE, "obgpu_bind_summary_peers needs a bound local buffer (obgpu_bind_summaries)");
+  c->n_summ_peer = n;
+  for (int i = 0; i < 8; i++) c->summ_peer[i] = i < n ? bufs[i] : nullptr;
+  return OBGPU_OK;
+}
+
 int obgpu_bind_summaries(obgpu_ctx* c, double* d_out) {
   if (!c) return OBGPU_EINVAL;
   if (reinterpret_cast<uintptr_t>(d_out) % 32) return fail(c, OBGPU_EINVAL, "summary buffer must be 32-byte aligned");
   c->d_summ = d_out;
   c->summ_written = nullptr;
+  if (!d_out) c->n_summ_peer = 0;
   return OBGPU_OK;
 }
 

@@ -31,6 +31,8 @@ struct obgpu_ctx {
   bool solved = false, have_stress = false, have_ff = true;
   std::vector<uint8_t> h_bnd_dofid;               // host copy of d_bnd_dofid
   double* d_summ = nullptr;                       // obgpu_bind_summaries target (caller's device buffer) or null
+  double* summ_peer[8] = {};                      // obgpu_bind_summary_peers
+  int n_summ_peer = 0;
   const double* summ_written = nullptr;           // where the last solve's own kernel left the summaries, if it did
   const char* kernel_info = "";  // dominant kernel of the last solve (obgpu_kernel_info)
   // general path: the batch arrays + symbolic slots on the device

@@ -19,6 +19,8 @@ struct TinyArgs {
   int32_t* info;           // [L]
   int32_t* fail;           // [1] set to 1 when any system has info != 0
   double* summ;            // [L][4] or null: per-case summaries written by the same kernel (obgpu_bind_summaries)
+  double* summ_peer[8];    // further copies of the same block (peer-mapped buffers of other GPUs: the all-gather of the
+  int n_summ_peer;         // summaries done by the solve kernel's own stores over NVLink, obgpu_bind_summary_peers)
   const uint8_t* bnd_dofid;                 // HOST [nb]: DoF_index of each bounded DOF (used with summ)
   const struct SummaryArgs* summ_fallback;  // HOST: arguments of the separate k_summaries launch for kernels without it
 };

@@ -482,7 +482,14 @@ cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cu
   if (which) *which = "k_tiny_fused (precompiled, thread per case, 128 threads/CTA)";
   if (a.summ && a.summ_fallback) {  // the precompiled kernels do not write summaries: separate pass over U_f / F_b
     const cudaError_t e = launch_tiny_precompiled(nf, n, a, sm_count, st);
-    return e != cudaSuccess ? e : launch_summaries(*a.summ_fallback, sm_count, st);
+    if (e != cudaSuccess) return e;
+    const cudaError_t e2 = launch_summaries(*a.summ_fallback, sm_count, st);
+    if (e2 != cudaSuccess) return e2;
+    for (int p = 0; p < a.n_summ_peer; p++) {  // peer copies: plain device-to-device copies behind the kernel
+      const cudaError_t e3 = cudaMemcpyAsync(a.summ_peer[p], a.summ, size_t(a.n_cases) * 32, cudaMemcpyDeviceToDevice, st);
+      if (e3 != cudaSuccess) return e3;
+    }
+    return cudaSuccess;
   }
   return launch_tiny_precompiled(nf, n, a, sm_count, st);
 }

@@ -413,7 +413,11 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
       reinterpret_cast<double2*>(RM + lane * 4)[0] = make_double2(umax, fx);
       reinterpret_cast<double2*>(RM + lane * 4)[1] = make_double2(fy, double(info));
 #else
-      if (valid && st_on) reinterpret_cast<double4*>(a.summ)[cs] = make_double4(umax, fx, fy, double(info));
+      if (valid && st_on) {
+        reinterpret_cast<double4*>(a.summ)[cs] = make_double4(umax, fx, fy, double(info));
+        for (int p = 0; p < a.n_summ_peer; p++)
+          reinterpret_cast<double4*>(a.summ_peer[p])[cs] = make_double4(umax, fx, fy, double(info));
+      }
 #endif
     }
 #endif
@@ -425,7 +429,10 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     if (st_on) {
       if (a.stress) tj_bulk_store(a.stress + c0 * E * 12, RS, E * 96, cnt, lane);
       if (NB > 0) tj_bulk_store(a.F_b + c0 * NB, RB, NB * 8, cnt, lane);
-      if (TJ_SUMM) tj_bulk_store(a.summ + c0 * 4, RM, 32, cnt, lane);
+      if (TJ_SUMM) {
+        tj_bulk_store(a.summ + c0 * 4, RM, 32, cnt, lane);
+        for (int p = 0; p < a.n_summ_peer; p++) tj_bulk_store(a.summ_peer[p] + c0 * 4, RM, 32, cnt, lane);
+      }
     }
 #else
     __syncwarp();

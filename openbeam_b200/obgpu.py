@@ -36,7 +36,7 @@ ABI_SYMBOLS = (
     "obgpu_host_free", "obgpu_batch_upload", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
     "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host",
-    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries",
+    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
 )
 
 
@@ -102,6 +102,7 @@ def lib():
         L.obgpu_solve_cases_host.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp]
         L.obgpu_summaries_device.argtypes = [vp, vp]
         L.obgpu_bind_summaries.argtypes = [vp, vp]
+        L.obgpu_bind_summary_peers.argtypes = [vp, C.c_int, C.POINTER(C.c_void_p)]
         L.obgpu_get_timings.argtypes = [vp, vp]
         L.obgpu_get_stream.argtypes = [vp, C.POINTER(vp)]
         _LIB = L
@@ -239,6 +240,11 @@ class Context:
 
     def bind_summaries(self, ptr):
         self._chk(lib().obgpu_bind_summaries(self.h, _p(int(ptr)) if ptr else None))
+
+    def bind_summary_peers(self, ptrs):
+        """ptrs: device pointers (ints) of this rank's slot in the other GPUs' gathered buffers; [] unbinds."""
+        arr = (C.c_void_p * max(len(ptrs), 1))(*[int(p) for p in ptrs])
+        self._chk(lib().obgpu_bind_summary_peers(self.h, len(ptrs), arr))
 
     def kernel_info(self):
         return lib().obgpu_kernel_info(self.h).decode()

@@ -24,6 +24,28 @@ def weak_range(per_rank: int, rank: int) -> tuple[int, int]:
     return rank * per_rank, (rank + 1) * per_rank
 
 
+class PeerGather:
+    """The final all-gather done by the solve kernel's own stores (``obgpu_bind_summary_peers``): ``buf`` is the gathered
+    array [world*n_local, 4] in symmetric memory (every rank's copy is mapped into every process); ``slots`` are the
+    addresses of THIS rank's block inside each rank's copy, which the last step's kernel writes over NVLink while it
+    computes.  ``fence()`` is the device-side barrier after which every rank's ``buf`` is complete.  torch is plumbing
+    here (allocation, handle exchange, barrier); the data moves by the kernel's bulk stores."""
+
+    def __init__(self, n_local: int, device: torch.device):
+        import torch.distributed._symmetric_memory as symm
+
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        if self.world > 8:
+            raise ValueError("obgpu_bind_summary_peers takes at most 8 destinations")
+        self.buf = symm.empty((self.world * n_local, SUMMARY_WIDTH), dtype=torch.float64, device=device)
+        self.hdl = symm.rendezvous(self.buf, dist.group.WORLD)
+        off = self.rank * n_local * SUMMARY_WIDTH * 8
+        self.slots = [int(p) + off for p in self.hdl.buffer_ptrs]
+
+    def fence(self):
+        self.hdl.barrier()   # on the current stream
+
+
 def gather_summaries(local: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     """All-gather of the per-system summaries [n_local, 4] -> [sum n_local, 4] in rank order.  Equal shard sizes
     use one ``all_gather_into_tensor``; ragged shards are padded to the maximum and trimmed."""
