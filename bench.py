@@ -346,10 +346,11 @@ def ours_arm(args, rank, local_rank, world):
     return 0
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one k_tiny_fused launch, per case, from the committed
-# `ncu --set full` capture of the current kernel at 1M cases (56.06 MB read + 382.85 MB written)
-TRAFFIC_BYTES_PER_CASE = 438.9
-TRAFFIC_SOURCE = "profiles/r01e_ncu_full_k_tiny_fused_v5_summary.txt (1M-case launch, scaled per case)"
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_tiny_jit launch (summaries bound, F_f skipped), per case, from the
+# committed `ncu --set full` capture of the current kernel at 1M cases: 56.03 MB read + 361.29 MB written (the kernel
+# hands 420 MB of records to L2; what is still dirty in L2 when the kernel ends is not in the DRAM counter)
+TRAFFIC_BYTES_PER_CASE = 417.3
+TRAFFIC_SOURCE = "profiles/r01o_ncu_full_k_tiny_jit_summary.txt (1M-case launch, scaled per case)"
 
 
 _JSON_FD = None
