@@ -81,6 +81,9 @@ void obgpu_destroy(obgpu_ctx* c) {
   cudaSetDevice(c->device);
   cudaDeviceSynchronize();
   if (c->h_scal) cudaFreeHost(c->h_scal);
+  for (auto& s : c->pcg_stream)
+    if (s) cudaStreamDestroy(s);
+  if (c->pcg_ev) cudaEventDestroy(c->pcg_ev);
   for (auto& e : c->ev)
     if (e) cudaEventDestroy(e);
   for (auto& s : c->slot_stream)

@@ -152,6 +152,8 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   double* const v_z = v_r + nfp;
   double* const v_minv = v_z + nfp;
   bool l2_window = false;
+  cudaStreamAttrValue l2_av;
+  std::memset(&l2_av, 0, sizeof(l2_av));
   {
     static const bool want = !(getenv("OBGPU_L2_PERSIST") && atoi(getenv("OBGPU_L2_PERSIST")) == 0);
     int max_persist = 0, max_window = 0;
@@ -170,20 +172,38 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
         av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
         av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
         l2_window = cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
+        l2_av = av;
       }
       cudaGetLastError();  // the window is an optimisation: never fail the solve over it
     }
   }
-  OB_CUDA(c, c->d_scal.reserve(16));
-  OB_CUDA(c, c->d_partial.reserve(size_t(2) * c->sm_count * 8));
-  OB_CUDA(c, c->d_counter.reserve(1));
-  if (!c->h_scal) OB_CUDA(c, cudaHostAlloc((void**)&c->h_scal, 8 * sizeof(double), cudaHostAllocDefault));
-  OB_CUDA(c, cudaMemsetAsync(c->d_counter.p, 0, sizeof(unsigned int), c->stream));
+  int NC = 1;  // structures in flight
+  if (S > 1) {
+    NC = int(std::min<int64_t>(S, obgpu_ctx::NPCG));
+    if (const char* ev = getenv("OBGPU_PCG_CONCURRENT")) NC = std::max(1, std::min(NC, atoi(ev)));
+  }
+  std::vector<cudaStream_t> pst(size_t(NC), c->stream);
+  if (NC > 1) {
+    if (!c->pcg_ev) OB_CUDA(c, cudaEventCreateWithFlags(&c->pcg_ev, cudaEventDisableTiming));
+    for (int k = 0; k < NC; k++) {
+      if (!c->pcg_stream[k]) OB_CUDA(c, cudaStreamCreateWithFlags(&c->pcg_stream[k], cudaStreamNonBlocking));
+      pst[size_t(k)] = c->pcg_stream[k];
+    }
+  }
+  if (l2_window)
+    for (int k = 0; k < NC && NC > 1; k++) cudaStreamSetAttribute(pst[size_t(k)], cudaStreamAttributeAccessPolicyWindow, &l2_av);
+  const size_t part_stride = size_t(2) * c->sm_count * 8;
+  OB_CUDA(c, c->d_scal.reserve(size_t(16) * obgpu_ctx::NPCG));
+  OB_CUDA(c, c->d_partial.reserve(part_stride * obgpu_ctx::NPCG));
+  OB_CUDA(c, c->d_counter.reserve(obgpu_ctx::NPCG));
+  if (!c->h_scal) OB_CUDA(c, cudaHostAlloc((void**)&c->h_scal, 8 * obgpu_ctx::NPCG * sizeof(double), cudaHostAllocDefault));
+  OB_CUDA(c, cudaMemsetAsync(c->d_counter.p, 0, obgpu_ctx::NPCG * sizeof(unsigned int), c->stream));
   OB_CUDA(c, cudaMemsetAsync(c->d_fail.p, 0, sizeof(int32_t), c->stream));
   OB_CUDA(c, cudaMemsetAsync(c->d_info.p, 0, size_t(L) * S * sizeof(int32_t), c->stream));
   OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
   const double rtol = o.rtol > 0 ? o.rtol : 1e-12;
-  const int chk = 25;
+  static const bool use_graph = !(getenv("OBGPU_PCG_GRAPH") && atoi(getenv("OBGPU_PCG_GRAPH")) == 0);
+  const int chk = use_graph ? 24 : 25;  // iterations between convergence checks (even when replayed as a graph)
   double iters_total = 0, worst_rel = 0;
   bool all_converged = true;
   std::vector<int32_t> h_info(size_t(L) * S, 0);
@@ -202,42 +222,102 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
       OB_CUDA(c, launch_load_vector(d, nl, q, eai, c->d_Ff.p + size_t(cs) * nf, c->stream));
       launches += 2;
     }
-    for (int64_t s = 0; s < S; s++) {
+    // ---- one PCG per structure; up to NC of them in flight on their own streams, so that the launch gaps and the
+    // 25-iteration convergence checks of one structure are covered by the kernels of the others (C5: 8 structures of
+    // 0.5 M DOF per GPU were launch-latency bound one after the other) ----
+    struct Job {
+      int64_t s = -1; PcgArgs a; int it = 0, max_iter = 0; bool busy = false;
+      cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr;  // `chk` iterations of THIS structure as one launch
+    };
+    auto drop_graph = [](Job& jb) {
+      if (jb.exec) cudaGraphExecDestroy(jb.exec);
+      if (jb.graph) cudaGraphDestroy(jb.graph);
+      jb.exec = nullptr; jb.graph = nullptr;
+    };
+    std::vector<Job> job;
+    job.resize(size_t(NC));
+    int64_t next_s = 0;
+    auto start_next = [&](int k) -> cudaError_t {
+      Job& jb = job[size_t(k)];
+      jb.busy = false;
+      while (next_s < S && sy.free_off[next_s + 1] == sy.free_off[next_s]) next_s++;
+      if (next_s >= S) return cudaSuccess;
+      const int64_t st_i = next_s++;
       PcgArgs a;
-      a.r0 = int32_t(sy.free_off[s]); a.r1 = int32_t(sy.free_off[s + 1]);
-      if (a.r1 == a.r0) continue;
+      a.r0 = int32_t(sy.free_off[st_i]); a.r1 = int32_t(sy.free_off[st_i + 1]);
       a.slptr = d.sl_ptr; a.col = d.ff_col; a.val = d.ff_val; a.minv = v_minv;
       a.b = c->d_Ff.p + size_t(cs) * nf;
       a.x = c->d_Uf.p + size_t(cs) * nf;
       a.r = v_r; a.z = v_z; a.p = v_p; a.ap = v_ap;
-      a.scal = c->d_scal.p; a.partial = c->d_partial.p; a.counter = c->d_counter.p;
-      OB_CUDA(c, launch_pcg_init(a, c->sm_count, c->stream));
-      launches += 1;
+      a.ctas_per_sm = NC > 1 ? 2 : 0;  // measured at C5's share (8 x 0.5 M DOF): 8 -> 1.84 s, 4 -> 1.67 s, 2 -> 1.62 s
+      a.scal = c->d_scal.p + 16 * k; a.partial = c->d_partial.p + size_t(k) * part_stride; a.counter = c->d_counter.p + k;
+      jb.s = st_i; jb.a = a; jb.it = 0; jb.busy = true;
       const int nrows = a.r1 - a.r0;
-      const int max_iter = o.max_iter > 0 ? o.max_iter : int(20.0 * std::sqrt(double(nrows))) + 1000;
-      int it = 0;
-      bool conv = false;
-      double rr = 0, bb = 0;
-      while (true) {
-        OB_CUDA(c, cudaMemcpyAsync(c->h_scal, c->d_scal.p, 8 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-        OB_CUDA(c, cudaStreamSynchronize(c->stream));
-        rr = c->h_scal[3]; bb = c->h_scal[4];
-        if (it == 0) rr = bb;
-        if (!(rr == rr)) break;                                  // NaN: breakdown (K_ff not positive definite)
-        if (rr <= rtol * rtol * bb) { conv = true; break; }
-        if (it >= max_iter) break;
-        const int n_it = std::min(chk, max_iter - it);
-        for (int j = 0; j < n_it; j++, it++) OB_CUDA(c, launch_pcg_iter(a, it, c->sm_count, c->stream));
-        launches += 3.0 * n_it;
-      }
-      iters_total += it;
-      const double rel = bb > 0 ? std::sqrt(rr / bb) : 0.0;
-      worst_rel = std::max(worst_rel, rel == rel ? rel : 1.0);
-      if (!conv) {
-        all_converged = false;
-        h_info[size_t(cs) * S + s] = -1;
+      jb.max_iter = o.max_iter > 0 ? o.max_iter : int(20.0 * std::sqrt(double(nrows))) + 1000;
+      cudaError_t e = launch_pcg_init(a, c->sm_count, pst[size_t(k)]);
+      launches += 1;
+      if (e != cudaSuccess) return e;
+      return cudaMemcpyAsync(c->h_scal + 8 * k, a.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, pst[size_t(k)]);
+    };
+    if (NC > 1) {
+      OB_CUDA(c, cudaEventRecord(c->pcg_ev, c->stream));
+      for (int k = 0; k < NC; k++) OB_CUDA(c, cudaStreamWaitEvent(pst[size_t(k)], c->pcg_ev, 0));
+    }
+    for (int k = 0; k < NC; k++) OB_CUDA(c, start_next(k));
+    for (bool any = true; any;) {
+      any = false;
+      for (int k = 0; k < NC; k++) {
+        Job& jb = job[size_t(k)];
+        if (!jb.busy) continue;
+        any = true;
+        OB_CUDA(c, cudaStreamSynchronize(pst[size_t(k)]));
+        double rr = c->h_scal[8 * k + 3];
+        const double bb = c->h_scal[8 * k + 4];
+        if (jb.it == 0) rr = bb;
+        bool conv = false, stop = false;
+        if (!(rr == rr)) stop = true;                              // NaN: breakdown (K_ff not positive definite)
+        else if (rr <= rtol * rtol * bb) { conv = true; stop = true; }
+        else if (jb.it >= jb.max_iter) stop = true;
+        if (!stop) {
+          const int n_it = std::min(chk, jb.max_iter - jb.it);
+          if (use_graph && n_it == chk && (jb.it & 1) == 0) {
+            // the 3*chk kernels of a check interval replayed as one graph launch: the host no longer has to feed
+            // ~13 us per kernel launch to a loop whose kernels take 5-20 us each (chk is even: same rz ping-pong parity)
+            if (!jb.exec) {
+              OB_CUDA(c, cudaStreamBeginCapture(pst[size_t(k)], cudaStreamCaptureModeRelaxed));
+              cudaError_t ce = cudaSuccess;
+              for (int q2 = 0; q2 < chk && ce == cudaSuccess; q2++) ce = launch_pcg_iter(jb.a, q2, c->sm_count, pst[size_t(k)]);
+              const cudaError_t ee = cudaStreamEndCapture(pst[size_t(k)], &jb.graph);
+              OB_CUDA(c, ce);
+              OB_CUDA(c, ee);
+              OB_CUDA(c, cudaGraphInstantiate(&jb.exec, jb.graph, 0));
+            }
+            OB_CUDA(c, cudaGraphLaunch(jb.exec, pst[size_t(k)]));
+            jb.it += chk;
+            launches += 3.0 * n_it;
+          } else {
+            for (int q2 = 0; q2 < n_it; q2++, jb.it++) OB_CUDA(c, launch_pcg_iter(jb.a, jb.it, c->sm_count, pst[size_t(k)]));
+            launches += 3.0 * n_it;
+          }
+          OB_CUDA(c, cudaMemcpyAsync(c->h_scal + 8 * k, jb.a.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, pst[size_t(k)]));
+          continue;
+        }
+        iters_total += jb.it;
+        const double rel = bb > 0 ? std::sqrt(rr / bb) : 0.0;
+        worst_rel = std::max(worst_rel, rel == rel ? rel : 1.0);
+        if (!conv) {
+          all_converged = false;
+          h_info[size_t(cs) * S + jb.s] = -1;
+        }
+        drop_graph(jb);
+        OB_CUDA(c, start_next(k));
       }
     }
+    if (NC > 1)
+      for (int k = 0; k < NC; k++) {
+        OB_CUDA(c, cudaEventRecord(c->pcg_ev, pst[size_t(k)]));
+        OB_CUDA(c, cudaStreamWaitEvent(c->stream, c->pcg_ev, 0));
+      }
     // reactions F_b = K_bf U_f - Eq, element end forces
     OB_CUDA(c, launch_reactions(d, c->d_Uf.p + size_t(cs) * nf, c->d_Fb.p + size_t(cs) * nb, c->stream));
     launches += 1;
@@ -254,6 +334,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     cudaStreamAttrValue av;
     std::memset(&av, 0, sizeof(av));
     cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+    for (int k = 0; k < NC && NC > 1; k++) cudaStreamSetAttribute(pst[size_t(k)], cudaStreamAttributeAccessPolicyWindow, &av);
     cudaCtxResetPersistingL2Cache();
     cudaGetLastError();
   }

@@ -64,7 +64,10 @@ struct obgpu_ctx {
   obgpu::DevBuf<int32_t> d_blk_elem_ptr, d_blk_elems;
   obgpu::DevBuf<uint16_t> d_seg_loc;
   bool elem_k_valid = false;  // d_elem_k holds the element blocks of the current batch (only the two-kernel path fills it)
-  double* h_scal = nullptr;  // pinned [8]
+  double* h_scal = nullptr;  // pinned [8 * NPCG]
+  static constexpr int NPCG = 8;                  // PCGs of different structures in flight (sparse route)
+  cudaStream_t pcg_stream[NPCG] = {};
+  cudaEvent_t pcg_ev = nullptr;
   double pcg_relres = 0;
 
   // chunk slots of obgpu_solve_cases_host

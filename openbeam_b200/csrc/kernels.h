@@ -112,6 +112,7 @@ struct PcgArgs {
   double* scal;         // [0..1] rz ping-pong, [2] pAp, [3] rr, [4] bb
   double* partial;      // [2 * max blocks]
   unsigned int* counter;
+  int ctas_per_sm;      // grid cap of the iteration kernels (0 = 8): small when several structures' PCGs share the GPU
 };
 cudaError_t launch_pcg_init(const PcgArgs& a, int sm_count, cudaStream_t st);
 cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t st);

@@ -157,13 +157,16 @@ cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t
   const int64_t n = a.r1 - a.r0;
   const int cur = it & 1;
   static const bool stream = getenv("OBGPU_SPMV_STREAM") ? atoi(getenv("OBGPU_SPMV_STREAM")) != 0 : false;
-  static const int cps = getenv("OBGPU_PCG_CTAS") ? atoi(getenv("OBGPU_PCG_CTAS")) : 8;
+  static const int cps_env = getenv("OBGPU_PCG_CTAS") ? atoi(getenv("OBGPU_PCG_CTAS")) : 0;
+  const int cps = cps_env > 0 ? cps_env : a.ctas_per_sm > 0 ? a.ctas_per_sm : 8;
   const int64_t slices = ((int64_t(a.r1) + 31) >> 5) - (a.r0 >> 5);
   const unsigned g = pcg_grid(slices * 32, sm_count, cps);  // one warp per slice, grid-stride
   if (stream) k_spmv_dot<true><<<g, PCG_BLOCK, 0, st>>>(a);
   else k_spmv_dot<false><<<g, PCG_BLOCK, 0, st>>>(a);
-  k_pcg_update<<<pcg_grid(n, sm_count), PCG_BLOCK, 0, st>>>(a, cur);
-  k_pcg_dir<<<pcg_grid(n, sm_count), PCG_BLOCK, 0, st>>>(a, cur);
+  static const int cpv_env = getenv("OBGPU_PCG_VEC_CTAS") ? atoi(getenv("OBGPU_PCG_VEC_CTAS")) : 0;
+  const int cpv = cpv_env > 0 ? cpv_env : a.ctas_per_sm > 0 ? a.ctas_per_sm : 8;
+  k_pcg_update<<<pcg_grid(n, sm_count, cpv), PCG_BLOCK, 0, st>>>(a, cur);
+  k_pcg_dir<<<pcg_grid(n, sm_count, cpv), PCG_BLOCK, 0, st>>>(a, cur);
   return cudaGetLastError();
 }
 
