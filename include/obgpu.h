@@ -184,6 +184,21 @@ int obgpu_bind_summary_peers(obgpu_ctx*, int n, double* const* bufs);
  * out[0] symbolic (host), [1] assembleProblem, [2] solveStatic.2_solve, [3] postProcCalcStress, [4] H2D, [5] D2H,
  * [6] kernel launches in the last solve/assemble call (count), [7] PCG iterations of the last solve */
 int obgpu_get_timings(const obgpu_ctx*, double out[8]);
+/* ---- CStructureProblem::mesh(): the caller-side step right before the path ----
+ * Subdivides every beam of every structure into ceil(L / max_element_length) pieces and splits the element loads, exactly
+ * as CStructureProblem_mesh.cpp:37-132, CBaseElementBeam.cpp:317-422 and the loads' meshLoad methods do (including the
+ * reference's treatment of un-subdivided RA/AA/RD beams and of concentrated loads).  Host
+ * side (integer/coordinate generation, once per topology); needs no device and no ctx.  Load cases are not carried over
+ * (n_cases = 1 in the result).  obgpu_mesh_desc fills a batch description whose arrays live in the mesh object until
+ * obgpu_mesh_destroy; obgpu_mesh_info gives MeshOutputInfo::element2elements / element2nodes as CSR over the INPUT
+ * elements (offsets [Etot_in + 1], values local to the meshed structure). */
+typedef struct obgpu_mesh obgpu_mesh;
+int obgpu_mesh_create(const obgpu_batch_desc* in, double max_element_length, obgpu_mesh** out);
+int obgpu_mesh_desc(const obgpu_mesh*, obgpu_batch_desc* out);
+int obgpu_mesh_info(const obgpu_mesh*, const int64_t** e2e_off, const uint32_t** e2e, const int64_t** e2n_off,
+                    const uint32_t** e2n);
+void obgpu_mesh_destroy(obgpu_mesh*);
+
 /* diagnostic: which kernel carried the last solve (the run-time specialised one, or the precompiled fallback when
  * NVRTC / the driver library could not be loaded); benchmark reports cite it.  Never NULL. */
 const char* obgpu_kernel_info(const obgpu_ctx*);

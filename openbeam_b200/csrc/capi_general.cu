@@ -26,8 +26,88 @@ int ensure_device_batch(obgpu_ctx* c) {
   OB_CUDA(c, c->d_nload_val.upload(hb.nload_val, st));
   OB_CUDA(c, c->d_eload_q.upload(hb.eload_q, st));
   OB_CUDA(c, c->d_eload_dir.upload(hb.eload_dir, st));
-  OB_CUDA(c, c->d_node_slot.upload(sy.node_slot, st));
+  // Band reduction for the batched-LDLt route.  The reference numbers DOFs by node id, and mesh() appends the
+  // intermediate nodes after all original ones, so a meshed beam's K_ff has a band as wide as the structure.  Where a
+  // reverse Cuthill-McKee order of the nodes narrows the band, the route factors K_ff in that order: the slots handed to
+  // the kernel are renumbered and U_f / F_f go back to the reference's numbering on the way out (free_inv).  Structures
+  // whose band does not shrink keep their numbering (and their bit-for-bit results).
+  std::vector<int32_t> fslot(sy.node_slot), fnl(sy.nload_slot), finv(size_t(sy.nf_tot()));
+  std::vector<int32_t> half_bw(sy.half_bw);
+  c->frame_renumbered = false;
+  for (int64_t s = 0; s < hb.S; s++) {
+    const int64_t n0 = hb.node_off[s], N = hb.node_off[s + 1] - n0, e0 = hb.elem_off[s], E = hb.elem_off[s + 1] - e0;
+    const int64_t f0 = sy.free_off[s], nf = sy.free_off[s + 1] - f0;
+    for (int64_t i = 0; i < nf; i++) finv[size_t(f0 + i)] = int32_t(i);
+    if (sy.half_bw[s] <= 12 || getenv("OBGPU_FRAME_NO_RCM")) continue;
+    std::vector<std::vector<int32_t>> adj;
+    adj.resize(size_t(N));
+    for (int64_t e = 0; e < E; e++) {
+      const int32_t a = int32_t(hb.elem_nodes[2 * (e0 + e)]), b = int32_t(hb.elem_nodes[2 * (e0 + e) + 1]);
+      if (a != b) { adj[size_t(a)].push_back(b); adj[size_t(b)].push_back(a); }
+    }
+    auto bfs = [&](int32_t root, std::vector<int32_t>& out, std::vector<char>& seen) {
+      size_t head = out.size();
+      out.push_back(root); seen[size_t(root)] = 1;
+      while (head < out.size()) {
+        const int32_t u = out[head++];
+        std::vector<int32_t> nb;
+        for (int32_t v : adj[size_t(u)]) if (!seen[size_t(v)]) { seen[size_t(v)] = 1; nb.push_back(v); }
+        std::sort(nb.begin(), nb.end(), [&](int32_t x, int32_t y) {
+          return adj[size_t(x)].size() != adj[size_t(y)].size() ? adj[size_t(x)].size() < adj[size_t(y)].size() : x < y; });
+        nb.erase(std::unique(nb.begin(), nb.end()), nb.end());
+        for (int32_t v : nb) out.push_back(v);
+      }
+    };
+    std::vector<int32_t> ord;
+    std::vector<char> seen(size_t(N), 0);
+    for (int64_t start = 0; start < N; start++) {
+      if (seen[size_t(start)]) continue;
+      // pseudo-peripheral root of this component: the last node of a BFS from its lowest-degree node
+      std::vector<int32_t> comp; std::vector<char> tmp(seen);
+      bfs(int32_t(start), comp, tmp);
+      int32_t root = comp[0];
+      for (int32_t v : comp) if (adj[size_t(v)].size() < adj[size_t(root)].size()) root = v;
+      std::vector<int32_t> far; std::vector<char> tmp2(seen);
+      bfs(root, far, tmp2);
+      bfs(far.back(), ord, seen);
+    }
+    std::reverse(ord.begin(), ord.end());
+    std::vector<int32_t> perm(size_t(nf), -1);  // reference free index -> internal slot
+    int32_t next = 0;
+    for (int32_t nd : ord)
+      for (int a = 0; a < 3; a++) {
+        const int32_t t = sy.node_slot[size_t(3 * (n0 + nd) + a)];
+        if (t >= 0) perm[size_t(t)] = next++;
+      }
+    if (next != nf) continue;  // free DOFs outside the planar slots: leave this structure alone
+    int32_t bw = 0;
+    for (int64_t e = 0; e < E; e++) {
+      int32_t lo = INT32_MAX, hi = -1;
+      for (int f = 0; f < 2; f++)
+        for (int a = 0; a < 3; a++) {
+          const int32_t t = sy.node_slot[size_t(3 * (n0 + hb.elem_nodes[2 * (e0 + e) + f]) + a)];
+          if (t >= 0) { lo = std::min(lo, perm[size_t(t)]); hi = std::max(hi, perm[size_t(t)]); }
+        }
+      if (hi >= 0) bw = std::max(bw, hi - lo);
+    }
+    if (bw >= sy.half_bw[s]) continue;
+    half_bw[size_t(s)] = bw;
+    c->frame_renumbered = true;
+    for (int64_t i = 0; i < 3 * N; i++) {
+      int32_t& t = fslot[size_t(3 * n0 + i)];
+      if (t >= 0) t = perm[size_t(t)];
+    }
+    for (int64_t l = hb.nload_off[s]; l < hb.nload_off[s + 1]; l++)
+      if (fnl[size_t(l)] >= 0) fnl[size_t(l)] = perm[size_t(fnl[size_t(l)])];
+    for (int64_t i = 0; i < nf; i++) finv[size_t(f0 + perm[size_t(i)])] = int32_t(i);
+  }
+  OB_CUDA(c, c->d_node_slot.upload(sy.node_slot, st));    // reference numbering: the sparse route's kernels
   OB_CUDA(c, c->d_nload_slot.upload(sy.nload_slot, st));
+  if (c->frame_renumbered) {
+    OB_CUDA(c, c->d_frame_slot.upload(fslot, st));
+    OB_CUDA(c, c->d_frame_nlslot.upload(fnl, st));
+    OB_CUDA(c, c->d_frame_inv.upload(finv, st));
+  }
   OB_CUDA(c, c->d_el_ptr.upload(sy.el_ptr, st));
   OB_CUDA(c, c->d_el_order.upload(sy.el_order, st));
   std::vector<FrameMeta> meta(hb.S);
@@ -42,7 +122,7 @@ int ensure_device_batch(obgpu_ctx* c) {
     m.n = int32_t(sy.dof_off[s + 1] - sy.dof_off[s]);
     m.nf = int32_t(sy.free_off[s + 1] - sy.free_off[s]);
     m.nb = int32_t(sy.bnd_off[s + 1] - sy.bnd_off[s]);
-    m.hb = std::min(sy.half_bw[s], std::max(m.nf - 1, 0));
+    m.hb = std::min(half_bw[size_t(s)], std::max(m.nf - 1, 0));
     m.pad = 0;
     c->max_band = std::max<int64_t>(c->max_band, int64_t(m.hb + 1) * m.nf);
     c->max_nf = std::max(c->max_nf, m.nf);
@@ -120,7 +200,9 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   a.node_xy = reinterpret_cast<const double2*>(c->d_node_xy.p);
   a.elem_nodes = reinterpret_cast<const uint2*>(c->d_elem_nodes.p);
   a.elem_type = c->d_elem_type.p; a.elem_EAI = c->d_elem_EAI.p;
-  a.node_slot = c->d_node_slot.p; a.nload_slot = c->d_nload_slot.p; a.nload_val = c->d_nload_val.p;
+  a.node_slot = c->frame_renumbered ? c->d_frame_slot.p : c->d_node_slot.p;
+  a.nload_slot = c->frame_renumbered ? c->d_frame_nlslot.p : c->d_nload_slot.p;
+  a.nload_val = c->d_nload_val.p;
   a.el_ptr = c->d_el_ptr.p; a.el_order = c->d_el_order.p; a.eload_q = c->d_eload_q.p; a.eload_dir = c->d_eload_dir.p;
   a.eload_type = c->hb.has_load_kinds ? c->d_eload_type.p : nullptr;
   a.eload_q2 = c->hb.has_load_kinds ? c->d_eload_q2.p : nullptr;
@@ -133,6 +215,7 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   a.stress = o.with_stress ? c->d_stress.p : nullptr;
   a.info = c->d_info.p; a.fail = c->d_fail.p;
   a.order = c->d_frame_order.p;
+  a.free_inv = c->frame_renumbered ? c->d_frame_inv.p : nullptr;
   OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
   for (auto it = c->frame_classes.rbegin(); it != c->frame_classes.rend(); ++it) {  // largest structures first
     const obgpu_ctx::FrameClass& fc = *it;

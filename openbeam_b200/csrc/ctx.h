@@ -27,6 +27,9 @@ struct obgpu_ctx {
   obgpu::DevBuf<int32_t> d_info;
   obgpu::DevBuf<int64_t> d_free_off, d_bnd_off;  // [S+1]
   obgpu::DevBuf<uint8_t> d_bnd_dofid;            // [nb_tot]
+  obgpu::DevBuf<int32_t> d_frame_slot, d_frame_nlslot;   // node / nodal-load slots in the band-reduced numbering
+  obgpu::DevBuf<int32_t> d_frame_inv;             // [nf_tot] band-reducing renumbering of the batched-LDLt route (or unused)
+  bool frame_renumbered = false;
   obgpu::DevBuf<int32_t> d_fail;  // [1] OR of per-system failures of the last solve
   bool solved = false, have_stress = false, have_ff = true;
   std::vector<uint8_t> h_bnd_dofid;               // host copy of d_bnd_dofid

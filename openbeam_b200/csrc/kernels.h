@@ -67,6 +67,7 @@ struct FrameArgs {
   // size class served by this launch: structures order[o0 .. o1), whose banded K_ff, n_f, n_b and half bandwidth
   // are bounded by the class maxima below (shared memory per warp is sized from them)
   const int32_t* order;         // [S] structure ids sorted by size class
+  const int32_t* free_inv;      // [nf_tot] or null: free index (reference numbering) of each internal (band-reduced) free slot
   int64_t o0, o1;
   int max_band;                 // max over the class of (hb+1)*nf   (doubles)
   int max_nf, max_nb, max_hb;

@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
         __syncwarp();
       }
       if (a.F_f)
-        for (int i = lane; i < nf; i += 32) a.F_f[c * a.nf_tot + m.f0 + i] = Ff[i];
+        for (int i = lane; i < nf; i += 32) a.F_f[c * a.nf_tot + m.f0 + (a.free_inv ? a.free_inv[m.f0 + i] : i)] = Ff[i];
     }
     }  // pass
     // ---- stage B: banded LDL^T (row i holds columns i-hb..i at band[i*W + (j-i+hb)]) ----
@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
       a.info[sys] = info;
       if (info) atomicOr(a.fail, 1);
     }
-    for (int i = lane; i < nf; i += 32) a.U_f[c * a.nf_tot + m.f0 + i] = Ff[i];
+    for (int i = lane; i < nf; i += 32) a.U_f[c * a.nf_tot + m.f0 + (a.free_inv ? a.free_inv[m.f0 + i] : i)] = Ff[i];
     // ---- stage C: element end forces, reactions ----
     double* sst = stage;                  // [CHUNK][12] stress staging
     double* sgf = stage + CHUNK * 12;     // [CHUNK][6]  global end forces

@@ -37,6 +37,7 @@ ABI_SYMBOLS = (
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
     "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host",
     "obgpu_summaries_device", "obgpu_get_timings", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
+    "obgpu_mesh_create", "obgpu_mesh_desc", "obgpu_mesh_info", "obgpu_mesh_destroy",
 )
 
 
@@ -101,6 +102,11 @@ def lib():
         L.obgpu_device_ptr.argtypes = [vp, C.c_int, C.POINTER(vp)]
         L.obgpu_solve_cases_host.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp]
         L.obgpu_summaries_device.argtypes = [vp, vp]
+        L.obgpu_mesh_create.argtypes = [C.POINTER(BatchDesc), C.c_double, C.POINTER(vp)]
+        L.obgpu_mesh_desc.argtypes = [vp, C.POINTER(BatchDesc)]
+        L.obgpu_mesh_info.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+        L.obgpu_mesh_destroy.argtypes = [vp]
+        L.obgpu_mesh_destroy.restype = None
         L.obgpu_bind_summaries.argtypes = [vp, vp]
         L.obgpu_bind_summary_peers.argtypes = [vp, C.c_int, C.POINTER(C.c_void_p)]
         L.obgpu_get_timings.argtypes = [vp, vp]
@@ -178,6 +184,61 @@ def pack_batch(structures):
         b["node_rotz"] = cat([s.node_rotz if s.node_rotz is not None else np.zeros(s.n_nodes) for s in structures],
                              np.float64)
     return b
+
+
+def _fill_desc(d, batch):
+    d.n_structures = batch["S"]
+    for k in ("node_off", "elem_off", "con_off", "nload_off", "eload_off", "node_xy", "node_rotz", "elem_nodes",
+              "elem_type", "elem_EAI", "con_node", "con_dof", "con_val", "nload_node", "nload_dof", "nload_val",
+              "eload_elem", "eload_q", "eload_dir", "eload_type", "eload_q2"):
+        a = batch.get(k)
+        setattr(d, k, None if a is None or a.size == 0 else a.ctypes.data)
+    d.n_cases = 1
+
+
+def mesh_structure(st, max_element_length):
+    """``CStructureProblem::mesh()`` (CStructureProblem_mesh.cpp:37-132) through ``obgpu_mesh_create``: returns the meshed
+    Structure and the MeshOutputInfo lists ``element2elements`` / ``element2nodes`` (one list per original element)."""
+    batch = pack_batch([st])
+    d = BatchDesc()
+    _fill_desc(d, batch)
+    h = C.c_void_p()
+    rc = lib().obgpu_mesh_create(C.byref(d), float(max_element_length), C.byref(h))
+    if rc != 0:
+        raise ObgpuError(rc, "obgpu_mesh_create: " + lib().obgpu_status_string(rc).decode())
+    try:
+        o = BatchDesc()
+        lib().obgpu_mesh_desc(h, C.byref(o))
+
+        def arr(ptr, n, dt):
+            if not ptr or n == 0:
+                return np.zeros(0, dt)
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(np.ctypeslib.as_ctypes_type(dt))), shape=(n,)).copy()
+
+        off = lambda ptr: int(arr(ptr, 2, np.int64)[1])
+        N, E, Cn, NL, EL = off(o.node_off), off(o.elem_off), off(o.con_off), off(o.nload_off), off(o.eload_off)
+        out = Structure(
+            node_xy=arr(o.node_xy, 2 * N, np.float64), elem_nodes=arr(o.elem_nodes, 2 * E, np.uint32),
+            elem_type=arr(o.elem_type, E, np.uint8), elem_EAI=arr(o.elem_EAI, 3 * E, np.float64),
+            con_node=arr(o.con_node, Cn, np.uint32), con_dof=arr(o.con_dof, Cn, np.uint8),
+            con_val=arr(o.con_val, Cn, np.float64), nload_node=arr(o.nload_node, NL, np.uint32),
+            nload_dof=arr(o.nload_dof, NL, np.uint8), nload_val=arr(o.nload_val, NL, np.float64),
+            eload_elem=arr(o.eload_elem, EL, np.uint32), eload_q=arr(o.eload_q, EL, np.float64),
+            eload_dir=arr(o.eload_dir, 3 * EL, np.float64),
+            node_rotz=arr(o.node_rotz, N, np.float64) if o.node_rotz else None,
+            eload_type=arr(o.eload_type, EL, np.uint8) if o.eload_type else None,
+            eload_q2=arr(o.eload_q2, EL, np.float64) if o.eload_q2 else None)
+        p = [C.c_void_p() for _ in range(4)]
+        lib().obgpu_mesh_info(h, *[C.byref(x) for x in p])
+        E0 = st.n_elems if not callable(st.n_elems) else st.n_elems()
+        e2e_off, e2n_off = arr(p[0].value, E0 + 1, np.int64), arr(p[2].value, E0 + 1, np.int64)
+        e2e, e2n = arr(p[1].value, int(e2e_off[-1]), np.uint32), arr(p[3].value, int(e2n_off[-1]), np.uint32)
+        info = {"element2elements": [e2e[e2e_off[i]:e2e_off[i + 1]].tolist() for i in range(E0)],
+                "element2nodes": [e2n[e2n_off[i]:e2n_off[i + 1]].tolist() for i in range(E0)],
+                "num_original_nodes": len(st.node_xy), "num_original_elements": E0}
+        return out, info
+    finally:
+        lib().obgpu_mesh_destroy(h)
 
 
 class Context:

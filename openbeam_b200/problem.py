@@ -65,6 +65,19 @@ class StressInfo:
     element_stress: np.ndarray = None     # [E][2] x {N,Vy,Vz,Mx,My,Mz}
 
 
+@dataclass
+class MeshParams:
+    max_element_length: float = 50e-3     # CStructureProblem_mesh.cpp:34
+
+
+@dataclass
+class MeshOutputInfo:                     # CFiniteElementProblem.h MeshOutputInfo
+    num_original_nodes: int = 0
+    num_original_elements: int = 0
+    element2nodes: list = None
+    element2elements: list = None
+
+
 class CStructureProblem:
     """One structure on one GPU context.  ``solveStatic`` raises RuntimeError with the reference's message
     when K_ff is not positive definite (solver_static.cpp:98-105)."""
@@ -85,6 +98,15 @@ class CStructureProblem:
     def updateAll(self):
         self.ctx.symbolic()
         self._sym = True
+
+    def mesh(self, params: "MeshParams | None" = None, ctx: obgpu.Context | None = None):
+        """CStructureProblem::mesh (CStructureProblem_mesh.cpp:37-132): returns ``(out_fem, MeshOutputInfo)``; the meshed
+        problem lives on ``ctx`` (default: this problem's context, which is then re-uploaded with the meshed structure)."""
+        params = params or MeshParams()
+        meshed, info = obgpu.mesh_structure(self.structure, params.max_element_length)
+        mo = MeshOutputInfo(info["num_original_nodes"], info["num_original_elements"], info["element2nodes"],
+                            info["element2elements"])
+        return CStructureProblem(meshed, ctx=ctx or self.ctx), mo
 
     def getProblemDoFs(self):
         """m_problem_DoFs as [n,2] (nodeId, dof)."""
