@@ -115,7 +115,7 @@ def tri_temp_frame():
     return build_structure(nodes, els, SEC, [(0, "DXDYRZ"), (3, "DXDY")], [(1, "DX", 1500.0)], loads)
 
 
-fixtures.ALL.setdefault("tri_temp_frame", tri_temp_frame)
+MESH_CASES = dict(fixtures.ALL, tri_temp_frame=tri_temp_frame)
 
 
 @pytest.mark.gpu
@@ -128,9 +128,7 @@ def test_meshed_structures_through_the_gpu_path(name, max_len):
     reference's numbering grows with the subdivision; the batched-LDLt route factors in a reverse Cuthill-McKee order
     (capi_general.cu) and returns U_f / F_f in the reference's numbering."""
     from openbeam_b200.problem import CStructureProblem, MeshParams, StaticSolveProblemInfo, StressInfo
-    if name not in fixtures.ALL:
-        pytest.skip("fixture not present")
-    p0 = CStructureProblem(fixtures.ALL[name]())
+    p0 = CStructureProblem(MESH_CASES[name]())
     p, mo = p0.mesh(MeshParams(max_len))
     assert mo.num_original_elements == p0.getNumberOfElements()
     info, sinfo = StaticSolveProblemInfo(), StressInfo()
