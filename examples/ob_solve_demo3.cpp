@@ -34,6 +34,17 @@ int main(int argc, char** argv) {
       for (int f = 0; f < 2; f++)
         std::printf("stress e%zu f%d N %.17g Vy %.17g Mz %.17g\n", e, f, st.element_stress[e][f].N,
                     st.element_stress[e][f].Vy, st.element_stress[e][f].Mz);
+    // CStructureProblem::mesh at 0.5 m: 4 + 8 + 4 pieces; the displacements of the original nodes do not change
+    obhost::CStructureProblem pm(device);
+    obhost::MeshOutputInfo mo;
+    obhost::MeshParams mp;
+    mp.max_element_length = 0.5;
+    p.mesh(pm, mo, mp);
+    std::printf("meshed nodes %zu elements %zu pieces_of_beam %zu\n", pm.getNumberOfNodes(), pm.getNumberOfElements(),
+                mo.element2elements[1].size());
+    obhost::StaticSolveProblemInfo im;
+    pm.solveStatic(im);
+    for (size_t i = 0; i < 6; i++) std::printf("meshed U_f[%zu] %.17g\n", im.build_info.free_dof_indices[i], im.U_f[i]);
   } catch (const std::exception& e) {
     std::printf("Exception: %s\n", e.what());  // ob-solve_main.cpp:1540-1548
     return -1;

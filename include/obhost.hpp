@@ -70,6 +70,14 @@ struct NodeDoF {  // CFiniteElementProblem.h:53-67
 };
 
 // One structure (2D beam elements RR/RA/AR/AA) bound to one GPU context.
+struct MeshParams {  // CStructureProblem_mesh.cpp:34
+  num_t max_element_length = 50e-3;
+};
+struct MeshOutputInfo {  // CFiniteElementProblem.h MeshOutputInfo
+  size_t num_original_nodes = 0, num_original_elements = 0;
+  std::vector<std::vector<size_t>> element2nodes, element2elements;
+};
+
 class CStructureProblem {
  public:
   explicit CStructureProblem(int device = 0) {
@@ -81,13 +89,16 @@ class CStructureProblem {
   CStructureProblem& operator=(const CStructureProblem&) = delete;
 
   // ---- model building (names follow CFiniteElementProblem.h:196-330) ----
-  size_t insertNode(num_t x, num_t y) {
+  // rot_z: yaw of the nodal frame in radians (parse_file.cpp:467; TRotationTrans3D of the node)
+  size_t insertNode(num_t x, num_t y, num_t rot_z = 0) {
     node_xy_.push_back(x);
     node_xy_.push_back(y);
+    node_rotz_.push_back(rot_z);
     dirty_ = true;
     return node_xy_.size() / 2 - 1;
   }
-  // type: OBGPU_BEAM2D_{RR,RA,AR,AA}; E, A, Iz as CBaseElementBeam
+  // type: OBGPU_BEAM2D_{RR,RA,AR,AA,RD} with E, A, Iz as CBaseElementBeam; OBGPU_SPRING_* with the spring constants in
+  // the same triple (include/obgpu.h)
   size_t insertElement(uint8_t type, size_t n0, size_t n1, num_t E, num_t A, num_t Iz) {
     elem_nodes_.push_back(uint32_t(n0));
     elem_nodes_.push_back(uint32_t(n1));
@@ -106,9 +117,53 @@ class CStructureProblem {
   }
   // CLoadDistributedUniform(q, dir)
   void addLoadAtBeam(size_t element, num_t q, num_t dx, num_t dy, num_t dz) {
-    el_elem_.push_back(uint32_t(element)); el_q_.push_back(q);
+    addLoadAtBeam(element, OBGPU_LOAD_UNIFORM, q, 0, dx, dy, dz);
+  }
+  // the other load classes of loads.h: kind = OBGPU_LOAD_TRIANGULAR (q = q_ini, q2 = q_end), OBGPU_LOAD_CONCENTRATED
+  // (q = P, q2 = dist), OBGPU_LOAD_TEMPERATURE (q = temperature increment, direction unused)
+  void addLoadAtBeam(size_t element, uint8_t kind, num_t q, num_t q2, num_t dx, num_t dy, num_t dz) {
+    el_elem_.push_back(uint32_t(element)); el_q_.push_back(q); el_q2_.push_back(q2); el_kind_.push_back(kind);
     el_dir_.insert(el_dir_.end(), {dx, dy, dz});
     dirty_ = true;
+  }
+
+  // CStructureProblem::mesh (CStructureProblem_mesh.cpp:37-132) through obgpu_mesh_create
+  void mesh(CStructureProblem& out_fem, MeshOutputInfo& mo, const MeshParams& params = MeshParams()) {
+    Offsets off(*this);
+    obgpu_batch_desc d = describe(off);
+    obgpu_mesh* m = nullptr;
+    int rc = obgpu_mesh_create(&d, params.max_element_length, &m);
+    if (rc != OBGPU_OK) throw std::runtime_error(std::string("obgpu_mesh_create: ") + obgpu_status_string(rc));
+    obgpu_batch_desc o{};
+    obgpu_mesh_desc(m, &o);
+    const size_t N = size_t(o.node_off[1]), E = size_t(o.elem_off[1]), C = size_t(o.con_off[1]);
+    const size_t NL = size_t(o.nload_off[1]), EL = size_t(o.eload_off[1]);
+    out_fem.node_xy_.assign(o.node_xy, o.node_xy + 2 * N);
+    if (o.node_rotz) out_fem.node_rotz_.assign(o.node_rotz, o.node_rotz + N);
+    else out_fem.node_rotz_.assign(N, 0.0);
+    out_fem.elem_nodes_.assign(o.elem_nodes, o.elem_nodes + 2 * E);
+    out_fem.elem_type_.assign(o.elem_type, o.elem_type + E);
+    out_fem.elem_EAI_.assign(o.elem_EAI, o.elem_EAI + 3 * E);
+    out_fem.con_node_.assign(o.con_node, o.con_node + C); out_fem.con_dof_.assign(o.con_dof, o.con_dof + C);
+    out_fem.con_val_.assign(o.con_val, o.con_val + C);
+    out_fem.nl_node_.assign(o.nload_node, o.nload_node + NL); out_fem.nl_dof_.assign(o.nload_dof, o.nload_dof + NL);
+    out_fem.nl_val_.assign(o.nload_val, o.nload_val + NL);
+    out_fem.el_elem_.assign(o.eload_elem, o.eload_elem + EL); out_fem.el_q_.assign(o.eload_q, o.eload_q + EL);
+    out_fem.el_dir_.assign(o.eload_dir, o.eload_dir + 3 * EL);
+    if (o.eload_type) { out_fem.el_kind_.assign(o.eload_type, o.eload_type + EL); out_fem.el_q2_.assign(o.eload_q2, o.eload_q2 + EL); }
+    else { out_fem.el_kind_.assign(EL, uint8_t(OBGPU_LOAD_UNIFORM)); out_fem.el_q2_.assign(EL, 0.0); }
+    out_fem.dirty_ = true;
+    const int64_t *e2e_off, *e2n_off;
+    const uint32_t *e2e, *e2n;
+    obgpu_mesh_info(m, &e2e_off, &e2e, &e2n_off, &e2n);
+    mo = MeshOutputInfo();
+    mo.num_original_nodes = getNumberOfNodes();
+    mo.num_original_elements = getNumberOfElements();
+    for (size_t e = 0; e < getNumberOfElements(); e++) {
+      mo.element2elements.emplace_back(e2e + e2e_off[e], e2e + e2e_off[e + 1]);
+      mo.element2nodes.emplace_back(e2n + e2n_off[e], e2n + e2n_off[e + 1]);
+    }
+    obgpu_mesh_destroy(m);
   }
   size_t getNumberOfNodes() const { return node_xy_.size() / 2; }
   size_t getNumberOfElements() const { return elem_type_.size(); }
@@ -191,20 +246,34 @@ class CStructureProblem {
     check(obgpu_get_sizes(ctx_, z.data()));
     return z;
   }
-  void upload() {
-    if (!dirty_) return;
-    const int64_t off_n[2] = {0, int64_t(getNumberOfNodes())}, off_e[2] = {0, int64_t(getNumberOfElements())};
-    const int64_t off_c[2] = {0, int64_t(con_node_.size())}, off_l[2] = {0, int64_t(nl_node_.size())};
-    const int64_t off_q[2] = {0, int64_t(el_elem_.size())};
+  struct Offsets {  // the [S+1] offset arrays of a one-structure batch
+    int64_t n[2], e[2], c[2], l[2], q[2];
+    explicit Offsets(const CStructureProblem& p)
+        : n{0, int64_t(p.getNumberOfNodes())}, e{0, int64_t(p.getNumberOfElements())}, c{0, int64_t(p.con_node_.size())},
+          l{0, int64_t(p.nl_node_.size())}, q{0, int64_t(p.el_elem_.size())} {}
+  };
+  obgpu_batch_desc describe(const Offsets& off) const {
     obgpu_batch_desc d{};
     d.n_structures = 1;
-    d.node_off = off_n; d.elem_off = off_e; d.con_off = off_c; d.nload_off = off_l; d.eload_off = off_q;
-    d.node_xy = node_xy_.data(); d.node_rotz = nullptr;
+    d.node_off = off.n; d.elem_off = off.e; d.con_off = off.c; d.nload_off = off.l; d.eload_off = off.q;
+    d.node_xy = node_xy_.data();
+    bool rot = false, kinds = false;
+    for (num_t r : node_rotz_) rot = rot || r != 0;
+    for (uint8_t k : el_kind_) kinds = kinds || k != OBGPU_LOAD_UNIFORM;
+    d.node_rotz = rot ? node_rotz_.data() : nullptr;
     d.elem_nodes = elem_nodes_.data(); d.elem_type = elem_type_.data(); d.elem_EAI = elem_EAI_.data();
     d.con_node = con_node_.data(); d.con_dof = con_dof_.data(); d.con_val = con_val_.data();
     d.nload_node = nl_node_.data(); d.nload_dof = nl_dof_.data(); d.nload_val = nl_val_.data();
     d.eload_elem = el_elem_.data(); d.eload_q = el_q_.data(); d.eload_dir = el_dir_.data();
+    d.eload_type = kinds ? el_kind_.data() : nullptr;
+    d.eload_q2 = kinds ? el_q2_.data() : nullptr;
     d.n_cases = 1;
+    return d;
+  }
+  void upload() {
+    if (!dirty_) return;
+    Offsets off(*this);
+    obgpu_batch_desc d = describe(off);
     check(obgpu_batch_upload(ctx_, &d));
     dirty_ = false;
   }
@@ -226,9 +295,9 @@ class CStructureProblem {
 
   obgpu_ctx* ctx_ = nullptr;
   bool dirty_ = true;
-  std::vector<double> node_xy_, elem_EAI_, con_val_, nl_val_, el_q_, el_dir_;
+  std::vector<double> node_xy_, node_rotz_, elem_EAI_, con_val_, nl_val_, el_q_, el_q2_, el_dir_;
   std::vector<uint32_t> elem_nodes_, con_node_, nl_node_, el_elem_;
-  std::vector<uint8_t> elem_type_, con_dof_, nl_dof_;
+  std::vector<uint8_t> elem_type_, con_dof_, nl_dof_, el_kind_;
 };
 
 }  // namespace obhost

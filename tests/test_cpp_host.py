@@ -29,10 +29,15 @@ def test_cpp_mirror_symbolic(tmp_path):
 @pytest.mark.gpu
 def test_cpp_mirror_solve(tmp_path):
     out = subprocess.check_output([build(tmp_path), "0"], text=True)
-    U = np.array([float(x) for x in re.findall(r"U_f\[\d+\] (\S+)", out)])
+    U = np.array([float(x) for x in re.findall(r"(?m)^U_f\[\d+\] (\S+)", out)])
     F = np.array([float(x) for x in re.findall(r"F_b\[\d+\] (\S+)", out)])
     assert np.allclose(U, [2.6013078134695e-5, -6.5563909774436e-5, -1.29984937854503e-3,
                            -2.6013078134695e-5, -6.5563909774436e-5, 1.29984937854503e-3], rtol=1e-10)
     assert np.allclose(F, [7784.41363180755, 19620, -5136.62044771133, -7784.41363180755, 19620, 5136.62044771133],
                        rtol=1e-10)
     assert re.search(r"stress e1 f0 N -7784\.41", out)
+    # mesh() through the C++ mirror: original nodes keep their ids and (Euler-Bernoulli, consistent loads) their
+    # displacements
+    assert "meshed nodes 17 elements 16 pieces_of_beam 8" in out
+    Um = np.array([float(x) for x in re.findall(r"meshed U_f\[\d+\] (\S+)", out)])
+    assert np.allclose(Um, U, rtol=1e-9)
