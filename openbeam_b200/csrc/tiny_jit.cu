@@ -103,7 +103,15 @@ void arr(std::string& s, const char* name, const int32_t* v, int cnt) {
   s += "};\n";
 }
 
-constexpr int JIT_BLOCK = 128, JIT_CS = JIT_BLOCK, JIT_RS = JIT_BLOCK + 16;  // = TJ_BLOCK, TJ_CS, TJ_RS of the kernel
+constexpr int JIT_RS = 128 + 16;  // = TJ_RS of the kernel (record staging pitch of the non-bulk variant)
+int jit_block() {            // threads per CTA (= TJ_BLOCK = TJ_CS of the kernel): 128, or OBGPU_TINY_JIT_BLOCK in {32, 64, 96, 128}
+  static const int b = [] {
+    const char* e = getenv("OBGPU_TINY_JIT_BLOCK");
+    const int v = e ? atoi(e) : 128;
+    return (v == 32 || v == 64 || v == 96 || v == 128) ? v : 128;
+  }();
+  return b;
+}
 
 }  // namespace
 
@@ -136,13 +144,15 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
   if (!c.fn) {
     const int nfp = nf * (nf + 1) / 2;
     int minb = nfp + n <= 40 ? 5 : nfp + n <= 64 ? 3 : 2;  // register budget: K_ff + F/U live in registers
+    minb = minb * 128 / jit_block();  // the same register budget per thread whatever the CTA width
     if (getenv("OBGPU_TINY_JIT_MINB")) minb = atoi(getenv("OBGPU_TINY_JIT_MINB"));  // tuning experiments
     // result records through the bulk-copy engine when a CTA's staging rows (final layout, 4 warps x 32 cases) stay small
-    const size_t bulk_bytes = size_t(JIT_BLOCK / 32) * (size_t(32) * (12 * E + (a.F_f ? 2 : 1) * nf + nb + (a.summ ? 4 : 0)) + 16) * 8;
+    const size_t bulk_bytes = size_t(jit_block() / 32) * (size_t(32) * (12 * E + (a.F_f ? 2 : 1) * nf + nb + (a.summ ? 4 : 0)) + 16) * 8;
     bool& bulk = c.bulk;
     bulk = bulk_bytes <= 60 * 1024;
     if (const char* ev = getenv("OBGPU_TINY_JIT_BULK")) bulk = bulk && atoi(ev) != 0;
     std::string src;
+    src += "#define TJ_BLOCK_SIZE " + std::to_string(jit_block()) + "\n";
     src += std::string("#define TJ_BULK ") + (bulk ? "1\n" : "0\n");
     src += std::string("#define TJ_FF ") + (a.F_f ? "1\n" : "0\n");
     const char* ef = getenv("OBGPU_TINY_JIT_EVICT_FIRST");
@@ -207,11 +217,11 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     }
     const int xw = std::max(std::max(nf, nb), 1);
     c.smem_base = size_t(4 * E + 2 * std::max(EL, 1)) * 8 + (bulk ? bulk_bytes : size_t(12 + xw) * JIT_RS * 8);
-    c.smem_nl = size_t(NL) * JIT_CS * 8;
-    c.smem_q = size_t(2 * EL) * JIT_CS * 8;
+    c.smem_nl = size_t(NL) * jit_block() * 8;
+    c.smem_q = size_t(2 * EL) * jit_block() * 8;
     const size_t smem_max = c.smem_base + c.smem_nl + c.smem_q;
     if (A.cuFuncSetAttribute(c.fn, 8 /*CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES*/, int(smem_max)) != 0 ||
-        A.cuOccupancyMaxActiveBlocksPerMultiprocessor(&c.per_sm, c.fn, JIT_BLOCK, smem_max) != 0 || c.per_sm < 1) {
+        A.cuOccupancyMaxActiveBlocksPerMultiprocessor(&c.per_sm, c.fn, jit_block(), smem_max) != 0 || c.per_sm < 1) {
       c.failed = true;
       return cudaErrorNotSupported;
     }
@@ -230,7 +240,7 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
   else
     V.push_back(0.0);
   const size_t smem = c.smem_base + (a.case_nl ? c.smem_nl : 0) + (a.case_q ? c.smem_q : 0);
-  const int64_t need = (a.n_cases + JIT_BLOCK - 1) / JIT_BLOCK;
+  const int64_t need = (a.n_cases + jit_block() - 1) / jit_block();
   int per_sm = c.per_sm;
   if (getenv("OBGPU_TINY_JIT_CTAS")) per_sm = std::max(1, std::min(per_sm, atoi(getenv("OBGPU_TINY_JIT_CTAS"))));  // tuning experiments
   int64_t grid = int64_t(sm_count) * per_sm;  // persistent: a whole number of CTAs per SM, grid-stride over cases
@@ -238,7 +248,7 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
   if (grid < 1) grid = 1;
   TinyArgs args = a;
   void* params[2] = {V.data(), &args};
-  if (A.cuLaunchKernel(c.fn, unsigned(grid), 1, 1, JIT_BLOCK, 1, 1, unsigned(smem), reinterpret_cast<CUstream>(st), params,
+  if (A.cuLaunchKernel(c.fn, unsigned(grid), 1, 1, jit_block(), 1, 1, unsigned(smem), reinterpret_cast<CUstream>(st), params,
                        nullptr) != 0)
     return cudaErrorLaunchFailure;
   if (which)

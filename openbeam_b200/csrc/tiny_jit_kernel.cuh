@@ -118,7 +118,7 @@ __device__ __forceinline__ void tj_bulk_store(void* g, const void* s, int rec_by
   }
 }
 
-constexpr int TJ_BLOCK = 128;
+constexpr int TJ_BLOCK = TJ_BLOCK_SIZE;  // threads per CTA (128 unless OBGPU_TINY_JIT_BLOCK says otherwise)
 constexpr int TJ_CS = TJ_BLOCK;  // pitch of the per-case input columns (read back by the owning thread only)
 constexpr int TJ_XW = TJ_NF > TJ_NB ? (TJ_NF > 0 ? TJ_NF : 1) : (TJ_NB > 0 ? TJ_NB : 1);  // widest U_f / F_f / F_b record
 
