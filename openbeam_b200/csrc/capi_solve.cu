@@ -81,7 +81,12 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
       for (int p = 0; p < c->n_summ_peer; p++) a.summ_peer[p] = c->summ_peer[p];
     }
     OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream, &c->kernel_info));
+    const cudaError_t le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream, &c->kernel_info);
+    if (le == cudaErrorNotSupported && c->prog.has_load_kinds) {  // no NVRTC here and non-uniform loads: general route
+      c->summ_written = nullptr;
+      return solve_general(c, o);
+    }
+    OB_CUDA(c, le);
     OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     c->t_have[1] = true;
     c->summ_written = c->d_summ;
@@ -241,7 +246,10 @@ int obgpu_solve_cases_host(obgpu_ctx* c, int64_t L, const double* nl, const doub
     if (eai) OB_CUDA(c, cudaMemcpyAsync(sl.eai.p, eai + c0 * 3 * E, size_t(n) * 3 * E * 8, cudaMemcpyHostToDevice, st));
     TinyArgs a = tiny_args(c, n, nl ? sl.nl.p : nullptr, q ? sl.q.p : nullptr, eai ? sl.eai.p : nullptr, sl.Uf.p, sl.Fb.p,
                            stress ? sl.stress.p : nullptr, nullptr, sl.info.p);
-    OB_CUDA(c, launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st, &c->kernel_info));
+    const cudaError_t le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st, &c->kernel_info);
+    if (le == cudaErrorNotSupported)
+      return fail(c, OBGPU_EUNSUPPORTED, "the host-buffer sweep with non-uniform element loads needs the run-time specialised kernel (NVRTC)");
+    OB_CUDA(c, le);
     launches++;
     if (U_f && nf) OB_CUDA(c, cudaMemcpyAsync(U_f + c0 * nf, sl.Uf.p, size_t(n) * nf * 8, cudaMemcpyDeviceToHost, st));
     if (F_b && nb) OB_CUDA(c, cudaMemcpyAsync(F_b + c0 * nb, sl.Fb.p, size_t(n) * nb * 8, cudaMemcpyDeviceToHost, st));

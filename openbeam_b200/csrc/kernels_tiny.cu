@@ -479,6 +479,12 @@ cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cu
     const cudaError_t je = launch_tiny_jit(dev, a, sm_count, st, which);
     if (je != cudaErrorNotSupported) return je;
   }
+  {  // the precompiled interpreter knows uniform element loads only: the caller takes the warp-per-structure route
+    const int32_t* I = a.prog_i;
+    const TinyLayout lay(I[0], I[1], I[2], I[3], I[4], I[5], I[6]);
+    for (int i = 0; i < I[6]; i++)
+      if (I[lay.o_elkind + i] != OBGPU_LOAD_UNIFORM) return cudaErrorNotSupported;
+  }
   if (which) *which = "k_tiny_fused (precompiled, thread per case, 128 threads/CTA)";
   if (a.summ && a.summ_fallback) {  // the precompiled kernels do not write summaries: separate pass over U_f / F_b
     const cudaError_t e = launch_tiny_precompiled(nf, n, a, sm_count, st);

@@ -103,6 +103,7 @@ struct Symbolic {
 // one double blob).  Layout documented in kernels_tiny.cu.
 struct TinyProgram {
   bool valid = false;
+  bool has_load_kinds = false;  // element loads other than uniform: only the run-time specialised kernel serves them
   int N = 0, E = 0, n = 0, nf = 0, nb = 0, NL = 0, EL = 0;
   std::vector<int32_t> ints;
   std::vector<double> dbls;

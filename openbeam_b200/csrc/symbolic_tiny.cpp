@@ -17,7 +17,7 @@ int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& pr
   const int N = int(hb.Ntot()), E = int(hb.Etot()), n = int(sym.n_tot()), nf = int(sym.nf_tot()), nb = int(sym.nb_tot());
   const int NL = int(hb.NLtot()), EL = int(hb.ELtot());
   if (nf > TINY_MAX_NF || n > TINY_MAX_N || E > TINY_MAX_E || N > TINY_MAX_NODES || NL > TINY_MAX_NL ||
-      EL > TINY_MAX_EL || hb.has_rotz || hb.has_load_kinds) {
+      EL > TINY_MAX_EL || hb.has_rotz) {
     err = "structure too large for the thread-per-system kernel";
     return OBGPU_EUNSUPPORTED;
   }
@@ -89,7 +89,10 @@ int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& pr
   for (int i = 0; i < EL; i++) {
     D[lay.o_elq + i] = hb.eload_q[i];
     for (int a = 0; a < 3; a++) D[lay.o_eldir + 3 * i + a] = hb.eload_dir[3 * i + a];
+    I[lay.o_elkind + i] = hb.has_load_kinds ? int(hb.eload_type[i]) : int(OBGPU_LOAD_UNIFORM);
+    D[lay.o_elq2 + i] = hb.has_load_kinds ? hb.eload_q2[i] : 0.0;
   }
+  prog.has_load_kinds = hb.has_load_kinds;
   prog.valid = true;
   return OBGPU_OK;
 }

@@ -169,6 +169,7 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     arr(src, "TJ_nldst", I + lay.o_nldst, NL);
     arr(src, "TJ_freek", I + lay.o_freek, nf);
     arr(src, "TJ_bndk", I + lay.o_bndk, nb);
+    arr(src, "TJ_elkind", I + lay.o_elkind, EL);
     {
       std::vector<int32_t> bd(size_t(std::max(nb, 1)), 0);
       for (int i = 0; i < nb && a.summ; i++) bd[size_t(i)] = a.bnd_dofid[i];
@@ -239,6 +240,7 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     }
   else
     V.push_back(0.0);
+  for (int i = 0; i < std::max(EL, 1); i++) V.push_back(i < EL ? D[lay.o_elq2 + i] : 0.0);
   const size_t smem = c.smem_base + (a.case_nl ? c.smem_nl : 0) + (a.case_q ? c.smem_q : 0);
   const int64_t need = (a.n_cases + jit_block() - 1) / jit_block();
   int per_sm = c.per_sm;

@@ -12,6 +12,7 @@
 //
 // The prelude must define:  TJ_N, TJ_E, TJ_n, TJ_NF, TJ_NB, TJ_NL, TJ_EL, TJ_MINB and the constexpr arrays
 //   TJ_enode[2E], TJ_etype[E], TJ_udof[6E] (-1 absent, k free, k|64 bounded), TJ_edst[21E] (packed K_ff index or -1),
+//   TJ_elkind[EL] (OBGPU_LOAD_* of every element load),
 //   TJ_SUMM + TJ_bnddof[NB] (per-case summaries written by this kernel; DoF_index of each bounded DOF),
 //   TJ_BULK (records through the bulk-copy engine), TJ_FF (F_f is kept), TJ_EVICT_FIRST,
 //   TJ_elptr[E+1], TJ_elslot[EL], TJ_nldst[NL], TJ_freek[NF], TJ_bndk[NB]
@@ -26,6 +27,7 @@ struct TinyJitVals {  // run-time values of the shared topology (kernel paramete
   double nlval[TJ_NL > 0 ? TJ_NL : 1];
   double elq[TJ_EL > 0 ? TJ_EL : 1];
   double eldir[TJ_EL > 0 ? 2 * TJ_EL : 1];
+  double elq2[TJ_EL > 0 ? TJ_EL : 1];  // second load parameter (q_end / dist); fixed over the cases
 };
 
 __host__ __device__ constexpr int tj_row(int d) {
@@ -257,7 +259,7 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
         LoadProj pr;
         pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
         double gl[6], ex[6];
-        uniform_load_p(type, g, q, pr, gl, ex);
+        elem_load_p(TJ_elkind[slot], type, g, q, V.elq2[slot], pr, Ee * Ae, gl, ex);
 #pragma unroll
         for (int k = 0; k < 6; k++) {
           const int d = TJ_udof[6 * e + k];
@@ -373,7 +375,7 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
           LoadProj pr;
           pr.plong = LP[2 * slot]; pr.pperp = LP[2 * slot + 1];
           double gl[6], ex[6];
-          uniform_load_p(type, g, q, pr, gl, ex);
+          elem_load_p(TJ_elkind[slot], type, g, q, V.elq2[slot], pr, Ee * Ae, gl, ex);
 #pragma unroll
           for (int k = 0; k < 6; k++) ext[k] += ex[k];
         }
