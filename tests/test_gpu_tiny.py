@@ -125,6 +125,27 @@ def test_ragged_case_counts_and_skip_ff(ctx, L):
         ctx.download(obgpu.RES_FF)
 
 
+@pytest.mark.parametrize("name", ["load_kinds", "springs_and_slider"])
+def test_case_sweeps_with_load_kinds_and_springs(ctx, name):
+    """Load-case sweeps (per-case first load parameter, nodal load values and sections) over structures with
+    triangular / concentrated / temperature loads and spring / slider elements, against the oracle case by case."""
+    st = fixtures.ALL[name]()
+    L = 777
+    rng = np.random.default_rng(99)
+    NL, EL, E = len(st.nload_val), len(st.eload_q), st.n_elems
+    nl = st.nload_val[None, :] * rng.uniform(0.5, 1.5, (L, NL)) if NL else None
+    q = st.eload_q[None, :] * rng.uniform(0.5, 1.5, (L, EL)) if EL else None
+    eai = (st.elem_EAI.reshape(1, -1) * rng.uniform(0.8, 1.2, (L, 3 * E)))
+    ctx.upload(st, L, nl, q, eai)
+    ctx.solve_static()
+    assert not ctx.download(obgpu.RES_INFO).any()
+    U, Fb, S = (ctx.download(w) for w in (obgpu.RES_UF, obgpu.RES_FB, obgpu.RES_STRESS))
+    _, oU, oF, oS = OracleProblem(st).run_cases(L, nl, q, eai, n_threads=2)
+    assert relerr(U, oU) <= RTOL and relerr(Fb, oF) <= RTOL and relerr(S, oS) <= RTOL
+    for c in range(0, L, 111):
+        assert relerr(U[c], oU[c]) <= RTOL and relerr(S[c], oS[c]) <= RTOL
+
+
 def test_bound_summaries_match_separate_kernel(ctx):
     """obgpu_bind_summaries: the summaries the solve kernel writes from registers are bit-identical to the separate
     k_summaries pass, and a later unbound solve leaves the bound buffer alone."""
