@@ -45,6 +45,16 @@ int main(int argc, char** argv) {
     obhost::StaticSolveProblemInfo im;
     pm.solveStatic(im);
     for (size_t i = 0; i < 6; i++) std::printf("meshed U_f[%zu] %.17g\n", im.build_info.free_dof_indices[i], im.U_f[i]);
+    // StaticSolverOptions::nonLinearIterative (solver_static.cpp:139-193): 40 passes, results of the last one; the
+    // problem is back on its original poses afterwards
+    obhost::StaticSolverOptions nl;
+    nl.nonLinearIterative = true;
+    obhost::StaticSolveProblemInfo in;
+    p.solveStatic(in, nl);
+    for (size_t i = 0; i < in.U_f.size(); i++) std::printf("iterative U_f[%zu] %.17g\n", in.build_info.free_dof_indices[i], in.U_f[i]);
+    for (size_t i = 0; i < in.F_b.size(); i++) std::printf("iterative F_b[%zu] %.17g\n", in.build_info.bounded_dof_indices[i], in.F_b[i]);
+    p.solveStatic(in);
+    for (size_t i = 0; i < in.U_f.size(); i++) std::printf("again U_f[%zu] %.17g\n", in.build_info.free_dof_indices[i], in.U_f[i]);
   } catch (const std::exception& e) {
     std::printf("Exception: %s\n", e.what());  // ob-solve_main.cpp:1540-1548
     return -1;

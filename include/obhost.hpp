@@ -169,6 +169,7 @@ class CStructureProblem {
   size_t getNumberOfElements() const { return elem_type_.size(); }
 
   void updateAll() {
+    if (stale_) { dirty_ = true; stale_ = false; }
     upload();
     check(obgpu_symbolic(ctx_));
   }
@@ -200,16 +201,40 @@ class CStructureProblem {
   void solveStatic(StaticSolveProblemInfo& out, const StaticSolverOptions& opts = StaticSolverOptions()) {
     if (opts.algorithm == StaticSolverAlgorithm::Dense_LLT || opts.algorithm == StaticSolverAlgorithm::Sparse_LLT)
       throw std::runtime_error("Dense_LLT/Sparse_LLT are the reference's CPU algorithms; libobgpu has no CPU fallback");
-    if (opts.nonLinearIterative) throw std::runtime_error("nonLinearIterative is outside the GPU path");
-    updateAll();
-    obgpu_solve_opts o;
-    o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI : OBGPU_BATCHED_LDLT;
-    o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.flags = 0;
-    check(obgpu_solve_static(ctx_, &o));
+    if (!opts.nonLinearIterative) {
+      solve_pass(opts);
+    } else {
+      // solver_static.cpp:55-58,63-66,139-193: the loop sits above assemble+solve, so above the C ABI.  Every pass
+      // re-assembles and re-solves on the GPU with the node poses moved by the previous pass's U_f (a translation adds
+      // to the global coordinate as it is, RZ composes into the node's frame angle); no convergence test, all 40
+      // passes run, the poses are restored, and the results are those of the last pass.
+      const std::vector<double> xy0 = node_xy_, rz0 = node_rotz_;
+      try {
+        for (unsigned nIter = 0; nIter < 40; nIter++) {
+          solve_pass(opts);
+          const auto z = sizes();
+          std::vector<int32_t> f(z[5]), nd(z[4]), id(z[4]);
+          std::vector<num_t> U(z[5]);
+          check(obgpu_get_symbolic(ctx_, OBGPU_SYM_FREE, f.data()));
+          check(obgpu_get_symbolic(ctx_, OBGPU_SYM_DOF_NODE, nd.data()));
+          check(obgpu_get_symbolic(ctx_, OBGPU_SYM_DOF_ID, id.data()));
+          check(obgpu_download(ctx_, OBGPU_RES_UF, U.data()));
+          if (nIter == 39) break;       // the device keeps the last pass for the downloads below and for stress
+          for (size_t i = 0; i < f.size(); i++) {
+            const int node = nd[f[i]], dof = id[f[i]];
+            if (dof < 2) node_xy_[2 * node + dof] += U[i];
+            else if (dof == 5) node_rotz_[node] += U[i];
+          }
+          dirty_ = true;
+        }
+      } catch (...) {
+        node_xy_ = xy0; node_rotz_ = rz0; dirty_ = true;
+        throw;
+      }
+      node_xy_ = xy0; node_rotz_ = rz0;
+      stale_ = true;                    // the next updateAll() uploads the original poses again
+    }
     const auto z = sizes();
-    std::vector<int32_t> info(z[0] * z[1]);
-    if (obgpu_download(ctx_, OBGPU_RES_INFO, info.data()) == OBGPU_ESINGULAR)
-      throw std::runtime_error(obgpu_status_string(OBGPU_ESINGULAR));  // solver_static.cpp:102-104
     fill_lists(out.build_info);
     out.build_info.U_b.resize(z[6]); out.build_info.F_f.resize(z[5]);
     out.U_f.resize(z[5]); out.F_b.resize(z[6]);
@@ -235,6 +260,17 @@ class CStructureProblem {
   obgpu_ctx* ctx() { return ctx_; }
 
  private:
+  void solve_pass(const StaticSolverOptions& opts) {
+    updateAll();
+    obgpu_solve_opts o;
+    o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI : OBGPU_BATCHED_LDLT;
+    o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.flags = 0;
+    check(obgpu_solve_static(ctx_, &o));
+    const auto z = sizes();
+    std::vector<int32_t> info(z[0] * z[1]);
+    if (obgpu_download(ctx_, OBGPU_RES_INFO, info.data()) == OBGPU_ESINGULAR)
+      throw std::runtime_error(obgpu_status_string(OBGPU_ESINGULAR));  // solver_static.cpp:102-104
+  }
   void check(int rc) {
     if (rc != OBGPU_OK) {
       const char* m = obgpu_last_error(ctx_);
@@ -294,7 +330,7 @@ class CStructureProblem {
   }
 
   obgpu_ctx* ctx_ = nullptr;
-  bool dirty_ = true;
+  bool dirty_ = true, stale_ = false;
   std::vector<double> node_xy_, node_rotz_, elem_EAI_, con_val_, nl_val_, el_q_, el_q2_, el_dir_;
   std::vector<uint32_t> elem_nodes_, con_node_, nl_node_, el_elem_;
   std::vector<uint8_t> elem_type_, con_dof_, nl_dof_, el_kind_;

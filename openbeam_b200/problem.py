@@ -15,6 +15,7 @@ from __future__ import annotations
 import enum
 from dataclasses import dataclass, field
 
+import dataclasses
 import numpy as np
 
 from . import obgpu
@@ -87,6 +88,7 @@ class CStructureProblem:
         self.ctx = ctx or obgpu.Context(device)
         self.ctx.upload(structure)
         self._sym = False
+        self._stale_upload = False
 
     # ---- getters named as in CFiniteElementProblem.h ----
     def getNumberOfNodes(self):
@@ -96,6 +98,9 @@ class CStructureProblem:
         return self.structure.n_elems
 
     def updateAll(self):
+        if self._stale_upload:            # the device still holds the last pass of a nonLinearIterative solve
+            self.ctx.upload(self.structure)
+            self._stale_upload = False
         self.ctx.symbolic()
         self._sym = True
 
@@ -142,18 +147,58 @@ class CStructureProblem:
         out_info.F_f = self.ctx.download(obgpu.RES_FF)[0]
         return out_info
 
+    def _solve_once(self, options):
+        self.updateAll()
+        self.ctx.solve_static(int(options.algorithm), True, options.pcg_rtol, options.pcg_max_iter)
+        info = self.ctx.download(obgpu.RES_INFO)
+        if np.any(info != 0):
+            raise RuntimeError(obgpu.lib().obgpu_status_string(obgpu.ESINGULAR).decode())
+
+    N_MAX_ITERS = 40                      # solver_static.cpp:63
+
+    def _solveStaticIterative(self, out_info, options):
+        """StaticSolverOptions::nonLinearIterative (solver_static.cpp:55-58,63-66,139-193): the reference's loop sits
+        above assemble+solve, so it sits above the C-ABI here too.  Every pass re-assembles and re-solves on the GPU
+        with the node poses moved by the previous pass's U_f — a translation DOF adds to the node's global
+        coordinate as it is (also for a node with a rotated frame, like the reference), RZ composes into the node's
+        frame angle.  As in the reference there is no convergence test: all 40 passes run, the poses are restored
+        afterwards, and U_f / F_b / the stresses are those of the LAST pass (an increment on the last geometry)."""
+        orig = self.structure
+        xy = orig.node_xy.copy()
+        rz = np.zeros(orig.n_nodes) if orig.node_rotz is None else orig.node_rotz.copy()
+        try:
+            for it in range(self.N_MAX_ITERS):
+                if it:
+                    self.structure = dataclasses.replace(orig, node_xy=xy.copy(), node_rotz=rz.copy())
+                    self.ctx.upload(self.structure)
+                self._solve_once(options)
+                U_f = self.ctx.download(obgpu.RES_UF)[0]
+                free = self.ctx.symbolic_array(obgpu.SYM_FREE).astype(np.int64)
+                node = self.ctx.symbolic_array(obgpu.SYM_DOF_NODE)[free]
+                dof = self.ctx.symbolic_array(obgpu.SYM_DOF_ID)[free]
+                for d in (0, 1):            # DZ, RX, RY do not exist in a planar problem
+                    m = dof == d
+                    np.add.at(xy[:, d], node[m], U_f[m])
+                m = dof == 5
+                np.add.at(rz, node[m], U_f[m])
+        finally:
+            self.structure = orig         # solver_static.cpp:188-191 — the device keeps the last pass for stress()
+            self._stale_upload = True
+        self._fill_lists(out_info.build_info)
+        out_info.build_info.U_b = self.ctx.download(obgpu.RES_UB)
+        out_info.build_info.F_f = self.ctx.download(obgpu.RES_FF)[0]
+        out_info.U_f = self.ctx.download(obgpu.RES_UF)[0]
+        out_info.F_b = self.ctx.download(obgpu.RES_FB)[0]
+        return out_info
+
     def solveStatic(self, out_info: StaticSolveProblemInfo, options: StaticSolverOptions | None = None):
         options = options or StaticSolverOptions()
         if options.algorithm < 0:
             raise RuntimeError("StaticSolverAlgorithm::%s is the reference's CPU path; libobgpu has no CPU fallback"
                                % options.algorithm.name)
         if options.nonLinearIterative:
-            raise RuntimeError("nonLinearIterative is outside the GPU path (SURVEY.md §8f)")
-        self.updateAll()
-        self.ctx.solve_static(int(options.algorithm), True, options.pcg_rtol, options.pcg_max_iter)
-        info = self.ctx.download(obgpu.RES_INFO)
-        if np.any(info != 0):
-            raise RuntimeError(obgpu.lib().obgpu_status_string(obgpu.ESINGULAR).decode())
+            return self._solveStaticIterative(out_info, options)
+        self._solve_once(options)
         self._fill_lists(out_info.build_info)
         out_info.build_info.U_b = self.ctx.download(obgpu.RES_UB)
         out_info.build_info.F_f = self.ctx.download(obgpu.RES_FF)[0]

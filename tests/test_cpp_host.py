@@ -30,7 +30,7 @@ def test_cpp_mirror_symbolic(tmp_path):
 def test_cpp_mirror_solve(tmp_path):
     out = subprocess.check_output([build(tmp_path), "0"], text=True)
     U = np.array([float(x) for x in re.findall(r"(?m)^U_f\[\d+\] (\S+)", out)])
-    F = np.array([float(x) for x in re.findall(r"F_b\[\d+\] (\S+)", out)])
+    F = np.array([float(x) for x in re.findall(r"(?m)^F_b\[\d+\] (\S+)", out)])
     assert np.allclose(U, [2.6013078134695e-5, -6.5563909774436e-5, -1.29984937854503e-3,
                            -2.6013078134695e-5, -6.5563909774436e-5, 1.29984937854503e-3], rtol=1e-10)
     assert np.allclose(F, [7784.41363180755, 19620, -5136.62044771133, -7784.41363180755, 19620, 5136.62044771133],
@@ -41,3 +41,22 @@ def test_cpp_mirror_solve(tmp_path):
     assert "meshed nodes 17 elements 16 pieces_of_beam 8" in out
     Um = np.array([float(x) for x in re.findall(r"meshed U_f\[\d+\] (\S+)", out)])
     assert np.allclose(Um, U, rtol=1e-9)
+    # nonLinearIterative through the C++ mirror against the same loop around the oracle
+    import dataclasses
+    import fixtures
+    from oracle.pyoracle import OracleProblem
+    st = fixtures.demo3_frame()
+    xy, rz = st.node_xy.copy(), np.zeros(st.n_nodes)
+    for _ in range(40):
+        o = OracleProblem(dataclasses.replace(st, node_xy=xy.copy(), node_rotz=rz.copy())).solveStatic()
+        for (node, dof), u in zip(o.problem_DoFs[np.asarray(o.free_dof_indices, np.int64)], np.asarray(o.U_f)):
+            if dof < 3:
+                xy[node, dof] += u
+            elif dof == 5:
+                rz[node] += u
+    Ui = np.array([float(x) for x in re.findall(r"iterative U_f\[\d+\] (\S+)", out)])
+    Fi = np.array([float(x) for x in re.findall(r"iterative F_b\[\d+\] (\S+)", out)])
+    assert np.allclose(Ui, o.U_f, rtol=1e-9, atol=0) and np.allclose(Fi, o.F_b, rtol=1e-9, atol=1e-6)
+    assert not np.allclose(Ui, U, rtol=1e-6)
+    Ua = np.array([float(x) for x in re.findall(r"again U_f\[\d+\] (\S+)", out)])
+    assert np.allclose(Ua, U, rtol=1e-12)

@@ -68,6 +68,42 @@ def test_demo1_closed_form(ctx):
     assert np.allclose(s.element_stress[:, 1, 0], [1000, -1000 * np.sqrt(5), 2000], rtol=1e-12)
 
 
+def _oracle_iterative(st, n_iters=40):
+    """The reference's nonLinearIterative loop (solver_static.cpp:63-193) around the oracle's assemble+solve."""
+    import dataclasses
+    xy = st.node_xy.copy()
+    rz = np.zeros(st.n_nodes) if st.node_rotz is None else st.node_rotz.copy()
+    for _ in range(n_iters):
+        o = OracleProblem(dataclasses.replace(st, node_xy=xy.copy(), node_rotz=rz.copy())).solveStatic()
+        dofs = o.problem_DoFs[np.asarray(o.free_dof_indices, np.int64)]
+        U = np.asarray(o.U_f)
+        for i, (node, dof) in enumerate(dofs):
+            if dof < 3:
+                xy[node, dof] += U[i]
+            elif dof == 5:
+                rz[node] += U[i]
+    return o.postProcCalcStress()
+
+
+@pytest.mark.parametrize("name", ["demo3_frame", "demo1", "inclined_mixed"])
+def test_non_linear_iterative(ctx, name):
+    """StaticSolverOptions::nonLinearIterative: 40 assemble+solve passes with the node poses moved by each pass's U_f,
+    results of the last pass; afterwards the problem solves on its original poses again."""
+    st = fixtures.ALL[name]()
+    p = CStructureProblem(st, ctx=ctx)
+    info, s = StaticSolveProblemInfo(), StressInfo()
+    p.solveStatic(info, StaticSolverOptions(nonLinearIterative=True))
+    p.postProcCalcStress(s)
+    o = _oracle_iterative(st)
+    assert relerr(info.U_f, o.U_f) <= RTOL and relerr(info.F_b, o.F_b) <= RTOL
+    assert relerr(s.element_stress, o.element_stress) <= RTOL
+    lin = OracleProblem(st).solveStatic()
+    assert relerr(info.U_f, lin.U_f) > 1e-9        # the passes did move the nodes
+    assert p.structure is st
+    p.solveStatic(info)
+    assert relerr(info.U_f, lin.U_f) <= RTOL and relerr(info.F_b, lin.F_b) <= RTOL
+
+
 def test_singular_raises_reference_message(ctx):
     p = CStructureProblem(fixtures.mechanism(), ctx=ctx)
     with pytest.raises(RuntimeError, match="Ill-conditioned matrix. Too few restrictions"):
