@@ -104,6 +104,16 @@ def test_non_linear_iterative(ctx, name):
     assert relerr(info.U_f, lin.U_f) <= RTOL and relerr(info.F_b, lin.F_b) <= RTOL
 
 
+def test_non_linear_iterative_singular_restores_poses(ctx):
+    """A mechanism throws out of the first pass with the reference's message (solver_static.cpp:98-105) and leaves the
+    problem on its original poses."""
+    st = fixtures.mechanism()
+    p = CStructureProblem(st, ctx=ctx)
+    with pytest.raises(RuntimeError, match="Ill-conditioned matrix. Too few restrictions"):
+        p.solveStatic(StaticSolveProblemInfo(), StaticSolverOptions(nonLinearIterative=True))
+    assert p.structure is st
+
+
 def test_singular_raises_reference_message(ctx):
     p = CStructureProblem(fixtures.mechanism(), ctx=ctx)
     with pytest.raises(RuntimeError, match="Ill-conditioned matrix. Too few restrictions"):
