@@ -8,7 +8,12 @@ one ob-solve run does per structure.  Weak scaling: every rank owns its own 1M c
 rank), no data-path collective; the job's one exchange is the final all-gather of the per-case summaries (N > 1):
 the last step's kernel stores them into every rank's gathered array over NVLink (symmetric memory), else NCCL.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--cases L]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c2|c3|c4|c5] [--cases L]
+
+--config selects the BASELINE.json configuration (default c2 = configs[1], the one the metric is quoted on):
+  c3  random small frames (10-60 elements), 524 288 per GPU (= 4M / 8), warp-per-structure fused route
+  c4  817 x 817 grid frame, 2.0M DOF, one structure on one GPU: assembly + multigrid-PCG + stress  (N = 1 only)
+  c5  408 x 408 grid frames (0.5M DOF each), 8 per GPU (= 64 / 8), their PCGs concurrent on 8 streams
 
 Prints ONE JSON line on rank 0 (contract in the task statement).  `--impl reference` times the CPU oracle
 (restatement of the reference's algorithm; the reference itself cannot be built here) on all host
@@ -40,13 +45,24 @@ QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,c
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", dest="steps_given", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cases", type=int, default=1_000_000, help="load cases per GPU per step")
     ap.add_argument("--per-case-section", action="store_true", help="variant C2b: per-case A, Iz sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    return ap.parse_args()
+    ap.add_argument("--config", default="c2", choices=["c2", "c3", "c4", "c5"])
+    ap.add_argument("--grid", type=int, default=0, help="c4/c5: nodes per side (default 817 / 408)")
+    ap.add_argument("--structures", type=int, default=0, help="c3/c5: structures per GPU (default 524288 / 8)")
+    ap.add_argument("--rtol", type=float, default=1e-10, help="c4/c5: PCG tolerance on the true residual")
+    ap.add_argument("--pcg", default="mg", choices=["mg", "jacobi"], help="c4/c5: preconditioner")
+    ap.add_argument("--check", action="store_true", help="c4/c5: also compare U_f with scipy splu (CPU, minutes)")
+    a = ap.parse_args()
+    if a.steps_given is None:
+        a.steps = {"c2": 20, "c3": 20, "c4": 10, "c5": 5}[a.config]
+    else:
+        a.steps = a.steps_given
+    return a
 
 
 def config_dict(args, world):
@@ -353,6 +369,13 @@ TRAFFIC_BYTES_PER_CASE = 417.3
 TRAFFIC_SOURCE = "profiles/r01o_ncu_full_k_tiny_jit_summary.txt (1M-case launch, scaled per case)"
 
 
+def peak_info():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        return json.load(open(peaks_path))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (measured copy)"
+    return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
 _JSON_FD = None
 
 
@@ -377,6 +400,11 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.config in ("c4", "c5"):
+        import bench_lattice
+        if args.impl == "reference":
+            return bench_lattice.reference(args, rank, world, emit)
+        return bench_lattice.ours(args, rank, local_rank, world, emit, ClockSampler, peak_info)
     if args.impl == "reference":
         return reference_arm(args, rank, world)
     return ours_arm(args, rank, local_rank, world)

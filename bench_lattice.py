@@ -1,0 +1,273 @@
+"""bench.py legs for BASELINE.json configs C4 / C5 (large grid frames on the sparse route).  Part of the bench harness, not
+of the product package: its cpu_baseline / --impl reference / --check legs are the only places that execute oracle/.
+
+C4: one 817 x 817 grid frame (2.0M DOF) on one GPU.  C5: 64 grid frames of 408 x 408 (0.5M DOF each), 8 per GPU, their
+PCGs concurrent on 8 streams.  A *step* = for every structure of the rank the complete solveStatic + postProcCalcStress:
+element stiffness + assembly (K1+K4), BC gathers (K5), multigrid hierarchy numerics, PCG to the tolerance on the TRUE
+residual, reactions, element end forces.  Topology-dependent integer work (DOF numbering, pattern, plans) is done once
+before the timed region, as the inputs-resident rule of the bench contract says; its time is reported beside.
+"""
+from __future__ import annotations
+
+import os
+import threading
+import time
+
+import numpy as np
+
+from openbeam_b200 import obgpu, sharding, workloads
+
+METRIC = "static solves/s (FP64; full assemble+factor+solve+stress per load case)"
+UNIT = "solves/s"
+
+
+def lattice_params(args):
+    if args.config == "c4":
+        return (args.grid or 817), 1
+    return (args.grid or 408), (args.structures or 8)
+
+
+def make_structures(args, rank):
+    n, per = lattice_params(args)
+    if args.config == "c4":
+        return [workloads.grid_frame(n, n)]
+    out = []
+    for i in range(per):
+        g = rank * per + i   # global structure index: its own load seed and its own section
+        row = int(workloads.uniform01(300, np.uint64(g)) * len(workloads.IPE))
+        out.append(workloads.grid_frame(n, n, seed_index=g, section=(workloads.E_STEEL, workloads.IPE[row][0], workloads.IPE[row][1])))
+    return out
+
+
+def config_dict(args, world, sizes, method):
+    n, per = lattice_params(args)
+    name = "C4: %d x %d RR grid frame" % (n, n) if args.config == "c4" else "C5: %d grid frames of %d x %d per GPU" % (per, n, n)
+    return {
+        "workload": "%s (IPE sections, bottom row fixed, UDL on beams + random lateral nodal loads), each structure: "
+                    "assembly + %s-preconditioned CG (rtol %.0e on the true residual) + reactions + stress"
+                    % (name, "aggregation-multigrid" if method == "mg" else "Jacobi", args.rtol),
+        "structures_per_gpu": per, "n_dof_per_structure": sizes["n_tot"] // per, "n_free_total_per_gpu": sizes["nf_tot"],
+        "elements_per_gpu": sizes["Etot"],
+        "parallelism": "independent structures sharded over %d GPU(s), no data-path collective; one final NCCL all-gather "
+                       "of the 32-byte per-structure summaries inside the timed region" % world if world > 1 else
+                       "one GPU (a single structure's solve stays on one GPU)",
+        "l2_policy": "no flush: one PCG iteration streams the %.0f MB matrix, larger than the 126 MB L2"
+                     % (12.0 * sizes.get("ff_entries", 0) / per / 1e6) if sizes.get("ff_entries") else "no flush",
+    }
+
+
+def splu_check(st, U):
+    """U_f against scipy splu on the oracle's K_ff (CPU; the oracle is the checker here)."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+    from oracle.pyoracle import OracleProblem
+    o = OracleProblem(st).assembleProblem(skip_subK=True)
+    outer, inner, val = o.K_csc_upper()
+    n = len(outer) - 1
+    Ku = sp.csc_matrix((val, inner, outer), shape=(n, n))
+    K = (Ku + sp.triu(Ku, 1).T).tocsc()
+    f = o.free_dof_indices
+    Uref = spla.splu(K[f][:, f].tocsc()).solve(o.F_f)
+    return float(np.abs(U - Uref).max() / np.abs(Uref).max())
+
+
+def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — libobgpu has no CPU fallback")
+    if args.config == "c4" and world > 1:
+        # a single structure's solve stays on one GPU (north_star): replicas only
+        pass
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        if "NCCL_DEBUG_FILE" not in os.environ:
+            os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
+        dist.init_process_group("nccl", device_id=dev)
+    K, W = args.steps, args.warmup
+    method = obgpu.PCG_MG if args.pcg == "mg" else obgpu.PCG_JACOBI
+    sts = make_structures(args, rank)
+    per = len(sts)
+    ctx = obgpu.Context(local_rank)
+    t0 = time.perf_counter(); ctx.upload(sts); t_upload = time.perf_counter() - t0
+    t0 = time.perf_counter(); ctx.symbolic(); t_sym = time.perf_counter() - t0
+    t0 = time.perf_counter(); ctx.solve_static(method=method, rtol=args.rtol); ctx.synchronize()
+    t_first = time.perf_counter() - t0   # includes the sparse + multigrid plans (host, once per topology)
+    z = ctx.sizes()
+    ext = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+    summ = torch.empty((per, 4), dtype=torch.float64, device=dev)
+    gathered = torch.empty((world * per, 4), dtype=torch.float64, device=dev) if world > 1 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def step():
+        ctx.solve_static(method=method, rtol=args.rtol)
+
+    # pinned host buffers of the end-to-end leg: this step's load values in, U_f / F_b / stress out
+    nl_tot, el_tot = z["NLtot"], z["ELtot"]
+    h_nl, h_q = obgpu.pinned_empty((1, nl_tot)), obgpu.pinned_empty((1, el_tot))
+    h_nl[0] = np.concatenate([s.nload_val for s in sts]); h_q[0] = np.concatenate([s.eload_q for s in sts])
+    h_U, h_Fb = obgpu.pinned_empty((1, z["nf_tot"])), obgpu.pinned_empty((1, z["nb_tot"]))
+    h_S = obgpu.pinned_empty((1, z["Etot"], 2, 6))
+
+    def e2e_step():
+        ctx.update_cases(1, h_nl, h_q)      # H2D: the step's inputs (a new load case for every structure)
+        step()
+        ctx.download(obgpu.RES_UF, h_U); ctx.download(obgpu.RES_FB, h_Fb); ctx.download(obgpu.RES_STRESS, h_S)
+
+    with torch.cuda.stream(ext):
+        for _ in range(max(W - 1, 0)):
+            step()
+        barrier()
+        sampler = ClockSampler(local_rank) if rank == 0 else None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if world > 1:
+            dist.all_reduce(torch.zeros(1, device=dev))
+        e0.record(ext)
+        iters = []
+        for _ in range(K):
+            step()
+            iters.append(ctx.pcg_info()["iters"])
+        ctx.summaries_device(summ.data_ptr())
+        if world > 1:
+            sharding.gather_summaries(summ, gathered)   # the job's one exchange
+        e1.record(ext)
+        barrier()
+        ms_total = e0.elapsed_time(e1)
+        pi = ctx.pcg_info()
+        t = ctx.timings()
+        launches_per_step = int(t["launches"])
+        kernel_name = ctx.kernel_info()
+        which = obgpu.PROF_MG_SPMV if args.pcg == "mg" else obgpu.PROF_SPMV
+        k_ms, k_bytes = ctx.profile_kernel(which, 50)
+        spmv_ms, spmv_bytes = ctx.profile_kernel(obgpu.PROF_SPMV, 50)
+        relerr = None
+        if args.check and rank == 0:
+            U = ctx.download(obgpu.RES_UF)[0]
+            fo = ctx.offsets(obgpu.OFF_FREE)
+            relerr = [splu_check(sts[s], U[fo[s]:fo[s + 1]]) for s in sorted({0, per - 1})]
+        barrier()
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            e2e_step()
+        torch.cuda.synchronize(dev)
+        e2e_s = time.perf_counter() - t0
+        barrier()
+        clocks = sampler.stop() if sampler else None
+    tt = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_total, e2e_s = tt.tolist()
+    if rank == 0:
+        peak, peak_src = peak_info()
+        value = world * per * K / (ms_total * 1e-3)
+        n_dof = z["n_tot"] // per
+        achieved = k_bytes / (k_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": config_dict(args, world, z, args.pcg),
+            "dof_per_s": value * n_dof,
+            "pcg": {"method": args.pcg, "iterations_per_step": float(np.mean(iters)), "true_relres": pi["true_relres"],
+                    "restarts": pi["restarts"], "levels": pi["levels"], "rtol": args.rtol,
+                    "relerr_vs_splu": relerr},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": kernel_name, "kernel_ms": k_ms,
+                         "algorithmic_bytes_per_launch": k_bytes,
+                         "spmv_alone": {"kernel": "k_spmv_dot", "ms": spmv_ms, "algorithmic_bytes": spmv_bytes,
+                                        "frac": spmv_bytes / (spmv_ms * 1e-3) / 1e9 / peak},
+                         "note": "one launch over the first structure's rows, timed alone (50 back-to-back launches "
+                                 "between CUDA events on the ctx stream)", "peak_source": peak_src},
+            "e2e": {"value": world * per * K / e2e_s, "unit": UNIT,
+                    "h2d_bytes_per_step": int(h_nl.nbytes + h_q.nbytes),
+                    "d2h_bytes_per_step": int(h_U.nbytes + h_Fb.nbytes + h_S.nbytes),
+                    "api": "obgpu_update_cases (pinned host load values) + obgpu_solve_static + obgpu_download of U_f, "
+                           "F_b, stress into pinned host buffers"},
+            "gpu_launches": int(K * launches_per_step),
+            "once_per_topology_s": {"upload": t_upload, "symbolic": t_sym, "first_solve_incl_plans": t_first},
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args, n_dof)
+        emit(line)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+SAMPLE_GRID = 32   # faithful reference algorithm: 32 x 32 nodes, 3072 DOF, ~2.6 s per solve on one core
+
+
+def faithful_sample(threads, repeats=1):
+    """The reference's own algorithm (dense-structured K_ff extraction + dense Cholesky, assemble.cpp:249-297,
+    solver_static.cpp:84-109) through the oracle port on SAMPLE_GRID^2-node grids of the same family, one structure per
+    host thread.  Returns (structures solved, seconds, DOF per structure)."""
+    from oracle.pyoracle import OracleProblem
+    sts = [workloads.grid_frame(SAMPLE_GRID, SAMPLE_GRID, seed_index=i) for i in range(threads)]
+    n_dof = [0]
+
+    def work(st):
+        for _ in range(repeats):
+            o = OracleProblem(st).solveStatic().postProcCalcStress()
+        n_dof[0] = o.sizes()["n"]
+
+    th = [threading.Thread(target=work, args=(st,)) for st in sts]
+    t0 = time.perf_counter()
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    return threads * repeats, time.perf_counter() - t0, n_dof[0]
+
+
+def cpu_baseline(args, n_dof_full):
+    cores = os.cpu_count() or 1
+    n, dt, nd = faithful_sample(cores)
+    return {
+        "value": n * nd / dt / n_dof_full, "unit": UNIT, "cores": cores, "kind": "port",
+        "dof_per_s": n * nd / dt,
+        "sample": "the reference's algorithm is O(n^2) memory and O(n^3) time (dense-structured K_ff, dense Cholesky) and "
+                  "cannot hold this structure: timed instead on %d grid frames of %d x %d nodes (%d DOF each), one "
+                  "solveStatic+postProcCalcStress per host thread; value = measured DOF/s divided by this config's %d DOF "
+                  "per structure, i.e. full-size solves/s under a linear-scaling assumption that flatters the CPU"
+                  % (n, SAMPLE_GRID, SAMPLE_GRID, nd, n_dof_full)}
+
+
+def reference(args, rank, world, emit):
+    if rank != 0:
+        return 0
+    n_side, per = lattice_params(args)
+    n_dof_full = 3 * n_side * n_side
+    cores = os.cpu_count() or 1
+    for _ in range(min(args.warmup, 1)):
+        faithful_sample(cores)
+    tot_n, tot_t, nd = 0, 0.0, 0
+    for _ in range(args.steps):
+        n, dt, nd = faithful_sample(cores)
+        tot_n += n; tot_t += dt
+    v = tot_n * nd / tot_t / n_dof_full
+    sizes = {"n_tot": n_dof_full * per, "nf_tot": per * 3 * n_side * (n_side - 1), "Etot": per * 2 * n_side * (n_side - 1)}
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args, world, sizes, args.pcg),
+        "dof_per_s": tot_n * nd / tot_t,
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "each step: %d grid frames of %d x %d nodes (%d DOF), faithful reference algorithm via the "
+                                   "oracle port, one per host thread; value = DOF/s / %d DOF (linear-scaling assumption "
+                                   "that flatters the CPU: the reference is O(n^3))" % (cores, SAMPLE_GRID, SAMPLE_GRID, nd, n_dof_full)},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference unbuildable here (needs MRPT>=2.4 + Eigen): this is the oracle port in faithful mode",
+    }
+    emit(line)
+    return 0

@@ -80,11 +80,17 @@ typedef struct obgpu_batch_desc {
   const double* eload_q2;       /* NULL or [ELtot] second parameter: q_end (TRIANGULAR), dist (CONCENTRATED) */
 } obgpu_batch_desc;
 
-enum { OBGPU_BATCHED_LDLT = 0, OBGPU_PCG_JACOBI = 1, OBGPU_PCG_BJ3 = 2, OBGPU_PCG_IC0 = 3 };
+/* Solvers.  OBGPU_BATCHED_LDLT stands for StaticSolverAlgorithm::Dense_LLT (solver_static.cpp:84-109): one dense
+ * factorisation per system.  The two CG variants stand for ::Sparse_LLT (solver_static.cpp:110-129) on structures far
+ * beyond what a dense-structured K_ff can hold: OBGPU_PCG_JACOBI (diagonal preconditioner) and OBGPU_PCG_MG (aggregation
+ * multigrid V-cycle over rigid-body-mode coarse spaces, Chebyshev smoother — 100x fewer iterations on large lattices;
+ * the sparse route's recommended method).  Both stop on the TRUE residual ||F_f - K_ff U_f||, recomputed at exit. */
+enum { OBGPU_BATCHED_LDLT = 0, OBGPU_PCG_JACOBI = 1, OBGPU_PCG_MG = 2 };
 typedef struct obgpu_solve_opts {
   int method;        /* OBGPU_BATCHED_LDLT (default) or a PCG variant            */
   int with_stress;   /* fuse postProcCalcStress into the solve kernel (default 1) */
-  double rtol;       /* PCG: ||r||_2 <= rtol*||b||_2 (default 1e-12)             */
+  double rtol;       /* PCG: ||F_f - K_ff U_f||_2 <= max(rtol*||F_f||_2, 16 eps || |K_ff||U_f| ||_2) (default 1e-12);
+                        the second term is the FP64 rounding floor of the residual itself */
   int max_iter;      /* PCG: default 20*sqrt(n_f)+1000                            */
   int flags;         /* OBGPU_SOLVE_* bits (default 0)                            */
 } obgpu_solve_opts;
@@ -184,6 +190,15 @@ int obgpu_bind_summary_peers(obgpu_ctx*, int n, double* const* bufs);
  * out[0] symbolic (host), [1] assembleProblem, [2] solveStatic.2_solve, [3] postProcCalcStress, [4] H2D, [5] D2H,
  * [6] kernel launches in the last solve/assemble call (count), [7] PCG iterations of the last solve */
 int obgpu_get_timings(const obgpu_ctx*, double out[8]);
+/* the last PCG solve (sparse route): out[0] iterations summed over the structures, [1] worst TRUE relative residual
+ * ||F_f - K_ff U_f||_2 / ||F_f||_2 recomputed from U_f at exit (the reference's SimplicialLLT branch has no such figure:
+ * it does not even check info(), solver_static.cpp:117-128), [2] restarts from the true residual, [3] multigrid levels */
+int obgpu_pcg_info(const obgpu_ctx*, double out[4]);
+/* measurement aid: times `reps` back-to-back launches of one iteration kernel of the last PCG solve (first structure's
+ * rows) with CUDA events on the ctx stream; *alg_bytes = the algorithmic HBM bytes of one launch.  The
+ * results of the solve are left untouched. */
+enum { OBGPU_PROF_SPMV = 0 /* k_spmv_dot */, OBGPU_PROF_MG_SPMV = 1 /* k_mg_spmv, fine level */ };
+int obgpu_profile_kernel(obgpu_ctx*, int which, int reps, double* ms_avg, double* alg_bytes);
 /* ---- CStructureProblem::mesh(): the caller-side step right before the path ----
  * Subdivides every beam of every structure into ceil(L / max_element_length) pieces and splits the element loads, exactly
  * as CStructureProblem_mesh.cpp:37-132, CBaseElementBeam.cpp:317-422 and the loads' meshLoad methods do (including the

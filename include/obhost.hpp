@@ -29,6 +29,7 @@ enum class StaticSolverAlgorithm : uint8_t {
   Sparse_LLT,
   GPU_Batched_LDLT,
   GPU_PCG_Jacobi,
+  GPU_PCG_MG,
 };
 
 struct StaticSolverOptions {
@@ -263,7 +264,9 @@ class CStructureProblem {
   void solve_pass(const StaticSolverOptions& opts) {
     updateAll();
     obgpu_solve_opts o;
-    o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI : OBGPU_BATCHED_LDLT;
+    o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI
+             : opts.algorithm == StaticSolverAlgorithm::GPU_PCG_MG   ? OBGPU_PCG_MG
+                                                                      : OBGPU_BATCHED_LDLT;
     o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.flags = 0;
     check(obgpu_solve_static(ctx_, &o));
     const auto z = sizes();

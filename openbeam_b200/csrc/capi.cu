@@ -209,6 +209,7 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   c->sym = Symbolic();
   c->dev_batch = false;
   c->dev_plan = false;
+  c->dev_mg = false;
   c->assembled = false;
   c->prog = TinyProgram();
   return upload_cases(c, hb.L, d->case_nload_val, d->case_eload_q, d->case_elem_EAI);
@@ -229,6 +230,7 @@ int obgpu_symbolic(obgpu_ctx* c) {
   std::string err;
   c->dev_batch = false;
   c->dev_plan = false;
+  c->dev_mg = false;
   c->assembled = false;
   // the K pattern costs O(T log T) host work: built eagerly for moderate batches, on demand otherwise
   int rc = run_symbolic(c->hb, c->sym, err, c->hb.Etot() <= (int64_t(1) << 22));

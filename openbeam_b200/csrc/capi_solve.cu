@@ -10,6 +10,7 @@ namespace obgpu {
 int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o);   // capi_general.cu
 int assemble_general(obgpu_ctx* c);                            // capi_general.cu
 int download_general(obgpu_ctx* c, int which, void* host_out, bool& handled);
+int profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, double* alg_bytes);  // capi_sparse.cu
 }
 
 static int ensure_symbolic(obgpu_ctx* c) {
@@ -203,6 +204,21 @@ int obgpu_get_timings(const obgpu_ctx* cc, double out[8]) {
   out[6] = c->launches;
   out[7] = c->pcg_iters;
   cudaGetLastError();
+  return OBGPU_OK;
+}
+
+int obgpu_profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, double* alg_bytes) {
+  if (!c) return OBGPU_EINVAL;
+  OB_NEED_DEVICE(c);
+  return profile_kernel(c, which, reps, ms_avg, alg_bytes);
+}
+
+int obgpu_pcg_info(const obgpu_ctx* c, double out[4]) {
+  if (!c || !out) return OBGPU_EINVAL;
+  out[0] = c->pcg_iters;
+  out[1] = c->pcg_relres;
+  out[2] = c->pcg_restarts;
+  out[3] = c->pcg_levels;
   return OBGPU_OK;
 }
 

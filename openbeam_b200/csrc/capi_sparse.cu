@@ -1,6 +1,7 @@
 // capi_sparse.cu — global K assembly (K1+K4), BC gather (K5) and the PCG route (K7-K9, K10) for large structures.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -55,6 +56,40 @@ static int ensure_plan(obgpu_ctx* c) {
   OB_CUDA(c, c->d_Eq.reserve(std::max<size_t>(c->sym.nb_tot(), 1)));
   OB_CUDA(c, cudaStreamSynchronize(st));  // node0/f0/eg are stack vectors
   c->dev_plan = true;
+  return OBGPU_OK;
+}
+
+// multigrid plan (host, once per topology) and its device arrays
+static int ensure_mg(obgpu_ctx* c) {
+  if (c->dev_mg) return OBGPU_OK;
+  std::string err;
+  int rc = build_mg_plan(c->hb, c->sym, c->plan, c->mg, err);
+  if (rc != OBGPU_OK) return fail(c, rc, err);
+  const size_t nl = c->mg.lev.size();
+  if (nl > size_t(MG_MAX_LEVELS)) return fail(c, OBGPU_EUNSUPPORTED, "multigrid hierarchy deeper than MG_MAX_LEVELS");
+  c->mg_lev.clear();
+  c->mg_lev.resize(nl);
+  cudaStream_t st = c->stream;
+  for (size_t l = 1; l < nl; l++) {
+    const MgLevel& L = c->mg.lev[l];
+    obgpu_ctx::MgLevelBufs& B = c->mg_lev[l];
+    OB_CUDA(c, B.sl_ptr.upload(L.sl_ptr, st));
+    OB_CUDA(c, B.col.upload(L.col, st));
+    OB_CUDA(c, B.f_agg.upload(L.f_agg, st));
+    OB_CUDA(c, B.f_kind.upload(L.f_kind, st));
+    OB_CUDA(c, B.f_w.upload(L.f_w, st));
+    OB_CUDA(c, B.mem_ptr.upload(L.mem_ptr, st));
+    OB_CUDA(c, B.mem.upload(L.mem, st));
+    OB_CUDA(c, B.val.reserve(std::max<size_t>(L.col.size(), 1)));
+    OB_CUDA(c, B.minv.reserve(size_t(L.n)));
+    OB_CUDA(c, B.vec.reserve(size_t(5) * L.n));
+    OB_CUDA(c, cudaMemsetAsync(B.vec.p, 0, size_t(5) * L.n * sizeof(double), st));
+    OB_CUDA(c, cudaMemsetAsync(B.minv.p, 0, size_t(L.n) * sizeof(double), st));
+  }
+  OB_CUDA(c, c->d_mg_lam.reserve(MG_MAX_LEVELS));
+  OB_CUDA(c, c->d_mg_cinv.reserve(size_t(obgpu_ctx::NPCG) * MgPlan::DENSE_MAX * MgPlan::DENSE_MAX));
+  OB_CUDA(c, cudaStreamSynchronize(st));
+  c->dev_mg = true;
   return OBGPU_OK;
 }
 
@@ -129,10 +164,15 @@ int assemble_general(obgpu_ctx* c) {
 }
 
 int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
-  if (o.method != OBGPU_PCG_JACOBI)
-    return fail(c, OBGPU_EUNSUPPORTED, "only OBGPU_PCG_JACOBI is implemented on the sparse route so far");
+  if (o.method != OBGPU_PCG_JACOBI && o.method != OBGPU_PCG_MG)
+    return fail(c, OBGPU_EINVAL, "obgpu_solve_static: unknown method (OBGPU_BATCHED_LDLT, OBGPU_PCG_JACOBI, OBGPU_PCG_MG)");
+  const bool use_mg = o.method == OBGPU_PCG_MG;
   int rc = assemble_general(c);
   if (rc != OBGPU_OK) return rc;
+  if (use_mg) {
+    rc = ensure_mg(c);
+    if (rc != OBGPU_OK) return rc;
+  }
   const Symbolic& sy = c->sym;
   const int64_t L = c->L, S = c->hb.S, nf = sy.nf_tot(), nb = sy.nb_tot(), Etot = c->hb.Etot();
   double launches = c->launches;
@@ -145,12 +185,16 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   // once per iteration and would evict them; an access-policy window marks the slab persisting (everything else on
   // the stream is treated as streaming), so the three vector kernels and the gathers of the SpMV run out of L2.
   const size_t nfp = (size_t(std::max<int64_t>(nf, 1)) + 31) & ~size_t(31);
-  OB_CUDA(c, c->d_pcgvec.reserve(5 * nfp));
+  const size_t nvec = use_mg ? 8 : 5;  // + the V-cycle's fine-level residual and two Chebyshev directions
+  OB_CUDA(c, c->d_pcgvec.reserve(nvec * nfp));
   double* const v_p = c->d_pcgvec.p;
   double* const v_ap = v_p + nfp;
   double* const v_r = v_ap + nfp;
   double* const v_z = v_r + nfp;
   double* const v_minv = v_z + nfp;
+  double* const v_mr = v_minv + nfp;
+  double* const v_md0 = v_mr + nfp;
+  double* const v_md1 = v_md0 + nfp;
   bool l2_window = false;
   cudaStreamAttrValue l2_av;
   std::memset(&l2_av, 0, sizeof(l2_av));
@@ -159,7 +203,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     int max_persist = 0, max_window = 0;
     cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, c->device);
     cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, c->device);
-    const size_t slab = 5 * nfp * sizeof(double);
+    const size_t slab = nvec * nfp * sizeof(double);
     if (want && max_persist > 0 && max_window > 0 && slab > (8u << 20)) {
       const size_t win = std::min(slab, size_t(max_window));
       const size_t carve = std::min(win, size_t(max_persist));
@@ -202,8 +246,13 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   OB_CUDA(c, cudaMemsetAsync(c->d_info.p, 0, size_t(L) * S * sizeof(int32_t), c->stream));
   OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
   const double rtol = o.rtol > 0 ? o.rtol : 1e-12;
+  c->prof_valid = false;
   static const bool use_graph = !(getenv("OBGPU_PCG_GRAPH") && atoi(getenv("OBGPU_PCG_GRAPH")) == 0);
-  const int chk = use_graph ? 24 : 25;  // iterations between convergence checks (even when replayed as a graph)
+  // iterations between convergence checks (even when replayed as a graph); a multigrid iteration is ~40 kernels and
+  // the whole solve ~100 iterations, so it is checked every other iteration
+  const int chk = use_mg ? 2 : use_graph ? 24 : 25;
+  double restarts_total = 0, worst_floor = 0;
+  std::vector<double> mg_lam(MG_MAX_LEVELS, 0.0);
   double iters_total = 0, worst_rel = 0;
   bool all_converged = true;
   std::vector<int32_t> h_info(size_t(L) * S, 0);
@@ -212,8 +261,35 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     SparseDev d = sparse_dev(c, k);
     if (cs == 0 || c->has_case_eai) {  // K5: BC elimination as gathers, Jacobi diagonal
       OB_CUDA(c, launch_bc_gather(d, c->stream));
-      OB_CUDA(c, launch_inv_diag(nf, d.ff_diag, d.ff_val, v_minv, c->stream));
-      launches += 3;
+      launches += 2;
+      if (!use_mg) {
+        OB_CUDA(c, launch_inv_diag(nf, d.ff_diag, d.ff_val, v_minv, c->stream));
+        launches += 1;
+      } else {
+        // numeric setup of the hierarchy from the current K_ff: Galerkin products level by level, Jacobi diagonals and
+        // Gershgorin bounds of D^-1 A (the Chebyshev intervals); the coarsest inverses are built per structure below
+        const size_t nl = c->mg.lev.size();
+        OB_CUDA(c, cudaMemsetAsync(c->d_mg_lam.p, 0, MG_MAX_LEVELS * sizeof(double), c->stream));
+        OB_CUDA(c, launch_mg_diag(0, nf, d.sl_ptr, d.ff_col, d.ff_val, v_minv, c->d_mg_lam.p, c->stream));
+        launches += 1;
+        for (size_t l = 1; l < nl; l++) {
+          const MgLevel& ML = c->mg.lev[l];
+          obgpu_ctx::MgLevelBufs& B = c->mg_lev[l];
+          MgGalerkinArgs g;
+          g.n_coarse = ML.n;
+          g.f_slptr = l == 1 ? d.sl_ptr : c->mg_lev[l - 1].sl_ptr.p;
+          g.f_col = l == 1 ? d.ff_col : c->mg_lev[l - 1].col.p;
+          g.f_val = l == 1 ? d.ff_val : c->mg_lev[l - 1].val.p;
+          g.f_agg = B.f_agg.p; g.f_kind = B.f_kind.p; g.f_w = B.f_w.p;
+          g.mem_ptr = B.mem_ptr.p; g.mem = B.mem.p;
+          g.c_slptr = B.sl_ptr.p; g.c_col = B.col.p; g.c_val = B.val.p;
+          OB_CUDA(c, launch_mg_galerkin(g, c->stream));
+          OB_CUDA(c, launch_mg_diag(0, ML.n, B.sl_ptr.p, B.col.p, B.val.p, B.minv.p, c->d_mg_lam.p + l, c->stream));
+          launches += 2;
+        }
+        OB_CUDA(c, cudaMemcpyAsync(mg_lam.data(), c->d_mg_lam.p, MG_MAX_LEVELS * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        OB_CUDA(c, cudaStreamSynchronize(c->stream));
+      }
     }
     const double* nl = c->has_case_nl ? c->d_case_nl.p + size_t(cs) * c->hb.NLtot() : c->d_nload_val.p;
     const double* q = c->has_case_q ? c->d_case_q.p + size_t(cs) * c->hb.ELtot() : c->d_eload_q.p;
@@ -227,6 +303,8 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     // 0.5 M DOF per GPU were launch-latency bound one after the other) ----
     struct Job {
       int64_t s = -1; PcgArgs a; int it = 0, max_iter = 0; bool busy = false;
+      bool verifying = false;   // the recurrence says converged: the true residual b - A x is being computed
+      int restarts = 0; double prev_true = -1;
       cudaGraph_t graph = nullptr; cudaGraphExec_t exec = nullptr;  // `chk` iterations of THIS structure as one launch
     };
     auto drop_graph = [](Job& jb) {
@@ -251,7 +329,55 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
       a.r = v_r; a.z = v_z; a.p = v_p; a.ap = v_ap;
       a.ctas_per_sm = NC > 1 ? 2 : 0;  // measured at C5's share (8 x 0.5 M DOF): 8 -> 1.84 s, 4 -> 1.67 s, 2 -> 1.62 s
       a.scal = c->d_scal.p + 16 * k; a.partial = c->d_partial.p + size_t(k) * part_stride; a.counter = c->d_counter.p + k;
-      jb.s = st_i; jb.a = a; jb.it = 0; jb.busy = true;
+      a.mg = nullptr;
+      if (use_mg) {
+        MgJob& J = c->mg_job[k];
+        J = MgJob();
+        J.nlev = c->mg.nlev[st_i];
+        J.dense = c->mg.dense[st_i] != 0;
+        J.cinv = c->d_mg_cinv.p + size_t(k) * MgPlan::DENSE_MAX * MgPlan::DENSE_MAX;
+        if (const char* ev = getenv("OBGPU_MG_OMEGA")) J.omega = atof(ev);
+        for (int l = 0; l < J.nlev; l++) {
+          MgLevelDev& V = J.lv[l];
+          if (l == 0) {
+            V.r0 = a.r0; V.r1 = a.r1;
+            V.slptr = d.sl_ptr; V.col = d.ff_col; V.val = d.ff_val; V.minv = v_minv;
+            V.x = v_z; V.b = v_r; V.r = v_mr; V.d0 = v_md0; V.d1 = v_md1;
+          } else {
+            const MgLevel& ML = c->mg.lev[size_t(l)];
+            obgpu_ctx::MgLevelBufs& B = c->mg_lev[size_t(l)];
+            V.r0 = ML.row_off[st_i]; V.r1 = V.r0 + ML.nrows[st_i];
+            V.slptr = B.sl_ptr.p; V.col = B.col.p; V.val = B.val.p; V.minv = B.minv.p;
+            V.x = B.vec.p; V.b = V.x + ML.n; V.r = V.b + ML.n; V.d0 = V.r + ML.n; V.d1 = V.d0 + ML.n;
+          }
+          if (l + 1 < J.nlev) {  // transfer to the next coarser level (arrays indexed by this level's rows)
+            obgpu_ctx::MgLevelBufs& BC = c->mg_lev[size_t(l) + 1];
+            V.f_agg = BC.f_agg.p; V.f_kind = BC.f_kind.p; V.f_w = BC.f_w.p; V.mem_ptr = BC.mem_ptr.p; V.mem = BC.mem.p;
+          } else {
+            V.f_agg = nullptr; V.f_kind = nullptr; V.f_w = nullptr; V.mem_ptr = nullptr; V.mem = nullptr;
+          }
+          // Chebyshev(2) on [lam/8, lam]
+          const double lmax = mg_lam[size_t(l)] > 0 ? mg_lam[size_t(l)] : 1.0, lmin = lmax / 8.0;
+          const double theta = 0.5 * (lmax + lmin), delta = 0.5 * (lmax - lmin), sigma = theta / delta;
+          const double rho0 = 1.0 / sigma, rho1 = 1.0 / (2.0 * sigma - rho0);
+          V.c0 = 1.0 / theta; V.c1 = rho1 * rho0; V.c2 = 2.0 * rho1 / delta;
+        }
+        if (J.dense) {
+          const MgLevelDev& C = J.lv[J.nlev - 1];
+          cudaError_t e = launch_mg_dense_inverse(C.r0, C.r1 - C.r0, C.slptr, C.col, C.val, const_cast<double*>(J.cinv), pst[size_t(k)]);
+          launches += 1;
+          if (e != cudaSuccess) return e;
+        }
+        a.mg = &J;
+      }
+      if (!c->prof_valid) {  // kept for obgpu_profile_kernel: the first structure's iteration arguments
+        c->prof_args = a;
+        c->prof_args.mg = nullptr;
+        c->prof_mg = use_mg;
+        if (use_mg) c->prof_lv0 = c->mg_job[k].lv[0];
+        c->prof_valid = true;
+      }
+      jb.s = st_i; jb.a = a; jb.it = 0; jb.busy = true; jb.verifying = false; jb.restarts = 0; jb.prev_true = -1;
       const int nrows = a.r1 - a.r0;
       jb.max_iter = o.max_iter > 0 ? o.max_iter : int(20.0 * std::sqrt(double(nrows))) + 1000;
       cudaError_t e = launch_pcg_init(a, c->sm_count, pst[size_t(k)]);
@@ -273,13 +399,37 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
         OB_CUDA(c, cudaStreamSynchronize(pst[size_t(k)]));
         double rr = c->h_scal[8 * k + 3];
         const double bb = c->h_scal[8 * k + 4];
-        if (jb.it == 0) rr = bb;
+        if (jb.it == 0 && !jb.verifying) rr = bb;
         bool conv = false, stop = false;
         if (!(rr == rr)) stop = true;                              // NaN: breakdown (K_ff not positive definite)
-        else if (rr <= rtol * rtol * bb) { conv = true; stop = true; }
-        else if (jb.it >= jb.max_iter) stop = true;
+        else if (jb.verifying) {
+          // rr is now ||F_f - K_ff U_f||^2 computed from U_f itself.  Below the tolerance: done.  Otherwise the
+          // recurrence drifted from the true residual: restart CG from it (at most 3 times, and only while a restart
+          // still gains something — a tolerance below what FP64 can attain for this K_ff is reported, not looped on)
+          jb.verifying = false;
+          // FP64 floor of this residual: 16 eps || |K_ff| |U_f| ||_2 (a stiff structure under a soft load pattern cannot
+          // be told from converged below it); a tolerance under the floor is met at the floor
+          const double floor2 = 256.0 * 4.930380657631324e-32 * c->h_scal[8 * k + 5];
+          worst_floor = std::max(worst_floor, bb > 0 ? std::sqrt(floor2 / bb) : 0.0);
+          if (rr <= std::max(rtol * rtol * bb, floor2)) { conv = true; stop = true; }
+          else if (jb.restarts >= 3 || jb.it >= jb.max_iter || (jb.prev_true >= 0 && rr > 0.25 * jb.prev_true)) stop = true;
+          else {
+            jb.prev_true = rr;
+            jb.restarts++;
+            restarts_total += 1;
+            OB_CUDA(c, launch_pcg_restart(jb.a, jb.it, c->sm_count, pst[size_t(k)]));
+            launches += use_mg ? 40 : 1;
+          }
+        } else if (rr <= rtol * rtol * bb || jb.it >= jb.max_iter) {
+          jb.verifying = true;
+          OB_CUDA(c, launch_pcg_true_residual(jb.a, c->sm_count, pst[size_t(k)]));
+          launches += 1;
+          OB_CUDA(c, cudaMemcpyAsync(c->h_scal + 8 * k, jb.a.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, pst[size_t(k)]));
+          continue;
+        }
         if (!stop) {
-          const int n_it = std::min(chk, jb.max_iter - jb.it);
+          const int n_it = std::min(chk, std::max(1, jb.max_iter - jb.it));
+          const double per_iter = jb.a.mg ? 3.0 + 1.0 + 6.0 * (jb.a.mg->nlev - 1) + 1.0 : 3.0;
           if (use_graph && n_it == chk && (jb.it & 1) == 0) {
             // the 3*chk kernels of a check interval replayed as one graph launch: the host no longer has to feed
             // ~13 us per kernel launch to a loop whose kernels take 5-20 us each (chk is even: same rz ping-pong parity)
@@ -294,10 +444,10 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
             }
             OB_CUDA(c, cudaGraphLaunch(jb.exec, pst[size_t(k)]));
             jb.it += chk;
-            launches += 3.0 * n_it;
+            launches += per_iter * n_it;
           } else {
             for (int q2 = 0; q2 < n_it; q2++, jb.it++) OB_CUDA(c, launch_pcg_iter(jb.a, jb.it, c->sm_count, pst[size_t(k)]));
-            launches += 3.0 * n_it;
+            launches += per_iter * n_it;
           }
           OB_CUDA(c, cudaMemcpyAsync(c->h_scal + 8 * k, jb.a.scal, 8 * sizeof(double), cudaMemcpyDeviceToHost, pst[size_t(k)]));
           continue;
@@ -342,11 +492,54 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   c->launches = launches;
   c->pcg_iters = iters_total;
   c->pcg_relres = worst_rel;
+  c->pcg_restarts = restarts_total;
+  c->pcg_levels = use_mg ? double(c->mg.lev.size()) : 1.0;
   c->solved = true;
   c->have_ff = true;
-  c->kernel_info = "k_spmv_dot (SELL-32 SpMV of the Jacobi-PCG iteration)";
+  c->kernel_info = use_mg ? "k_mg_spmv (SELL-32 SpMV + fused Chebyshev step of the multigrid-PCG V-cycle)"
+                          : "k_spmv_dot (SELL-32 SpMV of the Jacobi-PCG iteration)";
   c->have_stress = o.with_stress != 0;
-  if (!all_converged) return fail(c, OBGPU_ENOTCONVERGED, "PCG did not converge (or broke down: K_ff not positive definite?)");
+  if (!all_converged) {
+    char msg[384];
+    snprintf(msg, sizeof msg, "PCG did not converge: worst true relative residual ||F_f - K_ff U_f||/||F_f|| = %.3e against "
+             "rtol %.1e, FP64 floor %.1e (max_iter reached or K_ff not positive definite)", worst_rel, rtol, worst_floor);
+    return fail(c, OBGPU_ENOTCONVERGED, msg);
+  }
+  return OBGPU_OK;
+}
+
+// Times `reps` back-to-back launches of one iteration kernel of the last PCG solve on the first structure's rows with
+// CUDA events on the ctx stream (bench.py's live roofline figure).  The vectors it touches are scratch of the finished
+// solve (p, ap, z and the V-cycle's work vectors): U_f, F_b and the stresses are not disturbed.
+int profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, double* alg_bytes) {
+  if (!c->prof_valid || !c->solved) return fail(c, OBGPU_ESEQUENCE, "obgpu_profile_kernel: no PCG solve to profile");
+  if (which == OBGPU_PROF_MG_SPMV && !c->prof_mg) return fail(c, OBGPU_ESEQUENCE, "obgpu_profile_kernel: the last solve was not OBGPU_PCG_MG");
+  if (which != OBGPU_PROF_SPMV && which != OBGPU_PROF_MG_SPMV) return fail(c, OBGPU_EINVAL, "obgpu_profile_kernel: unknown kernel id");
+  reps = std::max(1, reps);
+  const PcgArgs& a = c->prof_args;
+  // entries of the structure's slices (padding included: it is read like the rest)
+  const int64_t s0 = a.r0 >> 5, s1 = (int64_t(a.r1) + 31) >> 5;
+  const int64_t entries = int64_t(c->plan.sl_ptr[s1]) - int64_t(c->plan.sl_ptr[s0]), n = a.r1 - a.r0;
+  cudaEvent_t e0, e1;
+  OB_CUDA(c, cudaEventCreate(&e0));
+  OB_CUDA(c, cudaEventCreate(&e1));
+  for (int pass = 0; pass < 2; pass++) {  // pass 0 = warm-up
+    OB_CUDA(c, cudaEventRecord(e0, c->stream));
+    for (int i = 0; i < reps; i++) {
+      if (which == OBGPU_PROF_SPMV) OB_CUDA(c, launch_spmv_only(a, c->sm_count, c->stream));
+      else OB_CUDA(c, launch_mg_cheb_only(c->prof_lv0, c->sm_count, c->stream));
+    }
+    OB_CUDA(c, cudaEventRecord(e1, c->stream));
+    OB_CUDA(c, cudaEventSynchronize(e1));
+  }
+  float ms = 0;
+  OB_CUDA(c, cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (ms_avg) *ms_avg = double(ms) / reps;
+  // SpMV = 12 B per stored entry + 20 B per row (x gathered once, y written, p read for the dot);
+  // the fused Chebyshev step additionally reads r, D^-1, x and writes r, d, x: 12 B per entry + 56 B per row
+  if (alg_bytes) *alg_bytes = 12.0 * double(entries) + (which == OBGPU_PROF_SPMV ? 20.0 : 56.0) * double(n);
   return OBGPU_OK;
 }
 

@@ -66,12 +66,27 @@ struct obgpu_ctx {
   obgpu::DevBuf<unsigned int> d_counter;
   obgpu::DevBuf<int32_t> d_blk_elem_ptr, d_blk_elems;
   obgpu::DevBuf<uint16_t> d_seg_loc;
+  // multigrid preconditioner of the sparse route (OBGPU_PCG_MG): plan + per-level device arrays (index 0 unused:
+  // level 0 is K_ff itself)
+  obgpu::MgPlan mg;
+  bool dev_mg = false;
+  struct MgLevelBufs {
+    obgpu::DevBuf<int32_t> sl_ptr, col, f_agg, mem_ptr, mem;
+    obgpu::DevBuf<uint8_t> f_kind;
+    obgpu::DevBuf<double> f_w, val, minv, vec;  // vec: x | b | r | d0 | d1
+  };
+  std::vector<MgLevelBufs> mg_lev;
+  obgpu::DevBuf<double> d_mg_lam, d_mg_cinv;   // Gershgorin bounds per level; explicit coarsest inverses, one per job slot
+  obgpu::MgJob mg_job[8];
+  obgpu::PcgArgs prof_args;          // obgpu_profile_kernel: iteration arguments of the last PCG solve's first structure
+  obgpu::MgLevelDev prof_lv0;
+  bool prof_valid = false, prof_mg = false;
   bool elem_k_valid = false;  // d_elem_k holds the element blocks of the current batch (only the two-kernel path fills it)
   double* h_scal = nullptr;  // pinned [8 * NPCG]
   static constexpr int NPCG = 8;                  // PCGs of different structures in flight (sparse route)
   cudaStream_t pcg_stream[NPCG] = {};
   cudaEvent_t pcg_ev = nullptr;
-  double pcg_relres = 0;
+  double pcg_relres = 0, pcg_restarts = 0, pcg_levels = 1;
 
   // chunk slots of obgpu_solve_cases_host
   struct Slot {

@@ -114,8 +114,55 @@ struct PcgArgs {
   double* partial;      // [2 * max blocks]
   unsigned int* counter;
   int ctas_per_sm;      // grid cap of the iteration kernels (0 = 8): small when several structures' PCGs share the GPU
+  const struct MgJob* mg;  // HOST pointer: multigrid V-cycle as the preconditioner (OBGPU_PCG_MG); null = Jacobi
 };
+// ---- multigrid preconditioner (kernels_mg.cu; plan in symbolic_mg.cpp) ----
+// One level of one structure: rows [r0, r1) of the level's SELL-32 matrix, its work vectors, and the transfer to the
+// next coarser level (arrays indexed by THIS level's rows; member lists indexed by the coarser level's aggregates).
+struct MgLevelDev {
+  int32_t r0, r1;
+  const int32_t *slptr, *col;
+  const double *val, *minv;
+  double *x, *b, *r, *d0, *d1;
+  const int32_t* f_agg; const uint8_t* f_kind; const double* f_w;
+  const int32_t *mem_ptr, *mem;
+  double c0, c1, c2;    // Chebyshev(2) smoother on [lambda_max/8, lambda_max] of D^-1 A: d0 = c0 D^-1 r, d1 = c1 d0 + c2 D^-1 r'
+};
+constexpr int MG_MAX_LEVELS = 16;
+struct MgJob {
+  int nlev = 1;
+  bool dense = false;          // coarsest level applied as an explicit inverse
+  const double* cinv = nullptr;  // [nc*nc] row-major inverse of the coarsest matrix
+  double omega = 1.4;          // over-correction of the (unsmoothed-aggregation) coarse-grid step
+  MgLevelDev lv[MG_MAX_LEVELS];
+};
+// z = M r for the job's structure (level-0 b = r, x = z); the last kernel also leaves r.z in *dot_out (partial/counter:
+// the job's reduction scratch)
+cudaError_t launch_mg_vcycle(const MgJob& J, double* dot_out, double* partial, unsigned int* counter, int sm_count,
+                             int ctas_per_sm, cudaStream_t st);
+// numeric setup of level `coarse` from level `fine` over the whole batch: A_c = P^T A P
+struct MgGalerkinArgs {
+  int64_t n_coarse;
+  const int32_t *f_slptr, *f_col; const double* f_val;
+  const int32_t* f_agg; const uint8_t* f_kind; const double* f_w;
+  const int32_t *mem_ptr, *mem;
+  const int32_t *c_slptr, *c_col; double* c_val;
+};
+cudaError_t launch_mg_galerkin(const MgGalerkinArgs& g, cudaStream_t st);
+// minv = 1/diag (0 where the diagonal is not positive) and lam = max_i sum_j |a_ij| / a_ii (Gershgorin bound of D^-1 A)
+cudaError_t launch_mg_diag(int64_t r0, int64_t r1, const int32_t* slptr, const int32_t* col, const double* val, double* minv,
+                           double* lam, cudaStream_t st);
+// dense explicit inverse of rows [r0, r0 + nc) of a SELL-32 matrix (one CTA; SPD, no pivoting, null rows skipped)
+cudaError_t launch_mg_dense_inverse(int32_t r0, int32_t nc, const int32_t* slptr, const int32_t* col, const double* val,
+                                    double* inv, cudaStream_t st);
+
+cudaError_t launch_spmv_only(const PcgArgs& a, int sm_count, cudaStream_t st);              // k_spmv_dot alone (profiling)
+cudaError_t launch_mg_cheb_only(const MgLevelDev& L, int sm_count, cudaStream_t st);         // k_mg_spmv<CHEB> alone (profiling)
 cudaError_t launch_pcg_init(const PcgArgs& a, int sm_count, cudaStream_t st);
+// r = b - A x on the job's rows (true residual, not the recurrence), scal[3] = r.r
+cudaError_t launch_pcg_true_residual(const PcgArgs& a, int sm_count, cudaStream_t st);
+// restart from the current r: z = M r, p = z
+cudaError_t launch_pcg_restart(const PcgArgs& a, int it, int sm_count, cudaStream_t st);
 cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t st);
 cudaError_t launch_inv_diag(int64_t nf, const int32_t* ff_diag, const double* ff_val, double* minv, cudaStream_t st);
 cudaError_t launch_reactions(const SparseDev& d, const double* U_f, double* F_b, cudaStream_t st);

@@ -4,64 +4,20 @@
 // step lengths alpha/beta are computed on the device from `scal`, so an iteration is 3 launches with no host sync.
 #include <cstdlib>
 
-#include "kernels.h"
+#include "pcg_common.cuh"
 
 namespace obgpu {
 
-constexpr int PCG_BLOCK = 256;
-
-__device__ __forceinline__ double block_sum(double v, double* sh) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  __syncthreads();
-  if (l == 0) sh[w] = v;
-  __syncthreads();
-  double t = 0.0;
-  if (w == 0) {
-    t = l < PCG_BLOCK / 32 ? sh[l] : 0.0;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-  }
-  return t;  // valid in thread 0
-}
-
-// Finish NV dots: every block deposits its partials; the last block to arrive sums them in index order.
-template <int NV>
-__device__ __forceinline__ void finish_dots(const double (&v)[NV], double* partial, unsigned int* counter, double* sh,
-                                            double* (&out)[NV]) {
-  __shared__ bool last;
-  double t[NV];
-#pragma unroll
-  for (int k = 0; k < NV; k++) t[k] = block_sum(v[k], sh);
-  if (threadIdx.x == 0) {
-#pragma unroll
-    for (int k = 0; k < NV; k++) partial[k * gridDim.x + blockIdx.x] = t[k];
-    __threadfence();
-    const unsigned int ticket = atomicInc(counter, gridDim.x - 1);  // wraps to 0: self-resetting
-    last = ticket == gridDim.x - 1;
-  }
-  __syncthreads();
-  if (last) {
-    __threadfence();
-#pragma unroll
-    for (int k = 0; k < NV; k++) {
-      double acc = 0.0;
-      for (unsigned i = threadIdx.x; i < gridDim.x; i += PCG_BLOCK) acc += __ldcg(partial + k * gridDim.x + i);
-      acc = block_sum(acc, sh);
-      if (threadIdx.x == 0) *out[k] = acc;
-    }
-  }
-}
-
+// MG = true: the preconditioner is the V-cycle (launched right after): only x, r, p = 0 and b.b here
+template <bool MG>
 __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_init(PcgArgs a) {
   __shared__ double sh[PCG_BLOCK / 32];
   double v[2] = {0.0, 0.0};
   for (int64_t i = a.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; i < a.r1; i += int64_t(gridDim.x) * PCG_BLOCK) {
-    const double b = a.b[i], z = a.minv[i] * b;
+    const double b = a.b[i], z = MG ? 0.0 : a.minv[i] * b;
     a.x[i] = 0.0;
     a.r[i] = b;
-    a.z[i] = z;
+    if (!MG) a.z[i] = z;
     a.p[i] = z;
     v[0] += b * z;
     v[1] += b * b;
@@ -115,6 +71,8 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_spmv_dot(PcgArgs a) {
 }
 
 // alpha = rz/pAp; x += alpha p; r -= alpha Ap; z = M^-1 r; rz_next = r.z; rr = r.r
+// MG = true: z and r.z come from the V-cycle that follows; only r.r is reduced here
+template <bool MG>
 __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_update(PcgArgs a, int cur) {
   __shared__ double sh[PCG_BLOCK / 32];
   const double rz = a.scal[cur], pap = a.scal[2];
@@ -123,14 +81,69 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_update(PcgArgs a, int cur) {
   for (int64_t i = a.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; i < a.r1; i += int64_t(gridDim.x) * PCG_BLOCK) {
     a.x[i] += alpha * a.p[i];
     const double r = a.r[i] - alpha * a.ap[i];
-    const double z = a.minv[i] * r;
     a.r[i] = r;
-    a.z[i] = z;
-    v[0] += r * z;
+    if (!MG) {
+      const double z = a.minv[i] * r;
+      a.z[i] = z;
+      v[0] += r * z;
+    }
     v[1] += r * r;
   }
-  double* out[2] = {a.scal + (cur ^ 1), a.scal + 3};
+  if (MG) {
+    double w[1] = {v[1]};
+    double* out[1] = {a.scal + 3};
+    finish_dots<1>(w, a.partial, a.counter, sh, out);
+  } else {
+    double* out[2] = {a.scal + (cur ^ 1), a.scal + 3};
+    finish_dots<2>(v, a.partial, a.counter, sh, out);
+  }
+}
+
+// r = b - A x on the structure's rows (the TRUE residual, not the recurrence), scal[3] = r.r, and
+// scal[5] = sum_i (sum_j |a_ij| |x_j|)^2: the scale of the rounding error of evaluating A x in FP64, i.e. the floor
+// below which no residual of this x can be told from zero
+__global__ void __launch_bounds__(PCG_BLOCK) k_pcg_true_residual(PcgArgs a) {
+  __shared__ double sh[PCG_BLOCK / 32];
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = int64_t(gridDim.x) * (PCG_BLOCK / 32);
+  const int64_t s1 = (int64_t(a.r1) + 31) >> 5;
+  double v[2] = {0.0, 0.0};
+  for (int64_t sl = (a.r0 >> 5) + int64_t(blockIdx.x) * (PCG_BLOCK / 32) + (threadIdx.x >> 5); sl < s1; sl += nwarps) {
+    const int32_t base = a.slptr[sl], w = (a.slptr[sl + 1] - base) >> 5;
+    double sum = 0.0, asum = 0.0;
+    for (int k = 0; k < w; k++) {
+      const double t = a.val[base + lane + 32 * k] * a.x[a.col[base + lane + 32 * k]];
+      sum += t;
+      asum += fabs(t);
+    }
+    const int64_t row = sl * 32 + lane;
+    if (row >= a.r0 && row < a.r1) {
+      const double r = a.b[row] - sum;
+      a.r[row] = r;
+      v[0] += r * r;
+      v[1] += asum * asum;
+    }
+  }
+  double* out[2] = {a.scal + 3, a.scal + 5};
   finish_dots<2>(v, a.partial, a.counter, sh, out);
+}
+
+// restart of the Jacobi variant from the current r: z = M^-1 r, p = z, scal[cur] = r.z
+__global__ void __launch_bounds__(PCG_BLOCK) k_pcg_restart_jacobi(PcgArgs a, int cur) {
+  __shared__ double sh[PCG_BLOCK / 32];
+  double v[1] = {0.0};
+  for (int64_t i = a.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; i < a.r1; i += int64_t(gridDim.x) * PCG_BLOCK) {
+    const double r = a.r[i], z = a.minv[i] * r;
+    a.z[i] = z;
+    a.p[i] = z;
+    v[0] += r * z;
+  }
+  double* out[1] = {a.scal + cur};
+  finish_dots<1>(v, a.partial, a.counter, sh, out);
+}
+__global__ void __launch_bounds__(PCG_BLOCK) k_pcg_set_p(PcgArgs a) {
+  for (int64_t i = a.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; i < a.r1; i += int64_t(gridDim.x) * PCG_BLOCK)
+    a.p[i] = a.z[i];
 }
 
 // beta = rz_next/rz; p = z + beta p
@@ -149,7 +162,42 @@ static unsigned pcg_grid(int64_t work_items, int sm_count, int ctas_per_sm = 8) 
 }
 
 cudaError_t launch_pcg_init(const PcgArgs& a, int sm_count, cudaStream_t st) {
-  k_pcg_init<<<pcg_grid(a.r1 - a.r0, sm_count), PCG_BLOCK, 0, st>>>(a);
+  if (!a.mg) {
+    k_pcg_init<false><<<pcg_grid(a.r1 - a.r0, sm_count), PCG_BLOCK, 0, st>>>(a);
+    return cudaGetLastError();
+  }
+  // x = 0, r = b, p = 0, scal[1] = 0;  z = M r with r.z -> scal[0];  p = z + (scal[0]/scal[1] -> 0) p
+  k_pcg_init<true><<<pcg_grid(a.r1 - a.r0, sm_count), PCG_BLOCK, 0, st>>>(a);
+  cudaError_t e = launch_mg_vcycle(*a.mg, a.scal + 0, a.partial, a.counter, sm_count, a.ctas_per_sm, st);
+  if (e != cudaSuccess) return e;
+  k_pcg_dir<<<pcg_grid(a.r1 - a.r0, sm_count, a.ctas_per_sm > 0 ? a.ctas_per_sm : 8), PCG_BLOCK, 0, st>>>(a, 1);
+  return cudaGetLastError();
+}
+
+static unsigned spmv_grid(const PcgArgs& a, int sm_count, int cps) {
+  const int64_t slices = ((int64_t(a.r1) + 31) >> 5) - (a.r0 >> 5);
+  return pcg_grid(slices * 32, sm_count, cps);
+}
+
+cudaError_t launch_spmv_only(const PcgArgs& a, int sm_count, cudaStream_t st) {
+  k_spmv_dot<false><<<spmv_grid(a, sm_count, a.ctas_per_sm > 0 ? a.ctas_per_sm : 8), PCG_BLOCK, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pcg_true_residual(const PcgArgs& a, int sm_count, cudaStream_t st) {
+  k_pcg_true_residual<<<spmv_grid(a, sm_count, a.ctas_per_sm > 0 ? a.ctas_per_sm : 8), PCG_BLOCK, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pcg_restart(const PcgArgs& a, int it, int sm_count, cudaStream_t st) {
+  const int cur = it & 1, cps = a.ctas_per_sm > 0 ? a.ctas_per_sm : 8;
+  if (!a.mg) {
+    k_pcg_restart_jacobi<<<pcg_grid(a.r1 - a.r0, sm_count, cps), PCG_BLOCK, 0, st>>>(a, cur);
+    return cudaGetLastError();
+  }
+  cudaError_t e = launch_mg_vcycle(*a.mg, a.scal + cur, a.partial, a.counter, sm_count, a.ctas_per_sm, st);
+  if (e != cudaSuccess) return e;
+  k_pcg_set_p<<<pcg_grid(a.r1 - a.r0, sm_count, cps), PCG_BLOCK, 0, st>>>(a);
   return cudaGetLastError();
 }
 
@@ -165,7 +213,13 @@ cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t
   else k_spmv_dot<false><<<g, PCG_BLOCK, 0, st>>>(a);
   static const int cpv_env = getenv("OBGPU_PCG_VEC_CTAS") ? atoi(getenv("OBGPU_PCG_VEC_CTAS")) : 0;
   const int cpv = cpv_env > 0 ? cpv_env : a.ctas_per_sm > 0 ? a.ctas_per_sm : 8;
-  k_pcg_update<<<pcg_grid(n, sm_count, cpv), PCG_BLOCK, 0, st>>>(a, cur);
+  if (a.mg) {
+    k_pcg_update<true><<<pcg_grid(n, sm_count, cpv), PCG_BLOCK, 0, st>>>(a, cur);
+    cudaError_t e = launch_mg_vcycle(*a.mg, a.scal + (cur ^ 1), a.partial, a.counter, sm_count, a.ctas_per_sm, st);
+    if (e != cudaSuccess) return e;
+  } else {
+    k_pcg_update<false><<<pcg_grid(n, sm_count, cpv), PCG_BLOCK, 0, st>>>(a, cur);
+  }
   k_pcg_dir<<<pcg_grid(n, sm_count, cpv), PCG_BLOCK, 0, st>>>(a, cur);
   return cudaGetLastError();
 }

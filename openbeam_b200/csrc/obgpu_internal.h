@@ -133,7 +133,34 @@ struct SparsePlan {
   std::vector<int32_t> fseg_ptr, fseg_src;
 };
 
+// Aggregation-multigrid hierarchy of the sparse route's preconditioner (symbolic_mg.cpp; OBGPU_PCG_MG).
+// Level 0 is K_ff itself (SparsePlan's SELL-32 arrays).  Level l >= 1 has three rows per aggregate — the rigid-body
+// modes (tx, ty, rot about the aggregate centre) of the level-(l-1) "nodes" it collects — and is stored in SELL-32
+// too, every structure's rows padded to a multiple of 96 so that row/3 is a global aggregate index.
+struct MgLevel {
+  int64_t n = 0;                        // rows of this level over the batch (padded)
+  std::vector<int32_t> row_off;         // [S+1] first row of each structure (multiples of 96)
+  std::vector<int32_t> nrows;           // [S] rows in use (3 * aggregates); 0 = the structure stops above this level
+  std::vector<int32_t> sl_ptr, col;     // SELL-32 pattern (padding: col = own row)
+  std::vector<int32_t> diag;            // [n] position of the diagonal entry, -1 on padding rows
+  // transfer between level l-1 (fine) and this level: per fine row its aggregate's first row here (-1: none),
+  // its DOF kind (0 tx, 1 ty, 2 rot) and the coefficient of the aggregate's rotation mode (-dy, +dx, 1)
+  std::vector<int32_t> f_agg;
+  std::vector<uint8_t> f_kind;
+  std::vector<double> f_w;
+  std::vector<int32_t> mem_ptr, mem;    // [n/3 + 1] fine rows of each aggregate, ascending
+};
+struct MgPlan {
+  bool valid = false;
+  std::vector<MgLevel> lev;             // lev[0] unused (fine level), lev[1..]
+  std::vector<int32_t> nlev;            // [S] number of levels of each structure, fine one included (>= 1)
+  std::vector<uint8_t> dense;           // [S] coarsest level small enough for the explicit dense inverse
+  static constexpr int DENSE_MAX = 768; // rows
+};
+
 int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want_pattern);
+int build_mg_plan(const HostBatch& hb, const Symbolic& sym, const SparsePlan& plan, MgPlan& mg, std::string& err);
+struct SparsePlan;
 int build_sparse_plan(const HostBatch& hb, const Symbolic& sym, SparsePlan& plan, std::string& err);
 int build_tiny_program(const HostBatch& hb, const Symbolic& sym, TinyProgram& prog, std::string& err);
 

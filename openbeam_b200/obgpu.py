@@ -23,7 +23,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("OBGPU_LIB") or os.path.join(_HERE, "libobgpu.so")  # OBGPU_LIB: kernel-variant experiments
 
 OK, EINVAL, ECUDA, ESINGULAR, ENOTCONVERGED, EUNSUPPORTED, ESEQUENCE = range(7)
-BATCHED_LDLT, PCG_JACOBI, PCG_BJ3, PCG_IC0 = range(4)
+BATCHED_LDLT, PCG_JACOBI, PCG_MG = range(3)
+PROF_SPMV, PROF_MG_SPMV = 0, 1
 SOLVE_SKIP_FF = 1  # obgpu_solve_opts.flags
 (RES_UF, RES_FB, RES_STRESS, RES_INFO, RES_FF, RES_UB, RES_KVAL, RES_ELEM_K) = range(8)
 (SYM_DOF_NODE, SYM_DOF_ID, SYM_FREE, SYM_BOUNDED, SYM_DOF_INDEX, SYM_K_ROWPTR, SYM_K_COL, SYM_TRI_NNZ) = range(8)
@@ -36,7 +37,7 @@ ABI_SYMBOLS = (
     "obgpu_host_free", "obgpu_batch_upload", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
     "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host",
-    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
+    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_pcg_info", "obgpu_profile_kernel", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
     "obgpu_mesh_create", "obgpu_mesh_desc", "obgpu_mesh_info", "obgpu_mesh_destroy",
 )
 
@@ -110,6 +111,8 @@ def lib():
         L.obgpu_bind_summaries.argtypes = [vp, vp]
         L.obgpu_bind_summary_peers.argtypes = [vp, C.c_int, C.POINTER(C.c_void_p)]
         L.obgpu_get_timings.argtypes = [vp, vp]
+        L.obgpu_pcg_info.argtypes = [vp, vp]
+        L.obgpu_profile_kernel.argtypes = [vp, C.c_int, C.c_int, vp, vp]
         L.obgpu_get_stream.argtypes = [vp, C.POINTER(vp)]
         _LIB = L
     return _LIB
@@ -376,6 +379,18 @@ class Context:
         self._chk(lib().obgpu_get_timings(self.h, _p(out)))
         return dict(zip(("symbolic", "assembleProblem", "solveStatic.2_solve", "postProcCalcStress", "H2D", "D2H",
                          "launches", "pcg_iters"), out.tolist()))
+
+    def profile_kernel(self, which, reps=20):
+        """(avg ms per launch, algorithmic bytes per launch) of one iteration kernel of the last PCG solve"""
+        ms, by = C.c_double(0), C.c_double(0)
+        self._chk(lib().obgpu_profile_kernel(self.h, which, reps, C.byref(ms), C.byref(by)))
+        return ms.value, by.value
+
+    def pcg_info(self):
+        """iterations, worst true relative residual, restarts, multigrid levels of the last PCG solve"""
+        out = np.zeros(4)
+        self._chk(lib().obgpu_pcg_info(self.h, _p(out)))
+        return dict(zip(("iters", "true_relres", "restarts", "levels"), out.tolist()))
 
     def stream(self):
         p = C.c_void_p()

@@ -30,8 +30,7 @@ class StaticSolverAlgorithm(enum.IntEnum):
     Sparse_LLT = -2
     GPU_Batched_LDLT = obgpu.BATCHED_LDLT
     GPU_PCG_Jacobi = obgpu.PCG_JACOBI
-    GPU_PCG_BJ3 = obgpu.PCG_BJ3
-    GPU_PCG_IC0 = obgpu.PCG_IC0
+    GPU_PCG_MG = obgpu.PCG_MG
 
 
 @dataclass
