@@ -88,6 +88,7 @@ static int ensure_mg(obgpu_ctx* c) {
   }
   OB_CUDA(c, c->d_mg_lam.reserve(MG_MAX_LEVELS));
   OB_CUDA(c, c->d_mg_cinv.reserve(size_t(obgpu_ctx::NPCG) * MgPlan::DENSE_MAX * MgPlan::DENSE_MAX));
+  OB_CUDA(c, c->d_mg_prow.reserve(size_t(obgpu_ctx::NPCG) * 2 * (MgPlan::DENSE_MAX + 2)));
   OB_CUDA(c, cudaStreamSynchronize(st));
   c->dev_mg = true;
   return OBGPU_OK;
@@ -364,7 +365,8 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
         }
         if (J.dense) {
           const MgLevelDev& C = J.lv[J.nlev - 1];
-          cudaError_t e = launch_mg_dense_inverse(C.r0, C.r1 - C.r0, C.slptr, C.col, C.val, const_cast<double*>(J.cinv), pst[size_t(k)]);
+          cudaError_t e = launch_mg_dense_inverse(C.r0, C.r1 - C.r0, C.slptr, C.col, C.val, const_cast<double*>(J.cinv),
+                                                  c->d_mg_prow.p + size_t(k) * 2 * (MgPlan::DENSE_MAX + 2), pst[size_t(k)]);
           launches += 1;
           if (e != cudaSuccess) return e;
         }
@@ -411,9 +413,11 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
           // be told from converged below it); a tolerance under the floor is met at the floor
           const double floor2 = 256.0 * 4.930380657631324e-32 * c->h_scal[8 * k + 5];
           worst_floor = std::max(worst_floor, bb > 0 ? std::sqrt(floor2 / bb) : 0.0);
-          if (rr <= std::max(rtol * rtol * bb, floor2)) { conv = true; stop = true; }
-          else if (jb.restarts >= 3 || jb.it >= jb.max_iter || (jb.prev_true >= 0 && rr > 0.25 * jb.prev_true)) stop = true;
-          else {
+          if (rr <= rtol * rtol * bb) { conv = true; stop = true; }
+          else if (jb.restarts >= 3 || jb.it >= jb.max_iter || (jb.prev_true >= 0 && rr > 0.25 * jb.prev_true)) {
+            stop = true;
+            conv = rr <= floor2;   // restarts no longer gain anything: at the floor the solve is as converged as FP64 allows
+          } else {
             jb.prev_true = rr;
             jb.restarts++;
             restarts_total += 1;

@@ -76,7 +76,7 @@ struct obgpu_ctx {
     obgpu::DevBuf<double> f_w, val, minv, vec;  // vec: x | b | r | d0 | d1
   };
   std::vector<MgLevelBufs> mg_lev;
-  obgpu::DevBuf<double> d_mg_lam, d_mg_cinv;   // Gershgorin bounds per level; explicit coarsest inverses, one per job slot
+  obgpu::DevBuf<double> d_mg_lam, d_mg_cinv, d_mg_prow;   // Gershgorin bounds per level; explicit coarsest inverses, one per job slot
   obgpu::MgJob mg_job[8];
   obgpu::PcgArgs prof_args;          // obgpu_profile_kernel: iteration arguments of the last PCG solve's first structure
   obgpu::MgLevelDev prof_lv0;

@@ -152,9 +152,10 @@ cudaError_t launch_mg_galerkin(const MgGalerkinArgs& g, cudaStream_t st);
 // minv = 1/diag (0 where the diagonal is not positive) and lam = max_i sum_j |a_ij| / a_ii (Gershgorin bound of D^-1 A)
 cudaError_t launch_mg_diag(int64_t r0, int64_t r1, const int32_t* slptr, const int32_t* col, const double* val, double* minv,
                            double* lam, cudaStream_t st);
-// dense explicit inverse of rows [r0, r0 + nc) of a SELL-32 matrix (one CTA; SPD, no pivoting, null rows skipped)
+// dense explicit inverse of rows [r0, r0 + nc) of a SELL-32 matrix (cooperative launch; SPD, no pivoting, null rows
+// skipped); prow = scratch of 2 * (nc + 2) doubles
 cudaError_t launch_mg_dense_inverse(int32_t r0, int32_t nc, const int32_t* slptr, const int32_t* col, const double* val,
-                                    double* inv, cudaStream_t st);
+                                    double* inv, double* prow, cudaStream_t st);
 
 cudaError_t launch_spmv_only(const PcgArgs& a, int sm_count, cudaStream_t st);              // k_spmv_dot alone (profiling)
 cudaError_t launch_mg_cheb_only(const MgLevelDev& L, int sm_count, cudaStream_t st);         // k_mg_spmv<CHEB> alone (profiling)

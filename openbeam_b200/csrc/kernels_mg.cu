@@ -12,7 +12,11 @@
 // order-independent max of the Gershgorin bound), so the preconditioner — hence the iterates — are reproducible.
 #include <cstdlib>
 
+#include <cooperative_groups.h>
+
 #include "pcg_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace obgpu {
 
@@ -87,72 +91,115 @@ cudaError_t launch_mg_diag(int64_t r0, int64_t r1, const int32_t* slptr, const i
   return cudaGetLastError();
 }
 
-// In-place Gauss-Jordan inverse of the SPD coarsest matrix, one CTA.  A pivot that is not positive relative to its
-// original diagonal marks a null direction (an aggregate without a rotation-capable member, a mechanism): that row and
+// Gauss-Jordan inverse of the SPD coarsest matrix (no pivoting) on MG_INV_CTAS co-resident CTAs (cooperative launch):
+// rows are dealt cyclically to the CTAs and live in shared memory for the whole elimination; step k needs one thing
+// from outside the CTA — the scaled pivot row — which its owner publishes to a double-buffered global row right after
+// finishing step k-1 on it, so a step costs ONE grid barrier.  A pivot that is not positive relative to the largest
+// original diagonal marks a null direction (an aggregate without a rotation-capable member, a mechanism): its row and
 // column of the inverse are zeroed, which keeps the preconditioner symmetric positive semi-definite there.
-__global__ void __launch_bounds__(1024) k_mg_dense_inverse(int32_t r0, int32_t nc, const int32_t* __restrict__ slptr,
-                                                           const int32_t* __restrict__ col, const double* __restrict__ val,
-                                                           double* __restrict__ A) {
-  __shared__ double s_p;
-  __shared__ int s_skip;
-  const int tid = threadIdx.x, nt = blockDim.x;
-  for (int64_t q = tid; q < int64_t(nc) * nc; q += nt) A[q] = 0.0;
+constexpr int MG_INV_CTAS = 64, MG_INV_THREADS = 256;
+__global__ void __launch_bounds__(MG_INV_THREADS) k_mg_dense_inverse(int32_t r0, int32_t nc, const int32_t* __restrict__ slptr,
+                                                                     const int32_t* __restrict__ col,
+                                                                     const double* __restrict__ val, double* __restrict__ inv,
+                                                                     double* __restrict__ prow /* [2][nc + 2] */) {
+  extern __shared__ double sA[];  // [rows of this CTA][nc]
+  cg::grid_group grid = cg::this_grid();
+  const int tid = threadIdx.x, nt = blockDim.x, cta = blockIdx.x, ncta = gridDim.x;
+  const int my_rows = (nc - cta + ncta - 1) / ncta;  // rows cta, cta + ncta, ...
+  for (int q = tid; q < my_rows * nc; q += nt) sA[q] = 0.0;
   __syncthreads();
-  for (int32_t i = tid; i < nc; i += nt) {
-    const int64_t r = int64_t(r0) + i;
+  for (int lr = tid; lr < my_rows; lr += nt) {
+    const int64_t r = int64_t(r0) + cta + int64_t(lr) * ncta;
     const int32_t base = slptr[r >> 5] + int32_t(r & 31), w = (slptr[(r >> 5) + 1] - slptr[r >> 5]) >> 5;
     for (int32_t k = 0; k < w; k++) {
       const int32_t c = col[base + 32 * k] - r0;
       const double v = val[base + 32 * k];
-      if (v != 0.0 && c >= 0 && c < nc) A[int64_t(i) * nc + c] += v;
+      if (v != 0.0 && c >= 0 && c < nc) sA[lr * nc + c] += v;
     }
   }
   __syncthreads();
-  // null-direction threshold: the running pivot against the largest original diagonal
-  __shared__ double s_dmax;
-  if (tid == 0) {
+  // largest original diagonal -> null-direction threshold (every CTA computes the same value from global data)
+  __shared__ double s_red[MG_INV_THREADS / 32];
+  __shared__ double s_tiny;
+  {
     double m = 0.0;
-    for (int32_t i = 0; i < nc; i++) m = fmax(m, A[int64_t(i) * nc + i]);
-    s_dmax = m;
-  }
-  __syncthreads();
-  const double tiny = 1e-13 * s_dmax;
-  for (int32_t k = 0; k < nc; k++) {
+    for (int i = tid; i < nc; i += nt) {
+      const int64_t r = int64_t(r0) + i;
+      const int32_t base = slptr[r >> 5] + int32_t(r & 31), w = (slptr[(r >> 5) + 1] - slptr[r >> 5]) >> 5;
+      for (int32_t k = 0; k < w; k++)
+        if (col[base + 32 * k] == r) m = fmax(m, val[base + 32 * k]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((tid & 31) == 0) s_red[tid >> 5] = m;
+    __syncthreads();
     if (tid == 0) {
-      const double p = A[int64_t(k) * nc + k];
-      s_skip = !(p > tiny);
-      s_p = s_skip ? 0.0 : 1.0 / p;
+      for (int w2 = 1; w2 < MG_INV_THREADS / 32; w2++) m = fmax(m, s_red[w2]);
+      s_tiny = 1e-13 * m;
     }
     __syncthreads();
-    const double p = s_p;
-    if (s_skip) {
-      for (int32_t j = tid; j < nc; j += nt) { A[int64_t(k) * nc + j] = 0.0; A[int64_t(j) * nc + k] = 0.0; }
-      __syncthreads();
-      continue;
+  }
+  const double tiny = s_tiny;
+  // publish pivot row k (scaled by 1/pivot, with [nc] = 1/pivot and [nc+1] = skip flag) from its owner's shared memory
+  auto publish = [&](int k) {
+    if (k >= nc || k % ncta != cta) return;
+    const double* row = sA + (k / ncta) * nc;
+    double* out = prow + (k & 1) * (nc + 2);
+    const double p = row[k];
+    const bool skip = !(p > tiny);
+    const double pinv = skip ? 0.0 : 1.0 / p;
+    for (int j = tid; j < nc; j += nt) out[j] = row[j] * pinv;
+    if (tid == 0) { out[nc] = pinv; out[nc + 1] = skip ? 1.0 : 0.0; }
+  };
+  publish(0);
+  __threadfence();
+  grid.sync();
+  for (int k = 0; k < nc; k++) {
+    const double* __restrict__ pk = prow + (k & 1) * (nc + 2);
+    const double pinv = __ldcg(pk + nc);
+    const bool skip = __ldcg(pk + nc + 1) != 0.0;
+    for (int lr = tid >> 5; lr < my_rows; lr += nt >> 5) {   // one warp per owned row
+      const int i = cta + lr * ncta;
+      double* row = sA + lr * nc;
+      const int lane = tid & 31;
+      if (skip) {
+        if (i == k) { for (int j = lane; j < nc; j += 32) row[j] = 0.0; }
+        else if (lane == 0) row[k] = 0.0;
+        continue;
+      }
+      if (i == k) {
+        for (int j = lane; j < nc; j += 32) row[j] = j == k ? pinv : __ldcg(pk + j);
+      } else {
+        const double f = row[k];
+        __syncwarp();
+        if (f != 0.0)
+          for (int j = lane; j < nc; j += 32) row[j] = j == k ? -f * pinv : row[j] - f * __ldcg(pk + j);
+      }
     }
-    for (int32_t j = tid; j < nc; j += nt)
-      if (j != k) A[int64_t(k) * nc + j] *= p;
     __syncthreads();
-    // rank-1 update of everything outside row k and column k; one warp per row keeps the row's reads coalesced
-    for (int32_t i = tid >> 5; i < nc; i += nt >> 5) {
-      if (i == k) continue;
-      const double f = A[int64_t(i) * nc + k];
-      if (f == 0.0) continue;
-      for (int32_t j = tid & 31; j < nc; j += 32)
-        if (j != k) A[int64_t(i) * nc + j] -= f * A[int64_t(k) * nc + j];
-    }
-    __syncthreads();
-    for (int32_t i = tid; i < nc; i += nt)
-      if (i != k) A[int64_t(i) * nc + k] *= -p;
-    if (tid == 0) A[int64_t(k) * nc + k] = p;
-    __syncthreads();
+    publish(k + 1);
+    __threadfence();
+    grid.sync();
+  }
+  for (int lr = 0; lr < my_rows; lr++) {
+    const int i = cta + lr * ncta;
+    for (int j = tid; j < nc; j += nt) inv[int64_t(i) * nc + j] = sA[lr * nc + j];
   }
 }
 cudaError_t launch_mg_dense_inverse(int32_t r0, int32_t nc, const int32_t* slptr, const int32_t* col, const double* val,
-                                    double* inv, cudaStream_t st) {
+                                    double* inv, double* prow, cudaStream_t st) {
   if (nc <= 0) return cudaSuccess;
-  k_mg_dense_inverse<<<1, 1024, 0, st>>>(r0, nc, slptr, col, val, inv);
-  return cudaGetLastError();
+  int ncta = MG_INV_CTAS;
+  if (ncta > nc) ncta = nc;
+  const size_t smem = size_t((nc + ncta - 1) / ncta) * nc * sizeof(double);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k_mg_dense_inverse, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  void* args[] = {&r0, &nc, &slptr, &col, &val, &inv, &prow};
+  return cudaLaunchCooperativeKernel((void*)k_mg_dense_inverse, dim3(unsigned(ncta)), dim3(MG_INV_THREADS), args, smem, st);
 }
 
 // ---------------------------------------------------------------- V-cycle kernels
