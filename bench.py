@@ -36,7 +36,9 @@ sys.path.insert(0, ROOT)
 METRIC = "static solves/s (FP64; full assemble+factor+solve+stress per load case)"
 UNIT = "solves/s"
 N_DOF = 12           # m_problem_DoFs.size() of demo3_frame (n_f = 6, n_b = 6)
-ALG_BYTES_PER_CASE = 440  # 8*(7 + n_f + n_b + 12E)
+ALG_BYTES_FULL = 440      # 8*(7 + n_f + n_b + 12E) with the reference's six-component FaceStress record
+ALG_BYTES_COMPACT = 296   # 8*(7 + n_f + n_b + 6E): (N, Vy, Mz) per face — Vz, Mx, My are structurally zero in 2D
+ALG_BYTES_PER_CASE = ALG_BYTES_COMPACT
 QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -51,6 +53,8 @@ def parse_args():
     ap.add_argument("--cases", type=int, default=1_000_000, help="load cases per GPU per step")
     ap.add_argument("--per-case-section", action="store_true", help="variant C2b: per-case A, Iz sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--full-stress", action="store_true",
+                    help="c2: six-component stress records (440 B/case, the r01 configuration) instead of compact ones")
     ap.add_argument("--config", default="c2", choices=["c2", "c3", "c4", "c5"])
     ap.add_argument("--grid", type=int, default=0, help="c4/c5: nodes per side (default 817 / 408)")
     ap.add_argument("--structures", type=int, default=0, help="c3/c5: structures per GPU (default 524288 / 8)")
@@ -66,7 +70,12 @@ def parse_args():
 
 
 def config_dict(args, world):
+    global ALG_BYTES_PER_CASE
+    ALG_BYTES_PER_CASE = ALG_BYTES_FULL if args.full_stress else ALG_BYTES_COMPACT
     return {
+        "stress_record": "six-component FaceStress [E][2][6] (reference layout)" if args.full_stress else
+                         "compact [E][2][3] = N, Vy, Mz per face (Vz, Mx, My are structurally zero in 2D; the host mirrors "
+                         "expand it into the reference's FaceStress)",
         "workload": "C2: demo3_frame.yaml x %d randomized load cases per GPU (q on beam + Fx,Fy,Mz on 2 nodes%s); "
                     "each case = full assembleProblem+solveStatic(LDLt)+postProcCalcStress" %
                     (args.cases, "; per-case section sweep" if args.per_case_section else ""),
@@ -214,7 +223,9 @@ def ours_arm(args, rank, local_rank, world):
     h_nl, h_q = obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 1))
     h_eai = obgpu.pinned_empty((L, 9)) if args.per_case_section else None
     workloads.c2_cases(sharding.weak_range(L, rank)[0], L, args.per_case_section, h_nl, h_q, h_eai)
-    h_U, h_Fb, h_S = obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 3, 2, 6))
+    compact = not args.full_stress
+    config_dict(args, world)   # fixes ALG_BYTES_PER_CASE for the record layout
+    h_U, h_Fb, h_S = obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 6)), obgpu.pinned_empty((L, 3, 2, 3 if compact else 6))
     h_info = obgpu.pinned_empty((L,), np.int32)
 
     ctx.upload(st, L, h_nl, h_q, h_eai)   # inputs resident in HBM from here on
@@ -236,7 +247,7 @@ def ours_arm(args, rank, local_rank, world):
         torch.cuda.synchronize(dev)
 
     def step():
-        ctx.solve_static(keep_Ff=False)          # 1 fused kernel: K1+K2+K4+K5+K6+K10 per case + summaries
+        ctx.solve_static(keep_Ff=False, compact_stress=compact)   # 1 fused kernel: K1+K2+K4+K5+K6+K10 per case + summaries
         ctx.summaries_device(summ.data_ptr())    # per-case {max|U|, sum Fb_x, sum Fb_y, info}: no launch when the
                                                  # solve kernel already wrote them (a 2nd kernel on the fallback path)
 
@@ -288,7 +299,7 @@ def ours_arm(args, rank, local_rank, world):
         # dominant kernel alone: CUDA-event pair around each fused-kernel launch (obgpu_get_timings)
         kern_ms = []
         for _ in range(K):
-            ctx.solve_static(keep_Ff=False)
+            ctx.solve_static(keep_Ff=False, compact_stress=compact)
             ctx.synchronize()
             kern_ms.append(ctx.timings()["solveStatic.2_solve"])
         kernel_name = ctx.kernel_info()
@@ -296,11 +307,11 @@ def ours_arm(args, rank, local_rank, world):
         barrier()
         # end-to-end through the public host-buffer entry point: H2D + solve + D2H inside the timed region
         for _ in range(min(W, 3)):
-            ctx.solve_cases_host(L, h_nl, h_q, h_eai, h_U, h_Fb, h_S, h_info)
+            ctx.solve_cases_host(L, h_nl, h_q, h_eai, h_U, h_Fb, h_S, h_info, compact_stress=compact)
         barrier()
         t0 = time.perf_counter()
         for _ in range(K):
-            ctx.solve_cases_host(L, h_nl, h_q, h_eai, h_U, h_Fb, h_S, h_info)
+            ctx.solve_cases_host(L, h_nl, h_q, h_eai, h_U, h_Fb, h_S, h_info, compact_stress=compact)
         torch.cuda.synchronize(dev)
         e2e_s = time.perf_counter() - t0
         e2e_launches = ctx.timings()["launches"]
@@ -322,7 +333,7 @@ def ours_arm(args, rank, local_rank, world):
         alg = ALG_BYTES_PER_CASE + (72 if args.per_case_section else 0)  # + the 3E per-case section values read
         achieved = alg * L / (kern_avg_ms * 1e-3) / 1e9
         jit = kernel_name.startswith("k_tiny_jit")
-        traffic = TRAFFIC_BYTES_PER_CASE if jit and not args.per_case_section else None
+        traffic = TRAFFIC_BYTES_PER_CASE if jit and not args.per_case_section and args.full_stress else None
         in_bytes = (h_nl.nbytes + h_q.nbytes + (h_eai.nbytes if h_eai is not None else 0))
         out_bytes = h_U.nbytes + h_Fb.nbytes + h_S.nbytes + h_info.nbytes
         line = {

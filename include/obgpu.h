@@ -96,7 +96,11 @@ typedef struct obgpu_solve_opts {
 } obgpu_solve_opts;
 /* OBGPU_SOLVE_SKIP_FF: do not keep BuildProblemInfo::F_f (the assembled free-DOF load vector is an intermediate of the
  * fused kernel; storing it costs 8*n_f bytes per case of HBM writes).  OBGPU_RES_FF is then unavailable after the solve. */
-enum { OBGPU_SOLVE_SKIP_FF = 1 };
+/* OBGPU_SOLVE_COMPACT_STRESS: element end forces are written as [Etot][2][3] = (N, Vy, Mz) per face instead of the
+ * reference's six-component FaceStress (types.h:78-157): Vz, Mx and My are structurally zero for every 2D element
+ * (postproc_stress.cpp:95-121 only feeds the planar DOFs), i.e. half of every stress record.  Read it back with
+ * OBGPU_RES_STRESS_COMPACT; the host mirrors expand it into FaceStress.  OBGPU_RES_STRESS needs a solve without the flag. */
+enum { OBGPU_SOLVE_SKIP_FF = 1, OBGPU_SOLVE_COMPACT_STRESS = 2 };
 
 /* sizes: obgpu_get_sizes fills out[0..11] with
  * S, L, Ntot, Etot, n_tot, nf_tot, nb_tot, T_tot (triplets), nnz_tot (K upper), Ctot, NLtot, ELtot */
@@ -123,7 +127,8 @@ enum {
   OBGPU_RES_FF = 4,      /* [L][nf_tot]        BuildProblemInfo::F_f                                */
   OBGPU_RES_UB = 5,      /* [nb_tot]           BuildProblemInfo::U_b                                */
   OBGPU_RES_KVAL = 6,    /* [LK][nnz_tot]      values of K (upper, CSC order); LK = L if case_elem_EAI else 1 */
-  OBGPU_RES_ELEM_K = 7   /* [LK][Etot][21]     compact global element blocks        */
+  OBGPU_RES_ELEM_K = 7,  /* [LK][Etot][21]     compact global element blocks        */
+  OBGPU_RES_STRESS_COMPACT = 8 /* [L][Etot][2][3] element_stress[e][face].{N,Vy,Mz} (OBGPU_SOLVE_COMPACT_STRESS) */
 };
 
 /* device >= 0: CUDA ordinal (must be sm_100).  OBGPU_DEVICE_NONE: symbolic-only ctx — batch_upload,
@@ -168,6 +173,10 @@ int obgpu_synchronize(obgpu_ctx*);
  * streams chunks H2D -> fused solve -> D2H on the ctx's copy/compute streams.  Any output may be NULL. */
 int obgpu_solve_cases_host(obgpu_ctx*, int64_t n_cases, const double* case_nload_val, const double* case_eload_q,
                            const double* case_elem_EAI, double* U_f, double* F_b, double* stress, int32_t* info);
+/* the same with OBGPU_SOLVE_* flags: with OBGPU_SOLVE_COMPACT_STRESS `stress` receives [n_cases][Etot][2][3] records
+ * (N, Vy, Mz per face) — 144 fewer bytes per demo3_frame case over PCIe and HBM than the six-component record */
+int obgpu_solve_cases_host_flags(obgpu_ctx*, int64_t n_cases, const double* case_nload_val, const double* case_eload_q,
+                            const double* case_elem_EAI, double* U_f, double* F_b, double* stress, int32_t* info, int flags);
 
 /* per-structure summaries {max|U_f|, sum F_b over DX dofs, sum F_b over DY dofs, info} = 4 doubles per system,
  * written to a caller-provided DEVICE buffer [L*S*4] (e.g. a torch tensor that is then NCCL-gathered) */

@@ -248,13 +248,14 @@ class CStructureProblem {
   void postProcCalcStress(StressInfo& out, const StaticSolveProblemInfo& /*solver_info*/) {
     check(obgpu_stress(ctx_));
     const size_t E = getNumberOfElements();
-    std::vector<num_t> s(E * 12);
-    check(obgpu_download(ctx_, OBGPU_RES_STRESS, s.data()));
+    // compact records (N, Vy, Mz per face): Vz, Mx, My are structurally zero for 2D elements
+    std::vector<num_t> s(E * 6);
+    check(obgpu_download(ctx_, OBGPU_RES_STRESS_COMPACT, s.data()));
     out.element_stress.assign(E, ElementStress(2));
     for (size_t e = 0; e < E; e++)
       for (int f = 0; f < 2; f++) {
-        const num_t* v = &s[e * 12 + f * 6];
-        out.element_stress[e][f] = FaceStress{v[0], v[1], v[2], v[3], v[4], v[5]};
+        const num_t* v = &s[e * 6 + f * 3];
+        out.element_stress[e][f] = FaceStress{v[0], v[1], 0, 0, 0, v[2]};
       }
   }
 
@@ -267,7 +268,7 @@ class CStructureProblem {
     o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI
              : opts.algorithm == StaticSolverAlgorithm::GPU_PCG_MG   ? OBGPU_PCG_MG
                                                                       : OBGPU_BATCHED_LDLT;
-    o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.flags = 0;
+    o.with_stress = 1; o.rtol = opts.pcg_rtol; o.max_iter = opts.pcg_max_iter; o.flags = OBGPU_SOLVE_COMPACT_STRESS;
     check(obgpu_solve_static(ctx_, &o));
     const auto z = sizes();
     std::vector<int32_t> info(z[0] * z[1]);

@@ -50,6 +50,7 @@ static TinyArgs tiny_args(obgpu_ctx* c, int64_t L, const double* nl, const doubl
   a.U_f = Uf; a.F_b = Fb; a.stress = stress; a.F_f = Ff; a.info = info;
   a.fail = c->d_fail.p;
   a.summ = nullptr; a.bnd_dofid = nullptr; a.summ_fallback = nullptr; a.n_summ_peer = 0;
+  a.stress_compact = 0;
   for (double*& p : a.summ_peer) p = nullptr;
   return a;
 }
@@ -65,14 +66,19 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
   o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.flags = 0;
   if (opts) o = *opts;
   c->summ_written = nullptr;
+  c->last_method = o.method; c->last_rtol = o.rtol; c->last_max_iter = o.max_iter;
+  const bool want_compact = o.with_stress && (o.flags & OBGPU_SOLVE_COMPACT_STRESS);
+  c->have_stress_c = false;
   if (o.method == OBGPU_BATCHED_LDLT && c->prog.valid) {
-    rc = alloc_results(c, c->L, o.with_stress != 0);
+    rc = alloc_results(c, c->L, o.with_stress != 0 && !want_compact);
     if (rc != OBGPU_OK) return rc;
+    if (want_compact) OB_CUDA(c, c->d_stress_c.reserve(size_t(c->L) * c->hb.Etot() * 6));
     OB_CUDA(c, cudaMemsetAsync(c->d_fail.p, 0, sizeof(int32_t), c->stream));
     TinyArgs a = tiny_args(c, c->L, c->has_case_nl ? c->d_case_nl.p : nullptr, c->has_case_q ? c->d_case_q.p : nullptr,
                            c->has_case_eai ? c->d_case_eai.p : nullptr, c->d_Uf.p, c->d_Fb.p,
-                           o.with_stress ? c->d_stress.p : nullptr,
+                           !o.with_stress ? nullptr : want_compact ? c->d_stress_c.p : c->d_stress.p,
                            (o.flags & OBGPU_SOLVE_SKIP_FF) ? nullptr : c->d_Ff.p, c->d_info.p);
+    a.stress_compact = want_compact ? 1 : 0;
     c->have_ff = !(o.flags & OBGPU_SOLVE_SKIP_FF);
     SummaryArgs sa;
     if (c->d_summ) {  // bound summaries: written by the solve kernel itself (or by k_summaries right behind it)
@@ -82,22 +88,41 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
       for (int p = 0; p < c->n_summ_peer; p++) a.summ_peer[p] = c->summ_peer[p];
     }
     OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
-    const cudaError_t le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream, &c->kernel_info);
+    cudaError_t le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream, &c->kernel_info);
+    bool compact_pass = false;
+    if (le == cudaErrorNotYetImplemented) {  // this kernel only writes the six-component record: compact it afterwards
+      cudaGetLastError();
+      OB_CUDA(c, c->d_stress.reserve(size_t(c->L) * c->hb.Etot() * 12));
+      a.stress = c->d_stress.p;
+      a.stress_compact = 0;
+      le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, c->stream, &c->kernel_info);
+      compact_pass = le == cudaSuccess;
+    }
     if (le == cudaErrorNotSupported && c->prog.has_load_kinds) {  // no NVRTC here and non-uniform loads: general route
       c->summ_written = nullptr;
       return solve_general(c, o);
     }
     OB_CUDA(c, le);
+    if (compact_pass) OB_CUDA(c, launch_compact_stress(c->d_stress.p, c->d_stress_c.p, c->L * c->hb.Etot(), c->stream));
     OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
     c->t_have[1] = true;
     c->summ_written = c->d_summ;
-    c->launches = (c->d_summ && std::strncmp(c->kernel_info, "k_tiny_jit", 10) != 0) ? 2 + c->n_summ_peer : 1;
+    c->launches = ((c->d_summ && std::strncmp(c->kernel_info, "k_tiny_jit", 10) != 0) ? 2 + c->n_summ_peer : 1) + (compact_pass ? 1 : 0);
     c->pcg_iters = 0;
     c->solved = true;
-    c->have_stress = o.with_stress != 0;
+    c->have_stress = o.with_stress != 0 && (!want_compact || compact_pass);
+    c->have_stress_c = want_compact;
     return OBGPU_OK;
   }
-  return solve_general(c, o);
+  rc = solve_general(c, o);
+  if ((rc == OBGPU_OK || rc == OBGPU_ESINGULAR || rc == OBGPU_ENOTCONVERGED) && want_compact && c->have_stress) {
+    // the warp-per-structure and sparse routes write the six-component record: one more pass compacts it
+    OB_CUDA(c, c->d_stress_c.reserve(size_t(c->L) * c->hb.Etot() * 6));
+    OB_CUDA(c, launch_compact_stress(c->d_stress.p, c->d_stress_c.p, c->L * c->hb.Etot(), c->stream));
+    c->have_stress_c = true;
+    c->launches += 1;
+  }
+  return rc;
 }
 
 const char* obgpu_kernel_info(const obgpu_ctx* c) { return c ? c->kernel_info : ""; }
@@ -132,10 +157,12 @@ int obgpu_assemble(obgpu_ctx* c) {
 int obgpu_stress(obgpu_ctx* c) {
   if (!c) return OBGPU_EINVAL;
   if (!c->solved) return fail(c, OBGPU_ESEQUENCE, "obgpu_stress before obgpu_solve_static");
-  if (c->have_stress) return OBGPU_OK;
+  if (c->have_stress || c->have_stress_c) return OBGPU_OK;
   obgpu_solve_opts o;
-  o.method = OBGPU_BATCHED_LDLT; o.with_stress = 1; o.rtol = 1e-12; o.max_iter = 0; o.flags = 0;
-  return obgpu_solve_static(c, &o);  // the fused kernels recompute; cheap relative to a second pass over HBM
+  // the same route as the solve it follows (a PCG solve must not be replaced by an LDL^T one, nor refused because the
+  // structure is too large for the batched route); the fused kernels recompute, the sparse route re-solves
+  o.method = c->last_method; o.with_stress = 1; o.rtol = c->last_rtol; o.max_iter = c->last_max_iter; o.flags = 0;
+  return obgpu_solve_static(c, &o);
 }
 
 int obgpu_device_ptr(obgpu_ctx* c, int which, void** p) {
@@ -145,6 +172,7 @@ int obgpu_device_ptr(obgpu_ctx* c, int which, void** p) {
     case OBGPU_RES_UF: *p = c->d_Uf.p; break;
     case OBGPU_RES_FB: *p = c->d_Fb.p; break;
     case OBGPU_RES_STRESS: *p = c->d_stress.p; break;
+    case OBGPU_RES_STRESS_COMPACT: *p = c->d_stress_c.p; break;
     case OBGPU_RES_INFO: *p = c->d_info.p; break;
     case OBGPU_RES_FF:
       if (!c->have_ff) return fail(c, OBGPU_ESEQUENCE, "F_f was not kept (OBGPU_SOLVE_SKIP_FF)");
@@ -173,8 +201,11 @@ int obgpu_download(obgpu_ctx* c, int which, void* out) {
     case OBGPU_RES_FB: src = c->d_Fb.p; bytes = size_t(c->L) * s.nb_tot() * 8; break;
     case OBGPU_RES_UB: src = c->d_Ub.p; bytes = size_t(s.nb_tot()) * 8; break;
     case OBGPU_RES_STRESS:
-      if (!c->have_stress) return fail(c, OBGPU_ESEQUENCE, "stress was not computed (with_stress = 0)");
+      if (!c->have_stress) return fail(c, OBGPU_ESEQUENCE, "six-component stress was not computed (with_stress = 0, or OBGPU_SOLVE_COMPACT_STRESS: read OBGPU_RES_STRESS_COMPACT)");
       src = c->d_stress.p; bytes = size_t(c->L) * c->hb.Etot() * 12 * 8; break;
+    case OBGPU_RES_STRESS_COMPACT:
+      if (!c->have_stress_c) return fail(c, OBGPU_ESEQUENCE, "no compact stress records (solve with OBGPU_SOLVE_COMPACT_STRESS)");
+      src = c->d_stress_c.p; bytes = size_t(c->L) * c->hb.Etot() * 6 * 8; break;
     case OBGPU_RES_INFO: src = c->d_info.p; bytes = size_t(c->L) * c->hb.S * 4; break;
     default: return fail(c, OBGPU_EINVAL, "unknown result id");
   }
@@ -226,7 +257,14 @@ int obgpu_pcg_info(const obgpu_ctx* c, double out[4]) {
 // copies in both directions overlap each other and the compute.
 int obgpu_solve_cases_host(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai, double* U_f,
                            double* F_b, double* stress, int32_t* info) {
+  return obgpu_solve_cases_host_flags(c, L, nl, q, eai, U_f, F_b, stress, info, 0);
+}
+
+int obgpu_solve_cases_host_flags(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai, double* U_f,
+                            double* F_b, double* stress, int32_t* info, int flags) {
   if (!c) return OBGPU_EINVAL;
+  const bool compact = stress && (flags & OBGPU_SOLVE_COMPACT_STRESS);
+  const int SR = compact ? 6 : 12;
   OB_NEED_DEVICE(c);
   int rc = ensure_symbolic(c);
   if (rc != OBGPU_OK) return rc;
@@ -247,7 +285,7 @@ int obgpu_solve_cases_host(obgpu_ctx* c, int64_t L, const double* nl, const doub
     if (eai) OB_CUDA(c, sl.eai.reserve(size_t(CH) * 3 * E));
     OB_CUDA(c, sl.Uf.reserve(size_t(CH) * std::max<int64_t>(nf, 1)));
     OB_CUDA(c, sl.Fb.reserve(size_t(CH) * std::max<int64_t>(nb, 1)));
-    if (stress) OB_CUDA(c, sl.stress.reserve(size_t(CH) * E * 12));
+    if (stress) OB_CUDA(c, sl.stress.reserve(size_t(CH) * E * SR));
     OB_CUDA(c, sl.info.reserve(size_t(CH)));
     OB_CUDA(c, cudaStreamWaitEvent(c->slot_stream[i], c->ev[0], 0));
   }
@@ -262,14 +300,26 @@ int obgpu_solve_cases_host(obgpu_ctx* c, int64_t L, const double* nl, const doub
     if (eai) OB_CUDA(c, cudaMemcpyAsync(sl.eai.p, eai + c0 * 3 * E, size_t(n) * 3 * E * 8, cudaMemcpyHostToDevice, st));
     TinyArgs a = tiny_args(c, n, nl ? sl.nl.p : nullptr, q ? sl.q.p : nullptr, eai ? sl.eai.p : nullptr, sl.Uf.p, sl.Fb.p,
                            stress ? sl.stress.p : nullptr, nullptr, sl.info.p);
-    const cudaError_t le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st, &c->kernel_info);
+    a.stress_compact = compact ? 1 : 0;
+    cudaError_t le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st, &c->kernel_info);
+    if (le == cudaErrorNotYetImplemented) {  // six-component kernel + compaction pass
+      cudaGetLastError();
+      OB_CUDA(c, sl.stress_full.reserve(size_t(CH) * E * 12));
+      a.stress = sl.stress_full.p;
+      a.stress_compact = 0;
+      le = launch_tiny_fused(c->prog.nf, c->prog.n, a, c->sm_count, st, &c->kernel_info);
+      if (le == cudaSuccess) {
+        le = launch_compact_stress(sl.stress_full.p, sl.stress.p, n * E, st);
+        launches++;
+      }
+    }
     if (le == cudaErrorNotSupported)
       return fail(c, OBGPU_EUNSUPPORTED, "the host-buffer sweep with non-uniform element loads needs the run-time specialised kernel (NVRTC)");
     OB_CUDA(c, le);
     launches++;
     if (U_f && nf) OB_CUDA(c, cudaMemcpyAsync(U_f + c0 * nf, sl.Uf.p, size_t(n) * nf * 8, cudaMemcpyDeviceToHost, st));
     if (F_b && nb) OB_CUDA(c, cudaMemcpyAsync(F_b + c0 * nb, sl.Fb.p, size_t(n) * nb * 8, cudaMemcpyDeviceToHost, st));
-    if (stress) OB_CUDA(c, cudaMemcpyAsync(stress + c0 * E * 12, sl.stress.p, size_t(n) * E * 96, cudaMemcpyDeviceToHost, st));
+    if (stress) OB_CUDA(c, cudaMemcpyAsync(stress + c0 * E * SR, sl.stress.p, size_t(n) * E * SR * 8, cudaMemcpyDeviceToHost, st));
     if (info) OB_CUDA(c, cudaMemcpyAsync(info + c0, sl.info.p, size_t(n) * 4, cudaMemcpyDeviceToHost, st));
   }
   int32_t failed = 0;

@@ -23,7 +23,7 @@ struct obgpu_ctx {
   obgpu::DevBuf<double> d_case_nl, d_case_q, d_case_eai;
   obgpu::DevBuf<int32_t> d_prog_i;
   obgpu::DevBuf<double> d_prog_d;
-  obgpu::DevBuf<double> d_Uf, d_Fb, d_stress, d_Ff, d_Ub;
+  obgpu::DevBuf<double> d_Uf, d_Fb, d_stress, d_stress_c, d_Ff, d_Ub;  // d_stress_c: compact (N,Vy,Mz) records
   obgpu::DevBuf<int32_t> d_info;
   obgpu::DevBuf<int64_t> d_free_off, d_bnd_off;  // [S+1]
   obgpu::DevBuf<uint8_t> d_bnd_dofid;            // [nb_tot]
@@ -31,7 +31,9 @@ struct obgpu_ctx {
   obgpu::DevBuf<int32_t> d_frame_inv;             // [nf_tot] band-reducing renumbering of the batched-LDLt route (or unused)
   bool frame_renumbered = false;
   obgpu::DevBuf<int32_t> d_fail;  // [1] OR of per-system failures of the last solve
-  bool solved = false, have_stress = false, have_ff = true;
+  bool solved = false, have_stress = false, have_stress_c = false, have_ff = true;
+  int last_method = 0;   // method of the last solve (obgpu_stress re-runs the same route)
+  double last_rtol = 1e-12; int last_max_iter = 0;
   std::vector<uint8_t> h_bnd_dofid;               // host copy of d_bnd_dofid
   double* d_summ = nullptr;                       // obgpu_bind_summaries target (caller's device buffer) or null
   double* summ_peer[8] = {};                      // obgpu_bind_summary_peers
@@ -90,7 +92,7 @@ struct obgpu_ctx {
 
   // chunk slots of obgpu_solve_cases_host
   struct Slot {
-    obgpu::DevBuf<double> nl, q, eai, Uf, Fb, stress;
+    obgpu::DevBuf<double> nl, q, eai, Uf, Fb, stress, stress_full;
     obgpu::DevBuf<int32_t> info;
   } slot[NSLOT];
 

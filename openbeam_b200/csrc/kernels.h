@@ -23,6 +23,8 @@ struct TinyArgs {
   int n_summ_peer;         // summaries done by the solve kernel's own stores over NVLink, obgpu_bind_summary_peers)
   const uint8_t* bnd_dofid;                 // HOST [nb]: DoF_index of each bounded DOF (used with summ)
   const struct SummaryArgs* summ_fallback;  // HOST: arguments of the separate k_summaries launch for kernels without it
+  int stress_compact;      // stress records are [E][2][3] = (N, Vy, Mz) per face (OBGPU_SOLVE_COMPACT_STRESS); a launcher
+                           // whose kernel only writes the full record answers cudaErrorNotYetImplemented
 };
 cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cudaStream_t st, const char** which = nullptr);
 cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStream_t st, const char** which = nullptr);  // tiny_jit.cu
@@ -179,5 +181,7 @@ struct SummaryArgs {
   double* out;               // [L][S][4], 32-byte aligned
 };
 cudaError_t launch_summaries(const SummaryArgs& a, int sm_count, cudaStream_t st);
+// full [n][2][6] element stress records -> compact [n][2][3] (N, Vy, Mz): for kernels that only write the full record
+cudaError_t launch_compact_stress(const double* full, double* compact, int64_t n_elem_records, cudaStream_t st);
 
 }  // namespace obgpu

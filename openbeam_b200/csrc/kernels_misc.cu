@@ -35,4 +35,22 @@ cudaError_t launch_summaries(const SummaryArgs& a, int sm_count, cudaStream_t st
   return cudaGetLastError();
 }
 
+// full element stress records [n][2][6] -> compact [n][2][3] = (N, Vy, Mz) per face
+__global__ void __launch_bounds__(256) k_compact_stress(const double* __restrict__ full, double* __restrict__ out, int64_t n6) {
+  for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n6; i += int64_t(gridDim.x) * blockDim.x) {
+    const int64_t rec = i / 6;
+    const int k = int(i - rec * 6);  // 0..2 face 0, 3..5 face 1
+    const int src = k < 3 ? (k == 2 ? 5 : k) : (k == 5 ? 11 : k + 3);
+    out[i] = full[rec * 12 + src];
+  }
+}
+cudaError_t launch_compact_stress(const double* full, double* compact, int64_t n_elem_records, cudaStream_t st) {
+  const int64_t n6 = n_elem_records * 6;
+  if (n6 == 0) return cudaSuccess;
+  int64_t grid = (n6 + 255) / 256;
+  if (grid > 148 * 16) grid = 148 * 16;
+  k_compact_stress<<<unsigned(grid), 256, 0, st>>>(full, compact, n6);
+  return cudaGetLastError();
+}
+
 }  // namespace obgpu

@@ -479,6 +479,7 @@ cudaError_t launch_tiny_fused(int nf, int n, const TinyArgs& a, int sm_count, cu
     const cudaError_t je = launch_tiny_jit(dev, a, sm_count, st, which);
     if (je != cudaErrorNotSupported) return je;
   }
+  if (a.stress_compact) return cudaErrorNotYetImplemented;  // the precompiled kernels write the full record
   {  // the precompiled interpreter knows uniform element loads only: the caller takes the warp-per-structure route
     const int32_t* I = a.prog_i;
     const TinyLayout lay(I[0], I[1], I[2], I[3], I[4], I[5], I[6]);

@@ -137,6 +137,7 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
   key += char('0' + device);
   key += a.F_f ? 'F' : '-';
   key += a.summ ? 'S' : '-';
+  key += a.stress_compact ? 'C' : '-';
   if (a.summ) key.append(reinterpret_cast<const char*>(a.bnd_dofid), size_t(nb));  // the kernel is also specialised on whether F_f is kept (staging rows, occupancy)
   std::lock_guard<std::mutex> lock(mu);
   Compiled& c = cache[key];
@@ -147,14 +148,20 @@ cudaError_t launch_tiny_jit(int device, const TinyArgs& a, int sm_count, cudaStr
     minb = minb * 128 / jit_block();  // the same register budget per thread whatever the CTA width
     if (getenv("OBGPU_TINY_JIT_MINB")) minb = atoi(getenv("OBGPU_TINY_JIT_MINB"));  // tuning experiments
     // result records through the bulk-copy engine when a CTA's staging rows (final layout, 4 warps x 32 cases) stay small
-    const size_t bulk_bytes = size_t(jit_block() / 32) * (size_t(32) * (12 * E + (a.F_f ? 2 : 1) * nf + nb + (a.summ ? 4 : 0)) + 16) * 8;
+    const int sr = a.stress_compact ? 6 : 12;
+    const size_t bulk_bytes = size_t(jit_block() / 32) * (size_t(32) * (sr * E + (a.F_f ? 2 : 1) * nf + nb + (a.summ ? 4 : 0)) + 16) * 8;
     bool& bulk = c.bulk;
     bulk = bulk_bytes <= 60 * 1024;
     if (const char* ev = getenv("OBGPU_TINY_JIT_BULK")) bulk = bulk && atoi(ev) != 0;
+    if (a.stress_compact && !bulk) {  // only the bulk-store variant writes compact records: the caller compacts afterwards
+      cache.erase(key);
+      return cudaErrorNotYetImplemented;
+    }
     std::string src;
     src += "#define TJ_BLOCK_SIZE " + std::to_string(jit_block()) + "\n";
     src += std::string("#define TJ_BULK ") + (bulk ? "1\n" : "0\n");
     src += std::string("#define TJ_FF ") + (a.F_f ? "1\n" : "0\n");
+    src += std::string("#define TJ_SC ") + (a.stress_compact ? "1\n" : "0\n");
     const char* ef = getenv("OBGPU_TINY_JIT_EVICT_FIRST");
     src += std::string("#define TJ_EVICT_FIRST ") + (ef && atoi(ef) == 0 ? "0\n" : "1\n");
     src += "#define TJ_N " + std::to_string(N) + "\n#define TJ_E " + std::to_string(E) + "\n#define TJ_n " + std::to_string(n) +

@@ -15,6 +15,7 @@
 //   TJ_elkind[EL] (OBGPU_LOAD_* of every element load),
 //   TJ_SUMM + TJ_bnddof[NB] (per-case summaries written by this kernel; DoF_index of each bounded DOF),
 //   TJ_BULK (records through the bulk-copy engine), TJ_FF (F_f is kept), TJ_EVICT_FIRST,
+//   TJ_SC (compact stress records [E][2][3] = N, Vy, Mz per face instead of the reference's [E][2][6]; TJ_BULK only),
 //   TJ_elptr[E+1], TJ_elslot[EL], TJ_nldst[NL], TJ_freek[NF], TJ_bndk[NB]
 // (arrays padded to at least one entry), then include this file after beam_math.cuh.
 #pragma once
@@ -92,8 +93,12 @@ struct TjStoreMap {
 // of the other warps behind a queue of STGs (measured: compute 45 us + stores 65 us ran back to back as 98 us).
 // The staging rows are reused one iteration later, after cp.async.bulk.wait_group.read.
 __device__ __forceinline__ void tj_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// waits until at most N of the most recently committed bulk groups of the issuing lane still have their source rows
+// unread: the records leave in a fixed order per iteration (F_f | info, U_f | stress, F_b, summaries), so each staging
+// array is waited for only where it is written again, one iteration later, with the younger groups left in flight
+template <int N>
 __device__ __forceinline__ void tj_bulk_wait_read(int lane) {
-  if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
   __syncwarp();
 }
 // All lanes call this after their row writes + tj_fence_async() + __syncwarp().  rec_bytes is a multiple of 4.
@@ -135,18 +140,21 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
 #if TJ_BULK
   // per warp: RS[32][12E] stress | RU[32][NF] U_f | RF[32][NF] F_f | RB[32][NB] F_b | RM[32][4] summaries | RI[32] info
   // (final layouts)
-  constexpr int WR = 32 * (12 * E + (TJ_FF ? 2 : 1) * NF + NB + (TJ_SUMM ? 4 : 0)) + 16;  // doubles per warp
+  constexpr int SR = TJ_SC ? 6 : 12;  // doubles per element of the stress record
+  constexpr int WR = 32 * (SR * E + (TJ_FF ? 2 : 1) * NF + NB + (TJ_SUMM ? 4 : 0)) + 16;  // doubles per warp
   double* RS = LP + 2 * (EL > 0 ? EL : 1) + (threadIdx.x >> 5) * WR;
-  double* RU = RS + 32 * 12 * E;
+  double* RU = RS + 32 * SR * E;
   double* RF = RU + 32 * NF;
   double* RB = RF + (TJ_FF ? 32 * NF : 0);
   double* RM = RB + 32 * NB;  // [32][4] summaries
   int* RI = reinterpret_cast<int*>(RM + (TJ_SUMM ? 32 * 4 : 0));
   double* SN = LP + 2 * (EL > 0 ? EL : 1) + (TJ_BLOCK / 32) * WR + threadIdx.x;
   double* SQ = SN + (a.case_nl ? NL * CS : 0);
-  double* rs = RS + lane * 12 * E;
+  double* rs = RS + lane * SR * E;
 #pragma unroll
-  for (int i = 0; i < 12 * E; i++) rs[i] = 0.0;  // the structural zeros of the stress records stay in place
+  for (int i = 0; i < SR * E; i++) rs[i] = 0.0;  // the structural zeros of the full stress records stay in place
+  // bulk groups a warp commits per iteration, in order: [F_f] | info, U_f | [stress], [F_b], [summaries (+ peers)]
+  const bool late_wait0 = TJ_SUMM && a.n_summ_peer > 0;  // peer copies add groups: fall back to waiting for everything
 #else
   double* SS = LP + 2 * (EL > 0 ? EL : 1) + threadIdx.x;
   double* SX = SS + 12 * TJ_RS;
@@ -272,7 +280,11 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     const long long c0 = base + wl0;
     const int cnt = int(min(32LL, a.n_cases - c0));
 #if TJ_BULK
-    tj_bulk_wait_read(lane);  // last iteration's records have left the staging rows
+    // last iteration's F_f / info / U_f rows have been read out (its stress, F_b and summary groups, committed after
+    // them, may still be in flight: their rows are not touched before stage B)
+    constexpr int G_LATE = 1 + (NB > 0 ? 1 : 0) + (TJ_SUMM ? 1 : 0);
+    if (late_wait0 || !a.stress) tj_bulk_wait_read<0>(lane);
+    else tj_bulk_wait_read<G_LATE>(lane);
     if (TJ_FF && a.F_f && NF > 0) {
 #pragma unroll
       for (int i = 0; i < NF; i++) RF[lane * NF + i] = b[i];
@@ -335,6 +347,10 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
 #pragma unroll
     for (int i = 0; i < NF; i++) umax = fmax(umax, fabs(b[i]));
 #endif
+#if TJ_BULK
+    // stage B rewrites the stress / F_b / summary rows: only this iteration's info and U_f groups (and F_f) may be pending
+    if (!late_wait0 && a.stress) tj_bulk_wait_read<2 + ((TJ_FF && NF > 0) ? 1 : 0)>(lane);
+#endif
     // bounded entries hold the equivalent loads: reactions start from their negative (solver_static.cpp:208-218)
 #pragma unroll
     for (int i = 0; i < NB; i++) fu[TJ_bndk[i]] = -fu[TJ_bndk[i]];
@@ -379,7 +395,11 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
 #pragma unroll
           for (int k = 0; k < 6; k++) ext[k] += ex[k];
         }
-#if TJ_BULK
+#if TJ_BULK && TJ_SC
+        reinterpret_cast<double2*>(rs + 6 * e)[0] = make_double2(-es[0] + ext[0], -es[1] + ext[1]);
+        reinterpret_cast<double2*>(rs + 6 * e)[1] = make_double2(-es[2] + ext[2], es[3] + ext[3]);
+        reinterpret_cast<double2*>(rs + 6 * e)[2] = make_double2(es[4] + ext[4], es[5] + ext[5]);
+#elif TJ_BULK
         reinterpret_cast<double2*>(rs + 12 * e)[0] = make_double2(-es[0] + ext[0], -es[1] + ext[1]);
         rs[12 * e + 5] = -es[2] + ext[2];
         reinterpret_cast<double2*>(rs + 12 * e)[3] = make_double2(es[3] + ext[3], es[4] + ext[4]);
@@ -429,7 +449,7 @@ extern "C" __global__ void __launch_bounds__(TJ_BLOCK, TJ_MINB) k_tiny_jit(const
     tj_fence_async();
     __syncwarp();
     if (st_on) {
-      if (a.stress) tj_bulk_store(a.stress + c0 * E * 12, RS, E * 96, cnt, lane);
+      if (a.stress) tj_bulk_store(a.stress + c0 * E * SR, RS, E * SR * 8, cnt, lane);
       if (NB > 0) tj_bulk_store(a.F_b + c0 * NB, RB, NB * 8, cnt, lane);
       if (TJ_SUMM) {
         tj_bulk_store(a.summ + c0 * 4, RM, 32, cnt, lane);

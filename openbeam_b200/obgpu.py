@@ -25,8 +25,8 @@ LIB_PATH = os.environ.get("OBGPU_LIB") or os.path.join(_HERE, "libobgpu.so")  # 
 OK, EINVAL, ECUDA, ESINGULAR, ENOTCONVERGED, EUNSUPPORTED, ESEQUENCE = range(7)
 BATCHED_LDLT, PCG_JACOBI, PCG_MG = range(3)
 PROF_SPMV, PROF_MG_SPMV = 0, 1
-SOLVE_SKIP_FF = 1  # obgpu_solve_opts.flags
-(RES_UF, RES_FB, RES_STRESS, RES_INFO, RES_FF, RES_UB, RES_KVAL, RES_ELEM_K) = range(8)
+SOLVE_SKIP_FF, SOLVE_COMPACT_STRESS = 1, 2  # obgpu_solve_opts.flags
+(RES_UF, RES_FB, RES_STRESS, RES_INFO, RES_FF, RES_UB, RES_KVAL, RES_ELEM_K, RES_STRESS_COMPACT) = range(9)
 (SYM_DOF_NODE, SYM_DOF_ID, SYM_FREE, SYM_BOUNDED, SYM_DOF_INDEX, SYM_K_ROWPTR, SYM_K_COL, SYM_TRI_NNZ) = range(8)
 OFF_DOF, OFF_FREE, OFF_BOUNDED, OFF_NNZ, OFF_TRIPLET = range(5)
 SIZE_NAMES = ("S", "L", "Ntot", "Etot", "n_tot", "nf_tot", "nb_tot", "T_tot", "nnz_tot", "Ctot", "NLtot", "ELtot")
@@ -36,7 +36,7 @@ ABI_SYMBOLS = (
     "obgpu_create", "obgpu_destroy", "obgpu_last_error", "obgpu_status_string", "obgpu_host_alloc",
     "obgpu_host_free", "obgpu_batch_upload", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
-    "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host",
+    "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host", "obgpu_solve_cases_host_flags",
     "obgpu_summaries_device", "obgpu_get_timings", "obgpu_pcg_info", "obgpu_profile_kernel", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
     "obgpu_mesh_create", "obgpu_mesh_desc", "obgpu_mesh_info", "obgpu_mesh_destroy",
 )
@@ -102,6 +102,7 @@ def lib():
         L.obgpu_download.argtypes = [vp, C.c_int, vp]
         L.obgpu_device_ptr.argtypes = [vp, C.c_int, C.POINTER(vp)]
         L.obgpu_solve_cases_host.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp]
+        L.obgpu_solve_cases_host_flags.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, vp, C.c_int]
         L.obgpu_summaries_device.argtypes = [vp, vp]
         L.obgpu_mesh_create.argtypes = [C.POINTER(BatchDesc), C.c_double, C.POINTER(vp)]
         L.obgpu_mesh_desc.argtypes = [vp, C.POINTER(BatchDesc)]
@@ -313,8 +314,10 @@ class Context:
     def kernel_info(self):
         return lib().obgpu_kernel_info(self.h).decode()
 
-    def solve_static(self, method=BATCHED_LDLT, with_stress=True, rtol=1e-12, max_iter=0, keep_Ff=True):
-        o = SolveOpts(method, int(with_stress), rtol, max_iter, 0 if keep_Ff else SOLVE_SKIP_FF)
+    def solve_static(self, method=BATCHED_LDLT, with_stress=True, rtol=1e-12, max_iter=0, keep_Ff=True,
+                     compact_stress=False):
+        o = SolveOpts(method, int(with_stress), rtol, max_iter,
+                      (0 if keep_Ff else SOLVE_SKIP_FF) | (SOLVE_COMPACT_STRESS if compact_stress else 0))
         self._chk(lib().obgpu_solve_static(self.h, C.byref(o)))
 
     def stress(self):
@@ -323,9 +326,12 @@ class Context:
     def synchronize(self):
         self._chk(lib().obgpu_synchronize(self.h))
 
-    def solve_cases_host(self, n_cases, case_nload_val, case_eload_q, case_elem_EAI, U_f, F_b, stress, info):
-        self._chk(lib().obgpu_solve_cases_host(self.h, n_cases, _p(case_nload_val), _p(case_eload_q),
-                                               _p(case_elem_EAI), _p(U_f), _p(F_b), _p(stress), _p(info)))
+    def solve_cases_host(self, n_cases, case_nload_val, case_eload_q, case_elem_EAI, U_f, F_b, stress, info,
+                         compact_stress=False):
+        """stress: [n_cases, E, 2, 6], or [n_cases, E, 2, 3] = (N, Vy, Mz) with compact_stress"""
+        self._chk(lib().obgpu_solve_cases_host_flags(self.h, n_cases, _p(case_nload_val), _p(case_eload_q),
+                                                _p(case_elem_EAI), _p(U_f), _p(F_b), _p(stress), _p(info),
+                                                SOLVE_COMPACT_STRESS if compact_stress else 0))
 
     def summaries_device(self, dptr):
         self._chk(lib().obgpu_summaries_device(self.h, _p(int(dptr))))
@@ -356,6 +362,7 @@ class Context:
         return {RES_UF: ((L, z["nf_tot"]), np.float64), RES_FF: ((L, z["nf_tot"]), np.float64),
                 RES_FB: ((L, z["nb_tot"]), np.float64), RES_UB: ((z["nb_tot"],), np.float64),
                 RES_STRESS: ((L, z["Etot"], 2, 6), np.float64), RES_INFO: ((L, z["S"]), np.int32),
+                RES_STRESS_COMPACT: ((L, z["Etot"], 2, 3), np.float64),
                 RES_KVAL: ((-1, z["nnz_tot"]), np.float64), RES_ELEM_K: ((-1, z["Etot"], 21), np.float64)}[which]
 
     def download(self, which, out=None, lk=None):

@@ -148,7 +148,8 @@ class CStructureProblem:
 
     def _solve_once(self, options):
         self.updateAll()
-        self.ctx.solve_static(int(options.algorithm), True, options.pcg_rtol, options.pcg_max_iter)
+        # element end forces come back as compact (N, Vy, Mz) records: Vz, Mx, My are structurally zero in 2D
+        self.ctx.solve_static(int(options.algorithm), True, options.pcg_rtol, options.pcg_max_iter, compact_stress=True)
         info = self.ctx.download(obgpu.RES_INFO)
         if np.any(info != 0):
             raise RuntimeError(obgpu.lib().obgpu_status_string(obgpu.ESINGULAR).decode())
@@ -207,5 +208,8 @@ class CStructureProblem:
 
     def postProcCalcStress(self, out_stress: StressInfo, solver_info: StaticSolveProblemInfo | None = None):
         self.ctx.stress()
-        out_stress.element_stress = self.ctx.download(obgpu.RES_STRESS)[0]
+        c = self.ctx.download(obgpu.RES_STRESS_COMPACT)[0]          # [E][2][3] = N, Vy, Mz
+        full = np.zeros((c.shape[0], 2, 6))                           # FaceStress order N,Vy,Vz,Mx,My,Mz (types.h:78-157)
+        full[:, :, 0], full[:, :, 1], full[:, :, 5] = c[:, :, 0], c[:, :, 1], c[:, :, 2]
+        out_stress.element_stress = full
         return out_stress

@@ -259,3 +259,62 @@ def test_timings_and_launch_count(ctx):
     ctx.synchronize()
     t = ctx.timings()
     assert t["launches"] == 1 and t["solveStatic.2_solve"] > 0
+
+
+def _compact_of(full):
+    """[.., 2, 6] FaceStress records -> the compact (N, Vy, Mz) ones; also checks Vz, Mx, My are exactly zero"""
+    full = np.asarray(full)
+    assert not full[..., 2:5].any()
+    return full[..., [0, 1, 5]]
+
+
+@pytest.mark.parametrize("L", [1, 31, 4096 + 17])
+@pytest.mark.parametrize("per_case_section", [False, True])
+def test_compact_stress_bit_identical(ctx, L, per_case_section):
+    """OBGPU_SOLVE_COMPACT_STRESS: the (N, Vy, Mz) records are the same bits as those columns of the six-component
+    record, on the device-resident route and through the host-buffer sweep."""
+    st = workloads.demo3_frame()
+    nl, q, eai = workloads.c2_cases(5, L, per_case_section)
+    ctx.upload(st, L, nl, q, eai)
+    ctx.solve_static()
+    full = ctx.download(obgpu.RES_STRESS)
+    U0, F0 = ctx.download(obgpu.RES_UF), ctx.download(obgpu.RES_FB)
+    ctx.solve_static(compact_stress=True, keep_Ff=False)
+    comp = ctx.download(obgpu.RES_STRESS_COMPACT)
+    assert comp.shape == (L, 3, 2, 3)
+    assert np.array_equal(comp, _compact_of(full))
+    assert np.array_equal(ctx.download(obgpu.RES_UF), U0) and np.array_equal(ctx.download(obgpu.RES_FB), F0)
+    with pytest.raises(obgpu.ObgpuError):
+        ctx.download(obgpu.RES_STRESS)          # the six-component record was not produced
+    hU, hF, hS, hi = np.zeros((L, 6)), np.zeros((L, 6)), np.zeros((L, 3, 2, 3)), np.zeros(L, np.int32)
+    ctx.solve_cases_host(L, nl, q, eai, hU, hF, hS, hi, compact_stress=True)
+    assert np.array_equal(hS, comp) and np.array_equal(hU, U0) and np.array_equal(hF, F0) and not hi.any()
+
+
+def test_compact_stress_other_routes(ctx):
+    """the warp-per-structure and sparse routes compact their six-component record in one more pass"""
+    sts = [workloads.c3_frame(i) for i in range(40)]
+    ctx.upload(sts)
+    ctx.solve_static()
+    full = ctx.download(obgpu.RES_STRESS)
+    ctx.solve_static(compact_stress=True)
+    assert np.array_equal(ctx.download(obgpu.RES_STRESS_COMPACT), _compact_of(full))
+    st = workloads.grid_frame(20, 17)
+    ctx.upload(st)
+    ctx.solve_static(method=obgpu.PCG_MG, rtol=1e-11)
+    full = ctx.download(obgpu.RES_STRESS)
+    ctx.solve_static(method=obgpu.PCG_MG, rtol=1e-11, compact_stress=True)
+    assert np.array_equal(ctx.download(obgpu.RES_STRESS_COMPACT), _compact_of(full))
+
+
+def test_stress_after_pcg_without_stress_keeps_the_route(ctx):
+    """obgpu_stress() after a with_stress=0 PCG solve re-runs the SAME route (it used to switch to LDLt)"""
+    st = workloads.grid_frame(30, 25)
+    ctx.upload(st)
+    ctx.solve_static(method=obgpu.PCG_MG, with_stress=False, rtol=1e-11)
+    U = ctx.download(obgpu.RES_UF)
+    ctx.stress()
+    assert "k_mg_spmv" in ctx.kernel_info()
+    assert np.array_equal(ctx.download(obgpu.RES_UF), U)
+    od = OracleProblem(st).solveStatic().postProcCalcStress()
+    assert relerr(ctx.download(obgpu.RES_STRESS)[0], od.element_stress) <= RTOL
