@@ -14,9 +14,15 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
+_REF = None
+REF_SOURCES = "/root/reference/libopenbeam"   # only needed to (re)build oracle/_ref; the built .so travels
 
 I_DOF_NODE, I_DOF_ID, I_FREE, I_BOUNDED, I_DOF_INDEX, I_TRI_ROW, I_TRI_COL, I_K_OUTER, I_K_INNER = range(9)
 (F_TRI_VAL, F_K_VAL, F_KFF, F_KBF, F_KBB, F_UB, F_FF, F_UF, F_FB, F_STRESS, F_ELEM_R, F_ELEM_KGLOBAL) = range(12)
+
+
+class OracleError(RuntimeError):
+    pass
 
 
 def build(force=False):
@@ -26,6 +32,53 @@ def build(force=False):
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "libob_oracle.so"])
     return so
+
+
+def build_ref(force=False):
+    """oracle/_ref/libob_ref.so: the reference's own unmodified hot-path sources compiled against oracle/ref_shim/ (see
+    Makefile.ref).  Built only where /root/reference exists (this container); elsewhere the prebuilt file is used."""
+    so = os.path.join(_HERE, "_ref", "libob_ref.so")
+    if os.path.isdir(REF_SOURCES):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-j8", "-f", "Makefile.ref"] + (["-B"] if force else []))
+    return so if os.path.exists(so) else None
+
+
+def ref_available():
+    return build_ref() is not None
+
+
+def _bind(L):
+    vp, i64, dp = C.c_void_p, C.c_int64, C.c_void_p
+    L.obo_create.restype = vp
+    L.obo_create.argtypes = [i64, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp]
+    L.obo_destroy.argtypes = [vp]
+    L.obo_set_load_values.argtypes = [vp, dp, dp]
+    L.obo_set_eload_kinds.argtypes = [vp, dp, dp]
+    L.obo_set_elem_EAI.argtypes = [vp, dp]
+    L.obo_assemble.argtypes = [vp, C.c_int]
+    L.obo_solve_static.argtypes = [vp, C.c_int]
+    L.obo_stress.argtypes = [vp]
+    L.obo_last_error.argtypes = [vp]
+    L.obo_last_error.restype = C.c_char_p
+    L.obo_get_sizes.argtypes = [vp, dp]
+    L.obo_get_i64.argtypes = [vp, C.c_int, dp, i64]
+    L.obo_get_i64.restype = i64
+    L.obo_get_f64.argtypes = [vp, C.c_int, dp, i64]
+    L.obo_get_f64.restype = i64
+    L.obo_run_cases.argtypes = [vp, i64, dp, dp, dp, C.c_int, dp, dp, dp]
+    L.obo_run_cases.restype = C.c_double
+    return L
+
+
+def ref_lib():
+    """the reference itself (oracle/_ref), same C ABI as the restated oracle"""
+    global _REF
+    if _REF is None:
+        so = build_ref()
+        if so is None:
+            raise OracleError("oracle/_ref/libob_ref.so is not built and /root/reference is not here to build it")
+        _REF = _bind(C.CDLL(so))
+    return _REF
 
 
 def lib():
@@ -59,16 +112,15 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
-class OracleError(RuntimeError):
-    pass
 
 
 class OracleProblem:
     """One structure inside the oracle; methods follow the reference's names."""
 
-    def __init__(self, st):
+    def __init__(self, st, reference=False):
+        """reference=True: run the reference's own sources (oracle/_ref) instead of the restatement"""
         self.st = st
-        L = lib()
+        L = self._L = ref_lib() if reference else lib()
         self._keep = st
         self.h = L.obo_create(
             st.n_nodes, _p(st.node_xy), _p(st.node_rotz), st.n_elems, _p(st.elem_nodes), _p(st.elem_type),
@@ -83,49 +135,49 @@ class OracleProblem:
 
     def __del__(self):
         if getattr(self, "h", None):
-            lib().obo_destroy(self.h)
+            self._L.obo_destroy(self.h)
             self.h = None
 
     def _chk(self, rc):
         if rc != 0:
-            raise OracleError(lib().obo_last_error(self.h).decode())
+            raise OracleError(self._L.obo_last_error(self.h).decode())
 
     def assembleProblem(self, skip_subK=False):
-        self._chk(lib().obo_assemble(self.h, int(skip_subK)))
+        self._chk(self._L.obo_assemble(self.h, int(skip_subK)))
         return self
 
     def solveStatic(self):
-        self._chk(lib().obo_solve_static(self.h, 0))
+        self._chk(self._L.obo_solve_static(self.h, 0))
         return self
 
     def postProcCalcStress(self):
-        self._chk(lib().obo_stress(self.h))
+        self._chk(self._L.obo_stress(self.h))
         return self
 
     def set_load_values(self, nl_val=None, el_q=None):
         nl = None if nl_val is None else np.ascontiguousarray(nl_val, np.float64)
         eq = None if el_q is None else np.ascontiguousarray(el_q, np.float64)
-        lib().obo_set_load_values(self.h, _p(nl), _p(eq))
+        self._L.obo_set_load_values(self.h, _p(nl), _p(eq))
 
     def set_elem_EAI(self, eai):
         eai = np.ascontiguousarray(eai, np.float64)
-        lib().obo_set_elem_EAI(self.h, _p(eai))
+        self._L.obo_set_elem_EAI(self.h, _p(eai))
 
     def sizes(self):
         out = np.zeros(8, np.int64)
-        lib().obo_get_sizes(self.h, _p(out))
+        self._L.obo_get_sizes(self.h, _p(out))
         return dict(zip(("N", "E", "n", "n_f", "n_b", "T", "nnz"), out[:7].tolist()))
 
     def geti(self, which):
-        n = lib().obo_get_i64(self.h, which, None, 0)
+        n = self._L.obo_get_i64(self.h, which, None, 0)
         out = np.zeros(max(n, 0), np.int64)
-        lib().obo_get_i64(self.h, which, _p(out), n)
+        self._L.obo_get_i64(self.h, which, _p(out), n)
         return out
 
     def getf(self, which):
-        n = lib().obo_get_f64(self.h, which, None, 0)
+        n = self._L.obo_get_f64(self.h, which, None, 0)
         out = np.zeros(max(n, 0), np.float64)
-        lib().obo_get_f64(self.h, which, _p(out), n)
+        self._L.obo_get_f64(self.h, which, _p(out), n)
         return out
 
     # named accessors (reference field names)
@@ -168,7 +220,7 @@ class OracleProblem:
         U = np.zeros((n_cases, s["n_f"])) if want_outputs else None
         F = np.zeros((n_cases, s["n_b"])) if want_outputs else None
         S = np.zeros((n_cases, s["E"], 2, 6)) if want_outputs else None
-        dt = lib().obo_run_cases(self.h, n_cases, _p(nl), _p(eq), _p(ea), n_threads, _p(U), _p(F), _p(S))
+        dt = self._L.obo_run_cases(self.h, n_cases, _p(nl), _p(eq), _p(ea), n_threads, _p(U), _p(F), _p(S))
         if dt < 0:
             raise OracleError("obo_run_cases failed")
         return dt, U, F, S

@@ -72,6 +72,9 @@ template <class D> struct MatrixBase {
   Scalar operator()(Index i, Index j) const { return coeff(i, j); }
   Scalar operator()(Index i) const { return coeff(i); }
   Scalar operator[](Index i) const { return coeff(i); }
+  Scalar x() const { return coeff(0); }
+  Scalar y() const { return coeff(1); }
+  Scalar z() const { return coeff(2); }
   Plain eval() const {
     Plain m(rows(), cols());
     for (Index j = 0; j < cols(); j++)
@@ -177,6 +180,12 @@ template <class T, int R, int C> class Matrix : public MatrixBase<Matrix<T, R, C
   T operator[](Index i) const { return s_.data()[i]; }
   T* data() { return s_.data(); }
   const T* data() const { return s_.data(); }
+  using Base::x;
+  using Base::y;
+  using Base::z;
+  T& x() { return s_.data()[0]; }
+  T& y() { return s_.data()[1]; }
+  T& z() { return s_.data()[2]; }
   void resize(Index n) {
     if (C == 1 || (C == Dynamic && R != 1)) s_.resize(n, C == Dynamic ? 1 : C);
     else s_.resize(1, n);
@@ -354,24 +363,31 @@ template <class MatrixType> class LLT {
   LLT() {}
   explicit LLT(const MatrixType& a) { compute(a); }
   LLT& compute(const MatrixType& a) {
-    // llt_inplace<Scalar, Lower>::unblocked: reads the LOWER triangle only
-    L_ = a;
+    // llt_inplace<Scalar, Lower>::unblocked: reads the LOWER triangle only.  Worked on a row-major copy so that the two
+    // rows of every inner product are contiguous (same operations in the same order, only the memory layout differs;
+    // Eigen's own kernel is blocked and vectorised, i.e. faster still)
     const Index n = a.rows();
+    std::vector<T> R(size_t(n) * size_t(n), T(0));
+    for (Index i = 0; i < n; i++)
+      for (Index j = 0; j <= i; j++) R[size_t(i) * n + j] = a(i, j);
     info_ = Success;
-    for (Index k = 0; k < n; k++) {
-      T x = L_(k, k);
-      for (Index j = 0; j < k; j++) x -= L_(k, j) * L_(k, j);
-      if (!(x > T(0))) { info_ = NumericalIssue; return *this; }
+    for (Index k = 0; k < n && info_ == Success; k++) {
+      const T* rk = &R[size_t(k) * n];
+      T x = rk[k];
+      for (Index j = 0; j < k; j++) x -= rk[j] * rk[j];
+      if (!(x > T(0))) { info_ = NumericalIssue; break; }
       x = std::sqrt(x);
-      L_(k, k) = x;
+      R[size_t(k) * n + k] = x;
       for (Index i = k + 1; i < n; i++) {
-        T s = L_(i, k);
-        for (Index j = 0; j < k; j++) s -= L_(i, j) * L_(k, j);
-        L_(i, k) = s / x;
+        T* ri = &R[size_t(i) * n];
+        T s = ri[k];
+        for (Index j = 0; j < k; j++) s -= ri[j] * rk[j];
+        ri[k] = s / x;
       }
     }
+    L_.resize(n, n);
     for (Index j = 0; j < n; j++)
-      for (Index i = 0; i < j; i++) L_(i, j) = T(0);
+      for (Index i = 0; i < n; i++) L_(i, j) = i >= j ? R[size_t(i) * n + j] : T(0);
     return *this;
   }
   ComputationInfo info() const { return info_; }

@@ -1,0 +1,1 @@
+#include <mrpt/opengl/CSetOfObjects.h>
