@@ -430,6 +430,11 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.config == "c3":
+        import bench_frames
+        if args.impl == "reference":
+            return bench_frames.reference(args, rank, world, emit)
+        return bench_frames.ours(args, rank, local_rank, world, emit, ClockSampler, peak_info)
     if args.config in ("c4", "c5"):
         import bench_lattice
         if args.impl == "reference":

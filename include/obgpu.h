@@ -146,6 +146,15 @@ int obgpu_host_free(void* p);
 
 /* upload a batch (copies everything it needs; host buffers may be freed afterwards) */
 int obgpu_batch_upload(obgpu_ctx*, const obgpu_batch_desc*);
+/* The same for batches of MANY small structures (parameter sweeps, config "4M random frames"): the arrays go straight from
+ * the caller's buffers (pinned ones from obgpu_host_alloc copy at PCIe speed) to the device, the library keeps no host
+ * copy beyond the five offset arrays, and obgpu_symbolic then runs the DOF numbering / partition / slot phase
+ * (CFiniteElementProblem.cpp:179-245, assemble.cpp:74-99) as device kernels, thread per structure, including the
+ * validation obgpu_batch_upload does on the host (a malformed structure refuses the batch with the same messages).
+ * The batched-LDLt route, summaries and downloads work on such a batch as they are; a call that needs the host-side
+ * integer artefacts (obgpu_get_symbolic, the PCG route) downloads the batch once and runs the host phase.  Band-reducing
+ * renumbering (meshed structures) is not applied in this mode. */
+int obgpu_batch_upload_device(obgpu_ctx*, const obgpu_batch_desc*);
 /* replace the per-case value arrays of the uploaded batch (same S and topology; L may change).
  * Host pointers; NULL = keep base values.  This is the per-step H2D traffic of a load-case sweep. */
 int obgpu_update_cases(obgpu_ctx*, int64_t n_cases, const double* case_nload_val, const double* case_eload_q,

@@ -21,6 +21,11 @@ static void copy_vec(std::vector<T>& dst, const T* src, int64_t n) {
   dst.assign(src, src + n);
 }
 }  // namespace obgpu
+namespace obgpu {
+int batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d);   // capi_devsym.cu
+int symbolic_device(obgpu_ctx* c);
+int materialize_host_batch(obgpu_ctx* c);
+}
 using namespace obgpu;
 
 extern "C" {
@@ -99,6 +104,14 @@ int obgpu_host_alloc(void** p, size_t bytes) {
 }
 int obgpu_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? OBGPU_OK : OBGPU_ECUDA; }
 
+static int upload_cases(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai);
+extern "C++" {
+namespace obgpu {
+int upload_cases_public(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai) {
+  return upload_cases(c, L, nl, q, eai);
+}
+}
+}
 static int upload_cases(obgpu_ctx* c, int64_t L, const double* nl, const double* q, const double* eai) {
   if (L < 1) return fail(c, OBGPU_EINVAL, "n_cases must be >= 1");
   c->L = L;
@@ -118,9 +131,17 @@ static int upload_cases(obgpu_ctx* c, int64_t L, const double* nl, const double*
   return OBGPU_OK;
 }
 
+int obgpu_batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d) {
+  if (!c || !d) return OBGPU_EINVAL;
+  OB_NEED_DEVICE(c);
+  return batch_upload_device(c, d);
+}
+
 int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   if (!c || !d) return OBGPU_EINVAL;
   OB_DEVICE(c);
+  c->device_batch_mode = false;
+  c->host_batch_valid = true;
   if (d->n_structures < 1) return fail(c, OBGPU_EINVAL, "n_structures must be >= 1");
   if (!d->node_off || !d->elem_off || !d->con_off || !d->nload_off || !d->eload_off)
     return fail(c, OBGPU_EINVAL, "offset arrays are mandatory");
@@ -226,6 +247,7 @@ int obgpu_symbolic(obgpu_ctx* c) {
   if (!c) return OBGPU_EINVAL;
   if (!c->uploaded) return fail(c, OBGPU_ESEQUENCE, "obgpu_symbolic before obgpu_batch_upload");
   OB_DEVICE(c);
+  if (c->device_batch_mode && !c->host_batch_valid) return symbolic_device(c);
   const auto t0 = std::chrono::steady_clock::now();
   std::string err;
   c->dev_batch = false;
@@ -265,6 +287,8 @@ int obgpu_symbolic(obgpu_ctx* c) {
     OB_CUDA(c, c->d_Ub.upload(c->sym.U_b, c->stream));
     OB_CUDA(c, cudaStreamSynchronize(c->stream));
   }
+  c->any_ub = false;
+  for (double v : c->sym.U_b) c->any_ub |= v != 0.0;
   c->t_symbolic_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return OBGPU_OK;
 }
@@ -293,8 +317,15 @@ int obgpu_get_offsets(const obgpu_ctx* c, int which, int64_t* out) {
   return OBGPU_OK;
 }
 
-int obgpu_get_symbolic(const obgpu_ctx* c, int which, int32_t* out) {
-  if (!c || !out || !c->sym.valid) return OBGPU_ESEQUENCE;
+int obgpu_get_symbolic(const obgpu_ctx* cc, int which, int32_t* out) {
+  if (!cc || !out || !cc->sym.valid) return OBGPU_ESEQUENCE;
+  if (cc->device_batch_mode && !cc->host_batch_valid) {  // a device batch: bring it to the host once, run the host phase
+    obgpu_ctx* m = const_cast<obgpu_ctx*>(cc);
+    int rc = materialize_host_batch(m);
+    if (rc == OBGPU_OK) rc = obgpu_symbolic(m);
+    if (rc != OBGPU_OK) return rc;
+  }
+  const obgpu_ctx* c = cc;
   const std::vector<int32_t>* v = nullptr;
   switch (which) {
     case OBGPU_SYM_DOF_NODE: v = &c->sym.dof_node; break;

@@ -7,6 +7,56 @@
 namespace obgpu {
 
 int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o);  // capi_sparse.cu
+int materialize_host_batch(obgpu_ctx* c);                     // capi_devsym.cu
+int build_frame_classes(obgpu_ctx* c, const std::vector<int32_t>& nf, const std::vector<int32_t>& nb, const std::vector<int32_t>& hbw);
+
+// Size classes of the warp-per-structure kernel: per-warp shared memory is sized for the largest structure a launch
+// serves, so structures are bucketed by their need (band + vectors, in doubles) and every class gets its own launch and
+// occupancy.  Inputs per structure: n_f, n_b and the half bandwidth the kernel will use.
+int build_frame_classes(obgpu_ctx* c, const std::vector<int32_t>& nf, const std::vector<int32_t>& nb, const std::vector<int32_t>& hbw) {
+  const int64_t S = int64_t(nf.size());
+  static const int64_t kClassLimit[] = {256, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2560, 3072, 4096, 6144, 8192,
+                                        12288, 16384, 24576, INT64_MAX};
+  constexpr int NCLS = int(sizeof(kClassLimit) / sizeof(kClassLimit[0]));
+  auto cls_of = [&](int64_t s) {
+    const int64_t need = int64_t(hbw[size_t(s)] + 1) * nf[size_t(s)] + 2 * int64_t(nf[size_t(s)]) + 2 * int64_t(nb[size_t(s)]);
+    int k = 0;
+    while (need > kClassLimit[k]) k++;
+    return k;
+  };
+  c->max_band = c->max_nf = c->max_nb = 0;
+  std::vector<uint8_t> cls;
+  cls.resize(size_t(S));
+  std::vector<int64_t> cnt(NCLS + 1, 0);
+  for (int64_t s = 0; s < S; s++) {
+    cls[size_t(s)] = uint8_t(cls_of(s));
+    cnt[cls[size_t(s)] + 1]++;
+    c->max_band = int(std::max<int64_t>(c->max_band, int64_t(hbw[size_t(s)] + 1) * nf[size_t(s)]));
+    c->max_nf = std::max(c->max_nf, nf[size_t(s)]);
+    c->max_nb = std::max(c->max_nb, nb[size_t(s)]);
+  }
+  for (int k = 0; k < NCLS; k++) cnt[k + 1] += cnt[k];
+  std::vector<int32_t> order;
+  order.resize(size_t(S));
+  c->frame_classes.clear();
+  std::vector<int64_t> pos(cnt.begin(), cnt.end() - 1);
+  for (int64_t s = 0; s < S; s++) order[size_t(pos[cls[size_t(s)]]++)] = int32_t(s);
+  for (int k = 0; k < NCLS; k++) {
+    if (cnt[k + 1] == cnt[k]) continue;
+    obgpu_ctx::FrameClass fc{cnt[k], cnt[k + 1], 0, 0, 0, 0};
+    for (int64_t i = cnt[k]; i < cnt[k + 1]; i++) {
+      const size_t s = size_t(order[size_t(i)]);
+      fc.max_band = int(std::max<int64_t>(fc.max_band, int64_t(hbw[s] + 1) * nf[s]));
+      fc.max_nf = std::max(fc.max_nf, nf[s]);
+      fc.max_nb = std::max(fc.max_nb, nb[s]);
+      fc.max_hb = std::max(fc.max_hb, hbw[s]);
+    }
+    c->frame_classes.push_back(fc);
+  }
+  OB_CUDA(c, c->d_frame_order.upload(order, c->stream));
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));  // order is a stack vector
+  return OBGPU_OK;
+}
 
 // Upload the batch arrays and the per-structure records once per (upload, symbolic).
 int ensure_device_batch(obgpu_ctx* c) {
@@ -129,39 +179,13 @@ int ensure_device_batch(obgpu_ctx* c) {
     c->max_nb = std::max(c->max_nb, m.nb);
   }
   OB_CUDA(c, c->d_meta.upload(meta, st));
-  // Size classes: per-warp shared memory is sized for the largest structure a launch serves, so structures are
-  // bucketed by their need (band + vectors, in doubles) and every class gets its own launch and occupancy.
-  static const int64_t kClassLimit[] = {256, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2560, 3072, 4096, 6144, 8192,
-                                        12288, 16384, 24576, INT64_MAX};
-  constexpr int NCLS = int(sizeof(kClassLimit) / sizeof(kClassLimit[0]));
-  auto cls_of = [&](const FrameMeta& m) {
-    const int64_t need = int64_t(m.hb + 1) * m.nf + 2 * int64_t(m.nf) + 2 * int64_t(m.nb);
-    int k = 0;
-    while (need > kClassLimit[k]) k++;
-    return k;
-  };
-  std::vector<int64_t> cnt(NCLS + 1, 0);
-  for (int64_t s = 0; s < hb.S; s++) cnt[cls_of(meta[s]) + 1]++;
-  for (int k = 0; k < NCLS; k++) cnt[k + 1] += cnt[k];
-  std::vector<int32_t> order(hb.S);
-  c->frame_classes.clear();
   {
-    std::vector<int64_t> pos(cnt.begin(), cnt.end() - 1);
-    for (int64_t s = 0; s < hb.S; s++) order[pos[cls_of(meta[s])]++] = int32_t(s);
-    for (int k = 0; k < NCLS; k++) {
-      if (cnt[k + 1] == cnt[k]) continue;
-      obgpu_ctx::FrameClass fc{cnt[k], cnt[k + 1], 0, 0, 0, 0};
-      for (int64_t i = cnt[k]; i < cnt[k + 1]; i++) {
-        const FrameMeta& m = meta[order[i]];
-        fc.max_band = std::max<int64_t>(fc.max_band, int64_t(m.hb + 1) * m.nf);
-        fc.max_nf = std::max(fc.max_nf, m.nf);
-        fc.max_nb = std::max(fc.max_nb, m.nb);
-        fc.max_hb = std::max(fc.max_hb, m.hb);
-      }
-      c->frame_classes.push_back(fc);
-    }
+    std::vector<int32_t> v_nf, v_nb, v_hb;
+    v_nf.resize(size_t(hb.S)); v_nb.resize(size_t(hb.S)); v_hb.resize(size_t(hb.S));
+    for (int64_t s = 0; s < hb.S; s++) { v_nf[size_t(s)] = meta[s].nf; v_nb[size_t(s)] = meta[s].nb; v_hb[size_t(s)] = meta[s].hb; }
+    const int rc = build_frame_classes(c, v_nf, v_nb, v_hb);
+    if (rc != OBGPU_OK) return rc;
   }
-  OB_CUDA(c, c->d_frame_order.upload(order, st));
   OB_CUDA(c, cudaStreamSynchronize(st));  // meta, order are stack vectors
   c->dev_batch = true;
   return OBGPU_OK;
@@ -174,9 +198,14 @@ static bool frame_kernel_fits(const obgpu_ctx* c) {
 int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   int rc = ensure_device_batch(c);
   if (rc != OBGPU_OK) return rc;
-  bool any_ub = false;
-  for (double v : c->sym.U_b) any_ub |= v != 0.0;
+  const bool any_ub = c->any_ub;
   if (o.method != OBGPU_BATCHED_LDLT || !frame_kernel_fits(c)) {
+    if (c->device_batch_mode && !c->host_batch_valid) {  // the sparse route plans on the host: bring the batch there once
+      rc = materialize_host_batch(c);
+      if (rc == OBGPU_OK) rc = obgpu_symbolic(c);
+      if (rc == OBGPU_OK) rc = ensure_device_batch(c);
+      if (rc != OBGPU_OK) return rc;
+    }
     if (o.method == OBGPU_BATCHED_LDLT)
       return fail(c, OBGPU_EUNSUPPORTED, "structure too large for the batched LDLt kernel: use a PCG method");
     if (any_ub)

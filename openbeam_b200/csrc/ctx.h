@@ -17,6 +17,14 @@ struct obgpu_ctx {
   obgpu::Symbolic sym;
   obgpu::TinyProgram prog;
   bool uploaded = false;
+  // device batch mode (obgpu_batch_upload_device, capi_devsym.cu): the arrays live in HBM only, K3 runs as kernels
+  bool device_batch_mode = false, host_batch_valid = true;
+  bool any_ub = false;                            // some prescribed displacement is non-zero
+  obgpu::DevBuf<int64_t> d_off_node, d_off_elem, d_off_con, d_off_nload, d_off_eload, d_dof_off;  // [S+1]
+  obgpu::DevBuf<uint32_t> d_con_node, d_nload_node, d_eload_elem;
+  obgpu::DevBuf<uint8_t> d_con_dof, d_nload_dof, d_sym_mask;
+  obgpu::DevBuf<double> d_con_val, d_sym_cval;
+  obgpu::DevBuf<int32_t> d_sym_counts, d_sym_cursor, d_sym_error;
   int64_t L = 1;
   bool has_case_nl = false, has_case_q = false, has_case_eai = false;
 

@@ -170,6 +170,28 @@ cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t
 cudaError_t launch_inv_diag(int64_t nf, const int32_t* ff_diag, const double* ff_val, double* minv, cudaStream_t st);
 cudaError_t launch_reactions(const SparseDev& d, const double* U_f, double* F_b, cudaStream_t st);
 
+// ---- device-side symbolic phase (kernels_symbolic.cu) ----
+enum { SYM_E_ELEM_NODE = 1, SYM_E_UNINIT, SYM_E_ELEM_TYPE, SYM_E_ZERO_LEN, SYM_E_NONPLANAR, SYM_E_CONSTRAINT, SYM_E_NLOAD,
+       SYM_E_ELOAD, SYM_E_LOAD_DIR, SYM_E_LOAD_ELEM, SYM_E_NO_DOFS };
+struct SymDev {
+  int64_t S;
+  const int64_t *node_off, *elem_off, *con_off, *nload_off, *eload_off;  // [S+1]
+  const double2* node_xy; const double* node_rotz;                         // node_rotz null = identity frames
+  const uint2* elem_nodes; const uint8_t* elem_type; const double* elem_EAI;
+  const uint32_t* con_node; const uint8_t* con_dof; const double* con_val;
+  const uint32_t* nload_node; const uint8_t* nload_dof;
+  const uint32_t* eload_elem; const uint8_t* eload_type; const double* eload_dir; const double* eload_q2;  // type null = uniform
+  uint8_t* node_mask;      // [Ntot] bits 0..2: DX, DY, RZ exist; bits 3..5: constrained
+  double* node_cval;       // [3*Ntot] prescribed values of the constrained DOFs
+  int32_t* counts;         // [S][4] n, n_f, n_b, half bandwidth
+  int64_t *dof_off, *free_off, *bnd_off;  // [S+1]
+  int32_t *node_slot, *nload_slot, *el_ptr, *el_order, *el_cursor;
+  FrameMeta* meta;
+  double* U_b; uint8_t* bnd_dofid;
+  int32_t* error;          // [0] first error code (SYM_E_*), [1] its structure, [2] any U_b != 0
+};
+cudaError_t launch_symbolic_device(const SymDev& d, cudaStream_t st);
+
 struct SummaryArgs {
   int64_t L, S, nf_tot, nb_tot;
   const int64_t* free_off;   // [S+1]

@@ -34,7 +34,7 @@ SIZE_NAMES = ("S", "L", "Ntot", "Etot", "n_tot", "nf_tot", "nb_tot", "T_tot", "n
 # every symbol include/obgpu.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = (
     "obgpu_create", "obgpu_destroy", "obgpu_last_error", "obgpu_status_string", "obgpu_host_alloc",
-    "obgpu_host_free", "obgpu_batch_upload", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
+    "obgpu_host_free", "obgpu_batch_upload", "obgpu_batch_upload_device", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
     "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host", "obgpu_solve_cases_host_flags",
     "obgpu_summaries_device", "obgpu_get_timings", "obgpu_pcg_info", "obgpu_profile_kernel", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
@@ -92,6 +92,7 @@ def lib():
         L.obgpu_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
         L.obgpu_host_free.argtypes = [vp]
         L.obgpu_batch_upload.argtypes = [vp, C.POINTER(BatchDesc)]
+        L.obgpu_batch_upload_device.argtypes = [vp, C.POINTER(BatchDesc)]
         L.obgpu_update_cases.argtypes = [vp, i64, vp, vp, vp]
         for f in ("obgpu_symbolic", "obgpu_assemble", "obgpu_stress", "obgpu_synchronize"):
             getattr(L, f).argtypes = [vp]
@@ -270,7 +271,9 @@ class Context:
             raise ObgpuError(rc, msg)
 
     # ---- upload ----
-    def upload(self, batch, n_cases=1, case_nload_val=None, case_eload_q=None, case_elem_EAI=None):
+    def upload(self, batch, n_cases=1, case_nload_val=None, case_eload_q=None, case_elem_EAI=None, device=False):
+        """batch: a Structure, a list of them, or a packed dict (pack_batch / workloads.c3_batch).  device=True:
+        obgpu_batch_upload_device — arrays straight to HBM, symbolic phase as device kernels (many small structures)."""
         if isinstance(batch, Structure):
             batch = pack_batch([batch])
         elif isinstance(batch, (list, tuple)):
@@ -289,7 +292,8 @@ class Context:
         d.case_eload_q = None if cq is None else cq.ctypes.data
         d.case_elem_EAI = None if ce is None else ce.ctypes.data
         self._keep = (batch, cn, cq, ce)
-        self._chk(lib().obgpu_batch_upload(self.h, C.byref(d)))
+        fn = lib().obgpu_batch_upload_device if device else lib().obgpu_batch_upload
+        self._chk(fn(self.h, C.byref(d)))
         self._keep = None
         return self
 

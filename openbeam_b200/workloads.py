@@ -114,6 +114,101 @@ def c3_frame(index) -> Structure:
                      np.tile([0.0, -1.0, 0.0], (len(ee), 1)))
 
 
+def c3_batch(first, count, pinned=None):
+    """Structures [first, first + count) of config C3 as ONE packed batch (the dict obgpu.pack_batch returns), generated
+    with array operations — the same structures, bit for bit, as [c3_frame(i) for i in range(first, first + count)],
+    in that order.  ``pinned``: an allocator ``(shape, dtype) -> ndarray`` (obgpu.pinned_empty) for the large arrays."""
+    alloc = pinned or (lambda shape, dt: np.empty(shape, dt))
+    idx = np.arange(first, first + count, dtype=np.uint64)
+    b = np.zeros(count, np.int64)
+    s = np.zeros(count, np.int64)
+    todo = np.ones(count, bool)
+    t = 0
+    while todo.any():
+        bb = 1 + (uniform01(30 + t, idx[todo]) * 5).astype(np.int64)
+        ss = 1 + (uniform01(60 + t, idx[todo]) * 6).astype(np.int64)
+        ok = (ss * (2 * bb + 1) >= 10) & (ss * (2 * bb + 1) <= 60)
+        w = np.nonzero(todo)[0]
+        b[w[ok]], s[w[ok]] = bb[ok], ss[ok]
+        todo[w[ok]] = False
+        t += 1
+    nN, nE = (b + 1) * (s + 1), s * (2 * b + 1)
+    nC, nNL, nEL = 3 * (b + 1), s, s * b
+
+    def off(c):
+        o = np.zeros(count + 1, np.int64)
+        np.cumsum(c, out=o[1:])
+        return o
+
+    node_off, elem_off, con_off, nload_off, eload_off = off(nN), off(nE), off(nC), off(nNL), off(nEL)
+    Nt, Et, Ct, NLt, ELt = (int(o[-1]) for o in (node_off, elem_off, con_off, nload_off, eload_off))
+    node_xy = alloc((Nt, 2), np.float64)
+    elem_nodes = alloc((Et, 2), np.uint32)
+    elem_type = alloc((Et,), np.uint8)
+    elem_EAI = alloc((Et, 3), np.float64)
+    con_node, con_dof, con_val = alloc((Ct,), np.uint32), alloc((Ct,), np.uint8), alloc((Ct,), np.float64)
+    nload_node, nload_dof, nload_val = alloc((NLt,), np.uint32), alloc((NLt,), np.uint8), alloc((NLt,), np.float64)
+    eload_elem, eload_q, eload_dir = alloc((ELt,), np.uint32), alloc((ELt,), np.float64), alloc((ELt, 3), np.float64)
+    con_val[:] = 0.0
+    nload_dof[:] = DX
+    eload_dir[:] = (0.0, -1.0, 0.0)
+    csec = IPE[(uniform01(102, idx) * len(IPE)).astype(np.int64)]
+    bsec = IPE[(uniform01(103, idx) * len(IPE)).astype(np.int64)]
+    for bv in range(1, 6):
+        for sv in range(1, 7):
+            m = np.nonzero((b == bv) & (s == sv))[0]
+            if len(m) == 0:
+                continue
+            i64 = idx[m]
+            k = len(m)
+            W = uniform(100, (i64 * np.uint64(8))[:, None] + np.arange(bv, dtype=np.uint64)[None, :], 3.0, 6.0)
+            H = uniform(101, (i64 * np.uint64(8))[:, None] + np.arange(sv, dtype=np.uint64)[None, :], 2.5, 4.0)
+            xs = np.concatenate([np.zeros((k, 1)), np.cumsum(W, 1)], 1)            # [k, b+1]
+            ys = np.concatenate([np.zeros((k, 1)), np.cumsum(H, 1)], 1)            # [k, s+1]
+            nn = (bv + 1) * (sv + 1)
+            rows = node_off[m][:, None] + np.arange(nn)[None, :]
+            jj, ii = np.divmod(np.arange(nn), bv + 1)
+            node_xy[rows, 0] = xs[:, ii]
+            node_xy[rows, 1] = ys[:, jj]
+            # elements: per storey j = 1..s the b+1 columns then the b beams
+            en = np.zeros((sv * (2 * bv + 1), 2), np.uint32)
+            is_beam = np.zeros(sv * (2 * bv + 1), bool)
+            key = np.zeros(sv * (2 * bv + 1), np.uint64)       # j*8 + i of a beam
+            e = 0
+            for j in range(1, sv + 1):
+                for i in range(bv + 1):
+                    en[e] = ((j - 1) * (bv + 1) + i, j * (bv + 1) + i); e += 1
+                for i in range(bv):
+                    en[e] = (j * (bv + 1) + i, j * (bv + 1) + i + 1); is_beam[e] = True; key[e] = j * 8 + i; e += 1
+            erows = elem_off[m][:, None] + np.arange(len(en))[None, :]
+            elem_nodes[erows] = en[None, :, :]
+            beams = np.nonzero(is_beam)[0]
+            u = uniform01(104, (i64 * np.uint64(64))[:, None] + key[beams][None, :])
+            ty = np.where(u < 0.6, RR, np.where(u < 0.75, RA, np.where(u < 0.9, AR, AA))).astype(np.uint8)
+            et = np.full((k, len(en)), RR, np.uint8)
+            et[:, beams] = ty
+            elem_type[erows] = et
+            eai = np.empty((k, len(en), 3))
+            eai[:, :, 0] = E_STEEL
+            eai[:, :, 1:] = csec[m][:, None, :]
+            eai[:, beams, 1:] = bsec[m][:, None, :]
+            elem_EAI[erows] = eai
+            crows = con_off[m][:, None] + np.arange(3 * (bv + 1))[None, :]
+            con_node[crows] = np.repeat(np.arange(bv + 1), 3)[None, :]
+            con_dof[crows] = np.tile([DX, DY, RZ], bv + 1)[None, :]
+            lrows = nload_off[m][:, None] + np.arange(sv)[None, :]
+            nload_node[lrows] = (np.arange(1, sv + 1) * (bv + 1))[None, :]
+            nload_val[lrows] = uniform(106, (i64 * np.uint64(8))[:, None] + np.arange(sv, dtype=np.uint64)[None, :], 0.0, 20e3)
+            qrows = eload_off[m][:, None] + np.arange(len(beams))[None, :]
+            eload_elem[qrows] = beams[None, :]
+            eload_q[qrows] = uniform(105, (i64 * np.uint64(64))[:, None] + key[beams][None, :], 5e3, 30e3)
+    return dict(S=count, node_off=node_off, elem_off=elem_off, con_off=con_off, nload_off=nload_off, eload_off=eload_off,
+                node_xy=node_xy.reshape(-1), elem_nodes=elem_nodes.reshape(-1), elem_type=elem_type,
+                elem_EAI=elem_EAI.reshape(-1), con_node=con_node, con_dof=con_dof, con_val=con_val, nload_node=nload_node,
+                nload_dof=nload_dof, nload_val=nload_val, eload_elem=eload_elem, eload_q=eload_q,
+                eload_dir=eload_dir.reshape(-1), node_rotz=None, eload_type=None, eload_q2=None)
+
+
 def grid_frame(nx, ny, etype=RR, seed_index=0, section=(E_STEEL, 28.5e-4, 1940e-8), spacing=1.0) -> Structure:
     """Configs C4/C5: nx x ny node grid, horizontal + vertical members of ``etype``, bottom row fixed,
     UDL 9810 N/m down on horizontal members, lateral nodal loads N(0, 5e3) (Box-Muller on the counter RNG)."""

@@ -532,3 +532,5 @@ static std::shared_ptr<CElement> createElementByType(int t) {
 #include "ob_assemble.ipp"  // updateNodeConnections / updateListDoFs / assembleProblem / equivalent loads
 #include "ob_solve.ipp"     // solveStatic / postProcCalcStress
 #include "ob_capi.ipp"      // extern "C" surface
+
+#include "ob_batch.ipp"

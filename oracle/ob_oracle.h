@@ -4,10 +4,13 @@
  *   assembleProblem()      libopenbeam/src/CFiniteElementProblem_assemble.cpp:37-437
  *   solveStatic()          libopenbeam/src/CFiniteElementProblem_solver_static.cpp:29-219
  *   postProcCalcStress()   libopenbeam/src/CFiniteElementProblem_postproc_stress.cpp:32-183
- * written because the reference itself cannot be compiled in this image (it needs
- * MRPT >= 2.4 and Eigen, both absent).  PARITY UNPINNED: the reference
- * ships no tests or golden vectors for this path; the oracle is pinned instead by
- * closed-form statics and independent numerics (tests/test_oracle_*.py).
+ * The reference's cmake build needs MRPT >= 2.4 and Eigen, both absent from this image, and it ships no tests or golden
+ * vectors for this path.  PARITY PINNED TO THE REFERENCE'S OWN CODE: oracle/_ref/libob_ref.so is libopenbeam's unmodified
+ * hot-path sources compiled where they lie against header stand-ins for the Eigen/MRPT subset they use
+ * (oracle/Makefile.ref, oracle/ref_shim/, oracle/ref_harness.cpp) and exposes THIS SAME C ABI; tests/test_reference_pin.py
+ * holds the restatement to it (integer artefacts and assembled matrices bit-exact, results to 1e-12) live and through
+ * committed vectors (tests/golden/reference/).  Also pinned by closed-form statics and independent numerics
+ * (tests/test_oracle.py).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
  * legs may load this library.  The product (openbeam_b200/) never does.
@@ -86,6 +89,15 @@ int64_t obo_get_f64(const obo_problem*, int which, double* out, int64_t cap);
  * Returns wall seconds spent inside the threaded region, <0 on error. */
 double obo_run_cases(const obo_problem* tmpl, int64_t n_cases, const double* nl_val, const double* el_q,
                      const double* elem_EAI, int n_threads, double* U_f, double* F_b, double* stress);
+
+/* CPU-baseline driver for a packed batch of DIFFERENT structures (obgpu_batch_desc layout, config C3): per structure a
+ * full problem set-up + solveStatic + postProcCalcStress, structures dealt to n_threads host threads; summ (nullable)
+ * receives {max|U_f|, sum F_b} per structure.  Returns wall seconds, <0 on error.  (oracle/ob_batch.ipp) */
+double obo_run_batch(int64_t S, const int64_t* node_off, const int64_t* elem_off, const int64_t* con_off,
+                     const int64_t* nload_off, const int64_t* eload_off, const double* node_xy, const uint32_t* elem_nodes,
+                     const uint8_t* elem_type, const double* elem_EAI, const uint32_t* con_node, const uint8_t* con_dof,
+                     const double* con_val, const uint32_t* nl_node, const uint8_t* nl_dof, const double* nl_val,
+                     const uint32_t* el_elem, const double* el_q, const double* el_dir, int n_threads, double* summ);
 
 #ifdef __cplusplus
 }

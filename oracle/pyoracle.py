@@ -28,7 +28,7 @@ class OracleError(RuntimeError):
 def build(force=False):
     so = os.path.join(_HERE, "libob_oracle.so")
     srcs = [os.path.join(_HERE, f) for f in
-            ("ob_oracle.cpp", "ob_assemble.ipp", "ob_solve.ipp", "ob_capi.ipp", "ob_oracle.h")]
+            ("ob_oracle.cpp", "ob_assemble.ipp", "ob_solve.ipp", "ob_capi.ipp", "ob_batch.ipp", "ob_oracle.h")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "libob_oracle.so"])
     return so
@@ -67,7 +67,23 @@ def _bind(L):
     L.obo_get_f64.restype = i64
     L.obo_run_cases.argtypes = [vp, i64, dp, dp, dp, C.c_int, dp, dp, dp]
     L.obo_run_cases.restype = C.c_double
+    L.obo_run_batch.argtypes = [i64] + [dp] * 18 + [C.c_int, dp]
+    L.obo_run_batch.restype = C.c_double
     return L
+
+
+def run_batch(batch, n_threads=1, reference=False, want_summaries=False):
+    """CPU baseline on a packed batch of different structures (obgpu.pack_batch / workloads.c3_batch dict): one problem
+    set-up + solveStatic + postProcCalcStress per structure.  Returns (seconds, summaries [S,2] or None)."""
+    L = ref_lib() if reference else lib()
+    S = batch["S"]
+    summ = np.zeros((S, 2)) if want_summaries else None
+    keys = ("node_off", "elem_off", "con_off", "nload_off", "eload_off", "node_xy", "elem_nodes", "elem_type", "elem_EAI",
+            "con_node", "con_dof", "con_val", "nload_node", "nload_dof", "nload_val", "eload_elem", "eload_q", "eload_dir")
+    dt = L.obo_run_batch(S, *[_p(np.ascontiguousarray(batch[k])) for k in keys], n_threads, _p(summ))
+    if dt < 0:
+        raise OracleError("obo_run_batch failed")
+    return dt, summ
 
 
 def ref_lib():
@@ -84,34 +100,12 @@ def ref_lib():
 def lib():
     global _LIB
     if _LIB is None:
-        L = C.CDLL(build())
-        vp, i64, dp = C.c_void_p, C.c_int64, C.c_void_p
-        L.obo_create.restype = vp
-        L.obo_create.argtypes = [i64, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp, i64, dp, dp, dp]
-        L.obo_destroy.argtypes = [vp]
-        L.obo_set_load_values.argtypes = [vp, dp, dp]
-        L.obo_set_eload_kinds.argtypes = [vp, dp, dp]
-        L.obo_set_elem_EAI.argtypes = [vp, dp]
-        L.obo_assemble.argtypes = [vp, C.c_int]
-        L.obo_solve_static.argtypes = [vp, C.c_int]
-        L.obo_stress.argtypes = [vp]
-        L.obo_last_error.argtypes = [vp]
-        L.obo_last_error.restype = C.c_char_p
-        L.obo_get_sizes.argtypes = [vp, dp]
-        L.obo_get_i64.argtypes = [vp, C.c_int, dp, i64]
-        L.obo_get_i64.restype = i64
-        L.obo_get_f64.argtypes = [vp, C.c_int, dp, i64]
-        L.obo_get_f64.restype = i64
-        L.obo_run_cases.argtypes = [vp, i64, dp, dp, dp, C.c_int, dp, dp, dp]
-        L.obo_run_cases.restype = C.c_double
-        _LIB = L
+        _LIB = _bind(C.CDLL(build()))
     return _LIB
 
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
-
-
 
 
 class OracleProblem:

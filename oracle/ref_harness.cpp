@@ -367,3 +367,5 @@ double obo_run_cases(const obo_problem* tmpl, int64_t n_cases, const double* nl_
 }
 
 }  // extern "C"
+
+#include "ob_batch.ipp"
