@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--cases", type=int, default=1_000_000, help="load cases per GPU per step")
     ap.add_argument("--per-case-section", action="store_true", help="variant C2b: per-case A, Iz sweep")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="root", choices=["root", "all"],
+                    help="c2, N > 1: the job's one exchange — a gather of the summaries to rank 0 (north_star) or an all-gather")
     ap.add_argument("--full-stress", action="store_true",
                     help="c2: six-component stress records (440 B/case, the r01 configuration) instead of compact ones")
     ap.add_argument("--config", default="c2", choices=["c2", "c3", "c4", "c5"])
@@ -80,10 +82,10 @@ def config_dict(args, world):
                     "each case = full assembleProblem+solveStatic(LDLt)+postProcCalcStress" %
                     (args.cases, "; per-case section sweep" if args.per_case_section else ""),
         "cases_per_gpu": args.cases, "n_dof": N_DOF, "n_free": 6, "n_bounded": 6, "elements": 3,
-        "parallelism": "independent load cases sharded over %d GPU(s), no data-path collective; one final "
-                       "all-gather of the 32-byte per-case summaries inside the timed region (peer stores of the last "
-                       "step's kernel over NVLink + device barrier; NCCL all-gather when symmetric memory is "
-                       "unavailable)" % world,
+        "parallelism": "independent load cases sharded over %d GPU(s), no data-path collective; one final %s of the "
+                       "32-byte per-case summaries of the last step inside the timed region (peer stores of the last "
+                       "step's kernel over NVLink + device barrier; NCCL when symmetric memory is unavailable)"
+                       % (world, "gather to rank 0" if args.gather == "root" else "all-gather"),
         "l2_policy": "no flush: per-step inputs+outputs (%.0f MB) exceed the 126 MB L2" %
                      (args.cases * (ALG_BYTES_PER_CASE + 48 + 36) / 1e6),
     }
@@ -268,11 +270,20 @@ def ours_arm(args, rank, local_rank, world):
         ctx.summaries_device(summ.data_ptr())    # per-case {max|U|, sum Fb_x, sum Fb_y, info}: no launch when the
                                                  # solve kernel already wrote them (a 2nd kernel on the fallback path)
 
+    root_only = args.gather == "root"
+
     def final_gather():
         # the only collective of the job (north_star: "a final NCCL gather of reaction and displacement
         # summaries"): once, after the last step; the solves themselves exchange nothing
         if world > 1:
-            sharding.gather_summaries(summ, gathered)
+            if root_only:
+                dist.gather(summ, list(gathered.view(world, L, 4).unbind(0)) if rank == 0 else None, dst=0)
+            else:
+                sharding.gather_summaries(summ, gathered)
+
+    # peer-store destinations of the last step's kernel: this rank's block inside rank 0's gathered array only (gather), or
+    # inside every rank's (all-gather)
+    peer_slots = None if peer is None else ([peer.slots[0]] if root_only else peer.slots)
 
     def run_steps(n):
         """n steps and the job's one exchange.  With symmetric memory the LAST step's kernel also stores its summaries
@@ -285,7 +296,7 @@ def ours_arm(args, rank, local_rank, world):
             return
         for _ in range(n - 1):
             step()
-        ctx.bind_summary_peers(peer.slots)
+        ctx.bind_summary_peers(peer_slots)
         step()
         ctx.bind_summary_peers([])
         peer.fence()
@@ -296,8 +307,8 @@ def ours_arm(args, rank, local_rank, world):
             torch.cuda.synchronize(dev)
             final_gather()
             torch.cuda.synchronize(dev)
-            if not torch.equal(gathered, peer.buf):
-                raise RuntimeError("peer-store gather differs from the NCCL all-gather")
+            if (rank == 0 or not root_only) and not torch.equal(gathered, peer.buf):
+                raise RuntimeError("peer-store gather differs from the NCCL gather")
         barrier()
         sampler = ClockSampler(local_rank) if rank == 0 else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -308,11 +319,41 @@ def ours_arm(args, rank, local_rank, world):
                 peer.fence()
             else:
                 dist.all_reduce(torch.zeros(1, device=dev))
+        def line_up():
+            if world > 1:
+                if peer is not None:
+                    peer.fence()
+                else:
+                    dist.all_reduce(torch.zeros(1, device=dev))
+
+        def timed_region(n_steps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            line_up()
+            a.record(ext)
+            run_steps(n_steps)
+            b.record(ext)
+            return a, b
+
         e0.record(ext)
         run_steps(K)
         e1.record(ext)
         barrier()
-        ms_total = e0.elapsed_time(e1)
+        first_ms = e0.elapsed_time(e1)
+        if world > 1:   # every rank must run the same number of regions (each holds device-side barriers)
+            fm = torch.tensor([first_ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(fm, op=dist.ReduceOp.MAX)
+            first_ms = float(fm.item())
+        # The K-step region lasts ~1.5 ms: it is repeated until >= 50 ms of device time have been timed, so that clock
+        # samples land inside timed work; the reported figure is the MEDIAN region (each = K steps + the one exchange)
+        reps = int(min(200, max(1, np.ceil(50.0 / max(first_ms, 1e-3)))))
+        evs = [timed_region(K) for _ in range(reps)]
+        barrier()
+        region_ms = sorted([first_ms] + [a.elapsed_time(b) for a, b in evs])
+        ms_total = region_ms[len(region_ms) // 2]
+        # the same job with ONE step: 1M cases per GPU solved once + their gather (nothing amortised)
+        evs1 = [timed_region(1) for _ in range(30)]
+        barrier()
+        single_ms = sorted(a.elapsed_time(b) for a, b in evs1)[15]
         # dominant kernel alone: CUDA-event pair around each fused-kernel launch (obgpu_get_timings)
         kern_ms = []
         for _ in range(K):
@@ -336,10 +377,10 @@ def ours_arm(args, rank, local_rank, world):
         clocks = sampler.stop() if sampler else None
     if h_info.any():
         raise SystemExit("bench.py: a system reported a non-positive pivot")
-    t = torch.tensor([ms_total, e2e_s, float(np.mean(kern_ms))], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms_total, e2e_s, float(np.mean(kern_ms)), single_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_s, kern_avg_ms = t.tolist()
+    ms_total, e2e_s, kern_avg_ms, single_ms = t.tolist()
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
@@ -369,6 +410,15 @@ def ours_arm(args, rank, local_rank, world):
             "e2e": {"value": world * L * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes,
                     "d2h_bytes_per_step": out_bytes,
                     "api": "obgpu_solve_cases_host (pinned host buffers in and out, chunked over 3 streams)"},
+            "timed_regions": {"count": len(region_ms), "ms_min": region_ms[0], "ms_median": region_ms[len(region_ms) // 2],
+                              "ms_max": region_ms[-1], "note": "value = world*cases*steps / median region"},
+            "single_pass_job": {"value": world * L / (single_ms * 1e-3), "unit": UNIT, "ms": single_ms,
+                                "what": "ONE step (every GPU solves its cases once) + the gather of all its summaries, "
+                                        "median of 30; the K-step figure above exchanges the summaries of its last step "
+                                        "only, i.e. 1/%d summary per counted solve" % K},
+            "gather": ("none (1 GPU)" if world == 1 else
+                       ("gather to rank 0" if root_only else "all-gather") +
+                       (": peer stores of the last step's kernel over NVLink (symmetric memory)" if peer is not None else ": NCCL")),
             "gpu_launches": int(K * launches_per_step), "e2e_launches_per_step": int(e2e_launches),
             "clocks": clocks,
         }
