@@ -41,8 +41,8 @@ def demo2(bis=False):
 
 def demo3_frame(variant="fixed"):
     """demo3_frame.yaml:30-51; variants: 'slider' (demo3_frame_slider.yaml:42-43, node 3 only DY),
-    'tilted_slider' (demo3_frame_tilted_slider.yaml:33, node 3 rot_z 30)."""
-    L, H = 4.0, 2.0
+    'tilted_slider' (demo3_frame_tilted_slider.yaml:13-14,33: H = 3, node 3 rot_z 30)."""
+    L, H = 4.0, (3.0 if variant == "tilted_slider" else 2.0)
     n3 = (L, 0, 30.0) if variant == "tilted_slider" else (L, 0)
     nodes = [(0, 0), (0, H), (L, H), n3]
     elements = [("BEAM2D_RR", 0, 1, "IPE200"), ("BEAM2D_RR", 1, 2, "IPE200"), ("BEAM2D_RR", 2, 3, "IPE200")]
@@ -138,6 +138,21 @@ def springs_and_slider():
                            [(0, 4000.0, DOWN), (1, "TEMPERATURE", 25.0)])
 
 
+def old_demo3():
+    """old_demo3.yaml:13-58 — textbook frame with a 135-degree rotated support frame and two 1e20 penalty springs tying
+    the coincident nodes 2 and 6 (cond(K_ff) ~ 1e13: the reference's own result carries only a few digits)."""
+    Gv, D = 9.81, 2.0
+    P, Q = Gv * 1000, Gv * 100
+    sec = dict(IPE200)
+    sec.update({"SXY": (0.0, 1e20, 0.0), "STOR": (1e20, 0.0, 0.0)})
+    nodes = [(0, 0, 135.0), (D, D), (2 * D, D), (3 * D, D), (0, D), (2 * D, 0), (2 * D, D)]
+    elements = [("BEAM2D_RR", 0, 1, "IPE200"), ("BEAM2D_RR", 1, 2, "IPE200"), ("BEAM2D_RR", 3, 6, "IPE200"),
+                ("BEAM2D_AA", 5, 6, "IPE200"), ("BEAM2D_RR", 4, 1, "IPE200"), ("SPRING_XY", 2, 6, "SXY"),
+                ("SPRING_TORSION", 2, 6, "STOR")]
+    cons = [(0, "DYRZ"), (5, "DXDY"), (3, "DX")]
+    return build_structure(nodes, elements, sec, cons, [(6, "DX", -P)], [(4, Q, DOWN)])
+
+
 def mechanism():
     """demo1 without the DY support at node 1 -> singular K_ff (the reference throws
     'Ill-conditioned matrix. Too few restrictions?', solver_static.cpp:98-105)."""
@@ -165,5 +180,7 @@ ALL = {
     "load_kinds": load_kinds,
     "springs_and_slider": springs_and_slider,
 }
+# ill-conditioned on purpose (1e20 penalty springs): integer artefacts and equilibrium are checked, not 1e-9 value parity
+ILL_CONDITIONED = {"old_demo3": old_demo3}
 # fixtures without nodal rotated frames (U_b = 0, identity node frames): the round-1 GPU scope
 PLAIN = [k for k in ALL if "tilted" not in k and "tilded" not in k]
