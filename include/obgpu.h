@@ -208,6 +208,11 @@ int obgpu_bind_summary_peers(obgpu_ctx*, int n, double* const* bufs);
  * out[0] symbolic (host), [1] assembleProblem, [2] solveStatic.2_solve, [3] postProcCalcStress, [4] H2D, [5] D2H,
  * [6] kernel launches in the last solve/assemble call (count), [7] PCG iterations of the last solve */
 int obgpu_get_timings(const obgpu_ctx*, double out[8]);
+/* StaticSolverOptions::nonLinearIterative support (solver_static.cpp:139-193).  The reference restores the node poses after
+ * its 40 passes, so the postProcCalcStress() that follows reads element LENGTHS from the restored poses while orientations,
+ * displacements and fixed-end terms are those of the last pass.  node_xy [2*Ntot] = the poses to take the stress lengths
+ * from (NULL clears it; every upload clears it); the next obgpu_solve_static runs on the batched-LDLt route with it. */
+int obgpu_set_stress_length_poses(obgpu_ctx*, const double* node_xy);
 /* the last PCG solve (sparse route): out[0] iterations summed over the structures, [1] worst TRUE relative residual
  * ||F_f - K_ff U_f||_2 / ||F_f||_2 recomputed from U_f at exit (the reference's SimplicialLLT branch has no such figure:
  * it does not even check info(), solver_static.cpp:117-128), [2] restarts from the true residual, [3] multigrid levels */

@@ -212,7 +212,9 @@ class CStructureProblem {
       const std::vector<double> xy0 = node_xy_, rz0 = node_rotz_;
       try {
         for (unsigned nIter = 0; nIter < 40; nIter++) {
-          solve_pass(opts);
+          // solver_static.cpp:190-193 restores the poses BEFORE the caller's postProcCalcStress: the last pass's stresses
+          // take their element lengths from the original poses, everything else from the pass itself
+          solve_pass(opts, nIter == 39 ? xy0.data() : nullptr);
           const auto z = sizes();
           std::vector<int32_t> f(z[5]), nd(z[4]), id(z[4]);
           std::vector<num_t> U(z[5]);
@@ -262,8 +264,9 @@ class CStructureProblem {
   obgpu_ctx* ctx() { return ctx_; }
 
  private:
-  void solve_pass(const StaticSolverOptions& opts) {
+  void solve_pass(const StaticSolverOptions& opts, const double* stress_length_poses = nullptr) {
     updateAll();
+    if (stress_length_poses) check(obgpu_set_stress_length_poses(ctx_, stress_length_poses));
     obgpu_solve_opts o;
     o.method = opts.algorithm == StaticSolverAlgorithm::GPU_PCG_Jacobi ? OBGPU_PCG_JACOBI
              : opts.algorithm == StaticSolverAlgorithm::GPU_PCG_MG   ? OBGPU_PCG_MG

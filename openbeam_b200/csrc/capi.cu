@@ -215,7 +215,8 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
                                            ? "Unsupported element type for load 'CLoadDistributedTriangular'"
                                            : "Unsupported element type for load 'CLoadConcentratedForce'");
         if (lt == OBGPU_LOAD_CONCENTRATED) {
-          const int64_t n0 = hb.node_off[s];
+          const int64_t n0 = hb.node_off[s], Ns = hb.node_off[s + 1] - n0;
+          if (hb.elem_nodes[2 * e] >= Ns || hb.elem_nodes[2 * e + 1] >= Ns) continue;  // reported by the symbolic phase
           const double* p0 = &hb.node_xy[2 * (n0 + hb.elem_nodes[2 * e])];
           const double* p1 = &hb.node_xy[2 * (n0 + hb.elem_nodes[2 * e + 1])];
           const double ax = p1[0] - p0[0], ay = p1[1] - p0[1], len = std::sqrt(ax * ax + ay * ay);
@@ -233,6 +234,7 @@ int obgpu_batch_upload(obgpu_ctx* c, const obgpu_batch_desc* d) {
   c->dev_mg = false;
   c->assembled = false;
   c->prog = TinyProgram();
+  c->have_xy_len = false;
   return upload_cases(c, hb.L, d->case_nload_val, d->case_eload_q, d->case_elem_EAI);
 }
 

@@ -100,6 +100,7 @@ int batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d) {
   c->dev_mg = false;
   c->assembled = false;
   c->prog = TinyProgram();
+  c->have_xy_len = false;
   const int rc = upload_cases_public(c, hb.L, d->case_nload_val, d->case_eload_q, d->case_elem_EAI);
   if (rc != OBGPU_OK) return rc;
   OB_CUDA(c, cudaStreamSynchronize(st));  // the caller's buffers may be reused as soon as this returns

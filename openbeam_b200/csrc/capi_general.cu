@@ -237,6 +237,7 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   a.eload_q2 = c->hb.has_load_kinds ? c->d_eload_q2.p : nullptr;
   a.U_b = any_ub ? c->d_Ub.p : nullptr;
   a.node_rot = c->hb.has_rotz ? c->d_node_rot.p : nullptr;
+  a.node_xy_len = c->have_xy_len ? reinterpret_cast<const double2*>(c->d_node_xy_len.p) : nullptr;
   a.case_nl = c->has_case_nl ? c->d_case_nl.p : nullptr;
   a.case_q = c->has_case_q ? c->d_case_q.p : nullptr;
   a.case_eai = c->has_case_eai ? c->d_case_eai.p : nullptr;

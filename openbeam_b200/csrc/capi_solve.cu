@@ -69,7 +69,7 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
   c->last_method = o.method; c->last_rtol = o.rtol; c->last_max_iter = o.max_iter;
   const bool want_compact = o.with_stress && (o.flags & OBGPU_SOLVE_COMPACT_STRESS);
   c->have_stress_c = false;
-  if (o.method == OBGPU_BATCHED_LDLT && c->prog.valid) {
+  if (o.method == OBGPU_BATCHED_LDLT && c->prog.valid && !c->have_xy_len) {
     rc = alloc_results(c, c->L, o.with_stress != 0 && !want_compact);
     if (rc != OBGPU_OK) return rc;
     if (want_compact) OB_CUDA(c, c->d_stress_c.reserve(size_t(c->L) * c->hb.Etot() * 6));
@@ -242,6 +242,18 @@ int obgpu_profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, doub
   if (!c) return OBGPU_EINVAL;
   OB_NEED_DEVICE(c);
   return profile_kernel(c, which, reps, ms_avg, alg_bytes);
+}
+
+int obgpu_set_stress_length_poses(obgpu_ctx* c, const double* node_xy) {
+  if (!c) return OBGPU_EINVAL;
+  OB_NEED_DEVICE(c);
+  if (!c->uploaded) return fail(c, OBGPU_ESEQUENCE, "obgpu_set_stress_length_poses before obgpu_batch_upload");
+  c->have_xy_len = false;
+  if (!node_xy) return OBGPU_OK;
+  OB_CUDA(c, c->d_node_xy_len.upload(node_xy, size_t(2 * c->hb.Ntot()), c->stream));
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->have_xy_len = true;
+  return OBGPU_OK;
 }
 
 int obgpu_pcg_info(const obgpu_ctx* c, double out[4]) {

@@ -20,6 +20,8 @@ struct obgpu_ctx {
   // device batch mode (obgpu_batch_upload_device, capi_devsym.cu): the arrays live in HBM only, K3 runs as kernels
   bool device_batch_mode = false, host_batch_valid = true;
   bool any_ub = false;                            // some prescribed displacement is non-zero
+  obgpu::DevBuf<double> d_node_xy_len;            // obgpu_set_stress_length_poses
+  bool have_xy_len = false;
   obgpu::DevBuf<int64_t> d_off_node, d_off_elem, d_off_con, d_off_nload, d_off_eload, d_dof_off;  // [S+1]
   obgpu::DevBuf<uint32_t> d_con_node, d_nload_node, d_eload_elem;
   obgpu::DevBuf<uint8_t> d_con_dof, d_nload_dof, d_sym_mask;

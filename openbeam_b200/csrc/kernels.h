@@ -57,6 +57,9 @@ struct FrameArgs {
   const double* eload_q2;       // [ELtot] second load parameter (with eload_type)
   const double* U_b;            // [nb_tot] prescribed displacements (nodal frames), or null when all are zero
   const double* node_rot;       // [Ntot] nodal frame yaw (radians), or null when every node frame is the identity
+  const double2* node_xy_len;   // [Ntot] or null: node positions the element LENGTHS of postProcCalcStress are taken from
+                                // (obgpu_set_stress_length_poses: the reference's nonLinearIterative restores the node poses
+                                // before the stresses are computed, while orientations stay those of the last pass)
   const double* case_nl;        // [L][NLtot] or null
   const double* case_q;         // [L][ELtot] or null
   const double* case_eai;       // [L][3*Etot] or null

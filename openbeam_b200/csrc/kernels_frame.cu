@@ -396,6 +396,13 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
         const double2 p0 = a.node_xy[m.n0 + nd.x], p1 = a.node_xy[m.n0 + nd.y];
         const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
         const ElemLocalK lk = elem_local_k(type, eai_base[3 * e], eai_base[3 * e + 1], eai_base[3 * e + 2], g);
+        // postproc_stress.cpp:124-125 reads the lengths from the CURRENT node poses and the orientation from the element's
+        // cache: after nonLinearIterative these differ (solver_static.cpp:190-193 restores the poses)
+        ElemLocalK lks = lk;
+        if (GEN && a.node_xy_len) {
+          const double2 q0 = a.node_xy_len[m.n0 + nd.x], q1 = a.node_xy_len[m.n0 + nd.y];
+          lks = elem_local_k(type, eai_base[3 * e], eai_base[3 * e + 1], eai_base[3 * e + 2], elem_geom(q0.x, q0.y, q1.x, q1.y));
+        }
         double ug[6], es[6];
         int32_t sl6[6];
 #pragma unroll
@@ -411,8 +418,8 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_f
           // postproc_stress.cpp:86-119: U as solved (nodal frames are NOT undone there, quirk Q6), U_b on bounded DOFs
           ug[k] = t >= 0 ? Ff[t] : (Ub && t != SLOT_NONE) ? Ub[-t - 1] : 0.0;
         }
-        elem_end_forces(lk, g, ug, es);
-        if (!Ub && !node_rot) {  // K_bf U_f of this element = its global end forces (U_b = 0, identity node frames)
+        elem_end_forces(lks, g, ug, es);
+        if (!Ub && !node_rot && !(GEN && a.node_xy_len)) {  // K_bf U_f of this element = its global end forces (U_b = 0, identity node frames)
           sgf[lane * 6 + 0] = g.c * es[0] - g.s * es[1];
           sgf[lane * 6 + 1] = g.s * es[0] + g.c * es[1];
           sgf[lane * 6 + 2] = es[2];
@@ -507,7 +514,7 @@ static cudaError_t launch_frame_rg(const FrameArgs& a, int sm_count, cudaStream_
 
 template <int MAXR>
 static cudaError_t launch_frame_r(const FrameArgs& a, int sm_count, cudaStream_t st) {
-  if (a.U_b || a.node_rot) return launch_frame_rg<MAXR, true>(a, sm_count, st);
+  if (a.U_b || a.node_rot || a.node_xy_len) return launch_frame_rg<MAXR, true>(a, sm_count, st);
   return launch_frame_rg<MAXR, false>(a, sm_count, st);
 }
 

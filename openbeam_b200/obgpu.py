@@ -37,7 +37,7 @@ ABI_SYMBOLS = (
     "obgpu_host_free", "obgpu_batch_upload", "obgpu_batch_upload_device", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
     "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host", "obgpu_solve_cases_host_flags",
-    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_pcg_info", "obgpu_profile_kernel", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
+    "obgpu_summaries_device", "obgpu_get_timings", "obgpu_pcg_info", "obgpu_profile_kernel", "obgpu_set_stress_length_poses", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
     "obgpu_mesh_create", "obgpu_mesh_desc", "obgpu_mesh_info", "obgpu_mesh_destroy",
 )
 
@@ -114,6 +114,7 @@ def lib():
         L.obgpu_bind_summary_peers.argtypes = [vp, C.c_int, C.POINTER(C.c_void_p)]
         L.obgpu_get_timings.argtypes = [vp, vp]
         L.obgpu_pcg_info.argtypes = [vp, vp]
+        L.obgpu_set_stress_length_poses.argtypes = [vp, vp]
         L.obgpu_profile_kernel.argtypes = [vp, C.c_int, C.c_int, vp, vp]
         L.obgpu_get_stream.argtypes = [vp, C.POINTER(vp)]
         _LIB = L
@@ -396,6 +397,11 @@ class Context:
         ms, by = C.c_double(0), C.c_double(0)
         self._chk(lib().obgpu_profile_kernel(self.h, which, reps, C.byref(ms), C.byref(by)))
         return ms.value, by.value
+
+    def set_stress_length_poses(self, node_xy):
+        """node_xy [Ntot,2] or None: poses the element lengths of the stress recovery are read from (nonLinearIterative)"""
+        a = None if node_xy is None else np.ascontiguousarray(node_xy, np.float64)
+        self._chk(lib().obgpu_set_stress_length_poses(self.h, _p(a)))
 
     def pcg_info(self):
         """iterations, worst true relative residual, restarts, multigrid levels of the last PCG solve"""

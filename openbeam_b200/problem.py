@@ -171,6 +171,12 @@ class CStructureProblem:
                 if it:
                     self.structure = dataclasses.replace(orig, node_xy=xy.copy(), node_rotz=rz.copy())
                     self.ctx.upload(self.structure)
+                if it == self.N_MAX_ITERS - 1:
+                    # solver_static.cpp:190-193 restores the poses BEFORE the caller's postProcCalcStress: its element
+                    # lengths come from the original poses, orientations / U / fixed-end terms from this last pass
+                    self._stale_upload = False
+                    self.ctx.symbolic()
+                    self.ctx.set_stress_length_poses(orig.node_xy)
                 self._solve_once(options)
                 U_f = self.ctx.download(obgpu.RES_UF)[0]
                 free = self.ctx.symbolic_array(obgpu.SYM_FREE).astype(np.int64)

@@ -30,7 +30,8 @@ enum { OBO_RR = 0, OBO_RA = 1, OBO_AR = 2, OBO_AA = 3,
         * (Kx,Ky,-) SPRING_XY, (Kx,Ky,KRz) SPRING_DXDYRZ */
        OBO_RD = 4, OBO_SPRING_1D = 5, OBO_SPRING_XY = 6, OBO_SPRING_DXDYRZ = 7, OBO_SPRING_TORSION = 8 };
 /* solver algorithm: StaticSolverAlgorithm (CFiniteElementProblem.h:69-73) */
-enum { OBO_DENSE_LLT = 0, OBO_SPARSE_SKIP_SUBK = 1 };
+enum { OBO_DENSE_LLT = 0, OBO_SPARSE_SKIP_SUBK = 1,
+       OBO_NONLINEAR_ITERATIVE = 2 /* OR-ed in: StaticSolverOptions::nonLinearIterative (solver_static.cpp:139-193) */ };
 
 /* integer arrays readable with obo_get_i64 */
 enum {

@@ -45,31 +45,69 @@ static void llt_solve(const std::vector<num_t>& Lm, int n, std::vector<num_t>& b
   }
 }
 
-// src/CFiniteElementProblem_solver_static.cpp:50-219 (+ solveStaticInternal :29-44)
+// src/CFiniteElementProblem_solver_static.cpp:50-219 (+ solveStaticInternal :29-44).
+// algorithm bit 1 (value 2) = StaticSolverOptions::nonLinearIterative (:55-58, :63-66, :139-193): 40 passes, each on the
+// node poses moved by the previous pass's U_f; the poses are restored afterwards while the elements keep the LAST pass's
+// cached orientation and the last pass's equivalent loads / fixed-end stresses (postProcCalcStress then reads lengths from
+// the restored poses and orientations from the cache).
 void Problem::solveStatic(int algorithm) {
+  const bool nonLinearIterative = (algorithm & 2) != 0;
+  algorithm &= ~2;
   if (algorithm != OBO_DENSE_LLT) throw std::runtime_error("Invalid solver algorithm value");
-  assembleProblem(false);  // :74
-  bool U_b_all_zeros = true;  // :82
-  for (num_t v : U_b)
-    if (v != 0) U_b_all_zeros = false;
-  const int nf = int(free_dof_indices.size()), nb = int(bounded_dof_indices.size());
+  std::deque<TRotationTrans3D> orig_nodes;
+  if (nonLinearIterative) orig_nodes = m_node_poses;  // :57-58
+  bool U_b_all_zeros = true;
+  int nf = 0, nb = 0;
+  const unsigned int nMaxIters = 40;  // :63
+  unsigned int nIter = 0;
+  while (nIter < nMaxIters) {
+    nIter++;
+    assembleProblem(false);  // :74
+    U_b_all_zeros = true;    // :82
+    for (num_t v : U_b)
+      if (v != 0) U_b_all_zeros = false;
+    nf = int(free_dof_indices.size());
+    nb = int(bounded_dof_indices.size());
 
-  std::vector<num_t> Kff = K_ff;  // :89 dense copy of the (lower-stored) sparse K_ff
-  const int bad = llt_inplace_lower(Kff, nf);  // :97
-  if (bad >= 0)
-    throw std::runtime_error("[CFiniteElementProblem::solveStatic] Ill-conditioned matrix. Too few restrictions?");
-  U_f = F_f;  // :35
-  llt_solve(Kff, nf, U_f);
-  if (!U_b_all_zeros) {  // :37-43  U_f -= Kff^-1 (Kbf^T U_b)
-    std::vector<num_t> t(nf, 0);
-    for (int c = 0; c < nf; c++) {
-      num_t s = 0;
-      for (int r = 0; r < nb; r++) s += K_bf[size_t(c) * nb + r] * U_b[r];
-      t[c] = s;
+    std::vector<num_t> Kff = K_ff;  // :89 dense copy of the (lower-stored) sparse K_ff
+    const int bad = llt_inplace_lower(Kff, nf);  // :97
+    if (bad >= 0)
+      throw std::runtime_error("[CFiniteElementProblem::solveStatic] Ill-conditioned matrix. Too few restrictions?");
+    U_f = F_f;  // :35
+    llt_solve(Kff, nf, U_f);
+    if (!U_b_all_zeros) {  // :37-43  U_f -= Kff^-1 (Kbf^T U_b)
+      std::vector<num_t> t(nf, 0);
+      for (int c = 0; c < nf; c++) {
+        num_t s = 0;
+        for (int r = 0; r < nb; r++) s += K_bf[size_t(c) * nb + r] * U_b[r];
+        t[c] = s;
+      }
+      llt_solve(Kff, nf, t);
+      for (int c = 0; c < nf; c++) U_f[c] -= t[c];
     }
-    llt_solve(Kff, nf, t);
-    for (int c = 0; c < nf; c++) U_f[c] -= t[c];
+    if (!nonLinearIterative) break;  // :179-183
+    for (size_t i = 0; i < free_dof_indices.size(); i++) {  // :146-176
+      const num_t delta_val = U_f[i];
+      const auto& D = m_problem_DoFs[free_dof_indices[i]];
+      if (D[1] < 3) {
+        m_node_poses[D[0]].t[D[1]] += delta_val;
+      } else {
+        const num_t rx = D[1] == 3 ? delta_val : 0, ry = D[1] == 4 ? delta_val : 0, rz = D[1] == 5 ? delta_val : 0;
+        const Matrix33 inc = TRotation3D(rx, ry, rz).rot;
+        const Matrix33 cur = m_node_poses[D[0]].r.rot;
+        Matrix33 prod;
+        for (int r = 0; r < 3; r++)
+          for (int c = 0; c < 3; c++) {
+            num_t acc = cur(r, 0) * inc(0, c);
+            acc += cur(r, 1) * inc(1, c);
+            acc += cur(r, 2) * inc(2, c);
+            prod(r, c) = acc;
+          }
+        m_node_poses[D[0]].r.setRot(prod);
+      }
+    }
   }
+  if (nonLinearIterative) m_node_poses = orig_nodes;  // :190-193
   // :196-200 reactions.  K_bb holds only r<=c (quirk Q1) and is used as a general matrix.
   F_b.assign(nb, 0);
   if (!U_b_all_zeros)

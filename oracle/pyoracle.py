@@ -140,8 +140,8 @@ class OracleProblem:
         self._chk(self._L.obo_assemble(self.h, int(skip_subK)))
         return self
 
-    def solveStatic(self):
-        self._chk(self._L.obo_solve_static(self.h, 0))
+    def solveStatic(self, nonLinearIterative=False):
+        self._chk(self._L.obo_solve_static(self.h, 2 if nonLinearIterative else 0))
         return self
 
     def postProcCalcStress(self):

@@ -159,6 +159,7 @@ obo_problem* obo_create(int64_t n_nodes, const double* node_xy, const double* no
                         const uint32_t* con_node, const uint8_t* con_dof, const double* con_val, int64_t n_nloads,
                         const uint32_t* nl_node, const uint8_t* nl_dof, const double* nl_val, int64_t n_eloads,
                         const uint32_t* el_elem, const double* el_q, const double* el_dir) {
+  openbeam::setVerbosityLevel(0);   // the library's OB_MESSAGE chatter (std::cout) has no place in a test harness
   auto* h = new obo_problem;
   Spec& s = h->spec;
   s.N = n_nodes; s.E = n_elems;
@@ -215,11 +216,13 @@ int obo_assemble(obo_problem* h, int /*skip_subK: the reference always extracts 
   }
 }
 
-int obo_solve_static(obo_problem* h, int /*algorithm*/) {
+int obo_solve_static(obo_problem* h, int algorithm) {
   try {
     Built* B = live(h);
     if (!B) { h->err = "bad element / load type"; return -1; }
-    B->P.solveStatic(B->sinfo);   // StaticSolverOptions defaults: Dense_LLT, linear (CFiniteElementProblem.h:165-171)
+    StaticSolverOptions opts;     // defaults: Dense_LLT, linear (CFiniteElementProblem.h:165-171)
+    opts.nonLinearIterative = (algorithm & 2) != 0;   // ob_oracle.h: algorithm bit 1
+    B->P.solveStatic(B->sinfo, opts);
     B->binfo = B->sinfo.build_info;
     B->assembled = B->solved = true;
     B->stressed = false;
