@@ -116,7 +116,9 @@ enum {
   OBGPU_SYM_DOF_INDEX = 4,  /* [6*Ntot]   m_problem_DoFs_inverse_list[node].dof_index[d], -1 unused */
   OBGPU_SYM_K_ROWPTR = 5,   /* [n_tot+S]  CSR(lower) row pointers == Eigen CSC(upper) outerIndexPtr */
   OBGPU_SYM_K_COL = 6,      /* [nnz_tot]  CSR(lower) columns     == Eigen CSC(upper) innerIndexPtr  */
-  OBGPU_SYM_TRI_NNZ = 7     /* [T_tot]    element->nnz map: triplet t (reference emission order) -> nnz slot */
+  OBGPU_SYM_TRI_NNZ = 7,    /* [T_tot]    element->nnz map: triplet t (reference emission order) -> nnz slot */
+  OBGPU_SYM_KFF_ROWPTR = 8, /* [nf_tot+S] CSR(lower) row pointers of the true-sparse K_ff, local to each structure   */
+  OBGPU_SYM_KFF_COL = 9     /* [nnz(K_ff lower)] columns (free indices local to the structure)                      */
 };
 /* device/host result arrays */
 enum {
@@ -128,7 +130,18 @@ enum {
   OBGPU_RES_UB = 5,      /* [nb_tot]           BuildProblemInfo::U_b                                */
   OBGPU_RES_KVAL = 6,    /* [LK][nnz_tot]      values of K (upper, CSC order); LK = L if case_elem_EAI else 1 */
   OBGPU_RES_ELEM_K = 7,  /* [LK][Etot][21]     compact global element blocks        */
-  OBGPU_RES_STRESS_COMPACT = 8 /* [L][Etot][2][3] element_stress[e][face].{N,Vy,Mz} (OBGPU_SOLVE_COMPACT_STRESS) */
+  OBGPU_RES_STRESS_COMPACT = 8, /* [L][Etot][2][3] element_stress[e][face].{N,Vy,Mz} (OBGPU_SOLVE_COMPACT_STRESS) */
+  /* BuildProblemInfo::K_ff / K_bf / K_bb (CFiniteElementProblem.h:86-91) after obgpu_assemble, as the reference builds them
+   * (assemble.cpp:249-297): DENSE-STRUCTURED per structure, column-major, structures concatenated —
+   *   K_ff n_f x n_f with only the LOWER triangle filled (what Eigen::LLT reads, :264-270),
+   *   K_bf n_b x n_f full (:273-286),  K_bb n_b x n_b with only the UPPER triangle filled (:258-262).
+   * For small structures (the whole batch must fit 2^28 doubles per view); large ones read the true-sparse K_ff below. */
+  OBGPU_RES_KFF_DENSE = 9,    /* [LK][sum_s n_f(s)^2]      */
+  OBGPU_RES_KBF_DENSE = 10,   /* [LK][sum_s n_b(s) n_f(s)] */
+  OBGPU_RES_KBB_DENSE = 11,   /* [LK][sum_s n_b(s)^2]      */
+  /* true-sparse K_ff: the entries of K (pattern bit-exact with Eigen's, OBGPU_SYM_K_*) whose row and column are free, lower
+   * triangle, CSR over free indices; pattern through OBGPU_SYM_KFF_ROWPTR / OBGPU_SYM_KFF_COL */
+  OBGPU_RES_KFF_CSR_VAL = 12  /* [LK][nnz(K_ff lower)]     */
 };
 
 /* device >= 0: CUDA ordinal (must be sm_100).  OBGPU_DEVICE_NONE: symbolic-only ctx — batch_upload,
@@ -173,6 +186,10 @@ int obgpu_get_offsets(const obgpu_ctx*, int which, int64_t* out);
 int obgpu_get_symbolic(const obgpu_ctx*, int which, int32_t* out);
 /* copy one result array to a host buffer (blocking); returns OBGPU_ESINGULAR if any info != 0 when which==INFO */
 int obgpu_download(obgpu_ctx*, int which, void* host_out);
+/* number of elements obgpu_download(which) writes / obgpu_get_symbolic(which) writes, for the ids whose extent is not one of
+ * obgpu_get_sizes' entries (the K_ff / K_bf / K_bb views); also valid for every other id */
+int obgpu_result_count(obgpu_ctx*, int which, int64_t* count);
+int obgpu_symbolic_count(obgpu_ctx*, int which, int64_t* count);
 /* device pointer of a result array (valid until the next upload/update), for zero-copy consumers */
 int obgpu_device_ptr(obgpu_ctx*, int which, void** dptr);
 /* wait for all work queued on the ctx */

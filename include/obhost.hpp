@@ -49,6 +49,12 @@ struct BuildProblemInfo {
   // K: upper triangle in Eigen's compressed column order (== CSR of the lower triangle)
   std::vector<int32_t> K_outer, K_inner;
   std::vector<num_t> K_values;
+  // CFiniteElementProblem.h:86-91, dense-structured and column-major as the reference fills them (assemble.cpp:249-297):
+  // K_ff [n_f x n_f] LOWER triangle, K_bf [n_b x n_f], K_bb [n_b x n_b] UPPER triangle (quirk Q1).  Filled for problems
+  // of up to 4096 DOFs; the true-sparse K_ff is always in K_ff_rowptr / K_ff_col / K_ff_val (CSR, lower, free indices).
+  std::vector<num_t> K_ff, K_bf, K_bb;
+  std::vector<int32_t> K_ff_rowptr, K_ff_col;
+  std::vector<num_t> K_ff_val;
   std::vector<num_t> U_b, F_f;
 };
 
@@ -197,6 +203,23 @@ class CStructureProblem {
     check(obgpu_download(ctx_, OBGPU_RES_UB, out.U_b.data()));
     out.F_f.resize(z[5]);
     check(obgpu_download(ctx_, OBGPU_RES_FF, out.F_f.data()));
+    int64_t cnt = 0;
+    check(obgpu_symbolic_count(ctx_, OBGPU_SYM_KFF_ROWPTR, &cnt));
+    out.K_ff_rowptr.resize(size_t(cnt));
+    check(obgpu_get_symbolic(ctx_, OBGPU_SYM_KFF_ROWPTR, out.K_ff_rowptr.data()));
+    check(obgpu_symbolic_count(ctx_, OBGPU_SYM_KFF_COL, &cnt));
+    out.K_ff_col.resize(size_t(cnt));
+    out.K_ff_val.resize(size_t(cnt));
+    if (cnt) {
+      check(obgpu_get_symbolic(ctx_, OBGPU_SYM_KFF_COL, out.K_ff_col.data()));
+      check(obgpu_download(ctx_, OBGPU_RES_KFF_CSR_VAL, out.K_ff_val.data()));
+    }
+    if (z[4] <= 4096) {
+      out.K_ff.assign(size_t(z[5] * z[5]), 0); out.K_bf.assign(size_t(z[6] * z[5]), 0); out.K_bb.assign(size_t(z[6] * z[6]), 0);
+      if (!out.K_ff.empty()) check(obgpu_download(ctx_, OBGPU_RES_KFF_DENSE, out.K_ff.data()));
+      if (!out.K_bf.empty()) check(obgpu_download(ctx_, OBGPU_RES_KBF_DENSE, out.K_bf.data()));
+      if (!out.K_bb.empty()) check(obgpu_download(ctx_, OBGPU_RES_KBB_DENSE, out.K_bb.data()));
+    }
   }
 
   void solveStatic(StaticSolveProblemInfo& out, const StaticSolverOptions& opts = StaticSolverOptions()) {

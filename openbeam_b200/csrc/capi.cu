@@ -25,6 +25,7 @@ namespace obgpu {
 int batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d);   // capi_devsym.cu
 int symbolic_device(obgpu_ctx* c);
 int materialize_host_batch(obgpu_ctx* c);
+int symbolic_general(obgpu_ctx* c, int which, int32_t* out, int64_t* count);   // capi_sparse.cu
 }
 using namespace obgpu;
 
@@ -328,6 +329,8 @@ int obgpu_get_symbolic(const obgpu_ctx* cc, int which, int32_t* out) {
     if (rc != OBGPU_OK) return rc;
   }
   const obgpu_ctx* c = cc;
+  if (which == OBGPU_SYM_KFF_ROWPTR || which == OBGPU_SYM_KFF_COL)
+    return symbolic_general(const_cast<obgpu_ctx*>(cc), which, out, nullptr);
   const std::vector<int32_t>* v = nullptr;
   switch (which) {
     case OBGPU_SYM_DOF_NODE: v = &c->sym.dof_node; break;

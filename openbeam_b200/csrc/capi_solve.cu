@@ -11,6 +11,9 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o);   // capi_general.cu
 int assemble_general(obgpu_ctx* c);                            // capi_general.cu
 int download_general(obgpu_ctx* c, int which, void* host_out, bool& handled);
 int profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, double* alg_bytes);  // capi_sparse.cu
+int result_count_general(obgpu_ctx* c, int which, int64_t* count);
+int symbolic_general(obgpu_ctx* c, int which, int32_t* out, int64_t* count);
+int materialize_host_batch(obgpu_ctx* c);
 }
 
 static int ensure_symbolic(obgpu_ctx* c) {
@@ -189,6 +192,12 @@ int obgpu_download(obgpu_ctx* c, int which, void* out) {
   bool handled = false;
   int rc = download_general(c, which, out, handled);
   if (handled) return rc;
+  if (which == OBGPU_RES_UB && c->sym.valid) {   // BuildProblemInfo::U_b is a product of the symbolic phase
+    const size_t bytes = size_t(c->sym.nb_tot()) * 8;
+    if (bytes) OB_CUDA(c, cudaMemcpyAsync(out, c->d_Ub.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+    OB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return OBGPU_OK;
+  }
   if (!c->solved) return fail(c, OBGPU_ESEQUENCE, "obgpu_download before obgpu_solve_static");
   const Symbolic& s = c->sym;
   const void* src = nullptr;
@@ -254,6 +263,44 @@ int obgpu_set_stress_length_poses(obgpu_ctx* c, const double* node_xy) {
   OB_CUDA(c, cudaStreamSynchronize(c->stream));
   c->have_xy_len = true;
   return OBGPU_OK;
+}
+
+int obgpu_result_count(obgpu_ctx* c, int which, int64_t* count) {
+  if (!c || !count || !c->sym.valid) return OBGPU_ESEQUENCE;
+  const Symbolic& s = c->sym;
+  const int64_t L = c->L, LK = c->has_case_eai ? c->L : 1, E = c->hb.Etot();
+  switch (which) {
+    case OBGPU_RES_UF: case OBGPU_RES_FF: *count = L * s.nf_tot(); return OBGPU_OK;
+    case OBGPU_RES_FB: *count = L * s.nb_tot(); return OBGPU_OK;
+    case OBGPU_RES_UB: *count = s.nb_tot(); return OBGPU_OK;
+    case OBGPU_RES_STRESS: *count = L * E * 12; return OBGPU_OK;
+    case OBGPU_RES_STRESS_COMPACT: *count = L * E * 6; return OBGPU_OK;
+    case OBGPU_RES_INFO: *count = L * c->hb.S; return OBGPU_OK;
+    case OBGPU_RES_KVAL: *count = LK * s.nnz_tot(); return OBGPU_OK;
+    case OBGPU_RES_ELEM_K: *count = LK * E * ELEM_K; return OBGPU_OK;
+  }
+  if (c->device_batch_mode && !c->host_batch_valid) {
+    int rc = materialize_host_batch(c);
+    if (rc == OBGPU_OK) rc = obgpu_symbolic(c);
+    if (rc != OBGPU_OK) return rc;
+  }
+  return result_count_general(c, which, count);
+}
+
+int obgpu_symbolic_count(obgpu_ctx* c, int which, int64_t* count) {
+  if (!c || !count || !c->sym.valid) return OBGPU_ESEQUENCE;
+  const Symbolic& s = c->sym;
+  switch (which) {
+    case OBGPU_SYM_DOF_NODE: case OBGPU_SYM_DOF_ID: *count = s.n_tot(); return OBGPU_OK;
+    case OBGPU_SYM_FREE: *count = s.nf_tot(); return OBGPU_OK;
+    case OBGPU_SYM_BOUNDED: *count = s.nb_tot(); return OBGPU_OK;
+    case OBGPU_SYM_DOF_INDEX: *count = 6 * c->hb.Ntot(); return OBGPU_OK;
+    case OBGPU_SYM_K_ROWPTR: *count = s.n_tot() + c->hb.S; return OBGPU_OK;
+    case OBGPU_SYM_K_COL: *count = s.nnz_tot(); return OBGPU_OK;
+    case OBGPU_SYM_TRI_NNZ: *count = s.T_tot(); return OBGPU_OK;
+    case OBGPU_SYM_KFF_ROWPTR: case OBGPU_SYM_KFF_COL: return symbolic_general(c, which, nullptr, count);
+  }
+  return OBGPU_EINVAL;
 }
 
 int obgpu_pcg_info(const obgpu_ctx* c, double out[4]) {

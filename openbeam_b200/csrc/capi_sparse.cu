@@ -547,8 +547,134 @@ int profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, double* al
   return OBGPU_OK;
 }
 
+static int ensure_pattern(obgpu_ctx* c) {
+  if (c->sym.has_pattern) return OBGPU_OK;
+  std::string err;
+  const int rc = run_symbolic(c->hb, c->sym, err, true);
+  if (rc != OBGPU_OK) return fail(c, rc, err);
+  return OBGPU_OK;
+}
+
+// extents of the K_ff / K_bf / K_bb views per K copy
+static void subk_counts(const Symbolic& sy, int64_t S, int64_t& ff, int64_t& bf, int64_t& bb) {
+  ff = bf = bb = 0;
+  for (int64_t s = 0; s < S; s++) {
+    const int64_t nf = sy.free_off[s + 1] - sy.free_off[s], nb = sy.bnd_off[s + 1] - sy.bnd_off[s];
+    ff += nf * nf; bf += nb * nf; bb += nb * nb;
+  }
+}
+
+// true-sparse K_ff (lower CSR over free indices) pattern, from the pattern of K
+static void kff_csr_pattern(const obgpu_ctx* c, std::vector<int32_t>* rowptr, std::vector<int32_t>* col, std::vector<int32_t>* src) {
+  const Symbolic& sy = c->sym;
+  const int64_t S = c->hb.S;
+  for (int64_t s = 0; s < S; s++) {
+    const int64_t k0 = sy.dof_off[s], n = sy.dof_off[s + 1] - k0, z0 = sy.nnz_off[s];
+    const int32_t* rp = &sy.k_rowptr[size_t(k0 + s)];
+    int32_t run = 0;
+    if (rowptr) rowptr->push_back(0);
+    for (int64_t hi = 0; hi < n; hi++) {
+      if (sy.dof_type[size_t(k0 + hi)] < 0) continue;
+      for (int32_t z = rp[hi]; z < rp[hi + 1]; z++) {
+        const int32_t tlo = sy.dof_type[size_t(k0 + sy.k_col[size_t(z0 + z)])];
+        if (tlo < 0) continue;
+        if (col) col->push_back(tlo);
+        if (src) src->push_back(int32_t(z0 + z));
+        run++;
+      }
+      if (rowptr) rowptr->push_back(run);
+    }
+  }
+}
+
+int symbolic_general(obgpu_ctx* c, int which, int32_t* out, int64_t* count) {  // OBGPU_SYM_KFF_*
+  int rc = ensure_pattern(c);
+  if (rc != OBGPU_OK) return rc;
+  std::vector<int32_t> v;
+  if (which == OBGPU_SYM_KFF_ROWPTR) kff_csr_pattern(c, &v, nullptr, nullptr);
+  else kff_csr_pattern(c, nullptr, &v, nullptr);
+  if (count) *count = int64_t(v.size());
+  if (out && !v.empty()) std::memcpy(out, v.data(), v.size() * sizeof(int32_t));
+  return OBGPU_OK;
+}
+
+int result_count_general(obgpu_ctx* c, int which, int64_t* count) {
+  int64_t ff, bf, bb;
+  subk_counts(c->sym, c->hb.S, ff, bf, bb);
+  const int64_t LK = c->has_case_eai ? c->L : 1;
+  switch (which) {
+    case OBGPU_RES_KFF_DENSE: *count = LK * ff; return OBGPU_OK;
+    case OBGPU_RES_KBF_DENSE: *count = LK * bf; return OBGPU_OK;
+    case OBGPU_RES_KBB_DENSE: *count = LK * bb; return OBGPU_OK;
+    case OBGPU_RES_KFF_CSR_VAL: {
+      int rc = ensure_pattern(c);
+      if (rc != OBGPU_OK) return rc;
+      std::vector<int32_t> col;
+      kff_csr_pattern(c, nullptr, &col, nullptr);
+      *count = LK * int64_t(col.size());
+      return OBGPU_OK;
+    }
+  }
+  return OBGPU_EINVAL;
+}
+
+// BuildProblemInfo::K_ff / K_bf / K_bb: the values of K (assembled on the device) regrouped on the host into the
+// reference's dense-structured sub-matrices — data movement only, no arithmetic.
+static int download_subk(obgpu_ctx* c, int which, double* out) {
+  if (!c->assembled) return fail(c, OBGPU_ESEQUENCE, "obgpu_download(K_ff/K_bf/K_bb) before obgpu_assemble");
+  int rc = ensure_pattern(c);
+  if (rc != OBGPU_OK) return rc;
+  const Symbolic& sy = c->sym;
+  const int64_t S = c->hb.S, nnz = sy.nnz_tot(), LK = c->LK;
+  std::vector<double> kval(size_t(LK * nnz));
+  if (!kval.empty()) OB_CUDA(c, cudaMemcpyAsync(kval.data(), c->d_kval.p, kval.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (which == OBGPU_RES_KFF_CSR_VAL) {
+    std::vector<int32_t> src;
+    kff_csr_pattern(c, nullptr, nullptr, &src);
+    for (int64_t k = 0; k < LK; k++)
+      for (size_t i = 0; i < src.size(); i++) out[size_t(k) * src.size() + i] = kval[size_t(k * nnz + src[i])];
+    return OBGPU_OK;
+  }
+  int64_t ff, bf, bb;
+  subk_counts(sy, S, ff, bf, bb);
+  const int64_t per = which == OBGPU_RES_KFF_DENSE ? ff : which == OBGPU_RES_KBF_DENSE ? bf : bb;
+  if (per > (int64_t(1) << 28)) return fail(c, OBGPU_EUNSUPPORTED, "dense-structured K_ff/K_bf/K_bb view too large: read OBGPU_RES_KFF_CSR_VAL");
+  std::memset(out, 0, size_t(LK * per) * 8);
+  for (int64_t k = 0; k < LK; k++) {
+    double* o = out + k * per;
+    int64_t base = 0;
+    for (int64_t s = 0; s < S; s++) {
+      const int64_t k0 = sy.dof_off[s], n = sy.dof_off[s + 1] - k0, z0 = sy.nnz_off[s];
+      const int64_t nf = sy.free_off[s + 1] - sy.free_off[s], nb = sy.bnd_off[s + 1] - sy.bnd_off[s];
+      const int32_t* rp = &sy.k_rowptr[size_t(k0 + s)];
+      for (int64_t hi = 0; hi < n; hi++) {
+        const int32_t thi = sy.dof_type[size_t(k0 + hi)];
+        for (int32_t z = rp[hi]; z < rp[hi + 1]; z++) {
+          const int32_t tlo = sy.dof_type[size_t(k0 + sy.k_col[size_t(z0 + z)])];
+          const double v = kval[size_t(k * nnz + z0 + z)];   // K(lo, hi), lo <= hi
+          if (which == OBGPU_RES_KFF_DENSE) {
+            if (thi >= 0 && tlo >= 0) o[base + int64_t(tlo) * nf + thi] = v;              // K_ff(c = f(hi), r = f(lo)): lower
+          } else if (which == OBGPU_RES_KBB_DENSE) {
+            if (thi < 0 && tlo < 0) o[base + int64_t(-thi - 1) * nb + (-tlo - 1)] = v;    // K_bb(b(lo), b(hi)): upper
+          } else {
+            if (thi < 0 && tlo >= 0) o[base + int64_t(tlo) * nb + (-thi - 1)] = v;        // K_bf(b, f)
+            else if (thi >= 0 && tlo < 0) o[base + int64_t(thi) * nb + (-tlo - 1)] = v;
+          }
+        }
+      }
+      base += which == OBGPU_RES_KFF_DENSE ? nf * nf : which == OBGPU_RES_KBF_DENSE ? nb * nf : nb * nb;
+    }
+  }
+  return OBGPU_OK;
+}
+
 int download_general(obgpu_ctx* c, int which, void* out, bool& handled) {
   handled = false;
+  if (which >= OBGPU_RES_KFF_DENSE && which <= OBGPU_RES_KFF_CSR_VAL) {
+    handled = true;
+    return download_subk(c, which, static_cast<double*>(out));
+  }
   if (which != OBGPU_RES_KVAL && which != OBGPU_RES_ELEM_K && !(which == OBGPU_RES_FF && c->assembled && !c->solved))
     return OBGPU_OK;
   handled = true;

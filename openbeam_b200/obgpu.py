@@ -26,8 +26,10 @@ OK, EINVAL, ECUDA, ESINGULAR, ENOTCONVERGED, EUNSUPPORTED, ESEQUENCE = range(7)
 BATCHED_LDLT, PCG_JACOBI, PCG_MG = range(3)
 PROF_SPMV, PROF_MG_SPMV = 0, 1
 SOLVE_SKIP_FF, SOLVE_COMPACT_STRESS = 1, 2  # obgpu_solve_opts.flags
-(RES_UF, RES_FB, RES_STRESS, RES_INFO, RES_FF, RES_UB, RES_KVAL, RES_ELEM_K, RES_STRESS_COMPACT) = range(9)
-(SYM_DOF_NODE, SYM_DOF_ID, SYM_FREE, SYM_BOUNDED, SYM_DOF_INDEX, SYM_K_ROWPTR, SYM_K_COL, SYM_TRI_NNZ) = range(8)
+(RES_UF, RES_FB, RES_STRESS, RES_INFO, RES_FF, RES_UB, RES_KVAL, RES_ELEM_K, RES_STRESS_COMPACT, RES_KFF_DENSE,
+ RES_KBF_DENSE, RES_KBB_DENSE, RES_KFF_CSR_VAL) = range(13)
+(SYM_DOF_NODE, SYM_DOF_ID, SYM_FREE, SYM_BOUNDED, SYM_DOF_INDEX, SYM_K_ROWPTR, SYM_K_COL, SYM_TRI_NNZ, SYM_KFF_ROWPTR,
+ SYM_KFF_COL) = range(10)
 OFF_DOF, OFF_FREE, OFF_BOUNDED, OFF_NNZ, OFF_TRIPLET = range(5)
 SIZE_NAMES = ("S", "L", "Ntot", "Etot", "n_tot", "nf_tot", "nb_tot", "T_tot", "nnz_tot", "Ctot", "NLtot", "ELtot")
 
@@ -36,7 +38,7 @@ ABI_SYMBOLS = (
     "obgpu_create", "obgpu_destroy", "obgpu_last_error", "obgpu_status_string", "obgpu_host_alloc",
     "obgpu_host_free", "obgpu_batch_upload", "obgpu_batch_upload_device", "obgpu_update_cases", "obgpu_symbolic", "obgpu_assemble",
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
-    "obgpu_download", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host", "obgpu_solve_cases_host_flags",
+    "obgpu_download", "obgpu_result_count", "obgpu_symbolic_count", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host", "obgpu_solve_cases_host_flags",
     "obgpu_summaries_device", "obgpu_get_timings", "obgpu_pcg_info", "obgpu_profile_kernel", "obgpu_set_stress_length_poses", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
     "obgpu_mesh_create", "obgpu_mesh_desc", "obgpu_mesh_info", "obgpu_mesh_destroy",
 )
@@ -114,6 +116,8 @@ def lib():
         L.obgpu_bind_summary_peers.argtypes = [vp, C.c_int, C.POINTER(C.c_void_p)]
         L.obgpu_get_timings.argtypes = [vp, vp]
         L.obgpu_pcg_info.argtypes = [vp, vp]
+        L.obgpu_result_count.argtypes = [vp, C.c_int, vp]
+        L.obgpu_symbolic_count.argtypes = [vp, C.c_int, vp]
         L.obgpu_set_stress_length_poses.argtypes = [vp, vp]
         L.obgpu_profile_kernel.argtypes = [vp, C.c_int, C.c_int, vp, vp]
         L.obgpu_get_stream.argtypes = [vp, C.POINTER(vp)]
@@ -353,10 +357,9 @@ class Context:
         return out
 
     def symbolic_array(self, which):
-        z = self.sizes()
-        n = {SYM_DOF_NODE: z["n_tot"], SYM_DOF_ID: z["n_tot"], SYM_FREE: z["nf_tot"], SYM_BOUNDED: z["nb_tot"],
-             SYM_DOF_INDEX: 6 * z["Ntot"], SYM_K_ROWPTR: z["n_tot"] + z["S"], SYM_K_COL: z["nnz_tot"],
-             SYM_TRI_NNZ: z["T_tot"]}[which]
+        cnt = C.c_int64(0)
+        self._chk(lib().obgpu_symbolic_count(self.h, which, C.byref(cnt)))
+        n = cnt.value
         out = np.zeros(max(n, 1), np.int32)
         self._chk(lib().obgpu_get_symbolic(self.h, which, _p(out)))
         return out[:n]
@@ -370,7 +373,38 @@ class Context:
                 RES_STRESS_COMPACT: ((L, z["Etot"], 2, 3), np.float64),
                 RES_KVAL: ((-1, z["nnz_tot"]), np.float64), RES_ELEM_K: ((-1, z["Etot"], 21), np.float64)}[which]
 
+    def result_count(self, which):
+        cnt = C.c_int64(0)
+        self._chk(lib().obgpu_result_count(self.h, which, C.byref(cnt)))
+        return cnt.value
+
+    def sub_matrices(self, k=0):
+        """BuildProblemInfo::K_ff (lower-stored), K_bf, K_bb (upper-stored) per structure, dense like the reference builds
+        them (assemble.cpp:249-297), for K copy k: three lists of 2-D arrays"""
+        z = self.sizes()
+        fo, bo = self.offsets(OFF_FREE), self.offsets(OFF_BOUNDED)
+        LK = z["L"] if self.result_count(RES_KVAL) > z["nnz_tot"] else 1
+        out = []
+        for which, rows, cols in ((RES_KFF_DENSE, "f", "f"), (RES_KBF_DENSE, "b", "f"), (RES_KBB_DENSE, "b", "b")):
+            flat = np.zeros(max(self.result_count(which), 1))
+            self._chk(lib().obgpu_download(self.h, which, _p(flat)))
+            per = self.result_count(which) // LK
+            flat = flat[k * per:(k + 1) * per]
+            mats, p = [], 0
+            for s in range(z["S"]):
+                nr = (fo if rows == "f" else bo)[s + 1] - (fo if rows == "f" else bo)[s]
+                nc = (fo if cols == "f" else bo)[s + 1] - (fo if cols == "f" else bo)[s]
+                mats.append(flat[p:p + nr * nc].reshape(nc, nr).T.copy())   # column-major blocks
+                p += nr * nc
+            out.append(mats)
+        return out
+
     def download(self, which, out=None, lk=None):
+        if which in (RES_KFF_DENSE, RES_KBF_DENSE, RES_KBB_DENSE, RES_KFF_CSR_VAL):
+            if out is None:
+                out = np.zeros(max(self.result_count(which), 1))
+            self._chk(lib().obgpu_download(self.h, which, _p(out)))
+            return out[:self.result_count(which)]
         shape, dt = self.result_shape(which)
         if shape[0] == -1:
             shape = ((lk or 1),) + shape[1:]

@@ -49,6 +49,9 @@ class BuildProblemInfo:
     K_outer: np.ndarray = None            # K: Eigen CSC(upper) == CSR(lower): outerIndexPtr
     K_inner: np.ndarray = None            #    innerIndexPtr
     K_values: np.ndarray = None           #    valuePtr
+    K_ff: np.ndarray = None               # [n_f,n_f] dense-structured, LOWER triangle filled (assemble.cpp:264-270)
+    K_bf: np.ndarray = None               # [n_b,n_f]                                       (assemble.cpp:273-286)
+    K_bb: np.ndarray = None               # [n_b,n_b] UPPER triangle filled (quirk Q1)      (assemble.cpp:258-262)
     U_b: np.ndarray = None
     F_f: np.ndarray = None
 
@@ -142,6 +145,11 @@ class CStructureProblem:
         self.ctx.assemble()
         self._fill_lists(out_info)
         out_info.K_values = self.ctx.download(obgpu.RES_KVAL)[0]
+        # BuildProblemInfo::K_ff / K_bf / K_bb (CFiniteElementProblem.h:86-91): dense-structured like the reference's
+        # (K_ff lower-stored, K_bb upper-stored), kept for problems small enough that this is not absurd
+        if self.ctx.sizes()["n_tot"] <= 4096:
+            kff, kbf, kbb = self.ctx.sub_matrices()
+            out_info.K_ff, out_info.K_bf, out_info.K_bb = kff[0], kbf[0], kbb[0]
         out_info.U_b = self.ctx.download(obgpu.RES_UB)
         out_info.F_f = self.ctx.download(obgpu.RES_FF)[0]
         return out_info
