@@ -208,8 +208,6 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
     }
     if (o.method == OBGPU_BATCHED_LDLT)
       return fail(c, OBGPU_EUNSUPPORTED, "structure too large for the batched LDLt kernel: use a PCG method");
-    if (any_ub)
-      return fail(c, OBGPU_EUNSUPPORTED, "non-zero prescribed displacements are not implemented on the PCG route yet");
     return solve_sparse(c, o);
   }
   const Symbolic& sy = c->sym;

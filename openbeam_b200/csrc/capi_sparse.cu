@@ -25,16 +25,23 @@ static int ensure_plan(obgpu_ctx* c) {
   const HostBatch& hb = c->hb;
   const SparsePlan& P = c->plan;
   cudaStream_t st = c->stream;
-  std::vector<int32_t> node0(hb.Etot()), f0(hb.Etot()), eg(hb.ELtot());
+  std::vector<int32_t> node0(hb.Etot()), f0(hb.Etot()), b0(hb.Etot()), nf0(hb.Ntot()), eg(hb.ELtot());
   for (int64_t s = 0; s < hb.S; s++) {
     for (int64_t e = hb.elem_off[s]; e < hb.elem_off[s + 1]; e++) {
       node0[e] = int32_t(hb.node_off[s]);
       f0[e] = int32_t(c->sym.free_off[s]);
+      b0[e] = int32_t(c->sym.bnd_off[s]);
     }
+    for (int64_t n = hb.node_off[s]; n < hb.node_off[s + 1]; n++) nf0[n] = int32_t(c->sym.free_off[s]);
     for (int64_t l = hb.eload_off[s]; l < hb.eload_off[s + 1]; l++) eg[l] = int32_t(hb.elem_off[s] + hb.eload_elem[l]);
   }
   OB_CUDA(c, c->d_elem_node0.upload(node0, st));
   OB_CUDA(c, c->d_elem_f0.upload(f0, st));
+  OB_CUDA(c, c->d_elem_b0.upload(b0, st));
+  OB_CUDA(c, c->d_node_f0.upload(nf0, st));
+  OB_CUDA(c, c->d_bb_rowptr.upload(P.bb_rowptr, st));
+  OB_CUDA(c, c->d_bb_col.upload(P.bb_col, st));
+  OB_CUDA(c, c->d_bb_src.upload(P.bb_src, st));
   OB_CUDA(c, c->d_eload_elem_g.upload(eg, st));
   OB_CUDA(c, c->d_seg_ptr.upload(P.seg_ptr, st));
   OB_CUDA(c, c->d_seg_src.upload(P.seg_src, st));
@@ -102,7 +109,11 @@ static SparseDev sparse_dev(obgpu_ctx* c, int64_t k /* K copy */) {
   d.elem_nodes = reinterpret_cast<const uint2*>(c->d_elem_nodes.p);
   d.elem_type = c->d_elem_type.p;
   d.node_xy = reinterpret_cast<const double2*>(c->d_node_xy.p);
-  d.elem_node0 = c->d_elem_node0.p; d.elem_f0 = c->d_elem_f0.p;
+  d.elem_node0 = c->d_elem_node0.p; d.elem_f0 = c->d_elem_f0.p; d.elem_b0 = c->d_elem_b0.p; d.node_f0 = c->d_node_f0.p;
+  d.Ntot = c->hb.Ntot();
+  d.node_rot = c->hb.has_rotz ? c->d_node_rot.p : nullptr;
+  d.U_b = c->any_ub ? c->d_Ub.p : nullptr;
+  d.bb_rowptr = c->d_bb_rowptr.p; d.bb_col = c->d_bb_col.p; d.bb_src = c->d_bb_src.p; d.bb_val = c->d_bb_val.p;
   d.node_slot = c->d_node_slot.p; d.el_ptr = c->d_el_ptr.p; d.el_order = c->d_el_order.p;
   d.eload_elem_g = c->d_eload_elem_g.p; d.eload_dir = c->d_eload_dir.p;
   d.eload_type = c->hb.has_load_kinds ? c->d_eload_type.p : nullptr;
@@ -124,7 +135,6 @@ static SparseDev sparse_dev(obgpu_ctx* c, int64_t k /* K copy */) {
 int assemble_general(obgpu_ctx* c) {
   int rc = ensure_plan(c);
   if (rc != OBGPU_OK) return rc;
-  if (c->hb.has_rotz) return fail(c, OBGPU_EUNSUPPORTED, "nodal rotated frames are not implemented on the GPU path yet");
   const int64_t L = c->L, LK = c->has_case_eai ? L : 1;
   c->LK = LK;
   const int64_t Etot = c->hb.Etot(), nnz = c->sym.nnz_tot(), nf = c->sym.nf_tot();
@@ -134,6 +144,7 @@ int assemble_general(obgpu_ctx* c) {
   OB_CUDA(c, c->d_kval.reserve(size_t(LK) * std::max<int64_t>(nnz, 1)));
   OB_CUDA(c, c->d_ff_val.reserve(std::max<size_t>(c->plan.ff_col.size(), 1)));
   OB_CUDA(c, c->d_bf_val.reserve(std::max<size_t>(c->plan.bf_col.size(), 1)));
+  OB_CUDA(c, c->d_bb_val.reserve(std::max<size_t>(c->plan.bb_col.size(), 1)));
   OB_CUDA(c, c->d_Ff.reserve(size_t(L) * std::max<int64_t>(nf, 1)));
   OB_CUDA(c, cudaEventRecord(c->ev[6], c->stream));
   double launches = 0;
@@ -295,9 +306,16 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     const double* nl = c->has_case_nl ? c->d_case_nl.p + size_t(cs) * c->hb.NLtot() : c->d_nload_val.p;
     const double* q = c->has_case_q ? c->d_case_q.p + size_t(cs) * c->hb.ELtot() : c->d_eload_q.p;
     const double* eai = c->has_case_eai ? c->d_case_eai.p + size_t(cs) * 3 * Etot : c->d_elem_EAI.p;
+    if (c->any_ub) {  // U_f = K_ff^-1 (F_f - K_bf^T U_b), solver_static.cpp:37-43
+      OB_CUDA(c, c->d_rhs.reserve(size_t(std::max<int64_t>(nf, 1))));
+    }
     if (L > 1) {  // Eq (equivalent loads on bounded DOFs) of THIS case; F_f was filled by assemble_general
       OB_CUDA(c, launch_load_vector(d, nl, q, eai, c->d_Ff.p + size_t(cs) * nf, c->stream));
       launches += 2;
+    }
+    if (c->any_ub) {
+      OB_CUDA(c, launch_rhs_prescribed(sparse_dev(c, k), c->d_Ff.p + size_t(cs) * nf, c->d_rhs.p, c->stream));
+      launches += 1;
     }
     // ---- one PCG per structure; up to NC of them in flight on their own streams, so that the launch gaps and the
     // 25-iteration convergence checks of one structure are covered by the kernels of the others (C5: 8 structures of
@@ -325,7 +343,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
       PcgArgs a;
       a.r0 = int32_t(sy.free_off[st_i]); a.r1 = int32_t(sy.free_off[st_i + 1]);
       a.slptr = d.sl_ptr; a.col = d.ff_col; a.val = d.ff_val; a.minv = v_minv;
-      a.b = c->d_Ff.p + size_t(cs) * nf;
+      a.b = c->any_ub ? c->d_rhs.p : c->d_Ff.p + size_t(cs) * nf;
       a.x = c->d_Uf.p + size_t(cs) * nf;
       a.r = v_r; a.z = v_z; a.p = v_p; a.ap = v_ap;
       a.ctas_per_sm = NC > 1 ? 2 : 0;  // measured at C5's share (8 x 0.5 M DOF): 8 -> 1.84 s, 4 -> 1.67 s, 2 -> 1.62 s

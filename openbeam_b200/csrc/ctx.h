@@ -72,8 +72,8 @@ struct obgpu_ctx {
   bool dev_plan = false, assembled = false;
   int64_t LK = 1;  // number of assembled K copies (L when sections vary per case, else 1)
   obgpu::DevBuf<int32_t> d_seg_ptr, d_seg_src, d_sl_ptr, d_ff_col, d_ff_src, d_ff_diag, d_bf_rowptr, d_bf_col, d_bf_src,
-      d_fseg_ptr, d_fseg_src, d_elem_node0, d_elem_f0, d_eload_elem_g;
-  obgpu::DevBuf<double> d_elem_k, d_kval, d_ff_val, d_bf_val, d_eload_g, d_Eq, d_scal, d_partial;
+      d_fseg_ptr, d_fseg_src, d_elem_node0, d_elem_f0, d_elem_b0, d_node_f0, d_eload_elem_g, d_bb_rowptr, d_bb_col, d_bb_src;
+  obgpu::DevBuf<double> d_elem_k, d_kval, d_ff_val, d_bf_val, d_bb_val, d_rhs, d_eload_g, d_Eq, d_scal, d_partial;
   obgpu::DevBuf<double> d_pcgvec;  // p | ap | r | z | minv in one slab: the L2 persistence window of the PCG loop
   obgpu::DevBuf<unsigned int> d_counter;
   obgpu::DevBuf<int32_t> d_blk_elem_ptr, d_blk_elems;

@@ -87,6 +87,13 @@ struct SparseDev {
   const uint2* elem_nodes; const uint8_t* elem_type; const double2* node_xy;
   const int32_t* elem_node0;   // [Etot] first node of the element's structure
   const int32_t* elem_f0;      // [Etot] first free DOF of the element's structure
+  const int32_t* elem_b0;      // [Etot] first bounded DOF of the element's structure
+  const int32_t* node_f0;      // [Ntot] first free DOF of the node's structure
+  const double* node_rot;      // [Ntot] nodal frame yaw, or null when every node frame is the identity
+  const double* U_b;           // [nb] prescribed displacements (nodal frames), or null when all are zero
+  int64_t Ntot;
+  const int32_t *bb_rowptr, *bb_col, *bb_src;  // K_bb (upper, as the reference stores it): rows / cols = bounded indices
+  double* bb_val;
   const int32_t* node_slot; const int32_t* el_ptr; const int32_t* el_order;
   const int32_t* eload_elem_g; // [ELtot] global element of each element load (caller slot order)
   const double* eload_dir;
@@ -172,6 +179,8 @@ cudaError_t launch_pcg_restart(const PcgArgs& a, int it, int sm_count, cudaStrea
 cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t st);
 cudaError_t launch_inv_diag(int64_t nf, const int32_t* ff_diag, const double* ff_val, double* minv, cudaStream_t st);
 cudaError_t launch_reactions(const SparseDev& d, const double* U_f, double* F_b, cudaStream_t st);
+// rhs = F_f - K_bf^T U_b (solver_static.cpp:37-43), deterministic (bounded rows applied one after the other)
+cudaError_t launch_rhs_prescribed(const SparseDev& d, const double* F_f, double* rhs, cudaStream_t st);
 
 // ---- device-side symbolic phase (kernels_symbolic.cu) ----
 enum { SYM_E_ELEM_NODE = 1, SYM_E_UNINIT, SYM_E_ELEM_TYPE, SYM_E_ZERO_LEN, SYM_E_NONPLANAR, SYM_E_CONSTRAINT, SYM_E_NLOAD,

@@ -46,51 +46,6 @@ __device__ __forceinline__ void cid_pair(int cid, int& a, int& b) {
   }
 }
 
-// ---- general path: nodal rotated frames and non-zero prescribed displacements ----------------------
-// Compact element block -> full symmetric 6x6 over (end0 x,y,rz, end1 x,y,rz).
-__device__ __forceinline__ double ke_at(const double* ke, int a, int b) {
-  if (a > b) { const int t = a; a = b; b = t; }
-  if (b < 3) return ke[a == 0 ? b : a == 1 ? 2 + b : 5];
-  if (a >= 3) return ke[6 + (a == 3 ? b - 3 : a == 4 ? b - 1 : 5)];
-  return ke[12 + 3 * a + (b - 3)];
-}
-// assemble.cpp:144-179: K_ij <- T_i^T K_ij T_j on every 3x3 sub-block, T = nodal frame (a rotation about z by the
-// node's yaw: Q = [[c,-s,0],[s,c,0],[0,0,1]] on (x,y,rz)).  (ci,si)/(cj,sj) = cos/sin of end 0 / end 1.
-__device__ __forceinline__ void rotate_nodal(double* ke, double ci, double si, double cj, double sj) {
-  double B[3][3][3];  // [block K11,K22,K12][r][c]
-#pragma unroll
-  for (int r = 0; r < 3; r++)
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-      B[0][r][c] = ke_at(ke, r, c);
-      B[1][r][c] = ke_at(ke, 3 + r, 3 + c);
-      B[2][r][c] = ke_at(ke, r, 3 + c);
-    }
-#pragma unroll
-  for (int k = 0; k < 3; k++) {
-    const double cl = k == 1 ? cj : ci, sl = k == 1 ? sj : si;  // left factor: node of the block's rows
-    const double cr = k == 0 ? ci : cj, sr = k == 0 ? si : sj;  // right factor: node of the block's columns
-#pragma unroll
-    for (int c = 0; c < 3; c++) {  // Q_l^T B
-      const double b0 = B[k][0][c], b1 = B[k][1][c];
-      B[k][0][c] = cl * b0 + sl * b1;
-      B[k][1][c] = -sl * b0 + cl * b1;
-    }
-#pragma unroll
-    for (int r = 0; r < 3; r++) {  // B Q_r
-      const double b0 = B[k][r][0], b1 = B[k][r][1];
-      B[k][r][0] = cr * b0 + sr * b1;
-      B[k][r][1] = -sr * b0 + cr * b1;
-    }
-  }
-  ke[0] = B[0][0][0]; ke[1] = B[0][0][1]; ke[2] = B[0][0][2]; ke[3] = B[0][1][1]; ke[4] = B[0][1][2]; ke[5] = B[0][2][2];
-  ke[6] = B[1][0][0]; ke[7] = B[1][0][1]; ke[8] = B[1][0][2]; ke[9] = B[1][1][1]; ke[10] = B[1][1][2]; ke[11] = B[1][2][2];
-#pragma unroll
-  for (int r = 0; r < 3; r++)
-#pragma unroll
-    for (int c = 0; c < 3; c++) ke[12 + 3 * r + c] = B[2][r][c];
-}
-
 // Flattened trailing triangle of one column step (see stage B): entry e = r*32 + lane is (p, q), 1 <= q <= p, rows p
 // in order, i.e. the entries of rows p <= m are exactly e < m(m+1)/2.  Byte offsets from the pivot (j, j):
 //   V(j+p, j+q) at (p*(W-1) + q)*8,   V(j+p, j) at p*(W-1)*8,   V(j+q, j) at q*(W-1)*8.

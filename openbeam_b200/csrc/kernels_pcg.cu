@@ -235,21 +235,28 @@ cudaError_t launch_inv_diag(int64_t nf, const int32_t* ff_diag, const double* ff
 }
 
 // F_b = K_bf U_f - equivalent loads on the bounded DOFs (solver_static.cpp:196-218); one warp per bounded row
+// bb_*: K_bb U_b with K_bb holding its upper triangle only, used as a general matrix (assemble.cpp:258-262,
+// solver_static.cpp:197: SURVEY quirk Q1); null when every prescribed displacement is zero
 __global__ void __launch_bounds__(256) k_reactions(int64_t nb, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
                                                    const double* __restrict__ val, const double* __restrict__ U,
-                                                   const double* __restrict__ Eq, double* __restrict__ F_b) {
+                                                   const double* __restrict__ Eq, const int32_t* __restrict__ bb_rowptr,
+                                                   const int32_t* __restrict__ bb_col, const double* __restrict__ bb_val,
+                                                   const double* __restrict__ U_b, double* __restrict__ F_b) {
   const int64_t row = (int64_t(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (row >= nb) return;
   double s = 0.0;
   for (int32_t k = rowptr[row] + lane; k < rowptr[row + 1]; k += 32) s += val[k] * U[col[k]];
+  if (U_b)
+    for (int32_t k = bb_rowptr[row] + lane; k < bb_rowptr[row + 1]; k += 32) s += bb_val[k] * U_b[bb_col[k]];
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane == 0) F_b[row] = s - Eq[row];
 }
 cudaError_t launch_reactions(const SparseDev& d, const double* U_f, double* F_b, cudaStream_t st) {
   if (d.nb == 0) return cudaSuccess;
-  k_reactions<<<unsigned((d.nb * 32 + 255) / 256), 256, 0, st>>>(d.nb, d.bf_rowptr, d.bf_col, d.bf_val, U_f, d.Eq, F_b);
+  k_reactions<<<unsigned((d.nb * 32 + 255) / 256), 256, 0, st>>>(d.nb, d.bf_rowptr, d.bf_col, d.bf_val, U_f, d.Eq, d.bb_rowptr,
+                                                                  d.bb_col, d.bb_val, d.U_b, F_b);
   return cudaGetLastError();
 }
 

@@ -18,7 +18,7 @@ namespace obgpu {
 __global__ void __launch_bounds__(256) k_elem_stiff(int64_t Etot, const uint2* __restrict__ elem_nodes,
                                                     const uint8_t* __restrict__ elem_type, const double* __restrict__ eai,
                                                     const double2* __restrict__ node_xy, const int32_t* __restrict__ elem_node0,
-                                                    double* __restrict__ elem_k) {
+                                                    const double* __restrict__ node_rot, double* __restrict__ elem_k) {
   // a lane's 21 values are a 168-byte record: staged per warp in shared memory (odd stride: conflict-free) and
   // written as 32 consecutive doubles per instruction instead of 32 scattered 8-byte stores
   __shared__ double stg[8][32 * ELEM_K];
@@ -32,6 +32,10 @@ __global__ void __launch_bounds__(256) k_elem_stiff(int64_t Etot, const uint2* _
     const ElemLocalK lk = elem_local_k(elem_type[e], eai[3 * e], eai[3 * e + 1], eai[3 * e + 2], g);
     double ke[ELEM_K];
     elem_global_k(lk, g, ke);
+    if (node_rot) {  // assemble.cpp:144-179: blocks of nodes with a rotated frame go to nodal coordinates
+      const double r0 = node_rot[n0 + nd.x], r1 = node_rot[n0 + nd.y];
+      if (r0 != 0.0 || r1 != 0.0) rotate_nodal(ke, cos(r0), sin(r0), cos(r1), sin(r1));
+    }
 #pragma unroll
     for (int k = 0; k < ELEM_K; k++) stg[warp][lane * ELEM_K + k] = ke[k];
   }
@@ -93,7 +97,8 @@ __global__ void __launch_bounds__(ASM_THREADS) k_assemble_fused(int64_t nnz, con
                                                         const int32_t* __restrict__ blk_elem_ptr, const int32_t* __restrict__ blk_elems,
                                                         const uint2* __restrict__ elem_nodes, const uint8_t* __restrict__ elem_type,
                                                         const double* __restrict__ eai, const double2* __restrict__ node_xy,
-                                                        const int32_t* __restrict__ elem_node0, double* __restrict__ kval) {
+                                                        const int32_t* __restrict__ elem_node0, const double* __restrict__ node_rot,
+                                                        double* __restrict__ kval) {
   extern __shared__ double kes[];  // [nloc][ELEM_K]
   constexpr int SPT = ASM_SPT;
   const int64_t g = int64_t(blockIdx.x) * ASM_SLOTS + SPT * threadIdx.x;
@@ -110,6 +115,10 @@ __global__ void __launch_bounds__(ASM_THREADS) k_assemble_fused(int64_t nnz, con
     const ElemLocalK lk = elem_local_k(elem_type[e], eai[3 * e], eai[3 * e + 1], eai[3 * e + 2], g);
     double ke[ELEM_K];
     elem_global_k(lk, g, ke);
+    if (node_rot) {
+      const double r0 = node_rot[n0 + nd.x], r1 = node_rot[n0 + nd.y];
+      if (r0 != 0.0 || r1 != 0.0) rotate_nodal(ke, cos(r0), sin(r0), cos(r1), sin(r1));
+    }
 #pragma unroll
     for (int k = 0; k < ELEM_K; k++) kes[i * ELEM_K + k] = ke[k];
   }
@@ -148,6 +157,14 @@ __global__ void __launch_bounds__(ASM_THREADS) k_assemble_fused(int64_t nnz, con
   }
 }
 
+// values of a CSR matrix whose entries are K slots (K_bb): thread per row
+__global__ void __launch_bounds__(256) k_gather_rows(int64_t nrows, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ src,
+                                                     const double* __restrict__ in, double* __restrict__ out) {
+  const int64_t r = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (r >= nrows) return;
+  for (int32_t k = rowptr[r]; k < rowptr[r + 1]; k++) out[k] = in[src[k]];
+}
+
 __global__ void __launch_bounds__(256) k_gather(int64_t n, const int32_t* __restrict__ src, const double* __restrict__ in,
                                                 double* __restrict__ out) {
   const int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -172,6 +189,37 @@ __global__ void __launch_bounds__(256) k_load_vector(int64_t nf, int64_t nb, con
   else Eq[t - nf] = acc;
 }
 
+// assemble.cpp:349-435: (Fx, Fy) of a rotated node's FREE DOFs go to the nodal frame (bounded components count as 0)
+__global__ void __launch_bounds__(256) k_rotate_loads(int64_t Ntot, const double* __restrict__ node_rot,
+                                                      const int32_t* __restrict__ node_slot, const int32_t* __restrict__ node_f0,
+                                                      double* __restrict__ F_f) {
+  const int64_t n = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (n >= Ntot) return;
+  const double r = node_rot[n];
+  if (r == 0.0) return;
+  const int32_t sx = node_slot[3 * n], sy = node_slot[3 * n + 1], f0 = node_f0[n];
+  const double fx = sx >= 0 ? F_f[f0 + sx] : 0.0, fy = sy >= 0 ? F_f[f0 + sy] : 0.0;
+  const double cr = cos(r), sr = sin(r);
+  if (sx >= 0) F_f[f0 + sx] = cr * fx + sr * fy;
+  if (sy >= 0) F_f[f0 + sy] = -sr * fx + cr * fy;
+}
+
+// rhs = F_f - K_bf^T U_b: one CTA; the bounded rows are applied one after the other (entries of a row hit distinct
+// free columns), so the sum into every free DOF has a fixed order
+__global__ void __launch_bounds__(256) k_rhs_prescribed(int64_t nf, int64_t nb, const int32_t* __restrict__ bf_rowptr,
+                                                        const int32_t* __restrict__ bf_col, const double* __restrict__ bf_val,
+                                                        const double* __restrict__ U_b, const double* __restrict__ F_f,
+                                                        double* __restrict__ rhs) {
+  for (int64_t i = threadIdx.x; i < nf; i += blockDim.x) rhs[i] = F_f[i];
+  __syncthreads();
+  for (int64_t r = 0; r < nb; r++) {
+    const double ub = U_b[r];
+    if (ub != 0.0)
+      for (int32_t k = bf_rowptr[r] + threadIdx.x; k < bf_rowptr[r + 1]; k += blockDim.x) rhs[bf_col[k]] -= bf_val[k] * ub;
+    __syncthreads();
+  }
+}
+
 __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __restrict__ elem_nodes,
                                                 const uint8_t* __restrict__ elem_type, const double* __restrict__ eai,
                                                 const double2* __restrict__ node_xy, const int32_t* __restrict__ elem_node0,
@@ -179,7 +227,8 @@ __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __res
                                                 const int32_t* __restrict__ el_ptr, const int32_t* __restrict__ el_order,
                                                 const double* __restrict__ q, const double* __restrict__ dir,
                                                 const uint8_t* __restrict__ eload_type, const double* __restrict__ eload_q2,
-                                                const double* __restrict__ U_f, double* __restrict__ stress) {
+                                                const double* __restrict__ U_f, const double* __restrict__ U_b,
+                                                const int32_t* __restrict__ elem_b0, double* __restrict__ stress) {
   __shared__ double stg[8][32 * 13];  // [lane][12] records, stride 13: conflict-free staging for coalesced stores
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t e = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -195,8 +244,9 @@ __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __res
 #pragma unroll
   for (int k = 0; k < 3; k++) {
     const int32_t t0 = node_slot[3 * (n0 + nd.x) + k], t1 = node_slot[3 * (n0 + nd.y) + k];
-    ug[k] = t0 >= 0 ? U[t0] : 0.0;
-    ug[3 + k] = t1 >= 0 ? U[t1] : 0.0;
+    // postproc_stress.cpp:50-78: U_b on bounded DOFs, U_f on free ones (nodal frames are not undone there: quirk Q6)
+    ug[k] = t0 >= 0 ? U[t0] : (U_b && t0 != SLOT_NONE) ? U_b[elem_b0[e] + (-t0 - 1)] : 0.0;
+    ug[3 + k] = t1 >= 0 ? U[t1] : (U_b && t1 != SLOT_NONE) ? U_b[elem_b0[e] + (-t1 - 1)] : 0.0;
   }
   elem_end_forces(lk, g, ug, es);
   double ext[6] = {0, 0, 0, 0, 0, 0};
@@ -224,7 +274,7 @@ __global__ void __launch_bounds__(256) k_stress(int64_t Etot, const uint2* __res
 static inline unsigned nblk(int64_t n, int b = 256) { return unsigned((n + b - 1) / b); }
 
 cudaError_t launch_elem_stiff(const SparseDev& d, const double* eai, cudaStream_t st) {
-  k_elem_stiff<<<nblk(d.Etot), 256, 0, st>>>(d.Etot, d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.elem_k);
+  k_elem_stiff<<<nblk(d.Etot), 256, 0, st>>>(d.Etot, d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.node_rot, d.elem_k);
   return cudaGetLastError();
 }
 cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st) {
@@ -240,12 +290,20 @@ cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStr
     configured = smem;
   }
   k_assemble_fused<<<nblk(d.nnz, ASM_SLOTS), ASM_THREADS, smem, st>>>(d.nnz, d.seg_ptr, d.seg_loc, d.blk_elem_ptr, d.blk_elems,
-                                                              d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.kval);
+                                                              d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.node_rot, d.kval);
   return cudaGetLastError();
 }
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st) {
   if (d.nnz_ff) k_gather<<<nblk(d.nnz_ff), 256, 0, st>>>(d.nnz_ff, d.ff_src, d.kval, d.ff_val);
   if (d.nnz_bf) k_gather<<<nblk(d.nnz_bf), 256, 0, st>>>(d.nnz_bf, d.bf_src, d.kval, d.bf_val);
+  if (d.U_b && d.bb_rowptr && d.nb) {
+    // K_bb is only needed when some prescribed displacement is non-zero (solver_static.cpp:196-198)
+    k_gather_rows<<<nblk(d.nb), 256, 0, st>>>(d.nb, d.bb_rowptr, d.bb_src, d.kval, d.bb_val);
+  }
+  return cudaGetLastError();
+}
+cudaError_t launch_rhs_prescribed(const SparseDev& d, const double* F_f, double* rhs, cudaStream_t st) {
+  k_rhs_prescribed<<<1, 256, 0, st>>>(d.nf, d.nb, d.bf_rowptr, d.bf_col, d.bf_val, d.U_b, F_f, rhs);
   return cudaGetLastError();
 }
 cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, const double* eai, double* F_f,
@@ -254,12 +312,14 @@ cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, cons
     k_elem_loads<<<nblk(d.ELtot), 256, 0, st>>>(d.ELtot, d.el_order, d.eload_elem_g, q, d.eload_dir, d.elem_nodes,
                                                  d.elem_type, d.node_xy, d.elem_node0, d.eload_type, d.eload_q2, eai, d.eload_g);
   k_load_vector<<<nblk(d.nf + d.nb), 256, 0, st>>>(d.nf, d.nb, d.fseg_ptr, d.fseg_src, nload_val, d.eload_g, F_f, d.Eq);
+  if (d.node_rot) k_rotate_loads<<<nblk(d.Ntot), 256, 0, st>>>(d.Ntot, d.node_rot, d.node_slot, d.node_f0, F_f);
   return cudaGetLastError();
 }
 cudaError_t launch_stress(const SparseDev& d, const double* eai, const double* q, const double* U_f, double* stress,
                           cudaStream_t st) {
   k_stress<<<nblk(d.Etot), 256, 0, st>>>(d.Etot, d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.elem_f0,
-                                         d.node_slot, d.el_ptr, d.el_order, q, d.eload_dir, d.eload_type, d.eload_q2, U_f, stress);
+                                         d.node_slot, d.el_ptr, d.el_order, q, d.eload_dir, d.eload_type, d.eload_q2, U_f, d.U_b, d.elem_b0,
+                                         stress);
   return cudaGetLastError();
 }
 

@@ -128,6 +128,7 @@ struct SparsePlan {
   std::vector<int32_t> ff_diag;               // [nf_tot] position of the diagonal entry inside ff_col/ff_src
   int64_t ff_nnz = 0;                         // structural entries of K_ff (without padding)
   std::vector<int32_t> bf_rowptr, bf_col, bf_src;  // K_bf: rows = global bounded index, cols = global free index
+  std::vector<int32_t> bb_rowptr, bb_col, bb_src;  // K_bb as the reference stores it (upper triangle): row b(lo), col b(hi)
   // load vector gather: target t < nf_tot -> F_f[t]; t >= nf_tot -> Eq[t - nf_tot] (equivalent loads on bounded DOFs)
   // src >= 0: ELOAD_G entry (multimap position*6 + k); src < 0: nodal load -(l+1)
   std::vector<int32_t> fseg_ptr, fseg_src;

@@ -119,6 +119,25 @@ int build_sparse_plan(const HostBatch& hb, const Symbolic& sym, SparsePlan& P, s
       P.bf_src[p] = slot;
     }
   });
+  // ---- K_bb (upper: row = bounded index of lo, column = bounded index of hi), only read when some U_b != 0 ----
+  {
+    std::vector<int32_t> cnt(nb + 1, 0);
+    for_each_entry([&](int32_t thi, int32_t tlo, bool, int64_t, int64_t b0, int32_t) {
+      if (thi < 0 && tlo < 0) cnt[b0 + (-tlo - 1) + 1]++;
+    });
+    for (int64_t r = 0; r < nb; r++) cnt[r + 1] += cnt[r];
+    P.bb_rowptr = cnt;
+    P.bb_col.resize(cnt[nb]);
+    P.bb_src.resize(cnt[nb]);
+    std::vector<int32_t> cur(cnt.begin(), cnt.end() - 1);
+    for_each_entry([&](int32_t thi, int32_t tlo, bool, int64_t, int64_t b0, int32_t slot) {
+      if (thi < 0 && tlo < 0) {
+        const int32_t p = cur[b0 + (-tlo - 1)]++;
+        P.bb_col[p] = int32_t(b0 + (-thi - 1));
+        P.bb_src[p] = slot;
+      }
+    });
+  }
   for (int64_t r = 0; r < nf; r++)
     if (P.ff_diag[r] < 0) {
       err = "free DOF without a diagonal entry in K";

@@ -216,8 +216,6 @@ def test_sub_matrices_match_oracle(ctx, name):
     storage — K_ff lower triangle only, K_bb upper triangle only (quirk Q1) — and the true-sparse K_ff CSR."""
     import fixtures
     st = fixtures.ALL[name]()
-    if st.node_rotz is not None and np.any(st.node_rotz != 0):
-        pytest.skip("rotated nodal frames are not assembled on the sparse route")
     ctx.upload(st)
     ctx.assemble()
     (kff,), (kbf,), (kbb,) = ctx.sub_matrices()
@@ -243,3 +241,23 @@ def test_sub_matrices_match_oracle(ctx, name):
     bi = BuildProblemInfo()
     CStructureProblem(st, ctx=ctx).assembleProblem(bi)
     assert np.array_equal(bi.K_ff, kff) and np.array_equal(bi.K_bf, kbf) and np.array_equal(bi.K_bb, kbb)
+
+
+@pytest.mark.parametrize("method", [obgpu.PCG_MG, obgpu.PCG_JACOBI])
+def test_pcg_rotated_frames_and_settlements(ctx, method):
+    """Nodal rotated frames (assemble.cpp:144-179, 349-435) and non-zero prescribed displacements (solver_static.cpp:37-43,
+    196-198, with the reference's upper-only K_bb, quirk Q1) on the sparse route: every fixture + the settlement cases of
+    the batched-LDLt tests in one batch, each structure solved by its own PCG, against the oracle."""
+    import fixtures
+    from test_gpu_frame import settlement_cases
+    sts = [fixtures.ALL[k]() for k in fixtures.ALL] + settlement_cases()
+    ctx.upload(sts)
+    ctx.solve_static(method=method, rtol=1e-13, max_iter=5000)
+    U, Fb, S = (ctx.download(w)[0] for w in (obgpu.RES_UF, obgpu.RES_FB, obgpu.RES_STRESS))
+    fo, bo = ctx.offsets(obgpu.OFF_FREE), ctx.offsets(obgpu.OFF_BOUNDED)
+    eo = np.concatenate([[0], np.cumsum([s.n_elems for s in sts])])
+    for s, st in enumerate(sts):
+        od = OracleProblem(st).solveStatic().postProcCalcStress()
+        assert relerr(U[fo[s]:fo[s + 1]], od.U_f) <= RTOL, s
+        assert relerr(Fb[bo[s]:bo[s + 1]], od.F_b) <= RTOL, s
+        assert relerr(S[eo[s]:eo[s + 1]], od.element_stress) <= RTOL, s
