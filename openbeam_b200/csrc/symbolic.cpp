@@ -98,8 +98,8 @@ int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want
   sym.half_bw.assign(S, 0);
   sym.has_pattern = want_pattern;
   std::vector<unsigned> node_mask;
-  std::vector<int64_t> keys;       // per-structure triplet keys col*n+row
-  std::vector<int64_t> uniq;
+  std::vector<int32_t> t_hi, t_lo;   // per-structure triplets: CSC(upper) column / row
+  std::vector<int32_t> colstart, bucket, colrows;
   std::vector<int32_t> order;
 
   for (int64_t s = 0; s < S; s++) {
@@ -232,8 +232,16 @@ int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want
       continue;
     }
     // ---- triplets in the reference's emission order (assemble.cpp:123-223) ----
-    keys.clear();
+    // (column hi, row lo) of CSC(upper) per triplet; the pattern is then built by a counting sort over the columns and a
+    // small sorted-unique pass inside each column (a column holds a few dozen entries at most): O(T), no global sort
+    t_hi.clear();
+    t_lo.clear();
     const size_t t0 = sym.tri_src.size();
+    t_hi.reserve(size_t(21) * E);
+    t_lo.reserve(size_t(21) * E);
+    sym.tri_src.reserve(t0 + size_t(21) * E);
+    sym.k_col.reserve(sym.k_col.size() + size_t(6) * N + size_t(9) * E);
+    sym.seg_ptr.reserve(sym.seg_ptr.size() + size_t(6) * N + size_t(9) * E);
     for (int64_t e = 0; e < E; e++) {
       const uint32_t nd[2] = {hb.elem_nodes[2 * (e0 + e)], hb.elem_nodes[2 * (e0 + e) + 1]};
       static const int bi[3] = {0, 1, 0}, bj[3] = {0, 1, 1};
@@ -245,42 +253,50 @@ int run_symbolic(const HostBatch& hb, Symbolic& sym, std::string& err, bool want
           if (ri[r] < 0) continue;
           for (int c = (in == jn ? r : 0); c < 6; c++) {
             if (ci[c] < 0) continue;
-            const int64_t lo = std::min(ri[r], ci[c]), hi = std::max(ri[r], ci[c]);
-            keys.push_back(hi * int64_t(n) + lo);  // CSC(upper): column = hi, row = lo
+            t_lo.push_back(std::min(ri[r], ci[c]));   // CSC(upper): column = hi, row = lo
+            t_hi.push_back(std::max(ri[r], ci[c]));
             const int cid = elemk_cid(j, r, c);
             sym.tri_src.push_back(cid < 0 ? -1 : int32_t(e * ELEM_K + cid));
           }
         }
       }
     }
-    const size_t T = keys.size();
+    const size_t T = t_hi.size();
     sym.tri_off[s + 1] = sym.tri_off[s] + int64_t(T);
-    // ---- pattern: unique keys sorted by (col,row) == Eigen's compressed CSC after setFromTriplets ----
-    uniq = keys;
-    std::sort(uniq.begin(), uniq.end());
-    uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
-    const int64_t z0 = sym.nnz_off[s];
-    const int64_t nnz = int64_t(uniq.size());
-    sym.nnz_off[s + 1] = z0 + nnz;
+    // ---- pattern: per column the sorted unique rows == Eigen's compressed CSC after setFromTriplets ----
+    colstart.assign(size_t(n) + 1, 0);
+    for (size_t t = 0; t < T; t++) colstart[size_t(t_hi[t]) + 1]++;
+    for (int32_t k = 0; k < n; k++) colstart[size_t(k) + 1] += colstart[size_t(k)];
+    bucket.resize(T);
     {
-      const size_t rp0 = sym.k_rowptr.size();
-      sym.k_rowptr.resize(rp0 + n + 1, 0);
-      int32_t* rp = &sym.k_rowptr[rp0];
-      for (int64_t u : uniq) {
-        rp[u / n + 1]++;
-        sym.k_col.push_back(int32_t(u % n));
-      }
-      for (int32_t k = 0; k < n; k++) rp[k + 1] += rp[k];
+      std::vector<int32_t> fill(colstart.begin(), colstart.end() - 1);
+      for (size_t t = 0; t < T; t++) bucket[size_t(fill[size_t(t_hi[t])]++)] = int32_t(t);   // stable: triplet order kept
     }
-    // ---- triplet -> slot, and per-slot source lists in triplet order (stable counting sort) ----
+    const int64_t z0 = sym.nnz_off[s];
+    const size_t rp0 = sym.k_rowptr.size();
+    sym.k_rowptr.resize(rp0 + n + 1, 0);
     const size_t tn0 = sym.tri_nnz.size();
     sym.tri_nnz.resize(tn0 + T);
-    std::vector<int64_t> cnt(nnz + 1, 0);
-    for (size_t t = 0; t < T; t++) {
-      const int32_t slot = int32_t(std::lower_bound(uniq.begin(), uniq.end(), keys[t]) - uniq.begin());
-      sym.tri_nnz[tn0 + t] = slot;
-      cnt[slot + 1]++;
+    int32_t nnz32 = 0;
+    for (int32_t hi = 0; hi < n; hi++) {
+      colrows.clear();
+      for (int32_t p = colstart[size_t(hi)]; p < colstart[size_t(hi) + 1]; p++) colrows.push_back(t_lo[size_t(bucket[size_t(p)])]);
+      std::sort(colrows.begin(), colrows.end());
+      colrows.erase(std::unique(colrows.begin(), colrows.end()), colrows.end());
+      for (int32_t p = colstart[size_t(hi)]; p < colstart[size_t(hi) + 1]; p++) {
+        const int32_t t = bucket[size_t(p)];
+        const int32_t at = int32_t(std::lower_bound(colrows.begin(), colrows.end(), t_lo[size_t(t)]) - colrows.begin());
+        sym.tri_nnz[tn0 + size_t(t)] = nnz32 + at;
+      }
+      for (int32_t lo : colrows) sym.k_col.push_back(lo);
+      nnz32 += int32_t(colrows.size());
+      sym.k_rowptr[rp0 + size_t(hi) + 1] = nnz32;
     }
+    const int64_t nnz = nnz32;
+    sym.nnz_off[s + 1] = z0 + nnz;
+    // ---- per-slot source lists in triplet order (stable counting sort) ----
+    std::vector<int64_t> cnt(nnz + 1, 0);
+    for (size_t t = 0; t < T; t++) cnt[sym.tri_nnz[tn0 + t] + 1]++;
     for (int64_t g = 0; g < nnz; g++) cnt[g + 1] += cnt[g];
     const int64_t sp0 = sym.seg_ptr.back();
     for (int64_t g = 1; g <= nnz; g++) sym.seg_ptr.push_back(sp0 + cnt[g]);
