@@ -20,6 +20,9 @@
 
 namespace obgpu {
 
+#ifndef OBGPU_FRAME_MINB
+#define OBGPU_FRAME_MINB(MAXR) ((MAXR) <= 6 ? 5 : 4)   // CTAs per SM the register allocation aims at
+#endif
 constexpr int STAGE_D = 27;  // doubles staged per element: 21 stiffness + 6 equivalent loads
 constexpr int CHUNK = 16;    // elements staged at a time
 
@@ -102,7 +105,7 @@ __device__ __forceinline__ void trailing_update(char* bj, const TriMap<MAXR>& tm
 // GEN: the general path (nodal rotated frames and/or non-zero prescribed displacements) is a separate
 // instantiation so that its extra state never costs the common kernel a register.
 template <int MAXR, bool GEN>
-__global__ void __launch_bounds__(FRAME_WARPS * 32, MAXR <= 6 ? 5 : 4) k_frame_fused(FrameArgs a, int doubles_per_warp) {
+__global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_frame_fused(FrameArgs a, int doubles_per_warp) {
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* band = smem + size_t(warp) * doubles_per_warp;
