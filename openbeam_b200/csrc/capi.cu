@@ -26,6 +26,7 @@ int batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d);   // capi_devs
 int symbolic_device(obgpu_ctx* c);
 int materialize_host_batch(obgpu_ctx* c);
 int symbolic_general(obgpu_ctx* c, int which, int32_t* out, int64_t* count);   // capi_sparse.cu
+int fetch_host_offsets(obgpu_ctx* c);                                           // capi_devsym.cu
 }
 using namespace obgpu;
 
@@ -292,6 +293,7 @@ int obgpu_symbolic(obgpu_ctx* c) {
   }
   c->any_ub = false;
   for (double v : c->sym.U_b) c->any_ub |= v != 0.0;
+  c->host_offsets_valid = true;
   c->t_symbolic_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   return OBGPU_OK;
 }
@@ -307,6 +309,10 @@ int obgpu_get_sizes(const obgpu_ctx* c, int64_t out[OBGPU_NSIZES]) {
 
 int obgpu_get_offsets(const obgpu_ctx* c, int which, int64_t* out) {
   if (!c || !out || !c->sym.valid) return OBGPU_ESEQUENCE;
+  if (!c->host_offsets_valid) {  // a device batch keeps its per-structure offsets in HBM until somebody asks
+    const int rc = fetch_host_offsets(const_cast<obgpu_ctx*>(c));
+    if (rc != OBGPU_OK) return rc;
+  }
   const std::vector<int64_t>* v = nullptr;
   switch (which) {
     case OBGPU_OFF_DOF: v = &c->sym.dof_off; break;

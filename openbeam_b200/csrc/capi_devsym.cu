@@ -131,7 +131,13 @@ int symbolic_device(obgpu_ctx* c) {
   OB_CUDA(c, c->d_Ub.reserve(std::max<size_t>(size_t(C), 1)));
   OB_CUDA(c, c->d_bnd_dofid.reserve(std::max<size_t>(size_t(C), 1)));
   OB_CUDA(c, c->d_sym_error.reserve(4));
+  const int64_t nchunk = (S + 1023) / 1024;
+  OB_CUDA(c, c->d_sym_partial.reserve(size_t(3 * (nchunk + 1))));
+  OB_CUDA(c, c->d_sym_cls.reserve(size_t(S)));
+  OB_CUDA(c, c->d_sym_cls_stats.reserve(size_t(FRAME_NCLS) * 5 + FRAME_NCLS));
+  OB_CUDA(c, c->d_frame_order.reserve(size_t(S)));
   OB_CUDA(c, cudaMemsetAsync(c->d_sym_error.p, 0, 4 * sizeof(int32_t), st));
+  OB_CUDA(c, cudaMemsetAsync(c->d_sym_cls_stats.p, 0, (size_t(FRAME_NCLS) * 5 + FRAME_NCLS) * sizeof(int32_t), st));
   SymDev d;
   d.S = S;
   d.node_off = c->d_off_node.p; d.elem_off = c->d_off_elem.p; d.con_off = c->d_off_con.p;
@@ -149,13 +155,15 @@ int symbolic_device(obgpu_ctx* c) {
   d.node_slot = c->d_node_slot.p; d.nload_slot = c->d_nload_slot.p; d.el_ptr = c->d_el_ptr.p; d.el_order = c->d_el_order.p;
   d.el_cursor = c->d_sym_cursor.p; d.meta = c->d_meta.p; d.U_b = c->d_Ub.p; d.bnd_dofid = c->d_bnd_dofid.p;
   d.error = c->d_sym_error.p;
+  d.scan_partial = c->d_sym_partial.p; d.cls = c->d_sym_cls.p; d.cls_stats = c->d_sym_cls_stats.p;
   OB_CUDA(c, launch_symbolic_device(d, st));
-  // what the host keeps: the per-structure counts (-> offsets, size classes) and the error word
-  std::vector<int32_t> counts;
-  counts.resize(size_t(4 * S));
+  // what comes back to the host: the error word, the three totals and 18 x 5 class statistics — a few hundred bytes
   int32_t err[4] = {0, 0, 0, 0};
-  OB_CUDA(c, cudaMemcpyAsync(counts.data(), c->d_sym_counts.p, counts.size() * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  int32_t stats[FRAME_NCLS * 5];
+  int64_t totals[3] = {0, 0, 0};
   OB_CUDA(c, cudaMemcpyAsync(err, c->d_sym_error.p, sizeof(err), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(c, cudaMemcpyAsync(stats, c->d_sym_cls_stats.p, sizeof(stats), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(c, cudaMemcpyAsync(totals, c->d_sym_partial.p + 3 * nchunk, sizeof(totals), cudaMemcpyDeviceToHost, st));
   OB_CUDA(c, cudaStreamSynchronize(st));
   if (err[0] != 0) {
     char msg[256];
@@ -163,28 +171,53 @@ int symbolic_device(obgpu_ctx* c) {
     return fail(c, OBGPU_EINVAL, msg);
   }
   Symbolic& sy = c->sym;
-  sy = Symbolic();
-  sy.dof_off.assign(size_t(S + 1), 0); sy.free_off.assign(size_t(S + 1), 0); sy.bnd_off.assign(size_t(S + 1), 0);
-  sy.nnz_off.assign(size_t(S + 1), 0); sy.tri_off.assign(size_t(S + 1), 0);
-  sy.half_bw.resize(size_t(S));
-  std::vector<int32_t> nf, nb, hbw;
-  nf.resize(size_t(S)); nb.resize(size_t(S)); hbw.resize(size_t(S));
-  for (int64_t s = 0; s < S; s++) {
-    const int32_t* k = &counts[size_t(4 * s)];
-    sy.dof_off[size_t(s + 1)] = sy.dof_off[size_t(s)] + k[0];
-    sy.free_off[size_t(s + 1)] = sy.free_off[size_t(s)] + k[1];
-    sy.bnd_off[size_t(s + 1)] = sy.bnd_off[size_t(s)] + k[2];
-    sy.half_bw[size_t(s)] = k[3];
-    nf[size_t(s)] = k[1]; nb[size_t(s)] = k[2]; hbw[size_t(s)] = std::min(k[3], std::max(k[1] - 1, 0));
+  const bool keep = sy.valid && !sy.has_pattern && int64_t(sy.dof_off.size()) == S + 1 && sy.dof_node.empty();
+  if (!keep) {
+    sy = Symbolic();
+    sy.dof_off.assign(size_t(S + 1), 0); sy.free_off.assign(size_t(S + 1), 0); sy.bnd_off.assign(size_t(S + 1), 0);
+    sy.nnz_off.assign(size_t(S + 1), 0); sy.tri_off.assign(size_t(S + 1), 0);
   }
+  // per-structure offsets stay on the device (obgpu_get_offsets fetches them on demand); the totals size every result
+  sy.dof_off.back() = totals[0]; sy.free_off.back() = totals[1]; sy.bnd_off.back() = totals[2];
+  c->host_offsets_valid = false;
   sy.has_pattern = false;
   sy.valid = true;
   c->any_ub = err[2] != 0;
   c->frame_renumbered = false;
-  int rc = build_frame_classes(c, nf, nb, hbw);
-  if (rc != OBGPU_OK) return rc;
+  // size classes from the device statistics; the order array is filled by one more kernel from the class starts
+  c->frame_classes.clear();
+  c->max_band = c->max_nf = c->max_nb = 0;
+  int32_t starts[FRAME_NCLS];
+  int64_t run = 0;
+  for (int k = 0; k < FRAME_NCLS; k++) {
+    const int32_t* sk = stats + 5 * k;
+    starts[k] = int32_t(run);
+    if (sk[0] > 0) {
+      c->frame_classes.push_back(obgpu_ctx::FrameClass{run, run + sk[0], sk[1], sk[2], sk[3], sk[4]});
+      c->max_band = std::max(c->max_band, sk[1]);
+      c->max_nf = std::max(c->max_nf, sk[2]);
+      c->max_nb = std::max(c->max_nb, sk[3]);
+    }
+    run += sk[0];
+  }
+  int32_t* d_cursor = c->d_sym_cls_stats.p + FRAME_NCLS * 5;
+  OB_CUDA(c, cudaMemcpyAsync(d_cursor, starts, sizeof(starts), cudaMemcpyHostToDevice, st));
+  OB_CUDA(c, launch_symbolic_order(S, c->d_sym_cls.p, d_cursor, c->d_frame_order.p, st));
+  OB_CUDA(c, cudaStreamSynchronize(st));  // starts is a stack array
   c->dev_batch = true;
   c->t_symbolic_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  return OBGPU_OK;
+}
+
+// per-structure DOF / free / bounded offsets of a device batch, fetched when a caller asks for them
+int fetch_host_offsets(obgpu_ctx* c) {
+  if (c->host_offsets_valid) return OBGPU_OK;
+  const size_t n = size_t(c->hb.S + 1);
+  OB_CUDA(c, cudaMemcpyAsync(c->sym.dof_off.data(), c->d_dof_off.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
+  OB_CUDA(c, cudaMemcpyAsync(c->sym.free_off.data(), c->d_free_off.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
+  OB_CUDA(c, cudaMemcpyAsync(c->sym.bnd_off.data(), c->d_bnd_off.p, n * 8, cudaMemcpyDeviceToHost, c->stream));
+  OB_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->host_offsets_valid = true;
   return OBGPU_OK;
 }
 

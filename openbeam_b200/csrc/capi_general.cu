@@ -15,15 +15,8 @@ int build_frame_classes(obgpu_ctx* c, const std::vector<int32_t>& nf, const std:
 // occupancy.  Inputs per structure: n_f, n_b and the half bandwidth the kernel will use.
 int build_frame_classes(obgpu_ctx* c, const std::vector<int32_t>& nf, const std::vector<int32_t>& nb, const std::vector<int32_t>& hbw) {
   const int64_t S = int64_t(nf.size());
-  static const int64_t kClassLimit[] = {256, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2560, 3072, 4096, 6144, 8192,
-                                        12288, 16384, 24576, INT64_MAX};
-  constexpr int NCLS = int(sizeof(kClassLimit) / sizeof(kClassLimit[0]));
-  auto cls_of = [&](int64_t s) {
-    const int64_t need = int64_t(hbw[size_t(s)] + 1) * nf[size_t(s)] + 2 * int64_t(nf[size_t(s)]) + 2 * int64_t(nb[size_t(s)]);
-    int k = 0;
-    while (need > kClassLimit[k]) k++;
-    return k;
-  };
+  constexpr int NCLS = FRAME_NCLS;
+  auto cls_of = [&](int64_t s) { return frame_class_of(hbw[size_t(s)], nf[size_t(s)], nb[size_t(s)]); };
   c->max_band = c->max_nf = c->max_nb = 0;
   std::vector<uint8_t> cls;
   cls.resize(size_t(S));

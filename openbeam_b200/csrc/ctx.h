@@ -26,7 +26,10 @@ struct obgpu_ctx {
   obgpu::DevBuf<uint32_t> d_con_node, d_nload_node, d_eload_elem;
   obgpu::DevBuf<uint8_t> d_con_dof, d_nload_dof, d_sym_mask;
   obgpu::DevBuf<double> d_con_val, d_sym_cval;
-  obgpu::DevBuf<int32_t> d_sym_counts, d_sym_cursor, d_sym_error;
+  obgpu::DevBuf<int32_t> d_sym_counts, d_sym_cursor, d_sym_error, d_sym_cls_stats;
+  obgpu::DevBuf<int64_t> d_sym_partial;
+  obgpu::DevBuf<uint8_t> d_sym_cls;
+  bool host_offsets_valid = true;                // device batch mode: dof/free/bounded offsets are fetched on demand
   int64_t L = 1;
   bool has_case_nl = false, has_case_q = false, has_case_eai = false;
 

@@ -201,8 +201,23 @@ struct SymDev {
   FrameMeta* meta;
   double* U_b; uint8_t* bnd_dofid;
   int32_t* error;          // [0] first error code (SYM_E_*), [1] its structure, [2] any U_b != 0
+  int64_t* scan_partial;   // [3 * (chunks + 1)] scratch of the scans; the last triple = totals (n, n_f, n_b)
+  uint8_t* cls;            // [S] size class of every structure
+  int32_t* cls_stats;      // [FRAME_NCLS][5] count, max_band, max_nf, max_nb, max_hb (zeroed by the caller)
 };
 cudaError_t launch_symbolic_device(const SymDev& d, cudaStream_t st);
+cudaError_t launch_symbolic_order(int64_t S, const uint8_t* cls, int32_t* cursor, int32_t* order, cudaStream_t st);
+
+// Size classes of the warp-per-structure kernel: a structure's shared-memory need (band + vectors, in doubles) bucketed
+constexpr int FRAME_NCLS = 18;
+__host__ __device__ inline int frame_class_of(int hb, int nf, int nb) {
+  const long long need = (long long)(hb + 1) * nf + 2LL * nf + 2LL * nb;
+  const long long lim[FRAME_NCLS - 1] = {256, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2560, 3072, 4096, 6144, 8192, 12288,
+                                          16384, 24576};
+  int k = 0;
+  while (k < FRAME_NCLS - 1 && need > lim[k]) k++;
+  return k;
+}
 
 struct SummaryArgs {
   int64_t L, S, nf_tot, nb_tot;

@@ -5,7 +5,7 @@
 //   free / bounded partition, U_b   assemble.cpp:74-99, :304-313 (+ nodal-frame rotation of U_b, :349-435)
 // as three kernels over the batch already in HBM — thread = structure (structures here have tens of nodes):
 //   k_sym_count  validates the structure, ORs the element-end masks into its nodes, marks constrained DOFs, counts n/n_f/n_b
-//   k_sym_scan   exclusive scans of the three counts over the structures (one CTA): DOF / free / bounded offsets
+//   k_sym_scan_* exclusive scans of the three counts over the structures (chunk sums, bases, apply): DOF / free / bounded offsets
 //   k_sym_fill   per-node slots (free index >= 0, bounded < 0), U_b, nodal-load slots, the element-load multimap order,
 //                half bandwidth and the per-structure record the batched-LDLt kernel reads
 // What it produces is bit-identical to the host phase (symbolic.cpp), which tests/test_gpu_devsym.py checks.
@@ -148,27 +148,73 @@ __global__ void __launch_bounds__(128) k_sym_count(SymDev d) {
   cnt[0] = n; cnt[1] = n - nb; cnt[2] = nb;
 }
 
-// exclusive scans of counts[.][0..2] over the structures, one CTA: every thread owns a contiguous run
-__global__ void __launch_bounds__(1024) k_sym_scan(int64_t S, const int32_t* __restrict__ counts, int64_t* __restrict__ dof_off,
-                                                   int64_t* __restrict__ free_off, int64_t* __restrict__ bnd_off) {
-  __shared__ int64_t part[3][1024];
-  const int t = threadIdx.x;
-  const int64_t per = (S + 1023) / 1024, a = min(S, per * t), b = min(S, a + per);
-  int64_t s0 = 0, s1 = 0, s2 = 0;
-  for (int64_t i = a; i < b; i++) { s0 += counts[4 * i]; s1 += counts[4 * i + 1]; s2 += counts[4 * i + 2]; }
-  part[0][t] = s0; part[1][t] = s1; part[2][t] = s2;
+// exclusive scans of counts[.][0..2] over the structures: per-CTA partial sums, a one-CTA scan of the partials, then every
+// CTA rescans its own chunk from its base (thread = structure inside the chunk; fixed order, integers: exact)
+constexpr int SCAN_CHUNK = 1024;
+__global__ void __launch_bounds__(SCAN_CHUNK) k_sym_scan_partial(int64_t S, const int32_t* __restrict__ counts,
+                                                                   int64_t* __restrict__ partial /* [nchunk][3] */) {
+  __shared__ int64_t red[3][SCAN_CHUNK / 32];
+  const int64_t i = int64_t(blockIdx.x) * SCAN_CHUNK + threadIdx.x;
+  const int4 c = i < S ? reinterpret_cast<const int4*>(counts)[i] : make_int4(0, 0, 0, 0);
+  int64_t v[3] = {c.x, c.y, c.z};
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    if ((threadIdx.x & 31) == 0) red[k][threadIdx.x >> 5] = v[k];
+  }
   __syncthreads();
-  if (t < 3) {
+  if (threadIdx.x < 3) {
+    int64_t t = 0;
+    for (int w = 0; w < SCAN_CHUNK / 32; w++) t += red[threadIdx.x][w];
+    partial[3 * int64_t(blockIdx.x) + threadIdx.x] = t;
+  }
+}
+__global__ void k_sym_scan_bases(int64_t nchunk, int64_t* __restrict__ partial) {  // in place: sums -> exclusive bases
+  if (threadIdx.x < 3) {
     int64_t run = 0;
-    for (int k = 0; k < 1024; k++) { const int64_t v = part[t][k]; part[t][k] = run; run += v; }
+    for (int64_t k = 0; k < nchunk; k++) {
+      const int64_t v = partial[3 * k + threadIdx.x];
+      partial[3 * k + threadIdx.x] = run;
+      run += v;
+    }
+    partial[3 * nchunk + threadIdx.x] = run;  // totals
+  }
+}
+__global__ void __launch_bounds__(SCAN_CHUNK) k_sym_scan_apply(int64_t S, const int32_t* __restrict__ counts,
+                                                                 const int64_t* __restrict__ partial, int64_t* __restrict__ dof_off,
+                                                                 int64_t* __restrict__ free_off, int64_t* __restrict__ bnd_off) {
+  __shared__ int64_t wsum[3][SCAN_CHUNK / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t i = int64_t(blockIdx.x) * SCAN_CHUNK + threadIdx.x;
+  const int4 c = i < S ? reinterpret_cast<const int4*>(counts)[i] : make_int4(0, 0, 0, 0);
+  int64_t v[3] = {c.x, c.y, c.z}, inc[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    int64_t x = v[k];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int64_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    inc[k] = x;  // inclusive within the warp
+    if (lane == 31) wsum[k][warp] = x;
   }
   __syncthreads();
-  s0 = part[0][t]; s1 = part[1][t]; s2 = part[2][t];
-  for (int64_t i = a; i < b; i++) {
-    dof_off[i] = s0; free_off[i] = s1; bnd_off[i] = s2;
-    s0 += counts[4 * i]; s1 += counts[4 * i + 1]; s2 += counts[4 * i + 2];
+  if (threadIdx.x < 3) {
+    int64_t run = 0;
+    for (int w = 0; w < SCAN_CHUNK / 32; w++) { const int64_t t = wsum[threadIdx.x][w]; wsum[threadIdx.x][w] = run; run += t; }
   }
-  if (b == S && a < S || (S == 0 && t == 0)) { dof_off[S] = s0; free_off[S] = s1; bnd_off[S] = s2; }
+  __syncthreads();
+  if (i < S) {
+    dof_off[i] = partial[3 * int64_t(blockIdx.x) + 0] + wsum[0][warp] + inc[0] - v[0];
+    free_off[i] = partial[3 * int64_t(blockIdx.x) + 1] + wsum[1][warp] + inc[1] - v[1];
+    bnd_off[i] = partial[3 * int64_t(blockIdx.x) + 2] + wsum[2][warp] + inc[2] - v[2];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    const int64_t nchunk = gridDim.x;
+    dof_off[S] = partial[3 * nchunk]; free_off[S] = partial[3 * nchunk + 1]; bnd_off[S] = partial[3 * nchunk + 2];
+  }
 }
 
 __global__ void __launch_bounds__(128) k_sym_fill(SymDev d) {
@@ -251,13 +297,40 @@ __global__ void __launch_bounds__(128) k_sym_fill(SymDev d) {
   m.N = int32_t(N); m.E = int32_t(E); m.NL = int32_t(d.nload_off[s + 1] - d.nload_off[s]);
   m.n = cnt[0]; m.nf = nf; m.nb = nb; m.hb = min(bw, max(nf - 1, 0)); m.pad = 0;
   d.meta[s] = m;
+  // size class of the warp-per-structure kernel (frame_class_of, kernels.h) + the class's extents
+  {
+    const int k = frame_class_of(m.hb, nf, nb);
+    d.cls[s] = uint8_t(k);
+    int32_t* st = d.cls_stats + 5 * k;   // count, max_band, max_nf, max_nb, max_hb
+    atomicAdd(st, 1);
+    atomicMax(st + 1, (m.hb + 1) * nf);
+    atomicMax(st + 2, nf);
+    atomicMax(st + 3, nb);
+    atomicMax(st + 4, m.hb);
+  }
+}
+
+// structure ids grouped by size class: class k occupies order[start[k] .. start[k+1]); the position inside a class comes
+// from an atomic cursor, so it varies from run to run — it only decides which warp serves which structure
+__global__ void __launch_bounds__(256) k_sym_order(int64_t S, const uint8_t* __restrict__ cls, int32_t* cursor /* [NCLS] starts */,
+                                                   int32_t* __restrict__ order) {
+  const int64_t s = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  order[atomicAdd(cursor + cls[s], 1)] = int32_t(s);
+}
+cudaError_t launch_symbolic_order(int64_t S, const uint8_t* cls, int32_t* cursor, int32_t* order, cudaStream_t st) {
+  k_sym_order<<<unsigned((S + 255) / 256), 256, 0, st>>>(S, cls, cursor, order);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_symbolic_device(const SymDev& d, cudaStream_t st) {
   if (d.S <= 0) return cudaSuccess;
   const unsigned g = unsigned((d.S + 127) / 128);
   k_sym_count<<<g, 128, 0, st>>>(d);
-  k_sym_scan<<<1, 1024, 0, st>>>(d.S, d.counts, d.dof_off, d.free_off, d.bnd_off);
+  const unsigned nchunk = unsigned((d.S + SCAN_CHUNK - 1) / SCAN_CHUNK);
+  k_sym_scan_partial<<<nchunk, SCAN_CHUNK, 0, st>>>(d.S, d.counts, d.scan_partial);
+  k_sym_scan_bases<<<1, 32, 0, st>>>(nchunk, d.scan_partial);
+  k_sym_scan_apply<<<nchunk, SCAN_CHUNK, 0, st>>>(d.S, d.counts, d.scan_partial, d.dof_off, d.free_off, d.bnd_off);
   k_sym_fill<<<g, 128, 0, st>>>(d);
   return cudaGetLastError();
 }
