@@ -54,6 +54,12 @@ static int ensure_plan(obgpu_ctx* c) {
   OB_CUDA(c, c->d_ff_col.upload(P.ff_col, st));
   OB_CUDA(c, c->d_ff_src.upload(P.ff_src, st));
   OB_CUDA(c, c->d_ff_diag.upload(P.ff_diag, st));
+  if (P.ff_blk.valid) {
+    OB_CUDA(c, c->d_ff_bslptr.upload(P.ff_blk.sl_ptr, st));
+    OB_CUDA(c, c->d_ff_bcol.upload(P.ff_blk.col, st));
+    OB_CUDA(c, c->d_ff_bmap.upload(P.ff_blk.map, st));
+    OB_CUDA(c, c->d_ff_bval.reserve(P.ff_blk.map.size()));
+  }
   OB_CUDA(c, c->d_bf_rowptr.upload(P.bf_rowptr, st));
   OB_CUDA(c, c->d_bf_col.upload(P.bf_col, st));
   OB_CUDA(c, c->d_bf_src.upload(P.bf_src, st));
@@ -88,6 +94,14 @@ static int ensure_mg(obgpu_ctx* c) {
     OB_CUDA(c, B.mem_ptr.upload(L.mem_ptr, st));
     OB_CUDA(c, B.mem.upload(L.mem, st));
     OB_CUDA(c, B.val.reserve(std::max<size_t>(L.col.size(), 1)));
+    B.nblk = 0;
+    if (L.blk.valid) {
+      OB_CUDA(c, B.bsl_ptr.upload(L.blk.sl_ptr, st));
+      OB_CUDA(c, B.bcol.upload(L.blk.col, st));
+      OB_CUDA(c, B.bmap.upload(L.blk.map, st));
+      OB_CUDA(c, B.bval.reserve(L.blk.map.size()));
+      B.nblk = int64_t(L.blk.col.size());
+    }
     OB_CUDA(c, B.minv.reserve(size_t(L.n)));
     OB_CUDA(c, B.vec.reserve(size_t(5) * L.n));
     OB_CUDA(c, cudaMemsetAsync(B.vec.p, 0, size_t(5) * L.n * sizeof(double), st));
@@ -274,6 +288,10 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
     if (cs == 0 || c->has_case_eai) {  // K5: BC elimination as gathers, Jacobi diagonal
       OB_CUDA(c, launch_bc_gather(d, c->stream));
       launches += 2;
+      if (c->plan.ff_blk.valid) {  // the 3x3 block-SELL copy the SpMV-class kernels stream (76 instead of 108 bytes per block)
+        OB_CUDA(c, launch_gather(int64_t(c->plan.ff_blk.map.size()), c->d_ff_bmap.p, d.ff_val, c->d_ff_bval.p, c->stream));
+        launches += 1;
+      }
       if (!use_mg) {
         OB_CUDA(c, launch_inv_diag(nf, d.ff_diag, d.ff_val, v_minv, c->stream));
         launches += 1;
@@ -296,6 +314,10 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
           g.mem_ptr = B.mem_ptr.p; g.mem = B.mem.p;
           g.c_slptr = B.sl_ptr.p; g.c_col = B.col.p; g.c_val = B.val.p;
           OB_CUDA(c, launch_mg_galerkin(g, c->stream));
+          if (B.nblk) {
+            OB_CUDA(c, launch_gather(9 * B.nblk, B.bmap.p, B.val.p, B.bval.p, c->stream));
+            launches += 1;
+          }
           OB_CUDA(c, launch_mg_diag(0, ML.n, B.sl_ptr.p, B.col.p, B.val.p, B.minv.p, c->d_mg_lam.p + l, c->stream));
           launches += 2;
         }
@@ -343,6 +365,8 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
       PcgArgs a;
       a.r0 = int32_t(sy.free_off[st_i]); a.r1 = int32_t(sy.free_off[st_i + 1]);
       a.slptr = d.sl_ptr; a.col = d.ff_col; a.val = d.ff_val; a.minv = v_minv;
+      const bool blk0 = c->plan.ff_blk.valid;
+      a.bslptr = blk0 ? c->d_ff_bslptr.p : nullptr; a.bcol = blk0 ? c->d_ff_bcol.p : nullptr; a.bval = blk0 ? c->d_ff_bval.p : nullptr;
       a.b = c->any_ub ? c->d_rhs.p : c->d_Ff.p + size_t(cs) * nf;
       a.x = c->d_Uf.p + size_t(cs) * nf;
       a.r = v_r; a.z = v_z; a.p = v_p; a.ap = v_ap;
@@ -361,12 +385,15 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
           if (l == 0) {
             V.r0 = a.r0; V.r1 = a.r1;
             V.slptr = d.sl_ptr; V.col = d.ff_col; V.val = d.ff_val; V.minv = v_minv;
+            static const bool fine_blk = !(getenv("OBGPU_MG_FINE_BLOCK") && atoi(getenv("OBGPU_MG_FINE_BLOCK")) == 0);
+            V.bslptr = fine_blk ? a.bslptr : nullptr; V.bcol = fine_blk ? a.bcol : nullptr; V.bval = fine_blk ? a.bval : nullptr;
             V.x = v_z; V.b = v_r; V.r = v_mr; V.d0 = v_md0; V.d1 = v_md1;
           } else {
             const MgLevel& ML = c->mg.lev[size_t(l)];
             obgpu_ctx::MgLevelBufs& B = c->mg_lev[size_t(l)];
             V.r0 = ML.row_off[st_i]; V.r1 = V.r0 + ML.nrows[st_i];
             V.slptr = B.sl_ptr.p; V.col = B.col.p; V.val = B.val.p; V.minv = B.minv.p;
+            V.bslptr = B.nblk ? B.bsl_ptr.p : nullptr; V.bcol = B.nblk ? B.bcol.p : nullptr; V.bval = B.nblk ? B.bval.p : nullptr;
             V.x = B.vec.p; V.b = V.x + ML.n; V.r = V.b + ML.n; V.d0 = V.r + ML.n; V.d1 = V.d0 + ML.n;
           }
           if (l + 1 < J.nlev) {  // transfer to the next coarser level (arrays indexed by this level's rows)
@@ -561,7 +588,15 @@ int profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, double* al
   if (ms_avg) *ms_avg = double(ms) / reps;
   // SpMV = 12 B per stored entry + 20 B per row (x gathered once, y written, p read for the dot);
   // the fused Chebyshev step additionally reads r, D^-1, x and writes r, d, x: 12 B per entry + 56 B per row
-  if (alg_bytes) *alg_bytes = 12.0 * double(entries) + (which == OBGPU_PROF_SPMV ? 20.0 : 56.0) * double(n);
+  if (alg_bytes) {
+    if (a.bval) {  // 3x3 block-SELL: 72 B of values + 4 B of column per stored block
+      const int64_t bs0 = (a.r0 / 3) >> 5, bs1 = (int64_t(a.r1) / 3 + 31) >> 5;
+      const double blocks = double(c->plan.ff_blk.sl_ptr[size_t(bs1)]) - double(c->plan.ff_blk.sl_ptr[size_t(bs0)]);
+      *alg_bytes = 76.0 * blocks + (which == OBGPU_PROF_SPMV ? 20.0 : 56.0) * double(n);
+    } else {
+      *alg_bytes = 12.0 * double(entries) + (which == OBGPU_PROF_SPMV ? 20.0 : 56.0) * double(n);
+    }
+  }
   return OBGPU_OK;
 }
 

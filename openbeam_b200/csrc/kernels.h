@@ -109,6 +109,7 @@ cudaError_t launch_elem_stiff(const SparseDev& d, const double* eai, cudaStream_
 cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st);
 cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStream_t st);
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st);
+cudaError_t launch_gather(int64_t n, const int32_t* src, const double* in, double* out, cudaStream_t st);  // out[i] = in[src[i]] (-1: 0)
 cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, const double* eai, double* F_f,
                                cudaStream_t st);
 cudaError_t launch_stress(const SparseDev& d, const double* eai, const double* q, const double* U_f, double* stress,
@@ -119,6 +120,8 @@ struct PcgArgs {
   int32_t r0, r1;
   const int32_t *slptr, *col;  // K_ff in SELL-32 (SparsePlan): slice offsets, column of every stored entry
   const double* val;
+  const int32_t *bslptr, *bcol;  // the same matrix in 3x3 block-SELL (BlockSell, obgpu_internal.h), or null
+  const double* bval;
   const double* minv;   // [nf] inverse diagonal
   const double* b;      // rhs (F_f)
   double *x, *r, *z, *p, *ap;
@@ -135,6 +138,8 @@ struct MgLevelDev {
   int32_t r0, r1;
   const int32_t *slptr, *col;
   const double *val, *minv;
+  const int32_t *bslptr, *bcol;   // 3x3 block-SELL view used by the SpMV-class kernels when present (else null)
+  const double* bval;
   double *x, *b, *r, *d0, *d1;
   const int32_t* f_agg; const uint8_t* f_kind; const double* f_w;
   const int32_t *mem_ptr, *mem;

@@ -262,6 +262,46 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_mg_spmv(MgLevelDev L, const doubl
   }
 }
 
+// the same on the 3x3 block-SELL view of the level: warp per slice of 32 block rows, lane = block row (3 rows)
+template <int MODE, bool DOT>
+__global__ void __launch_bounds__(PCG_BLOCK) k_mg_spmv_blk(MgLevelDev L, const double* __restrict__ din, const double* rin,
+                                                           double* dout, double c1, double c2, const double* __restrict__ dotv,
+                                                           double* dot_out, double* partial, unsigned int* counter) {
+  __shared__ double sh[PCG_BLOCK / 32];
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = int64_t(gridDim.x) * (PCG_BLOCK / 32);
+  const int64_t b0 = L.r0 / 3, b1 = L.r1 / 3;
+  const int64_t s1 = (b1 + 31) >> 5;
+  double v[1] = {0.0};
+  for (int64_t sl = (b0 >> 5) + int64_t(blockIdx.x) * (PCG_BLOCK / 32) + (threadIdx.x >> 5); sl < s1; sl += nwarps) {
+    // (redistributing the sums so that lane l serves rows l, 32 + l, 64 + l — fully coalesced vector accesses — measured
+    // SLOWER on B200 than letting every lane finish its own three consecutive rows: 97.6 vs 96.0 us here, 83 vs 60 us in
+    // k_spmv_dot_blk)
+    double sum[3];
+    block_row_product(L.bslptr, L.bcol, L.bval, sl, lane, din, sum);
+    const int64_t I = sl * 32 + lane;
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const int64_t row = 3 * I + j;
+      if (I >= b0 && I < b1) {
+        const double rn = rin[row] - sum[j];
+        L.r[row] = rn;
+        if (MODE == MG_CHEB) {
+          const double d = c1 * din[row] + c2 * L.minv[row] * rn;
+          dout[row] = d;
+          const double xn = L.x[row] + d;
+          L.x[row] = xn;
+          if (DOT) v[0] += xn * dotv[row];
+        }
+      }
+    }
+  }
+  if (DOT) {
+    double* out[1] = {dot_out};
+    finish_dots<1>(v, partial, counter, sh, out);
+  }
+}
+
 // b_c = P^T r (thread = coarse row, fixed member order), optionally followed by the coarse level's first smoothing step
 __global__ void __launch_bounds__(PCG_BLOCK) k_mg_restrict(MgLevelDev F, MgLevelDev C, int smooth0) {
   for (int64_t R = C.r0 + int64_t(blockIdx.x) * PCG_BLOCK + threadIdx.x; R < C.r1; R += int64_t(gridDim.x) * PCG_BLOCK) {
@@ -329,6 +369,12 @@ static unsigned mg_grid(int64_t items, int sm_count, int cps) {
 }
 
 cudaError_t launch_mg_cheb_only(const MgLevelDev& L, int sm_count, cudaStream_t st) {
+  if (L.bval) {
+    const int64_t bs = ((int64_t(L.r1) / 3 + 31) >> 5) - ((L.r0 / 3) >> 5);
+    k_mg_spmv_blk<MG_CHEB, false><<<balanced_grid(k_mg_spmv_blk<MG_CHEB, false>, bs, sm_count, 0), PCG_BLOCK, 0, st>>>(
+        L, L.d0, L.r, L.d1, L.c1, L.c2, nullptr, nullptr, nullptr, nullptr);
+    return cudaGetLastError();
+  }
   const int64_t threads = (((int64_t(L.r1) + 31) >> 5) - (L.r0 >> 5)) * 32;
   k_mg_spmv<MG_CHEB, false><<<mg_grid(threads, sm_count, 0), PCG_BLOCK, 0, st>>>(L, L.d0, L.r, L.d1, L.c1, L.c2, nullptr, nullptr,
                                                                                 nullptr, nullptr);
@@ -340,7 +386,17 @@ cudaError_t launch_mg_vcycle(const MgJob& J, double* dot_out, double* partial, u
   const int nl = J.nlev;
   auto rows = [](const MgLevelDev& L) { return int64_t(L.r1 - L.r0); };
   auto slice_threads = [](const MgLevelDev& L) { return (((int64_t(L.r1) + 31) >> 5) - (L.r0 >> 5)) * 32; };
+  auto blk_slices = [](const MgLevelDev& L) { return ((int64_t(L.r1) / 3 + 31) >> 5) - ((L.r0 / 3) >> 5); };
   auto cheb = [&](const MgLevelDev& L, const double* din, const double* rin, double* dout, double c1, double c2, bool dot) {
+    if (L.bval) {
+      if (dot)
+        k_mg_spmv_blk<MG_CHEB, true><<<balanced_grid(k_mg_spmv_blk<MG_CHEB, true>, blk_slices(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
+            L, din, rin, dout, c1, c2, L.b, dot_out, partial, counter);
+      else
+        k_mg_spmv_blk<MG_CHEB, false><<<balanced_grid(k_mg_spmv_blk<MG_CHEB, false>, blk_slices(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
+            L, din, rin, dout, c1, c2, nullptr, nullptr, nullptr, nullptr);
+      return;
+    }
     const unsigned g = mg_grid(slice_threads(L), sm_count, cps);
     if (dot) k_mg_spmv<MG_CHEB, true><<<g, PCG_BLOCK, 0, st>>>(L, din, rin, dout, c1, c2, L.b, dot_out, partial, counter);
     else k_mg_spmv<MG_CHEB, false><<<g, PCG_BLOCK, 0, st>>>(L, din, rin, dout, c1, c2, nullptr, nullptr, nullptr, nullptr);
@@ -350,8 +406,12 @@ cudaError_t launch_mg_vcycle(const MgJob& J, double* dot_out, double* partial, u
   for (int l = 0; l + 1 < nl; l++) {
     const MgLevelDev& L = J.lv[l];
     cheb(L, L.d0, L.b, L.d1, L.c1, L.c2, false);  // x = d0 + d1, r = b - A d0
-    k_mg_spmv<MG_RESID, false><<<mg_grid(slice_threads(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
-        L, L.d1, L.r, nullptr, 0.0, 0.0, nullptr, nullptr, nullptr, nullptr);  // r = b - A x
+    if (L.bval)
+      k_mg_spmv_blk<MG_RESID, false><<<balanced_grid(k_mg_spmv_blk<MG_RESID, false>, blk_slices(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
+          L, L.d1, L.r, nullptr, 0.0, 0.0, nullptr, nullptr, nullptr, nullptr);
+    else
+      k_mg_spmv<MG_RESID, false><<<mg_grid(slice_threads(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
+          L, L.d1, L.r, nullptr, 0.0, 0.0, nullptr, nullptr, nullptr, nullptr);  // r = b - A x
     const MgLevelDev& C = J.lv[l + 1];
     const bool coarsest = l + 2 == nl;
     k_mg_restrict<<<mg_grid(rows(C), sm_count, cps), PCG_BLOCK, 0, st>>>(L, C, !(coarsest && J.dense));

@@ -72,6 +72,44 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_spmv_dot(PcgArgs a) {
 
 // alpha = rz/pAp; x += alpha p; r -= alpha Ap; z = M^-1 r; rz_next = r.z; rr = r.r
 // MG = true: z and r.z come from the V-cycle that follows; only r.r is reduced here
+// the same on the 3x3 block-SELL view: warp per slice of 32 block rows (96 rows), lane = block row
+template <bool ROWS>
+__global__ void __launch_bounds__(PCG_BLOCK) k_spmv_dot_blk(PcgArgs a) {
+  __shared__ double sh[PCG_BLOCK / 32];
+  const int lane = threadIdx.x & 31;
+  const int64_t nwarps = int64_t(gridDim.x) * (PCG_BLOCK / 32);
+  const int64_t b0 = a.r0 / 3, b1 = a.r1 / 3;   // block rows of the structure
+  const int64_t s1 = (b1 + 31) >> 5;
+  double v[1] = {0.0};
+  for (int64_t sl = (b0 >> 5) + int64_t(blockIdx.x) * (PCG_BLOCK / 32) + (threadIdx.x >> 5); sl < s1; sl += nwarps) {
+    double sum[3];
+    block_row_product(a.bslptr, a.bcol, a.bval, sl, lane, a.p, sum);
+    if (ROWS) {
+      double t[3];
+      block_sums_to_rows(sum, lane, t);
+#pragma unroll
+      for (int j = 0; j < 3; j++) {
+        const int64_t row = sl * 96 + 32 * j + lane;
+        if (row >= a.r0 && row < a.r1) {
+          a.ap[row] = t[j];
+          v[0] += t[j] * a.p[row];
+        }
+      }
+    } else {
+      const int64_t I = sl * 32 + lane;
+      if (I >= b0 && I < b1) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          a.ap[3 * I + k] = sum[k];
+          v[0] += sum[k] * a.p[3 * I + k];
+        }
+      }
+    }
+  }
+  double* out[1] = {a.scal + 2};
+  finish_dots<1>(v, a.partial, a.counter, sh, out);
+}
+
 template <bool MG>
 __global__ void __launch_bounds__(PCG_BLOCK) k_pcg_update(PcgArgs a, int cur) {
   __shared__ double sh[PCG_BLOCK / 32];
@@ -180,7 +218,11 @@ static unsigned spmv_grid(const PcgArgs& a, int sm_count, int cps) {
 }
 
 cudaError_t launch_spmv_only(const PcgArgs& a, int sm_count, cudaStream_t st) {
-  k_spmv_dot<false><<<spmv_grid(a, sm_count, 8), PCG_BLOCK, 0, st>>>(a);  // timed alone: the whole GPU
+  static const bool blk_rows = getenv("OBGPU_BLK_ROWS") && atoi(getenv("OBGPU_BLK_ROWS")) != 0;
+  const int64_t bslices = ((int64_t(a.r1) / 3 + 31) >> 5) - ((a.r0 / 3) >> 5);
+  if (a.bval && blk_rows) k_spmv_dot_blk<true><<<balanced_grid(k_spmv_dot_blk<true>, bslices, sm_count, 0), PCG_BLOCK, 0, st>>>(a);
+  else if (a.bval) k_spmv_dot_blk<false><<<balanced_grid(k_spmv_dot_blk<false>, bslices, sm_count, 0), PCG_BLOCK, 0, st>>>(a);
+  else k_spmv_dot<false><<<spmv_grid(a, sm_count, 8), PCG_BLOCK, 0, st>>>(a);  // timed alone: the whole GPU
   return cudaGetLastError();
 }
 
@@ -209,7 +251,11 @@ cudaError_t launch_pcg_iter(const PcgArgs& a, int it, int sm_count, cudaStream_t
   const int cps = cps_env > 0 ? cps_env : a.ctas_per_sm > 0 ? a.ctas_per_sm : 8;
   const int64_t slices = ((int64_t(a.r1) + 31) >> 5) - (a.r0 >> 5);
   const unsigned g = pcg_grid(slices * 32, sm_count, cps);  // one warp per slice, grid-stride
-  if (stream) k_spmv_dot<true><<<g, PCG_BLOCK, 0, st>>>(a);
+  static const bool blk_rows = getenv("OBGPU_BLK_ROWS") && atoi(getenv("OBGPU_BLK_ROWS")) != 0;  // experiment: see k_mg_spmv_blk
+  const int64_t bslices = ((int64_t(a.r1) / 3 + 31) >> 5) - ((a.r0 / 3) >> 5);
+  if (a.bval && blk_rows) k_spmv_dot_blk<true><<<balanced_grid(k_spmv_dot_blk<true>, bslices, sm_count, cps), PCG_BLOCK, 0, st>>>(a);
+  else if (a.bval) k_spmv_dot_blk<false><<<balanced_grid(k_spmv_dot_blk<false>, bslices, sm_count, cps), PCG_BLOCK, 0, st>>>(a);
+  else if (stream) k_spmv_dot<true><<<g, PCG_BLOCK, 0, st>>>(a);
   else k_spmv_dot<false><<<g, PCG_BLOCK, 0, st>>>(a);
   static const int cpv_env = getenv("OBGPU_PCG_VEC_CTAS") ? atoi(getenv("OBGPU_PCG_VEC_CTAS")) : 0;
   const int cpv = cpv_env > 0 ? cpv_env : a.ctas_per_sm > 0 ? a.ctas_per_sm : 8;

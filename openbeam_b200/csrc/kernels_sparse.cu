@@ -293,6 +293,10 @@ cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStr
                                                               d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.node_rot, d.kval);
   return cudaGetLastError();
 }
+cudaError_t launch_gather(int64_t n, const int32_t* src, const double* in, double* out, cudaStream_t st) {
+  if (n > 0) k_gather<<<nblk(n), 256, 0, st>>>(n, src, in, out);
+  return cudaGetLastError();
+}
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st) {
   if (d.nnz_ff) k_gather<<<nblk(d.nnz_ff), 256, 0, st>>>(d.nnz_ff, d.ff_src, d.kval, d.ff_val);
   if (d.nnz_bf) k_gather<<<nblk(d.nnz_bf), 256, 0, st>>>(d.nnz_bf, d.bf_src, d.kval, d.bf_val);

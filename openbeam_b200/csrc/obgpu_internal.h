@@ -109,6 +109,20 @@ struct TinyProgram {
   std::vector<double> dbls;
 };
 
+// 3x3 block-SELL view of a scalar SELL-32 matrix whose rows come in triples (block row I = rows 3I..3I+2): slices of 32
+// block rows, block k of lane l at (sl_ptr[slice] + 32 k + l), its 9 values (row-major a*3+b) at
+// 9*sl_ptr[slice] + (9 k + v)*32 + l — every load of a warp reads 32 consecutive words.  One column index per 9 values:
+// 8.44 instead of 12 bytes per stored entry.  `map` gathers the values out of the scalar SELL value array (-1 = zero).
+struct BlockSell {
+  bool valid = false;
+  std::vector<int32_t> sl_ptr;   // [n/96 + 1] in blocks
+  std::vector<int32_t> col;      // [blocks] block column
+  std::vector<int32_t> map;      // [9 * blocks] position in the scalar SELL arrays, -1 = structural zero / padding
+};
+// n rows (multiple of 96 unless `ragged_ok`), scalar pattern in SELL-32; false when the fill of the blocks is below 70 %
+bool build_block_sell(int64_t n, const std::vector<int32_t>& sl_ptr, const std::vector<int32_t>& col,
+                      const std::vector<int32_t>* src /* -1 = padding entry, may be null */, BlockSell& out);
+
 // Plan of the sparse route (K4 segmented reduction, K5 BC gathers, PCG): all indices GLOBAL over the batch.
 struct SparsePlan {
   bool valid = false;
@@ -128,6 +142,7 @@ struct SparsePlan {
   std::vector<int32_t> ff_diag;               // [nf_tot] position of the diagonal entry inside ff_col/ff_src
   int64_t ff_nnz = 0;                         // structural entries of K_ff (without padding)
   std::vector<int32_t> bf_rowptr, bf_col, bf_src;  // K_bf: rows = global bounded index, cols = global free index
+  BlockSell ff_blk;                           // K_ff in 3x3 block-SELL when every structure's free DOFs come in triples
   std::vector<int32_t> bb_rowptr, bb_col, bb_src;  // K_bb as the reference stores it (upper triangle): row b(lo), col b(hi)
   // load vector gather: target t < nf_tot -> F_f[t]; t >= nf_tot -> Eq[t - nf_tot] (equivalent loads on bounded DOFs)
   // src >= 0: ELOAD_G entry (multimap position*6 + k); src < 0: nodal load -(l+1)
@@ -150,6 +165,7 @@ struct MgLevel {
   std::vector<uint8_t> f_kind;
   std::vector<double> f_w;
   std::vector<int32_t> mem_ptr, mem;    // [n/3 + 1] fine rows of each aggregate, ascending
+  BlockSell blk;                        // the same matrix in 3x3 block-SELL (SpMV-class kernels)
 };
 struct MgPlan {
   bool valid = false;

@@ -50,4 +50,67 @@ __device__ __forceinline__ void finish_dots(const double (&v)[NV], double* parti
   }
 }
 
+// Grid of a warp-per-slice kernel: at most `resident` CTAs per SM (what the kernel's registers allow, so that no second
+// partial wave forms), capped by the caller's request, and shrunk so that every warp serves the same number of slices
+// (a 3x3 block-SELL level has a third of the scalar slices: 2.2 per warp left some warps with 3 and others with 2)
+template <class K>
+static unsigned balanced_grid(K kernel, int64_t slices, int sm_count, int request) {
+  static int resident = 0;   // one instance per kernel type
+  if (resident == 0) {
+    int r = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&r, kernel, PCG_BLOCK, 0) != cudaSuccess || r < 1) r = 4;
+    resident = r;
+  }
+  const int per_sm = request > 0 && request < resident ? request : resident;
+  const int64_t warps_cap = int64_t(sm_count) * per_sm * (PCG_BLOCK / 32);
+  const int64_t k = (slices + warps_cap - 1) / warps_cap;                  // slices per warp
+  const int64_t g = (slices + k * (PCG_BLOCK / 32) - 1) / (k * (PCG_BLOCK / 32));
+  return unsigned(g < 1 ? 1 : g);
+}
+
+// y(3I..3I+2) = sum over the blocks of block row I (lane = block row of the slice), 3x3 block-SELL (BlockSell): every
+// load of the warp reads 32 consecutive words; 76 bytes per block instead of 108 for nine scalar entries
+__device__ __forceinline__ void block_row_product(const int32_t* __restrict__ bslptr, const int32_t* __restrict__ bcol,
+                                                  const double* __restrict__ bval, int64_t sl, int lane,
+                                                  const double* __restrict__ x, double (&s)[3]) {
+  const int32_t base = bslptr[sl], w = (bslptr[sl + 1] - base) >> 5;
+  const int32_t* __restrict__ pc = bcol + base + lane;
+  const double* __restrict__ pv = bval + size_t(9) * base + lane;
+  s[0] = s[1] = s[2] = 0.0;
+  int k = 0;
+  for (; k + 2 <= w; k += 2) {   // two blocks per trip: 2 + 18 coalesced loads in flight ahead of the 6 gathers
+    const int32_t c0 = pc[32 * k], c1 = pc[32 * (k + 1)];
+    double m[18];
+#pragma unroll
+    for (int v = 0; v < 18; v++) m[v] = pv[(9 * k + v) * 32];
+    const double x0 = x[3 * c0], x1 = x[3 * c0 + 1], x2 = x[3 * c0 + 2];
+    const double y0 = x[3 * c1], y1 = x[3 * c1 + 1], y2 = x[3 * c1 + 2];
+#pragma unroll
+    for (int a = 0; a < 3; a++)
+      s[a] += m[3 * a] * x0 + m[3 * a + 1] * x1 + m[3 * a + 2] * x2 + m[9 + 3 * a] * y0 + m[9 + 3 * a + 1] * y1 + m[9 + 3 * a + 2] * y2;
+  }
+  for (; k < w; k++) {
+    const int32_t c0 = pc[32 * k];
+    double m[9];
+#pragma unroll
+    for (int v = 0; v < 9; v++) m[v] = pv[(9 * k + v) * 32];
+    const double x0 = x[3 * c0], x1 = x[3 * c0 + 1], x2 = x[3 * c0 + 2];
+#pragma unroll
+    for (int a = 0; a < 3; a++) s[a] += m[3 * a] * x0 + m[3 * a + 1] * x1 + m[3 * a + 2] * x2;
+  }
+}
+
+// block_row_product leaves row 3 l + a of the slice in lane l; the row-local work that follows (vector reads and writes)
+// wants lane l on rows l, 32 + l, 64 + l so that every access of the warp is 32 consecutive doubles: t[j] = the sum of
+// slice row 32 j + l, fetched from lane (32 j + l) / 3, component (32 j + l) % 3
+__device__ __forceinline__ void block_sums_to_rows(const double (&s)[3], int lane, double (&t)[3]) {
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const int row = 32 * j + lane, src = row / 3, comp = row - 3 * src;
+    const double v0 = __shfl_sync(0xffffffffu, s[0], src), v1 = __shfl_sync(0xffffffffu, s[1], src),
+                 v2 = __shfl_sync(0xffffffffu, s[2], src);
+    t[j] = comp == 0 ? v0 : comp == 1 ? v1 : v2;
+  }
+}
+
 }  // namespace obgpu

@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <cmath>
 #include <numeric>
+#include <cstdlib>
 
 #include "obgpu_internal.h"
 
@@ -28,6 +29,70 @@ struct LevelNodes {                 // the "nodes" of one structure at one level
 inline int32_t pad96(int64_t n) { return int32_t((n + 95) / 96 * 96); }
 
 }  // namespace
+
+bool build_block_sell(int64_t n, const std::vector<int32_t>& sl_ptr, const std::vector<int32_t>& col,
+                      const std::vector<int32_t>* src, BlockSell& out) {
+  out = BlockSell();
+  if (n <= 0 || n % 3 != 0) return false;
+  const int64_t nbr = n / 3, nsl = (nbr + 31) / 32;
+  // block columns of every block row: union over its three scalar rows, ascending
+  std::vector<int32_t> bptr(size_t(nbr) + 1, 0), bcols, tmp;
+  int64_t scalar_entries = 0;
+  for (int64_t I = 0; I < nbr; I++) {
+    tmp.clear();
+    for (int a = 0; a < 3; a++) {
+      const int64_t r = 3 * I + a;
+      const int32_t base = sl_ptr[size_t(r >> 5)], w = (sl_ptr[size_t(r >> 5) + 1] - base) >> 5;
+      for (int32_t k = 0; k < w; k++) {
+        const int32_t q = base + 32 * k + int32_t(r & 31);
+        if (src && (*src)[size_t(q)] < 0) continue;   // padding entry of the scalar layout (level 0 marks them)
+        tmp.push_back(col[size_t(q)] / 3);             // (coarse levels pad with the row's own column: same block)
+        scalar_entries++;
+      }
+    }
+    std::sort(tmp.begin(), tmp.end());
+    tmp.erase(std::unique(tmp.begin(), tmp.end()), tmp.end());
+    bcols.insert(bcols.end(), tmp.begin(), tmp.end());
+    bptr[size_t(I) + 1] = int32_t(bcols.size());
+  }
+  if (double(scalar_entries) < 0.7 * 9.0 * double(bcols.size())) return false;  // poorly filled blocks: scalar SELL is smaller
+  out.sl_ptr.assign(size_t(nsl) + 1, 0);
+  for (int64_t sl = 0; sl < nsl; sl++) {
+    int32_t w = 0;
+    for (int64_t I = sl * 32; I < std::min<int64_t>(nbr, sl * 32 + 32); I++) w = std::max(w, bptr[size_t(I) + 1] - bptr[size_t(I)]);
+    const int64_t next = int64_t(out.sl_ptr[size_t(sl)]) + int64_t(w) * 32;
+    if (next * 9 >= INT32_MAX) return false;
+    out.sl_ptr[size_t(sl) + 1] = int32_t(next);
+  }
+  const size_t nblk = size_t(out.sl_ptr[size_t(nsl)]);
+  out.col.assign(nblk, 0);
+  out.map.assign(nblk * 9, -1);
+  for (int64_t sl = 0; sl < nsl; sl++) {
+    const int32_t base = out.sl_ptr[size_t(sl)], w = (out.sl_ptr[size_t(sl) + 1] - base) >> 5;
+    for (int l = 0; l < 32; l++) {
+      const int64_t I = sl * 32 + l;
+      for (int32_t k = 0; k < w; k++) out.col[size_t(base + 32 * k + l)] = int32_t(std::min<int64_t>(I, nbr - 1));  // padding: own block
+      if (I >= nbr) continue;
+      const int32_t nb = bptr[size_t(I) + 1] - bptr[size_t(I)];
+      for (int32_t k = 0; k < nb; k++) out.col[size_t(base + 32 * k + l)] = bcols[size_t(bptr[size_t(I)] + k)];
+      for (int a = 0; a < 3; a++) {
+        const int64_t r = 3 * I + a;
+        const int32_t sb = sl_ptr[size_t(r >> 5)], sw = (sl_ptr[size_t(r >> 5) + 1] - sb) >> 5;
+        for (int32_t k = 0; k < sw; k++) {
+          const int32_t q = sb + 32 * k + int32_t(r & 31);
+          if (src && (*src)[size_t(q)] < 0) continue;
+          const int32_t c = col[size_t(q)], J = c / 3, b = c - 3 * J;
+          const int32_t* first = &bcols[size_t(bptr[size_t(I)])];
+          const int32_t slot = int32_t(std::lower_bound(first, first + nb, J) - first);
+          const size_t pos = size_t(9) * size_t(base) + size_t((9 * slot + 3 * a + b) * 32 + l);
+          if (out.map[pos] < 0) out.map[pos] = q;   // a coarse row may list its own column twice through padding: first wins
+        }
+      }
+    }
+  }
+  out.valid = true;
+  return true;
+}
 
 int build_mg_plan(const HostBatch& hb, const Symbolic& sym, const SparsePlan& plan, MgPlan& mg, std::string& err) {
   mg = MgPlan();
@@ -222,6 +287,7 @@ int build_mg_plan(const HostBatch& hb, const Symbolic& sym, const SparsePlan& pl
         }
       }
     }
+    if (!getenv("OBGPU_NO_BLOCK_SELL")) build_block_sell(L.n, L.sl_ptr, L.col, nullptr, L.blk);
     mg.lev.push_back(std::move(L));
     for (int64_t s = 0; s < S; s++)
       if (active[s]) {

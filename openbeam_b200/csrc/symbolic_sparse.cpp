@@ -4,6 +4,7 @@
 //   * K5: K_ff / K_bf as gathers out of K (assemble.cpp:249-297), K_ff expanded to full symmetric CSR for SpMV
 //   * load vector: per DOF the nodal loads and element-load contributions to sum (assemble.cpp:317-341)
 #include <algorithm>
+#include <cstdlib>
 
 #include "obgpu_internal.h"
 
@@ -182,6 +183,11 @@ int build_sparse_plan(const HostBatch& hb, const Symbolic& sym, SparsePlan& P, s
     P.ff_col.swap(col);
     P.ff_src.swap(src);
     P.ff_diag.swap(diag);
+    // 3x3 block view for the SpMV-class kernels when every structure's free DOFs come in whole triples (frames whose
+    // nodes are either free or fully fixed: the C4 / C5 lattices) and the blocks are well filled
+    bool triples = nf % 3 == 0 && !getenv("OBGPU_NO_BLOCK_SELL");
+    for (int64_t s = 0; s <= S && triples; s++) triples = sym.free_off[s] % 3 == 0;
+    if (triples) build_block_sell(nf, P.sl_ptr, P.ff_col, &P.ff_src, P.ff_blk);
     P.ff_rowptr.clear();
     P.ff_rowptr.shrink_to_fit();
   }
