@@ -24,7 +24,7 @@ int build_frame_classes(obgpu_ctx* c, const std::vector<int32_t>& nf, const std:
   for (int64_t s = 0; s < S; s++) {
     cls[size_t(s)] = uint8_t(cls_of(s));
     cnt[cls[size_t(s)] + 1]++;
-    c->max_band = int(std::max<int64_t>(c->max_band, int64_t(hbw[size_t(s)] + 1) * nf[size_t(s)]));
+    c->max_band = int(std::max<int64_t>(c->max_band, int64_t(frame_ld(hbw[size_t(s)])) * nf[size_t(s)]));
     c->max_nf = std::max(c->max_nf, nf[size_t(s)]);
     c->max_nb = std::max(c->max_nb, nb[size_t(s)]);
   }
@@ -39,7 +39,7 @@ int build_frame_classes(obgpu_ctx* c, const std::vector<int32_t>& nf, const std:
     obgpu_ctx::FrameClass fc{cnt[k], cnt[k + 1], 0, 0, 0, 0};
     for (int64_t i = cnt[k]; i < cnt[k + 1]; i++) {
       const size_t s = size_t(order[size_t(i)]);
-      fc.max_band = int(std::max<int64_t>(fc.max_band, int64_t(hbw[s] + 1) * nf[s]));
+      fc.max_band = int(std::max<int64_t>(fc.max_band, int64_t(frame_ld(hbw[s])) * nf[s]));
       fc.max_nf = std::max(fc.max_nf, nf[s]);
       fc.max_nb = std::max(fc.max_nb, nb[s]);
       fc.max_hb = std::max(fc.max_hb, hbw[s]);
@@ -167,7 +167,7 @@ int ensure_device_batch(obgpu_ctx* c) {
     m.nb = int32_t(sy.bnd_off[s + 1] - sy.bnd_off[s]);
     m.hb = std::min(half_bw[size_t(s)], std::max(m.nf - 1, 0));
     m.pad = 0;
-    c->max_band = std::max<int64_t>(c->max_band, int64_t(m.hb + 1) * m.nf);
+    c->max_band = std::max<int64_t>(c->max_band, int64_t(frame_ld(m.hb)) * m.nf);
     c->max_nf = std::max(c->max_nf, m.nf);
     c->max_nb = std::max(c->max_nb, m.nb);
   }

@@ -74,7 +74,7 @@ struct FrameArgs {
   const int32_t* order;         // [S] structure ids sorted by size class
   const int32_t* free_inv;      // [nf_tot] or null: free index (reference numbering) of each internal (band-reduced) free slot
   int64_t o0, o1;
-  int max_band;                 // max over the class of (hb+1)*nf   (doubles)
+  int max_band;                 // max over the class of frame_ld(hb)*nf   (doubles)
   int max_nf, max_nb, max_hb;
 };
 cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st);
@@ -215,8 +215,11 @@ cudaError_t launch_symbolic_order(int64_t S, const uint8_t* cls, int32_t* cursor
 
 // Size classes of the warp-per-structure kernel: a structure's shared-memory need (band + vectors, in doubles) bucketed
 constexpr int FRAME_NCLS = 18;
+// Row stride (doubles) of the banded K_ff of k_frame_fused: hb + 1 entries per row, rounded up to an even number so that
+// the column stride LD - 1 is odd and the 16 lanes of a shared-memory wavefront that walk down a column hit 16 banks
+__host__ __device__ inline int frame_ld(int hb) { return (hb + 2) & ~1; }
 __host__ __device__ inline int frame_class_of(int hb, int nf, int nb) {
-  const long long need = (long long)(hb + 1) * nf + 2LL * nf + 2LL * nb;
+  const long long need = (long long)frame_ld(hb) * nf + 2LL * nf + 2LL * nb;
   const long long lim[FRAME_NCLS - 1] = {256, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2560, 3072, 4096, 6144, 8192, 12288,
                                           16384, 24576};
   int k = 0;

@@ -23,6 +23,24 @@ namespace obgpu {
 #ifndef OBGPU_FRAME_MINB
 #define OBGPU_FRAME_MINB(MAXR) ((MAXR) <= 6 ? 5 : 4)   // CTAs per SM the register allocation aims at
 #endif
+#ifdef OBGPU_FRAME_CLOCKS  // experiment build only: per-stage cycle sums (lane 0 of every warp), read by scripts/exp
+__device__ unsigned long long g_frame_clk[8];
+#define OB_CLK(i)                                               \
+  do {                                                          \
+    const long long t_now = clock64();                          \
+    if (lane == 0) atomicAdd(&g_frame_clk[i], (unsigned long long)(t_now - t_prev)); \
+    t_prev = t_now;                                             \
+  } while (0)
+extern "C" void obgpu_debug_frame_clocks(unsigned long long* out, int reset) {
+  cudaMemcpyFromSymbol(out, g_frame_clk, sizeof(g_frame_clk));
+  if (reset) {
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaMemcpyToSymbol(g_frame_clk, z, sizeof(z));
+  }
+}
+#else
+#define OB_CLK(i)
+#endif
 constexpr int STAGE_D = 27;  // doubles staged per element: 21 stiffness + 6 equivalent loads
 constexpr int CHUNK = 16;    // elements staged at a time
 
@@ -49,57 +67,49 @@ __device__ __forceinline__ void cid_pair(int cid, int& a, int& b) {
   }
 }
 
-// Flattened trailing triangle of one column step (see stage B): entry e = r*32 + lane is (p, q), 1 <= q <= p, rows p
-// in order, i.e. the entries of rows p <= m are exactly e < m(m+1)/2.  Byte offsets from the pivot (j, j):
-//   V(j+p, j+q) at (p*(W-1) + q)*8,   V(j+p, j) at p*(W-1)*8,   V(j+q, j) at q*(W-1)*8.
-// (p, q) depend on (round, lane) only, so the map is built once per structure.
+// Stage B works on PANELS of 4 columns (see the kernel).  The trailing triangle of a panel is cut into 2 x 2 tiles, tile
+// e = r*32 + lane is (P, Q), 0 <= Q <= P, rows P in order, i.e. the tiles of tile rows P < m are exactly e < m(m+1)/2.
+// Window coordinates (row a, column c relative to the panel's pivot (j, j)): tile rows a0 = 4 + 2P, a0 + 1, tile columns
+// c0 = 4 + 2Q, c0 + 1; V(j+a, j+c) sits (a*(LD-1) + c) doubles after the pivot.  (P, Q) depend on (round, lane) only, so
+// the map is built once per structure.
 template <int MAXR>
-struct TriMap {
-  int v[MAXR > 0 ? MAXR : 1], p[MAXR > 0 ? MAXR : 1], q[MAXR > 0 ? MAXR : 1];
-  __device__ __forceinline__ void init(int lane, int W) {
+struct TileMap {
+  int v[MAXR > 0 ? MAXR : 1], a0[MAXR > 0 ? MAXR : 1], c0[MAXR > 0 ? MAXR : 1];
+  __device__ __forceinline__ void init(int lane, int LD) {
 #pragma unroll
     for (int r = 0; r < MAXR; r++) {
       const int e = r * 32 + lane;
       int pp = int((sqrtf(8.0f * float(e) + 1.0f) + 1.0f) * 0.5f);
       while (pp * (pp - 1) / 2 > e) pp--;
       while (pp * (pp + 1) / 2 <= e) pp++;
-      const int qq = e - pp * (pp - 1) / 2 + 1;
-      v[r] = (pp * (W - 1) + qq) * 8;
-      p[r] = pp * (W - 1) * 8;
-      q[r] = qq * (W - 1) * 8;
+      const int qq = e - pp * (pp - 1) / 2 + 1;  // 1 <= qq <= pp
+      a0[r] = 4 + 2 * (pp - 1);
+      c0[r] = 4 + 2 * (qq - 1);
+      v[r] = a0[r] * (LD - 1) + c0[r];
     }
   }
 };
 
-// One column step of the factorisation for bands narrower than 32 (TriMap rounds), returns nothing: updates the
-// trailing triangle of column j.  Rounds are entered through a switch so that rounds beyond R_j cost nothing (real
-// branches: an `if (r < R_j)` guard is if-converted by the compiler and every round would issue, predicated off).
-template <int MAXR>
-__device__ __forceinline__ void trailing_update(char* bj, const TriMap<MAXR>& tm, double inv, int tri_j, int lane) {
-  const int R_j = (tri_j + 31) >> 5;
-  const int rem = tri_j - lane;  // entry (r, lane) is inside the triangle iff rem > 32 r
-  double v[MAXR > 0 ? MAXR : 1];
-#define OB_LD(r)                                                                                   \
-  case r + 1:                                                                                      \
-    if (MAXR > r && rem > 32 * r)                                                                  \
-      v[r < MAXR ? r : 0] = *reinterpret_cast<double*>(bj + tm.v[r < MAXR ? r : 0]) -              \
-                            *reinterpret_cast<double*>(bj + tm.p[r < MAXR ? r : 0]) *              \
-                                (*reinterpret_cast<double*>(bj + tm.q[r < MAXR ? r : 0]) * inv);
-#define OB_ST(r)                                                                                   \
-  case r + 1:                                                                                      \
-    if (MAXR > r && rem > 32 * r) *reinterpret_cast<double*>(bj + tm.v[r < MAXR ? r : 0]) = v[r < MAXR ? r : 0];
-  switch (R_j) {
-    OB_LD(15) OB_LD(14) OB_LD(13) OB_LD(12) OB_LD(11) OB_LD(10) OB_LD(9) OB_LD(8)
-    OB_LD(7) OB_LD(6) OB_LD(5) OB_LD(4) OB_LD(3) OB_LD(2) OB_LD(1) OB_LD(0)
-    default: break;
+// Rank-4 update of one 2 x 2 tile: V(a, c) -= sum_k V(a, k) * (V(c, k) / D(k)), k = the panel's 4 columns in order (the
+// same operations, in the same order, as four successive column eliminations).  pu = unscaled panel rows, ps = scaled.
+__device__ __forceinline__ void tile_update(double* bj, int voff, int a0, int c0, int LDm1, int nrows, const double2* pu01,
+                                            const double2* pu23, const double2* ps01, const double2* ps23) {
+  const bool row1 = a0 + 1 < nrows, offd = c0 < a0;  // second row inside the window; (a0, c0+1) below the diagonal
+  double* v0 = bj + voff;
+  double* v1 = v0 + LDm1;
+  const double2 pa = pu01[a0], pb = pu23[a0], pc = pu01[a0 + 1], pd = pu23[a0 + 1];
+  const double2 qa = ps01[c0], qb = ps23[c0], qc = ps01[c0 + 1], qd = ps23[c0 + 1];
+  double v00 = v0[0], v01 = offd ? v0[1] : 0.0, v10 = row1 ? v1[0] : 0.0, v11 = row1 ? v1[1] : 0.0;
+  v00 -= pa.x * qa.x; v01 -= pa.x * qc.x; v10 -= pc.x * qa.x; v11 -= pc.x * qc.x;
+  v00 -= pa.y * qa.y; v01 -= pa.y * qc.y; v10 -= pc.y * qa.y; v11 -= pc.y * qc.y;
+  v00 -= pb.x * qb.x; v01 -= pb.x * qd.x; v10 -= pd.x * qb.x; v11 -= pd.x * qd.x;
+  v00 -= pb.y * qb.y; v01 -= pb.y * qd.y; v10 -= pd.y * qb.y; v11 -= pd.y * qd.y;
+  v0[0] = v00;
+  if (offd) v0[1] = v01;
+  if (row1) {
+    v1[0] = v10;
+    v1[1] = v11;
   }
-  switch (R_j) {
-    OB_ST(15) OB_ST(14) OB_ST(13) OB_ST(12) OB_ST(11) OB_ST(10) OB_ST(9) OB_ST(8)
-    OB_ST(7) OB_ST(6) OB_ST(5) OB_ST(4) OB_ST(3) OB_ST(2) OB_ST(1) OB_ST(0)
-    default: break;
-  }
-#undef OB_LD
-#undef OB_ST
 }
 
 // GEN: the general path (nodal rotated frames and/or non-zero prescribed displacements) is a separate
@@ -127,7 +137,10 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
     const int64_t s = a.order[a.o0 + (it - c * n_cls)];
     const int64_t sys = c * a.S + s;
     const FrameMeta m = a.meta[s];
-    const int nf = m.nf, nb = m.nb, hb = m.hb, W = hb + 1;
+    const int nf = m.nf, nb = m.nb, hb = m.hb, W = frame_ld(hb);  // row stride (>= hb + 1)
+#ifdef OBGPU_FRAME_CLOCKS
+    long long t_prev = clock64();
+#endif
     for (int i = lane; i < W * nf; i += 32) band[i] = 0.0;
     for (int i = lane; i < nf; i += 32) Ff[i] = 0.0;
     for (int i = lane; i < nb; i += 32) { R[i] = 0.0; Eq[i] = 0.0; }
@@ -143,6 +156,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
     __syncwarp();
     const double* eai_base = a.case_eai ? a.case_eai + c * 3 * a.Etot : a.elem_EAI;
     const double* q_base = a.case_q ? a.case_q + c * a.ELtot : a.eload_q;
+    OB_CLK(0);
     // ---- stage A ----  (pass 1 only with prescribed displacements: F_f -= K_fb U_b, solver_static.cpp:37-43)
     const double* Ub = GEN && a.U_b ? a.U_b + m.b0 : nullptr;
     const double* node_rot = GEN ? a.node_rot : nullptr;
@@ -203,6 +217,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
         }
       }
       __syncwarp();
+      OB_CLK(1);
       // Scatter, one element per step in the reference's order.  band | Ff | R | Eq are one contiguous block, so a
       // lane's target is a single offset from `band`; the next element's offset and value are fetched while the
       // current read-modify-write is in flight (the RMW chain is the only serial dependency left).
@@ -233,6 +248,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
         if (off >= 0) band[off] += v;
         __syncwarp();
       }
+      OB_CLK(2);
     }
     if (pass == 0) {
       if (node_rot) {  // assemble.cpp:349-435: (Fx,Fy) of a rotated node's FREE DOFs -> nodal frame (bounded ones count as 0)
@@ -261,31 +277,97 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
     int info = 0;
     const int q = lane + 1;
     if (MAXR > 0) {
-      TriMap<MAXR> tm;
+      // PANELS of 4 columns (hb + 4 <= 32).  Lane p owns window row j+p: it holds V(j+p, j..j+3) and F(j+p) in registers, the
+      // four pivots are eliminated there (values of the pivot rows travel by shuffle), and the finished panel goes to a
+      // scratch copy [row][k] (unscaled and scaled by 1/D) that the trailing update reads with 16-byte loads.  The trailing
+      // triangle is then updated ONCE per panel, every lane a 2 x 2 tile: 16 FMAs per 12 shared-memory accesses, where a
+      // column-at-a-time update pays 4 accesses per FMA (the shared-memory pipe was the limiter of this stage).
+      TileMap<MAXR> tm;
       tm.init(lane, W);
-      const int tri_full = hb * (hb + 1) / 2;
-      // The pivot chain (load d, reciprocal, scale, update, store, sync) is the serial latency of a column; the
-      // NEXT pivot V(j+1,j+1) - V(j+1,j)^2/D(j) is therefore formed (bit-identically to the trailing update) and
-      // inverted at the top of step j, so its reciprocal overlaps the update of column j.
-      double d = nf > 0 ? band[hb] : 1.0;
-      double inv = 1.0 / d;
-      for (int j = 0; j < nf; j++) {
+      const int LDm1 = W - 1;
+      double2* pu01 = reinterpret_cast<double2*>((reinterpret_cast<uintptr_t>(stage) + 15) & ~uintptr_t(15));  // scratch over stage[]
+      double2* pu23 = pu01 + 32;
+      double2* ps01 = pu23 + 32;
+      double2* ps23 = ps01 + 32;
+      for (int j = 0; j < nf; j += 4) {
         double* bj = band + j * W + hb;  // (j, j)
-        if (!(d > 0.0)) {  // Eigen LLT stops at the first x <= 0 (solver_static.cpp:97-105)
-          info = j + 1;
-          break;
+        const int nrows = min(hb + 4, nf - j);
+        double* rp = bj + lane * LDm1;   // V(j+lane, j+k) = rp[k]
+        double x0 = 0.0, x1 = 0.0, x2 = 0.0, x3 = 0.0, f = 0.0;
+        const bool in = lane < nrows;
+        const bool e0 = in && lane <= hb, e1 = in && lane >= 1 && lane <= hb + 1, e2 = in && lane >= 2 && lane <= hb + 2,
+                   e3 = in && lane >= 3;
+        if (e0) x0 = rp[0];
+        if (e1) x1 = rp[1];
+        if (e2) x2 = rp[2];
+        if (e3) x3 = rp[3];
+        if (in) f = Ff[j + lane];
+        double i0, i1 = 0.0, i2 = 0.0, i3 = 0.0;
+        {  // column j
+          const double d = __shfl_sync(0xffffffffu, x0, 0);
+          if (!(d > 0.0)) {  // Eigen LLT stops at the first x <= 0 (solver_static.cpp:97-105)
+            info = j + 1;
+            break;
+          }
+          i0 = 1.0 / d;
+          const double t = __shfl_sync(0xffffffffu, f, 0) * i0;
+          const double c1 = __shfl_sync(0xffffffffu, x0, 1) * i0, c2 = __shfl_sync(0xffffffffu, x0, 2) * i0,
+                       c3 = __shfl_sync(0xffffffffu, x0, 3) * i0;
+          if (lane >= 1) f -= x0 * t;
+          if (lane >= 1) x1 -= x0 * c1;
+          if (lane >= 2) x2 -= x0 * c2;
+          if (lane >= 3) x3 -= x0 * c3;
         }
-        const double inv_j = inv;
-        const int mrows = min(hb, nf - 1 - j);
-        if (j + 1 < nf) {
-          const double c1 = mrows > 0 ? bj[W - 1] : 0.0;
-          d = bj[W] - c1 * (c1 * inv_j);
-          inv = 1.0 / d;
+        if (nrows > 1) {  // column j+1
+          const double d = __shfl_sync(0xffffffffu, x1, 1);
+          if (!(d > 0.0)) {
+            info = j + 2;
+            break;
+          }
+          i1 = 1.0 / d;
+          const double t = __shfl_sync(0xffffffffu, f, 1) * i1;
+          const double c2 = __shfl_sync(0xffffffffu, x1, 2) * i1, c3 = __shfl_sync(0xffffffffu, x1, 3) * i1;
+          if (lane >= 2) f -= x1 * t;
+          if (lane >= 2) x2 -= x1 * c2;
+          if (lane >= 3) x3 -= x1 * c3;
         }
-        const double tj = Ff[j] * inv_j;
-        if (lane == 0) Dinv[j] = inv_j;
-        if (q <= mrows) Ff[j + q] -= bj[q * (W - 1)] * tj;
-        trailing_update<MAXR>(reinterpret_cast<char*>(bj), tm, inv_j, mrows == hb ? tri_full : mrows * (mrows + 1) / 2, lane);
+        if (nrows > 2) {  // column j+2
+          const double d = __shfl_sync(0xffffffffu, x2, 2);
+          if (!(d > 0.0)) {
+            info = j + 3;
+            break;
+          }
+          i2 = 1.0 / d;
+          const double t = __shfl_sync(0xffffffffu, f, 2) * i2;
+          const double c3 = __shfl_sync(0xffffffffu, x2, 3) * i2;
+          if (lane >= 3) f -= x2 * t;
+          if (lane >= 3) x3 -= x2 * c3;
+        }
+        if (nrows > 3) {  // column j+3
+          const double d = __shfl_sync(0xffffffffu, x3, 3);
+          if (!(d > 0.0)) {
+            info = j + 4;
+            break;
+          }
+          i3 = 1.0 / d;
+          const double t = __shfl_sync(0xffffffffu, f, 3) * i3;
+          if (lane >= 4) f -= x3 * t;
+        }
+        if (in) Ff[j + lane] = f;
+        if (e1) rp[1] = x1;  // column j was final already
+        if (e2) rp[2] = x2;
+        if (e3) rp[3] = x3;
+        if (lane < 4 && in) Dinv[j + lane] = lane == 0 ? i0 : lane == 1 ? i1 : lane == 2 ? i2 : i3;
+        pu01[lane] = make_double2(x0, x1);
+        pu23[lane] = make_double2(x2, x3);
+        ps01[lane] = make_double2(x0 * i0, x1 * i1);
+        ps23[lane] = make_double2(x2 * i2, x3 * i3);
+        __syncwarp();
+        const int mt = (nrows - 4 + 1) >> 1;       // tile rows of the trailing triangle (<= 0: none)
+        const int rem = mt * (mt + 1) / 2 - lane;  // tile (r, lane) exists iff rem > 32 r
+#pragma unroll
+        for (int r = 0; r < MAXR; r++)
+          if (rem > 32 * r) tile_update(bj, tm.v[r], tm.a0[r], tm.c0[r], LDm1, nrows, pu01, pu23, ps01, ps23);
         __syncwarp();
       }
     } else {  // wide bands (hb >= 32: more than 10 nodes per storey): lanes stride over the columns of each row
@@ -307,6 +389,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
         __syncwarp();
       }
     }
+    OB_CLK(3);
     if (info == 0 && MAXR > 0) {
       // L^T x = D^-1 y as a column sweep from the last row up: x(j) = Dinv(j) * (y(j) - sum_k V(k,j) x(k)).  The
       // running sums live in REGISTERS: row i is carried by lane i%32 from the step it first receives a term
@@ -341,6 +424,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
       if (info) atomicOr(a.fail, 1);
     }
     for (int i = lane; i < nf; i += 32) a.U_f[c * a.nf_tot + m.f0 + (a.free_inv ? a.free_inv[m.f0 + i] : i)] = Ff[i];
+    OB_CLK(4);
     // ---- stage C: element end forces, reactions ----
     double* sst = stage;                  // [CHUNK][12] stress staging
     double* sgf = stage + CHUNK * 12;     // [CHUNK][6]  global end forces
@@ -446,6 +530,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
     // F_b = K_bf*U_f - equivalent loads on bounded DOFs (solver_static.cpp:196-218)
     for (int i = lane; i < nb; i += 32) a.F_b[c * a.nb_tot + m.b0 + i] = R[i] - Eq[i];
     __syncwarp();
+    OB_CLK(5);
   }
 }
 
@@ -478,14 +563,12 @@ static cudaError_t launch_frame_r(const FrameArgs& a, int sm_count, cudaStream_t
 
 cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st) {
   if (a.o1 <= a.o0) return cudaSuccess;
-  if (a.max_hb >= 32) return launch_frame_r<0>(a, sm_count, st);
-  const int rounds = (a.max_hb * (a.max_hb + 1) / 2 + 31) / 32;  // update rounds of the widest band in the class
+  if (a.max_hb + 4 > 32) return launch_frame_r<0>(a, sm_count, st);  // a panel's window (hb + 4 rows) must fit the 32 lanes
+  const int ht = (a.max_hb + 1) / 2;                 // tile rows of the widest band in the class
+  const int rounds = (ht * (ht + 1) / 2 + 31) / 32;  // 2 x 2 tiles per lane
+  if (rounds <= 1) return launch_frame_r<1>(a, sm_count, st);
   if (rounds <= 2) return launch_frame_r<2>(a, sm_count, st);
-  if (rounds <= 4) return launch_frame_r<4>(a, sm_count, st);
-  if (rounds <= 6) return launch_frame_r<6>(a, sm_count, st);
-  if (rounds <= 8) return launch_frame_r<8>(a, sm_count, st);
-  if (rounds <= 12) return launch_frame_r<12>(a, sm_count, st);
-  return launch_frame_r<16>(a, sm_count, st);
+  return launch_frame_r<4>(a, sm_count, st);
 }
 
 }  // namespace obgpu

@@ -303,7 +303,7 @@ __global__ void __launch_bounds__(128) k_sym_fill(SymDev d) {
     d.cls[s] = uint8_t(k);
     int32_t* st = d.cls_stats + 5 * k;   // count, max_band, max_nf, max_nb, max_hb
     atomicAdd(st, 1);
-    atomicMax(st + 1, (m.hb + 1) * nf);
+    atomicMax(st + 1, frame_ld(m.hb) * nf);
     atomicMax(st + 2, nf);
     atomicMax(st + 3, nb);
     atomicMax(st + 4, m.hb);
