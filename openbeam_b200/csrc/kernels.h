@@ -215,9 +215,9 @@ cudaError_t launch_symbolic_order(int64_t S, const uint8_t* cls, int32_t* cursor
 
 // Size classes of the warp-per-structure kernel: a structure's shared-memory need (band + vectors, in doubles) bucketed
 constexpr int FRAME_NCLS = 18;
-// Row stride (doubles) of the banded K_ff of k_frame_fused: hb + 1 entries per row, rounded up to an even number so that
-// the column stride LD - 1 is odd and the 16 lanes of a shared-memory wavefront that walk down a column hit 16 banks
-__host__ __device__ inline int frame_ld(int hb) { return (hb + 2) & ~1; }
+// Row stride (doubles) of the banded K_ff of k_frame_fused: hb + 1 entries per row.  (Rounding up to an even stride, so
+// that a walk down a column hits 16 distinct banks, measured no faster and costs shared memory.)
+__host__ __device__ inline int frame_ld(int hb) { return hb + 1; }
 __host__ __device__ inline int frame_class_of(int hb, int nf, int nb) {
   const long long need = (long long)frame_ld(hb) * nf + 2LL * nf + 2LL * nb;
   const long long lim[FRAME_NCLS - 1] = {256, 384, 512, 640, 768, 1024, 1280, 1536, 2048, 2560, 3072, 4096, 6144, 8192, 12288,

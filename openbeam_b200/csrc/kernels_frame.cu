@@ -7,8 +7,9 @@
 //            elements are applied in the reference's order (assemble.cpp:123-223), so the sums are
 //            deterministic and need no atomics.  Bounded rows/columns are dropped on the fly (BC elimination as
 //            a gather through the per-node slots, assemble.cpp:249-341).
-//   stage B  banded LDL^T in shared memory on the unscaled factor V = L D, the trailing triangle of every column
-//            flattened over the 32 lanes; L y = b fused into the column loop; L^T x = D^-1 y as a column sweep.
+//   stage B  banded LDL^T in shared memory on the unscaled factor V = L D, by PANELS of 4 columns: the panel's pivots are
+//            eliminated in registers (lane = window row), the trailing triangle gets one rank-4 update per panel with
+//            a 2 x 2 tile per lane; L y = b rides along in the panel; L^T x = D^-1 y as a column sweep.
 //            Non-positive pivot -> info = row+1 (solver_static.cpp:97-105).
 //   stage C  lane = element: end forces (postproc_stress.cpp:86-165) staged and written coalesced; global end
 //            forces of the elements that touch a support scattered into the bounded DOFs = K_bf*U_f
@@ -21,7 +22,8 @@
 namespace obgpu {
 
 #ifndef OBGPU_FRAME_MINB
-#define OBGPU_FRAME_MINB(MAXR) ((MAXR) <= 6 ? 5 : 4)   // CTAs per SM the register allocation aims at
+#define OBGPU_FRAME_MINB(MAXR) 4   // CTAs per SM the register allocation aims at: 128 registers, no spills (5 and 6 CTAs
+                                  // were measured: the spill code costs more than the extra warps hide)
 #endif
 #ifdef OBGPU_FRAME_CLOCKS  // experiment build only: per-stage cycle sums (lane 0 of every warp), read by scripts/exp
 __device__ unsigned long long g_frame_clk[8];
@@ -42,7 +44,8 @@ extern "C" void obgpu_debug_frame_clocks(unsigned long long* out, int reset) {
 #define OB_CLK(i)
 #endif
 constexpr int STAGE_D = 27;  // doubles staged per element: 21 stiffness + 6 equivalent loads
-constexpr int CHUNK = 16;    // elements staged at a time
+constexpr int CHUNK = 16;    // elements computed and staged at a time.  Measured and rejected: 32 (the larger staging buffer costs
+                             // resident warps), and computing 32 in registers + staging in two halves (no fewer instructions)
 
 // per-warp shared memory: band[max_band] | Ff[max_nf] | R[max_nb] | Eq[max_nb] | Dinv[max_nf] | stage[CHUNK*STAGE_D]
 // | slots[CHUNK*6] (int).  Stage C reuses stage[] as [CHUNK][12] stress + [CHUNK][6] global end forces.
@@ -302,6 +305,10 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
         if (e2) x2 = rp[2];
         if (e3) x3 = rp[3];
         if (in) f = Ff[j + lane];
+        // The 4 x 4 head of the panel (rows j..j+3) and F(j..j+3) are read by EVERY lane (broadcast loads) and factored
+        // redundantly: reciprocal pivots i_k, scaled pivot-row entries c_rk = V(j+r, j+k) / D(j+k) and t_k = y(j+k) / D(j+k)
+        // are then in registers everywhere, with no shuffle in the pivot chain.  The operations on a pivot row are the
+        // ones its own lane applies to x0..x3 below, in the same order, so both copies agree bit for bit.
         double i0, i1 = 0.0, i2 = 0.0, i3 = 0.0;
         {  // column j
           const double d = __shfl_sync(0xffffffffu, x0, 0);
@@ -357,7 +364,12 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
         if (e1) rp[1] = x1;  // column j was final already
         if (e2) rp[2] = x2;
         if (e3) rp[3] = x3;
-        if (lane < 4 && in) Dinv[j + lane] = lane == 0 ? i0 : lane == 1 ? i1 : lane == 2 ? i2 : i3;
+        if (lane == 0) {
+          Dinv[j] = i0;
+          if (nrows > 1) Dinv[j + 1] = i1;
+          if (nrows > 2) Dinv[j + 2] = i2;
+          if (nrows > 3) Dinv[j + 3] = i3;
+        }
         pu01[lane] = make_double2(x0, x1);
         pu23[lane] = make_double2(x2, x3);
         ps01[lane] = make_double2(x0 * i0, x1 * i1);
