@@ -260,6 +260,20 @@ const char* obgpu_kernel_info(const obgpu_ctx*);
 /* the CUDA stream the ctx launches on (a cudaStream_t), so callers can record their own events on it */
 int obgpu_get_stream(obgpu_ctx*, void** stream);
 
+/* The offset scans of the symbolic phase with NO allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  From d_counts [n_structures][4] int32 in DEVICE memory (per structure: n DOFs, n_f free, n_b bounded,
+ * one unused word; 16-byte aligned) it writes the three exclusive-scan offset arrays obgpu_get_offsets returns after
+ * obgpu_symbolic (OBGPU_OFF_DOF / OFF_FREE / OFF_BOUNDED), each [n_structures + 1] int64 in DEVICE memory, on `stream`
+ * (a cudaStream_t, may be 0) of device `device`; it returns after the launches, without synchronising.  The per-chunk
+ * partial sums live in a file-scope device array of 96 KB that every GPU loading the library holds until exit.
+ * Limit: 1 <= n_structures <= 4 194 304; larger counts return OBGPU_EINVAL with the reason in err (nullable, err_cap bytes).
+ * Calls no cudaMalloc / cudaFree and no allocating routine.  All calls share the one scratch array: calls that overlap on
+ * the GPU (different streams) race on it, so issue them on one stream.  The first call on a device looks the array's
+ * address up (cudaGetSymbolAddress): make that call outside graph capture. */
+int obgpu_scan_offsets_static(int device, int64_t n_structures, const int32_t* d_counts, int64_t* d_dof_off,
+                              int64_t* d_free_off, int64_t* d_bnd_off, void* stream, char* err, size_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -335,4 +335,72 @@ cudaError_t launch_symbolic_device(const SymDev& d, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+// ---- obgpu_scan_offsets_static: the offset scans with their scratch in a file-scope device array (no allocation) ----
+// Added for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+// serving loops); it has no counterpart in the reference.  The same three scan kernels as launch_symbolic_device, but the
+// per-chunk partial sums live in g_scan_static instead of the context's cudaMalloc'ed d_sym_partial.
+//   * the array is held by every GPU that loads the library until the process exits: 3 * (4096 + 1) * 8 B = 96 KB
+//   * nothing in it has to start at zero: k_sym_scan_partial writes every entry [0, 3 * nchunk) before k_sym_scan_bases
+//     reads them and writes the totals, so the contents a previous call left behind are never read
+//   * every call shares the array: two calls that overlap on the GPU (different streams, or a graph replayed while
+//     another call runs) race on it.  Serialise them on one stream.
+constexpr int64_t SCAN_STATIC_MAX_CHUNKS = 4096;                                 // 4 194 304 structures (BASELINE config C3)
+constexpr int64_t SCAN_STATIC_MAX_STRUCTURES = SCAN_STATIC_MAX_CHUNKS * SCAN_CHUNK;
+static __device__ __align__(256) int64_t g_scan_static[3 * (SCAN_STATIC_MAX_CHUNKS + 1)];
+
+// In host code `g_scan_static` is only the symbol's host-side stand-in: the device address comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+constexpr int SCAN_STATIC_MAX_DEVICES = 64;
+static int64_t* g_scan_static_addr[SCAN_STATIC_MAX_DEVICES];   // device address of g_scan_static on device d (0 = not asked yet)
+
+static void scan_static_msg(char* err, size_t cap, const char* msg) {
+  if (!err || cap == 0) return;
+  size_t i = 0;
+  for (; msg[i] && i + 1 < cap; i++) err[i] = msg[i];
+  err[i] = 0;
+}
+
 }  // namespace obgpu
+
+extern "C" int obgpu_scan_offsets_static(int device, int64_t n_structures, const int32_t* d_counts, int64_t* d_dof_off,
+                                         int64_t* d_free_off, int64_t* d_bnd_off, void* stream, char* err, size_t err_cap) {
+  using namespace obgpu;
+  scan_static_msg(err, err_cap, "");
+  if (n_structures < 1 || !d_counts || !d_dof_off || !d_free_off || !d_bnd_off) {
+    scan_static_msg(err, err_cap, "obgpu_scan_offsets_static: null array or n_structures < 1");
+    return OBGPU_EINVAL;
+  }
+  if (n_structures > SCAN_STATIC_MAX_STRUCTURES) {
+    scan_static_msg(err, err_cap,
+                    "obgpu_scan_offsets_static: n_structures exceeds the static scratch (maximum 4194304 structures); use "
+                    "obgpu_batch_upload_device + obgpu_symbolic, which allocate their scratch");
+    return OBGPU_EINVAL;
+  }
+  if (device < 0 || device >= SCAN_STATIC_MAX_DEVICES) {
+    scan_static_msg(err, err_cap, "obgpu_scan_offsets_static: device index out of range");
+    return OBGPU_EINVAL;
+  }
+  int prev = -1;
+  cudaError_t e = cudaGetDevice(&prev);
+  if (e == cudaSuccess && prev != device) e = cudaSetDevice(device);
+  if (e == cudaSuccess && !g_scan_static_addr[device]) {  // set-up, once per device (racing first calls store the same value)
+    int64_t* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_scan_static);
+    if (e == cudaSuccess) g_scan_static_addr[device] = p;
+  }
+  if (e == cudaSuccess) {
+    int64_t* scratch = g_scan_static_addr[device];
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned nchunk = unsigned((n_structures + SCAN_CHUNK - 1) / SCAN_CHUNK);
+    k_sym_scan_partial<<<nchunk, SCAN_CHUNK, 0, st>>>(n_structures, d_counts, scratch);
+    k_sym_scan_bases<<<1, 32, 0, st>>>(nchunk, scratch);
+    k_sym_scan_apply<<<nchunk, SCAN_CHUNK, 0, st>>>(n_structures, d_counts, scratch, d_dof_off, d_free_off, d_bnd_off);
+    e = cudaGetLastError();
+  }
+  if (prev >= 0 && prev != device) cudaSetDevice(prev);
+  if (e != cudaSuccess) {
+    scan_static_msg(err, err_cap, cudaGetErrorString(e));
+    return OBGPU_ECUDA;
+  }
+  return OBGPU_OK;
+}

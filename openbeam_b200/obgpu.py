@@ -40,7 +40,7 @@ ABI_SYMBOLS = (
     "obgpu_solve_static", "obgpu_stress", "obgpu_get_sizes", "obgpu_get_offsets", "obgpu_get_symbolic",
     "obgpu_download", "obgpu_result_count", "obgpu_symbolic_count", "obgpu_device_ptr", "obgpu_synchronize", "obgpu_solve_cases_host", "obgpu_solve_cases_host_flags",
     "obgpu_summaries_device", "obgpu_get_timings", "obgpu_pcg_info", "obgpu_profile_kernel", "obgpu_set_stress_length_poses", "obgpu_get_stream", "obgpu_kernel_info", "obgpu_bind_summaries", "obgpu_bind_summary_peers",
-    "obgpu_mesh_create", "obgpu_mesh_desc", "obgpu_mesh_info", "obgpu_mesh_destroy",
+    "obgpu_mesh_create", "obgpu_mesh_desc", "obgpu_mesh_info", "obgpu_mesh_destroy", "obgpu_scan_offsets_static",
 )
 
 
@@ -121,6 +121,7 @@ def lib():
         L.obgpu_set_stress_length_poses.argtypes = [vp, vp]
         L.obgpu_profile_kernel.argtypes = [vp, C.c_int, C.c_int, vp, vp]
         L.obgpu_get_stream.argtypes = [vp, C.POINTER(vp)]
+        L.obgpu_scan_offsets_static.argtypes = [C.c_int, i64, vp, vp, vp, vp, vp, C.c_char_p, C.c_size_t]
         _LIB = L
     return _LIB
 
@@ -148,6 +149,16 @@ def pinned_empty(shape, dtype=np.float64):
     buf = (C.c_char * n).from_address(ptr.value)
     weakref.finalize(buf, _free_pinned, ptr.value)  # numpy keeps buf alive through the buffer protocol
     return np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+
+
+def scan_offsets_static(device, n_structures, d_counts, d_dof_off, d_free_off, d_bnd_off, stream=0):
+    """obgpu_scan_offsets_static: the symbolic phase's offset scans with static device scratch (allocates nothing).  All
+    array arguments are DEVICE addresses (ints): counts [S][4] int32 in, three [S+1] int64 offset arrays out."""
+    err = C.create_string_buffer(256)
+    rc = lib().obgpu_scan_offsets_static(int(device), int(n_structures), int(d_counts), int(d_dof_off), int(d_free_off),
+                                         int(d_bnd_off), int(stream) or None, err, len(err))
+    if rc != OK:
+        raise ObgpuError(rc, err.value.decode() or lib().obgpu_status_string(rc).decode())
 
 
 def pack_batch(structures):
