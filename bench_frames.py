@@ -6,8 +6,10 @@ A *step* = one pass over the rank's frames: per structure the complete solveStat
 stiffness, assembly into the banded K_ff, BC elimination, LDL^T, solve, reactions, element end forces) in the
 warp-per-structure kernel, one launch per size class.
   value  the batch and its symbolic products resident in HBM (uploaded and numbered once, before the timed region)
-  e2e    per step, from pinned HOST buffers: obgpu_batch_upload_device (H2D of the whole batch) + obgpu_symbolic (DOF
-         numbering, partition, slots as device kernels) + obgpu_solve_static + download of U_f, F_b, compact stresses, info
+  e2e    per step, from pinned HOST buffers to pinned HOST buffers: the rank's frames cut into 8 sub-batches and dealt to
+         4 contexts (openbeam_b200/pipeline.py); per sub-batch obgpu_batch_upload_device (H2D) + obgpu_symbolic (DOF
+         numbering, partition, slots as device kernels) + obgpu_solve_static + download of U_f, F_b, compact stresses,
+         info — the H2D copy of one sub-batch overlaps the kernels of another and the D2H copy of a third
 """
 from __future__ import annotations
 
@@ -17,6 +19,9 @@ import time
 import numpy as np
 
 from openbeam_b200 import obgpu, sharding, workloads
+from openbeam_b200.pipeline import BatchPipeline
+
+E2E_SUB, E2E_WORKERS = 8, 4   # sub-batches per step and contexts of the end-to-end leg (scripts/exp/c3_pipeline.py)
 
 METRIC = "static solves/s (FP64; full assemble+factor+solve+stress per load case)"
 UNIT = "solves/s"
@@ -92,16 +97,10 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    h_U, h_Fb = obgpu.pinned_empty((1, z["nf_tot"])), obgpu.pinned_empty((1, z["nb_tot"]))
-    h_S = obgpu.pinned_empty((1, z["Etot"], 2, 3))
-    h_info = obgpu.pinned_empty((1, S), np.int32)
-
-    def e2e_step():
-        ctx.upload(batch, device=True)     # H2D of the whole batch from pinned host memory
-        ctx.symbolic()                     # DOF numbering / partition / slots on the device
-        ctx.solve_static(compact_stress=True)
-        ctx.download(obgpu.RES_UF, h_U); ctx.download(obgpu.RES_FB, h_Fb)
-        ctx.download(obgpu.RES_STRESS_COMPACT, h_S); ctx.download(obgpu.RES_INFO, h_info)
+    flops = flops_estimate(batch)
+    in_bytes = int(sum(v.nbytes for v in batch.values() if isinstance(v, np.ndarray)))
+    ctx._keep = None
+    del batch            # the value leg works on the device-resident batch: give the pinned host copy back
 
     with torch.cuda.stream(ext):
         for _ in range(W):
@@ -129,15 +128,27 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
         kernel_name = ctx.kernel_info()
         if ctx.download(obgpu.RES_INFO).any():
             raise SystemExit("bench.py: a structure reported a non-positive pivot")
+        U_res = ctx.download(obgpu.RES_UF)
         barrier()
+        # ---- end to end: host buffers in, host buffers out, every step ----
+        per = S // E2E_SUB
+        subs = [workloads.c3_batch(rank * S + i * per, per if i < E2E_SUB - 1 else S - per * (E2E_SUB - 1),
+                                   pinned=lambda shape, dt: obgpu.pinned_empty(shape, dt)) for i in range(E2E_SUB)]
+        pipe = BatchPipeline(local_rank, E2E_WORKERS)
+        res = None
         for _ in range(2):
-            e2e_step()
+            res = pipe.run(subs, res)
         barrier()
         t0 = time.perf_counter()
         for _ in range(K):
-            e2e_step()
+            res = pipe.run(subs, res)
         torch.cuda.synchronize(dev)
         e2e_s = time.perf_counter() - t0
+        out_bytes = int(sum(r[k].nbytes for r in res for k in ("U_f", "F_b", "stress", "info")))
+        e2e_same = bool(np.array_equal(np.concatenate([r["U_f"][0] for r in res]), U_res[0]))
+        if any(r["info"].any() for r in res):
+            raise SystemExit("bench.py: a structure of the end-to-end leg reported a non-positive pivot")
+        pipe.close()
         t_last = ctx.timings()
         barrier()
         clocks = sampler.stop() if sampler else None
@@ -150,9 +161,6 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
         value = world * S * K / (ms_total * 1e-3)
         alg = alg_bytes_in(z) + alg_bytes_out(z)
         achieved = alg / (k_ms * 1e-3) / 1e9
-        flops = flops_estimate(batch)
-        in_bytes = int(sum(v.nbytes for v in batch.values() if isinstance(v, np.ndarray)))
-        out_bytes = int(h_U.nbytes + h_Fb.nbytes + h_S.nbytes + h_info.nbytes)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -169,9 +177,11 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
                          "peak_source": peak_src},
             "e2e": {"value": world * S * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": in_bytes,
                     "d2h_bytes_per_step": out_bytes,
-                    "api": "obgpu_batch_upload_device (pinned host arrays of the whole batch) + obgpu_symbolic (device "
-                           "kernels) + obgpu_solve_static + obgpu_download of U_f, F_b, compact stress, info into pinned "
-                           "host buffers", "symbolic_ms_last": t_last["symbolic"], "h2d_ms_last": t_last["H2D"]},
+                    "api": "openbeam_b200.pipeline.BatchPipeline: %d sub-batches over %d contexts; per sub-batch "
+                           "obgpu_batch_upload_device (pinned host arrays) + obgpu_symbolic (device kernels) + "
+                           "obgpu_solve_static + obgpu_download of U_f, F_b, compact stress, info into pinned host "
+                           "buffers" % (E2E_SUB, E2E_WORKERS),
+                    "U_f_identical_to_resident_leg": e2e_same, "symbolic_ms_whole_batch": t_last["symbolic"]},
             "gpu_launches": int(K * launches_per_step),
             "once_s": {"generate_inputs_host": t_gen, "upload": t_upload, "symbolic_device": t_sym},
             "clocks": clocks,

@@ -38,20 +38,20 @@ int batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d) {
   if (!d->node_off || !d->elem_off || !d->con_off || !d->nload_off || !d->eload_off)
     return fail(c, OBGPU_EINVAL, "offset arrays are mandatory");
   HostBatch& hb = c->hb;
-  hb = HostBatch();
-  const int64_t S = hb.S = d->n_structures;
-  hb.node_off.assign(d->node_off, d->node_off + S + 1);
-  hb.elem_off.assign(d->elem_off, d->elem_off + S + 1);
-  hb.con_off.assign(d->con_off, d->con_off + S + 1);
-  hb.nload_off.assign(d->nload_off, d->nload_off + S + 1);
-  hb.eload_off.assign(d->eload_off, d->eload_off + S + 1);
-  for (auto* v : {&hb.node_off, &hb.elem_off, &hb.con_off, &hb.nload_off, &hb.eload_off}) {
-    if ((*v)[0] != 0) return fail(c, OBGPU_EINVAL, "offset arrays must start at 0");
-    for (int64_t s = 0; s < S; s++)
-      if ((*v)[s + 1] < (*v)[s]) return fail(c, OBGPU_EINVAL, "offset arrays must be non-decreasing");
+  {  // reset, keeping the capacity of the five offset vectors (a job that uploads batch after batch reuses the pages)
+    std::vector<int64_t> keep[5] = {std::move(hb.node_off), std::move(hb.elem_off), std::move(hb.con_off), std::move(hb.nload_off),
+                                    std::move(hb.eload_off)};
+    hb = HostBatch();
+    hb.node_off = std::move(keep[0]); hb.elem_off = std::move(keep[1]); hb.con_off = std::move(keep[2]);
+    hb.nload_off = std::move(keep[3]); hb.eload_off = std::move(keep[4]);
+    for (auto* v : {&hb.node_off, &hb.elem_off, &hb.con_off, &hb.nload_off, &hb.eload_off}) v->clear();
   }
-  const int64_t N = hb.Ntot(), E = hb.Etot(), C = hb.Ctot(), NL = hb.NLtot(), EL = hb.ELtot();
+  const int64_t S = hb.S = d->n_structures;
+  // totals straight from the caller's arrays: the copies below are issued first, the offset arrays are checked on the host
+  // while the DMA runs
+  const int64_t N = d->node_off[S], E = d->elem_off[S], C = d->con_off[S], NL = d->nload_off[S], EL = d->eload_off[S];
   if (N < 1 || E < 1) return fail(c, OBGPU_EINVAL, "empty structure (ASSERT_(nDOFs > 0))");
+  if (C < 0 || NL < 0 || EL < 0) return fail(c, OBGPU_EINVAL, "offset arrays must be non-decreasing");
   if (N >= INT32_MAX / 3 || E >= INT32_MAX / 21) return fail(c, OBGPU_EUNSUPPORTED, "batch too large for 32-bit slots: split it");
   if (!d->node_xy || !d->elem_nodes || !d->elem_type || !d->elem_EAI) return fail(c, OBGPU_EINVAL, "null geometry array");
   if ((C && (!d->con_node || !d->con_dof || !d->con_val)) || (NL && (!d->nload_node || !d->nload_dof || !d->nload_val)) ||
@@ -61,11 +61,11 @@ int batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d) {
   hb.has_load_kinds = d->eload_type != nullptr && EL > 0;
   cudaStream_t st = c->stream;
   OB_CUDA(c, cudaEventRecord(c->ev[0], st));
-  OB_CUDA(c, c->d_off_node.upload(hb.node_off, st));
-  OB_CUDA(c, c->d_off_elem.upload(hb.elem_off, st));
-  OB_CUDA(c, c->d_off_con.upload(hb.con_off, st));
-  OB_CUDA(c, c->d_off_nload.upload(hb.nload_off, st));
-  OB_CUDA(c, c->d_off_eload.upload(hb.eload_off, st));
+  OB_CUDA(c, c->d_off_node.upload(d->node_off, size_t(S + 1), st));
+  OB_CUDA(c, c->d_off_elem.upload(d->elem_off, size_t(S + 1), st));
+  OB_CUDA(c, c->d_off_con.upload(d->con_off, size_t(S + 1), st));
+  OB_CUDA(c, c->d_off_nload.upload(d->nload_off, size_t(S + 1), st));
+  OB_CUDA(c, c->d_off_eload.upload(d->eload_off, size_t(S + 1), st));
   OB_CUDA(c, c->d_node_xy.upload(d->node_xy, size_t(2 * N), st));
   if (hb.has_rotz) OB_CUDA(c, c->d_node_rot.upload(d->node_rotz, size_t(N), st));
   OB_CUDA(c, c->d_elem_nodes.upload(d->elem_nodes, size_t(2 * E), st));
@@ -90,6 +90,21 @@ int batch_upload_device(obgpu_ctx* c, const obgpu_batch_desc* d) {
   }
   OB_CUDA(c, cudaEventRecord(c->ev[1], st));
   c->t_have[0] = true;
+  // host copies of the offset arrays (totals, on-demand per-structure offsets) + their checks, while the copies are in flight
+  hb.node_off.assign(d->node_off, d->node_off + S + 1);
+  hb.elem_off.assign(d->elem_off, d->elem_off + S + 1);
+  hb.con_off.assign(d->con_off, d->con_off + S + 1);
+  hb.nload_off.assign(d->nload_off, d->nload_off + S + 1);
+  hb.eload_off.assign(d->eload_off, d->eload_off + S + 1);
+  for (auto* v : {&hb.node_off, &hb.elem_off, &hb.con_off, &hb.nload_off, &hb.eload_off}) {
+    bool ok = (*v)[0] == 0;
+    for (int64_t s = 0; s < S && ok; s++) ok = (*v)[s + 1] >= (*v)[s];
+    if (!ok) {
+      cudaStreamSynchronize(st);
+      c->uploaded = false;
+      return fail(c, OBGPU_EINVAL, (*v)[0] != 0 ? "offset arrays must start at 0" : "offset arrays must be non-decreasing");
+    }
+  }
   hb.L = d->n_cases < 1 ? 1 : d->n_cases;
   c->uploaded = true;
   c->device_batch_mode = true;

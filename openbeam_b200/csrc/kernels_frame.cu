@@ -552,7 +552,9 @@ static cudaError_t launch_frame_rg(const FrameArgs& a, int sm_count, cudaStream_
   const size_t smem = per_warp * FRAME_WARPS;
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
   auto kern = k_frame_fused<MAXR, GEN>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+  // always the device maximum: the attribute is per function, not per launch, and contexts on other host threads launch
+  // the same instantiation with other class sizes (a smaller value set there would fail this launch)
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return e;
   int per_sm = 1;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FRAME_WARPS * 32, smem);

@@ -283,12 +283,10 @@ cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st) {
 }
 cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStream_t st) {
   const size_t smem = size_t(d.asm_max_loc) * ELEM_K * sizeof(double);
-  static size_t configured = 0;
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(k_assemble_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  // the attribute belongs to the (function, device) pair, not to the launch: always the device maximum, set on every call
+  // (contexts on other devices or host threads launch the same function with other sizes)
+  cudaError_t e = cudaFuncSetAttribute(k_assemble_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return e;
   k_assemble_fused<<<nblk(d.nnz, ASM_SLOTS), ASM_THREADS, smem, st>>>(d.nnz, d.seg_ptr, d.seg_loc, d.blk_elem_ptr, d.blk_elems,
                                                               d.elem_nodes, d.elem_type, eai, d.node_xy, d.elem_node0, d.node_rot, d.kval);
   return cudaGetLastError();

@@ -453,7 +453,7 @@ static cudaError_t launch_nf(const TinyParam& P, const TinyArgs& a, int n, int s
   const size_t smem = size_t(4 * P.E + 2 * P.EL) * 8 +
                       size_t((BLK ? 12 + (NF > 6 ? NF : 6) : (NFP > 12 ? NFP : 12)) + n + (a.case_nl ? P.NL : 0) + (a.case_q ? 2 * P.EL : 0)) * (TINY_BLOCK + 1) * 8;
   auto kern = k_tiny_fused<NF, MINB, BLK>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);  // per function, not per launch: other host threads launch it with other sizes
   if (e != cudaSuccess) return e;
   int per_sm = 1;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TINY_BLOCK, smem);

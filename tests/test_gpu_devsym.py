@@ -126,3 +126,26 @@ def test_device_batch_refuses_malformed_structure(ctx):
     with pytest.raises(obgpu.ObgpuError) as e:
         ctx.symbolic()
     assert "unknown element type" in str(e.value)
+
+
+def test_batch_pipeline_matches_one_context():
+    """openbeam_b200/pipeline.py: sub-batches dealt to several contexts on concurrent host threads give, concatenated, the
+    results of one context over the whole list (bit for bit: independent structures, same kernel)."""
+    from openbeam_b200.pipeline import BatchPipeline
+    S, nsub = 6000, 5
+    ctx = obgpu.Context(0)
+    ctx.upload(workloads.c3_batch(100, S), device=True)
+    ctx.symbolic()
+    ctx.solve_static(compact_stress=True)
+    U, Fb, St = ctx.download(obgpu.RES_UF), ctx.download(obgpu.RES_FB), ctx.download(obgpu.RES_STRESS_COMPACT)
+    ctx.close()
+    per = S // nsub
+    subs = [workloads.c3_batch(100 + i * per, per) for i in range(nsub)]
+    pipe = BatchPipeline(0, workers=3)
+    res = pipe.run(subs, offsets=True)
+    res = pipe.run(subs, res, offsets=True)   # second pass reuses the result buffers
+    pipe.close()
+    assert np.array_equal(np.concatenate([r["U_f"][0] for r in res]), U[0])
+    assert np.array_equal(np.concatenate([r["F_b"][0] for r in res]), Fb[0])
+    assert np.array_equal(np.concatenate([r["stress"][0] for r in res]), St[0])
+    assert all(not r["info"].any() for r in res) and all(len(r["free_off"]) == per + 1 for r in res)
