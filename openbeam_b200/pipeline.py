@@ -19,13 +19,13 @@ from . import obgpu
 
 
 class BatchPipeline:
-    def __init__(self, device=0, workers=3):
+    def __init__(self, device=0, workers=3, copy_slots=1):
         self.device = device
         self.ctxs = [obgpu.Context(device) for _ in range(max(1, int(workers)))]
         # one sub-batch at a time per resource (H2D copy engine, SMs, D2H copy engine): the workers then fall into a
         # staggered rhythm in which the three resources are busy at once.  Without the locks all workers upload together,
         # compute together and download together, and the two PCIe directions never overlap.
-        self._h2d, self._sm, self._d2h = threading.Lock(), threading.Lock(), threading.Lock()
+        self._h2d, self._sm, self._d2h = threading.Semaphore(copy_slots), threading.Lock(), threading.Semaphore(copy_slots)
 
     def close(self):
         for c in self.ctxs:
