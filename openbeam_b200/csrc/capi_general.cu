@@ -1,5 +1,6 @@
 // capi_general.cu — general (any-topology) path: device copies of the batch, the warp-per-structure fused
 // kernel for small structures, summaries.  Assembly of the global K and the PCG route live in capi_sparse.cu.
+#include <cstdlib>
 #include <algorithm>
 
 #include "ctx.h"
@@ -237,20 +238,36 @@ int solve_general(obgpu_ctx* c, const obgpu_solve_opts& o) {
   a.info = c->d_info.p; a.fail = c->d_fail.p;
   a.order = c->d_frame_order.p;
   a.free_inv = c->frame_renumbered ? c->d_frame_inv.p : nullptr;
+  // One load case, identity node frames, U_b = 0 and at least a few thousand structures: the three-kernel path (element
+  // arithmetic of stages A and C in kernels of their own, kernels_frame.cu).  Everything else: the fused kernel.
+  // (OBGPU_FRAME_SPLIT=0 switches it off, OBGPU_FRAME_SPLIT_MIN=n moves the structure-count threshold: tests, A/B runs)
+  const char* env_split = std::getenv("OBGPU_FRAME_SPLIT");
+  const char* env_min = std::getenv("OBGPU_FRAME_SPLIT_MIN");
+  const int64_t split_min = env_min ? std::atoll(env_min) : 4096;
+  const bool split = !(env_split && env_split[0] == '0') && L == 1 && !a.U_b && !a.node_rot && !a.node_xy_len && !a.case_nl && !a.case_q && !a.case_eai &&
+                     c->hb.S >= split_min && c->max_nb <= 1024;
+  a.erec = nullptr;
+  if (split) {
+    OB_CUDA(c, c->d_erec.reserve(size_t(c->hb.Etot()) * FRAME_EREC));
+    a.erec = c->d_erec.p;
+  }
   OB_CUDA(c, cudaEventRecord(c->ev[2], c->stream));
+  if (split) OB_CUDA(c, launch_frame_pre(a, c->sm_count, c->stream));
   for (auto it = c->frame_classes.rbegin(); it != c->frame_classes.rend(); ++it) {  // largest structures first
     const obgpu_ctx::FrameClass& fc = *it;
     a.o0 = fc.o0; a.o1 = fc.o1;
     a.max_band = fc.max_band; a.max_nf = fc.max_nf; a.max_nb = fc.max_nb; a.max_hb = fc.max_hb;
     OB_CUDA(c, launch_frame_fused(a, c->sm_count, c->stream));
   }
+  if (split) OB_CUDA(c, launch_frame_post(a, c->max_nb, c->sm_count, c->stream));
   OB_CUDA(c, cudaEventRecord(c->ev[3], c->stream));
   c->t_have[1] = true;
-  c->launches = double(c->frame_classes.size());
+  c->launches = double(c->frame_classes.size()) + (split ? 2 : 0);
   c->pcg_iters = 0;
   c->solved = true;
   c->have_ff = true;
-  c->kernel_info = "k_frame_fused (warp per structure, banded LDLt in shared memory)";
+  c->kernel_info = split ? "k_frame_pre + k_frame_fused<split> + k_frame_post (warp per structure, banded LDLt in shared memory)"
+                         : "k_frame_fused (warp per structure, banded LDLt in shared memory)";
   c->have_stress = o.with_stress != 0;
   return OBGPU_OK;
 }

@@ -36,6 +36,7 @@ struct obgpu_ctx {
   obgpu::DevBuf<double> d_case_nl, d_case_q, d_case_eai;
   obgpu::DevBuf<int32_t> d_prog_i;
   obgpu::DevBuf<double> d_prog_d;
+  obgpu::DevBuf<double> d_erec;   // element records of the three-kernel frame path (kernels_frame.cu)
   obgpu::DevBuf<double> d_Uf, d_Fb, d_stress, d_stress_c, d_Ff, d_Ub;  // d_stress_c: compact (N,Vy,Mz) records
   obgpu::DevBuf<int32_t> d_info;
   obgpu::DevBuf<int64_t> d_free_off, d_bnd_off;  // [S+1]

@@ -69,6 +69,7 @@ struct FrameArgs {
   double* stress;               // [L][Etot][12] or null
   int32_t* info;                // [L][S]
   int32_t* fail;                // [1]
+  double* erec;                 // [Etot][FRAME_EREC] element records of the three-kernel path, or null: fused kernel
   // size class served by this launch: structures order[o0 .. o1), whose banded K_ff, n_f, n_b and half bandwidth
   // are bounded by the class maxima below (shared memory per warp is sized from them)
   const int32_t* order;         // [S] structure ids sorted by size class
@@ -77,7 +78,10 @@ struct FrameArgs {
   int max_band;                 // max over the class of frame_ld(hb)*nf   (doubles)
   int max_nf, max_nb, max_hb;
 };
+constexpr int FRAME_EREC = 30;  // doubles per element record: 21 stiffness entries + 6 equivalent loads + 6 int32 slots
 cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st);
+cudaError_t launch_frame_pre(const FrameArgs& a, int sm_count, cudaStream_t st);                // FrameArgs::erec != null
+cudaError_t launch_frame_post(const FrameArgs& a, int max_nb, int sm_count, cudaStream_t st);
 size_t frame_smem_per_warp(int max_band, int max_nf, int max_nb);
 constexpr int FRAME_WARPS = 4;  // warps per CTA of k_frame_fused
 

@@ -43,6 +43,12 @@ extern "C" void obgpu_debug_frame_clocks(unsigned long long* out, int reset) {
 #else
 #define OB_CLK(i)
 #endif
+#ifndef OBGPU_FRAME_SPLIT_MINB
+#define OBGPU_FRAME_SPLIT_MINB 6
+#endif
+#ifndef OBGPU_FRAME_PRE_MINB
+#define OBGPU_FRAME_PRE_MINB 6    // k_frame_pre / k_frame_post: 80 registers, 24 warps per SM (64 registers spill)
+#endif
 constexpr int STAGE_D = 27;  // doubles staged per element: 21 stiffness + 6 equivalent loads
 constexpr int CHUNK = 16;    // elements computed and staged at a time.  Measured and rejected: 32 (the larger staging buffer costs
                              // resident warps), and computing 32 in registers + staging in two halves (no fewer instructions)
@@ -117,8 +123,13 @@ __device__ __forceinline__ void tile_update(double* bj, int voff, int a0, int c0
 
 // GEN: the general path (nodal rotated frames and/or non-zero prescribed displacements) is a separate
 // instantiation so that its extra state never costs the common kernel a register.
-template <int MAXR, bool GEN>
-__global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_frame_fused(FrameArgs a, int doubles_per_warp) {
+// SPLIT: the middle kernel of the three-kernel path (k_frame_pre -> this -> k_frame_post, see below): the element records
+// arrive precomputed from global memory instead of being formed here, and stage C is left to k_frame_post.  Without the
+// element arithmetic the kernel needs fewer registers and runs more resident warps, which is what this latency-bound
+// factorisation is short of.
+template <int MAXR, bool GEN, bool SPLIT>
+__global__ void __launch_bounds__(FRAME_WARPS * 32, SPLIT ? OBGPU_FRAME_SPLIT_MINB : OBGPU_FRAME_MINB(MAXR))
+    k_frame_fused(FrameArgs a, int doubles_per_warp) {
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double* band = smem + size_t(warp) * doubles_per_warp;
@@ -166,6 +177,10 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
     for (int pass = 0; pass < (Ub ? 2 : 1); pass++) {
     for (int eb = 0; eb < m.E; eb += CHUNK) {
       const int cnt = min(CHUNK, m.E - eb);
+      if (SPLIT) {  // records of k_frame_pre: [FRAME_EREC] doubles per element = 21 stiffness + 6 loads + 6 int32 slots
+        const double* src = a.erec + (m.e0 + eb) * FRAME_EREC;
+        for (int i = lane; i < cnt * FRAME_EREC; i += 32) stage[i] = src[i];
+      } else
       if (lane < cnt) {
         const int64_t e = m.e0 + eb + lane;
         const uint2 nd = a.elem_nodes[e];
@@ -225,11 +240,11 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
       // lane's target is a single offset from `band`; the next element's offset and value are fetched while the
       // current read-modify-write is in flight (the RMW chain is the only serial dependency left).
       auto fetch = [&](int ee, int& off, double& v) {
-        const int32_t* sl = slots + ee * 6;
+        const int32_t* sl = SPLIT ? reinterpret_cast<const int32_t*>(stage + ee * FRAME_EREC + STAGE_D) : slots + ee * 6;
         off = -1;
         v = 0.0;
         if (lane < STAGE_D && (pass == 0 || lane >= ELEM_K)) {
-          v = stage[ee * STAGE_D + lane];
+          v = stage[ee * (SPLIT ? FRAME_EREC : STAGE_D) + lane];
           const int32_t fi = sl[pa];
           if (lane < ELEM_K) {
             const int32_t fj = sl[pb];
@@ -238,7 +253,7 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
               off = i * W + (j - i + hb);
             }
           } else if (fi >= 0) off = offF + fi;
-          else if (fi != SLOT_NONE) off = offEq + (-fi - 1);
+          else if (!SPLIT && fi != SLOT_NONE) off = offEq + (-fi - 1);   // SPLIT: k_frame_post sums the bounded loads
         }
       };
       int off_n;
@@ -437,6 +452,10 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
     }
     for (int i = lane; i < nf; i += 32) a.U_f[c * a.nf_tot + m.f0 + (a.free_inv ? a.free_inv[m.f0 + i] : i)] = Ff[i];
     OB_CLK(4);
+    if (SPLIT) {
+      __syncwarp();
+      continue;
+    }
     // ---- stage C: element end forces, reactions ----
     double* sst = stage;                  // [CHUNK][12] stress staging
     double* sgf = stage + CHUNK * 12;     // [CHUNK][6]  global end forces
@@ -546,12 +565,200 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, OBGPU_FRAME_MINB(MAXR)) k_fr
   }
 }
 
-template <int MAXR, bool GEN>
+// ---- the three-kernel path (FrameArgs::erec != null): k_frame_pre -> k_frame_fused<., false, true> per class -> k_frame_post
+// For one load case, identity node frames and U_b = 0.  The element arithmetic of stages A and C runs in two kernels of
+// their own — warp per structure, lane per element, almost no shared memory, so 48-64 resident warps per SM instead of 16 —
+// and the factorisation kernel in between keeps only what it needs.  The price is one round trip of the element records
+// through HBM (240 B per element written and read once).  Sums are formed in the same order as in the fused kernel.
+
+// k_frame_pre: stage A's arithmetic.  Record of element e at erec[e * FRAME_EREC]: the 21 compact global stiffness entries,
+// the 6 summed equivalent nodal loads, the 6 node slots (int32) of its two ends.
+constexpr int PRE_LD = FRAME_EREC + 1;  // odd row stride of the staging rows: the per-lane record writes hit 16 banks
+__global__ void __launch_bounds__(128, OBGPU_FRAME_PRE_MINB) k_frame_pre(FrameArgs a) {
+  // The records leave through a shared-memory transpose: a lane forms its element's record, the warp then writes the
+  // chunk's records — contiguous in erec — as whole 128-byte lines (per-lane stores at a 240-byte stride cost one L2
+  // write transaction per lane and instruction, and that, not HBM, bounded the first version of this kernel).
+  __shared__ double rows_all[4][32 * PRE_LD];
+  const int lane = threadIdx.x & 31;
+  double* rows = rows_all[threadIdx.x >> 5];
+  const int64_t wstride = int64_t(gridDim.x) * (blockDim.x >> 5);
+  for (int64_t s = int64_t(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); s < a.S; s += wstride) {
+    const FrameMeta m = a.meta[s];
+    for (int eb = 0; eb < m.E; eb += 32) {
+      const int cnt = min(32, m.E - eb);
+      if (lane < cnt) {
+        const int64_t e = m.e0 + eb + lane;
+        const uint2 nd = a.elem_nodes[e];
+        const int type = a.elem_type[e];
+        const double2 p0 = a.node_xy[m.n0 + nd.x], p1 = a.node_xy[m.n0 + nd.y];
+        const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
+        const ElemLocalK lk = elem_local_k(type, a.elem_EAI[3 * e], a.elem_EAI[3 * e + 1], a.elem_EAI[3 * e + 2], g);
+        double* o = rows + lane * PRE_LD;
+        {
+          double ke[ELEM_K];
+          elem_global_k(lk, g, ke);
+#pragma unroll
+          for (int k = 0; k < ELEM_K; k++) o[k] = ke[k];
+        }
+        double gsum[6] = {0, 0, 0, 0, 0, 0};
+        for (int j = a.el_ptr[e]; j < a.el_ptr[e + 1]; j++) {
+          const int sl = a.el_order[j];
+          double gl[6], ex[6];
+          if (a.eload_type)
+            elem_load(a.eload_type[sl], type, g, a.eload_q[sl], a.eload_q2[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1],
+                      a.elem_EAI[3 * e] * a.elem_EAI[3 * e + 1], gl, ex);
+          else
+            uniform_load(type, g, a.eload_q[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
+#pragma unroll
+          for (int k = 0; k < 6; k++) gsum[k] += gl[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 6; k++) o[ELEM_K + k] = gsum[k];
+        int32_t* os = reinterpret_cast<int32_t*>(o + STAGE_D);
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          os[k] = a.node_slot[3 * (m.n0 + nd.x) + k];
+          os[3 + k] = a.node_slot[3 * (m.n0 + nd.y) + k];
+        }
+      }
+      __syncwarp();
+      double* dst = a.erec + (m.e0 + eb) * FRAME_EREC;
+      for (int i = lane; i < cnt * FRAME_EREC; i += 32) {
+        const int r = i / FRAME_EREC;
+        dst[i] = rows[r * PRE_LD + (i - r * FRAME_EREC)];
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// k_frame_post: stage C (postproc_stress.cpp:86-165, solver_static.cpp:196-218).  Per-warp shared memory:
+// sg[32][12] (global end forces | equivalent loads of the chunk's elements) | slots[32][6] | R[max_nb] | Eq[max_nb] |
+// sst[32][13] (stress rows, odd stride; written to global as whole lines like k_frame_pre's records)
+constexpr int POST_WARPS = 4;
+__global__ void __launch_bounds__(POST_WARPS * 32, OBGPU_FRAME_PRE_MINB) k_frame_post(FrameArgs a, int max_nb) {
+  extern __shared__ __align__(16) double smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int per_warp = 32 * 12 + 32 * 3 + 2 * max_nb + 32 * 13;
+  double* sg = smem + size_t(warp) * per_warp;
+  int32_t* slots = reinterpret_cast<int32_t*>(sg + 32 * 12);
+  double* R = sg + 32 * 12 + 32 * 3;
+  double* Eq = R + max_nb;
+  double* sst = Eq + max_nb;
+  const int64_t wstride = int64_t(gridDim.x) * POST_WARPS;
+  for (int64_t s = int64_t(blockIdx.x) * POST_WARPS + warp; s < a.S; s += wstride) {
+    const FrameMeta m = a.meta[s];
+    const int nb = m.nb;
+    for (int i = lane; i < nb; i += 32) { R[i] = 0.0; Eq[i] = 0.0; }
+    const double* U = a.U_f + m.f0;
+    const int32_t* finv = a.free_inv ? a.free_inv + m.f0 : nullptr;
+    __syncwarp();
+    for (int eb = 0; eb < m.E; eb += 32) {
+      const int cnt = min(32, m.E - eb);
+      bool hasb = false;
+      if (lane < cnt) {
+        const int64_t e = m.e0 + eb + lane;
+        const uint2 nd = a.elem_nodes[e];
+        const int type = a.elem_type[e];
+        const double2 p0 = a.node_xy[m.n0 + nd.x], p1 = a.node_xy[m.n0 + nd.y];
+        const ElemGeom g = elem_geom(p0.x, p0.y, p1.x, p1.y);
+        const ElemLocalK lk = elem_local_k(type, a.elem_EAI[3 * e], a.elem_EAI[3 * e + 1], a.elem_EAI[3 * e + 2], g);
+        double ug[6], es[6];
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+          const int32_t t = a.node_slot[3 * (m.n0 + (k < 3 ? nd.x : nd.y)) + (k < 3 ? k : k - 3)];
+          slots[lane * 6 + k] = t;
+          hasb |= t < 0 && t != SLOT_NONE;
+          ug[k] = t >= 0 ? U[finv ? finv[t] : t] : 0.0;   // postproc_stress.cpp:86-119 (U_b = 0 on this path)
+        }
+        if (hasb) {  // the element's summed equivalent loads (k_frame_pre's record): only supports need them here
+          const double* rec = a.erec + e * FRAME_EREC + ELEM_K;
+#pragma unroll
+          for (int k = 0; k < 6; k++) sg[lane * 12 + 6 + k] = rec[k];
+        }
+        elem_end_forces(lk, g, ug, es);
+        // K_bf U_f of this element = its global end forces (U_b = 0, identity node frames)
+        sg[lane * 12 + 0] = g.c * es[0] - g.s * es[1];
+        sg[lane * 12 + 1] = g.s * es[0] + g.c * es[1];
+        sg[lane * 12 + 2] = es[2];
+        sg[lane * 12 + 3] = g.c * es[3] - g.s * es[4];
+        sg[lane * 12 + 4] = g.s * es[3] + g.c * es[4];
+        sg[lane * 12 + 5] = es[5];
+        if (a.stress) {
+          double ext[6] = {0, 0, 0, 0, 0, 0};
+          for (int j = a.el_ptr[e]; j < a.el_ptr[e + 1]; j++) {
+            const int sl = a.el_order[j];
+            double gl[6], ex[6];
+            if (a.eload_type)
+              elem_load(a.eload_type[sl], type, g, a.eload_q[sl], a.eload_q2[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1],
+                        a.elem_EAI[3 * e] * a.elem_EAI[3 * e + 1], gl, ex);
+            else
+              uniform_load(type, g, a.eload_q[sl], a.eload_dir[3 * sl], a.eload_dir[3 * sl + 1], gl, ex);
+#pragma unroll
+            for (int k = 0; k < 6; k++) ext[k] += ex[k];
+          }
+          double* o = sst + lane * 13;  // {N,Vy,Vz,Mx,My,Mz} x 2 faces; face 0 negated (postproc_stress.cpp:152-165)
+          o[0] = -es[0] + ext[0]; o[1] = -es[1] + ext[1]; o[2] = 0.0; o[3] = 0.0; o[4] = 0.0; o[5] = -es[2] + ext[2];
+          o[6] = es[3] + ext[3];  o[7] = es[4] + ext[4];  o[8] = 0.0; o[9] = 0.0; o[10] = 0.0; o[11] = es[5] + ext[5];
+        }
+      }
+      __syncwarp();
+      if (a.stress) {
+        double* o = a.stress + (m.e0 + eb) * 12;
+        for (int i = lane; i < cnt * 12; i += 32) {
+          const int r = i / 12;
+          o[i] = sst[r * 13 + (i - r * 12)];
+        }
+      }
+      unsigned todo = __ballot_sync(0xffffffffu, hasb);  // elements touching a support, in element order
+      while (todo) {
+        const int ee = __ffs(todo) - 1;
+        todo &= todo - 1;
+        if (lane < 6) {
+          const int32_t t = slots[ee * 6 + lane];
+          if (t < 0 && t != SLOT_NONE) {
+            R[-t - 1] += sg[ee * 12 + lane];
+            Eq[-t - 1] += sg[ee * 12 + 6 + lane];
+          }
+        }
+        __syncwarp();
+      }
+    }
+    // F_b = K_bf*U_f - equivalent loads on bounded DOFs (solver_static.cpp:196-218)
+    for (int i = lane; i < nb; i += 32) a.F_b[m.b0 + i] = R[i] - Eq[i];
+    __syncwarp();
+  }
+}
+
+cudaError_t launch_frame_pre(const FrameArgs& a, int sm_count, cudaStream_t st) {
+  int64_t grid = (a.S + 3) / 4;
+  const int64_t cap = int64_t(sm_count) * OBGPU_FRAME_PRE_MINB;
+  if (grid > cap) grid = cap;
+  k_frame_pre<<<unsigned(grid < 1 ? 1 : grid), 128, 0, st>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_frame_post(const FrameArgs& a, int max_nb, int sm_count, cudaStream_t st) {
+  const size_t smem = size_t(32 * 12 + 32 * 3 + 2 * max_nb + 32 * 13) * 8 * POST_WARPS;
+  if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
+  cudaError_t e = cudaFuncSetAttribute(k_frame_post, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e != cudaSuccess) return e;
+  int per_sm = 1;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_frame_post, POST_WARPS * 32, smem);
+  if (e != cudaSuccess) return e;
+  int64_t grid = int64_t(sm_count) * (per_sm < 1 ? 1 : per_sm);
+  const int64_t need = (a.S + POST_WARPS - 1) / POST_WARPS;
+  if (grid > need) grid = need;
+  k_frame_post<<<unsigned(grid < 1 ? 1 : grid), POST_WARPS * 32, smem, st>>>(a, max_nb);
+  return cudaGetLastError();
+}
+
+template <int MAXR, bool GEN, bool SPLIT>
 static cudaError_t launch_frame_rg(const FrameArgs& a, int sm_count, cudaStream_t st) {
   const size_t per_warp = frame_smem_per_warp(a.max_band, a.max_nf, a.max_nb);
   const size_t smem = per_warp * FRAME_WARPS;
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
-  auto kern = k_frame_fused<MAXR, GEN>;
+  auto kern = k_frame_fused<MAXR, GEN, SPLIT>;
   // always the device maximum: the attribute is per function, not per launch, and contexts on other host threads launch
   // the same instantiation with other class sizes (a smaller value set there would fail this launch)
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -571,8 +778,9 @@ static cudaError_t launch_frame_rg(const FrameArgs& a, int sm_count, cudaStream_
 
 template <int MAXR>
 static cudaError_t launch_frame_r(const FrameArgs& a, int sm_count, cudaStream_t st) {
-  if (a.U_b || a.node_rot || a.node_xy_len) return launch_frame_rg<MAXR, true>(a, sm_count, st);
-  return launch_frame_rg<MAXR, false>(a, sm_count, st);
+  if (a.U_b || a.node_rot || a.node_xy_len) return launch_frame_rg<MAXR, true, false>(a, sm_count, st);
+  if (a.erec) return launch_frame_rg<MAXR, false, true>(a, sm_count, st);
+  return launch_frame_rg<MAXR, false, false>(a, sm_count, st);
 }
 
 cudaError_t launch_frame_fused(const FrameArgs& a, int sm_count, cudaStream_t st) {

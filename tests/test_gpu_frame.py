@@ -159,3 +159,26 @@ def test_summaries(ctx):
         # global equilibrium: sum of horizontal reactions = -(sum of wind loads)
         assert abs(out[s, 1] + st.nload_val.sum()) <= 1e-9 * max(1.0, np.abs(fb[:, 0]).max())
         assert out[s, 3] == 0
+
+
+def test_three_kernel_path_is_bitwise_the_fused_kernel(monkeypatch):
+    """kernels_frame.cu: k_frame_pre -> k_frame_fused<split> -> k_frame_post (the default for >= 4096 structures, one load
+    case, identity node frames, U_b = 0) forms every sum in the fused kernel's order: identical bits, both symbolic modes."""
+    from openbeam_b200 import workloads
+    batch = workloads.c3_batch(300, 3000)
+    for device_mode in (True, False):
+        got = {}
+        for split in ("0", "1"):
+            monkeypatch.setenv("OBGPU_FRAME_SPLIT", split)
+            monkeypatch.setenv("OBGPU_FRAME_SPLIT_MIN", "1")
+            ctx = obgpu.Context(0)
+            ctx.upload(batch, device=device_mode)
+            ctx.symbolic()
+            ctx.solve_static()
+            assert ("k_frame_pre" in ctx.kernel_info()) == (split == "1")
+            got[split] = [ctx.download(w).copy() for w in (obgpu.RES_UF, obgpu.RES_FB, obgpu.RES_STRESS, obgpu.RES_FF, obgpu.RES_INFO)]
+            ctx.solve_static(compact_stress=True)
+            got[split].append(ctx.download(obgpu.RES_STRESS_COMPACT).copy())
+            ctx.close()
+        for x, y in zip(got["0"], got["1"]):
+            assert np.array_equal(x, y)
