@@ -103,7 +103,8 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
     }
     if (le == cudaErrorNotSupported && c->prog.has_load_kinds) {  // no NVRTC here and non-uniform loads: general route
       c->summ_written = nullptr;
-      return solve_general(c, o);
+      cudaGetLastError();
+      goto general_route;   // (not a plain return: the compact-record pass below must follow this solve too)
     }
     OB_CUDA(c, le);
     if (compact_pass) OB_CUDA(c, launch_compact_stress(c->d_stress.p, c->d_stress_c.p, c->L * c->hb.Etot(), c->stream));
@@ -117,6 +118,7 @@ int obgpu_solve_static(obgpu_ctx* c, const obgpu_solve_opts* opts) {
     c->have_stress_c = want_compact;
     return OBGPU_OK;
   }
+general_route:
   rc = solve_general(c, o);
   if ((rc == OBGPU_OK || rc == OBGPU_ESINGULAR || rc == OBGPU_ENOTCONVERGED) && want_compact && c->have_stress) {
     // the warp-per-structure and sparse routes write the six-component record: one more pass compacts it
