@@ -276,7 +276,8 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   static const bool use_graph = !(getenv("OBGPU_PCG_GRAPH") && atoi(getenv("OBGPU_PCG_GRAPH")) == 0);
   // iterations between convergence checks (even when replayed as a graph); a multigrid iteration is ~40 kernels and
   // the whole solve ~100 iterations, so it is checked every other iteration
-  const int chk = use_mg ? 2 : use_graph ? 24 : 25;
+  int chk = use_mg ? 2 : use_graph ? 24 : 25;   // iterations between convergence checks (even: the rz ping-pong parity)
+  if (const char* ev = getenv("OBGPU_PCG_CHECK")) chk = std::max(2, atoi(ev) & ~1);
   double restarts_total = 0, worst_floor = 0;
   std::vector<double> mg_lam(MG_MAX_LEVELS, 0.0);
   double iters_total = 0, worst_rel = 0;

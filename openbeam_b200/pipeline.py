@@ -19,9 +19,9 @@ from . import obgpu
 
 
 class BatchPipeline:
-    def __init__(self, device=0, workers=3, copy_slots=1):
+    def __init__(self, device=0, workers=3, copy_slots=1, context=obgpu.Context):
         self.device = device
-        self.ctxs = [obgpu.Context(device) for _ in range(max(1, int(workers)))]
+        self.ctxs = [context(device) for _ in range(max(1, int(workers)))]   # `context`: the ctx class (tests pass a stub)
         # one sub-batch at a time per resource (H2D copy engine, SMs, D2H copy engine): the workers then fall into a
         # staggered rhythm in which the three resources are busy at once.  Without the locks all workers upload together,
         # compute together and download together, and the two PCIe directions never overlap.
