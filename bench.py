@@ -391,7 +391,9 @@ def ours_arm(args, rank, local_rank, world):
         alg = ALG_BYTES_PER_CASE + (72 if args.per_case_section else 0)  # + the 3E per-case section values read
         achieved = alg * L / (kern_avg_ms * 1e-3) / 1e9
         jit = kernel_name.startswith("k_tiny_jit")
-        traffic = TRAFFIC_BYTES_PER_CASE if jit and not args.per_case_section and args.full_stress else None
+        traffic = None
+        if jit and not args.per_case_section:
+            traffic, traffic_src = (TRAFFIC_BYTES_PER_CASE, TRAFFIC_SOURCE) if args.full_stress else (TRAFFIC_BYTES_PER_CASE_COMPACT, TRAFFIC_SOURCE_COMPACT)
         in_bytes = (h_nl.nbytes + h_q.nbytes + (h_eai.nbytes if h_eai is not None else 0))
         out_bytes = h_U.nbytes + h_Fb.nbytes + h_S.nbytes + h_info.nbytes
         line = {
@@ -401,7 +403,7 @@ def ours_arm(args, rank, local_rank, world):
             "dof_per_s": value * N_DOF,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None if traffic is None else traffic * L,
-                         "traffic_source": TRAFFIC_SOURCE if traffic is not None else None,
+                         "traffic_source": traffic_src if traffic is not None else None,
                          "kernel": kernel_name,
                          "frac_counting_summary_record": (alg + 32) * L / (kern_avg_ms * 1e-3) / 1e9 / peak
                          if launches_per_step == 1 else None,  # the kernel also writes the 32-B per-case summary
@@ -447,6 +449,10 @@ def ours_arm(args, rank, local_rank, world):
 # hands 420 MB of records to L2; what is still dirty in L2 when the kernel ends is not in the DRAM counter)
 TRAFFIC_BYTES_PER_CASE = 417.3
 TRAFFIC_SOURCE = "profiles/r01o_ncu_full_k_tiny_jit_summary.txt (1M-case launch, scaled per case)"
+# compact (N, Vy, Mz) records: dram__bytes_read 56.03 MB + dram__bytes_write 217.43 MB per 1M-case launch; below the 296 MB
+# algorithmic figure (+ 32 MB of summaries) because the tail of a launch's stores is still dirty in the 126 MB L2
+TRAFFIC_BYTES_PER_CASE_COMPACT = 273.5
+TRAFFIC_SOURCE_COMPACT = "profiles/r02e_tiny_jit_compact_ncu_full_summary.txt (1M-case launch, scaled per case)"
 
 
 def peak_info():

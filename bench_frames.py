@@ -21,6 +21,12 @@ import numpy as np
 from openbeam_b200 import obgpu, sharding, workloads
 from openbeam_b200.pipeline import BatchPipeline
 
+# dram__bytes_read + dram__bytes_write of the three-kernel path, all launches of one solve of 262 144 frames together:
+# k_frame_pre 545 + 1 668 MB, the nine k_frame_fused<split> launches 1 940 + 165 MB, k_frame_post 884 + 677 MB.  4.7 x the
+# algorithmic bytes: the 240-byte element records make a round trip through HBM, and gathers of 16-byte node records fetch
+# whole sectors — on a path that uses 3 % of the HBM bandwidth
+TRAFFIC_PER_STRUCTURE = 5879e6 / 262144
+TRAFFIC_SOURCE = "profiles/README.md r02o table + profiles/r02o_ncu_full_k_frame_split_summary.txt (262 144 frames, scaled per structure)"
 E2E_SUB, E2E_WORKERS = 8, 4   # sub-batches per step and contexts of the end-to-end leg (scripts/exp/c3_pipeline.py)
 
 METRIC = "static solves/s (FP64; full assemble+factor+solve+stress per load case)"
@@ -170,7 +176,9 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
             "dtype": "f64", "data": "synthetic", "config": config_dict(args, world, z),
             "dof_per_s": value * z["n_tot"] / S,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": kernel_name, "kernel_ms": k_ms,
+                         "traffic": TRAFFIC_PER_STRUCTURE * S if "k_frame_pre" in kernel_name else None,
+                         "traffic_source": TRAFFIC_SOURCE if "k_frame_pre" in kernel_name else None,
+                         "kernel": kernel_name, "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": alg,
                          "note": "all size-class launches of one step together (%d launches); this kernel is bound by "
                                  "instruction issue and shared-memory latency, not by HBM (DESIGN.md 4)" % launches_per_step,

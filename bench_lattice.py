@@ -180,9 +180,12 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
                     "restarts": pi["restarts"], "levels": pi["levels"], "rtol": args.rtol,
                     "relerr_vs_splu": relerr},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": kernel_name, "kernel_ms": k_ms,
+                         # dram__bytes_read 335.97 MB + dram__bytes_write 15.43 MB of the fine-level k_mg_spmv_blk at 817 x 817
+                         "traffic": 351.4e6 if (args.config == "c4" and lattice_params(args)[0] == 817 and args.pcg == "mg" and "blk" in kernel_name) else None,
+                         "traffic_source": "profiles/r02q_mg_spmv_blk_ncu_full_summary.txt" if (args.config == "c4" and lattice_params(args)[0] == 817 and args.pcg == "mg" and "blk" in kernel_name) else None,
+                         "kernel": kernel_name, "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": k_bytes,
-                         "spmv_alone": {"kernel": "k_spmv_dot", "ms": spmv_ms, "algorithmic_bytes": spmv_bytes,
+                         "spmv_alone": {"kernel": "k_spmv_dot_blk" if "blk" in kernel_name else "k_spmv_dot", "ms": spmv_ms, "algorithmic_bytes": spmv_bytes,
                                         "frac": spmv_bytes / (spmv_ms * 1e-3) / 1e9 / peak},
                          "note": "one launch over the first structure's rows, timed alone (50 back-to-back launches "
                                  "between CUDA events on the ctx stream)", "peak_source": peak_src},

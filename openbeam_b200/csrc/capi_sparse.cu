@@ -546,8 +546,11 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   c->pcg_levels = use_mg ? double(c->mg.lev.size()) : 1.0;
   c->solved = true;
   c->have_ff = true;
-  c->kernel_info = use_mg ? "k_mg_spmv (SELL-32 SpMV + fused Chebyshev step of the multigrid-PCG V-cycle)"
-                          : "k_spmv_dot (SELL-32 SpMV of the Jacobi-PCG iteration)";
+  const bool blk_info = c->plan.ff_blk.valid;
+  c->kernel_info = use_mg ? (blk_info ? "k_mg_spmv_blk (3x3 block-SELL SpMV + fused Chebyshev step of the multigrid-PCG V-cycle)"
+                                      : "k_mg_spmv (SELL-32 SpMV + fused Chebyshev step of the multigrid-PCG V-cycle)")
+                          : (blk_info ? "k_spmv_dot_blk (3x3 block-SELL SpMV of the Jacobi-PCG iteration)"
+                                      : "k_spmv_dot (SELL-32 SpMV of the Jacobi-PCG iteration)");
   c->have_stress = o.with_stress != 0;
   if (!all_converged) {
     char msg[384];
