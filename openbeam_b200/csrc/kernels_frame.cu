@@ -121,12 +121,28 @@ __device__ __forceinline__ void tile_update(double* bj, int voff, int a0, int c0
   }
 }
 
+// Reciprocal of a pivot: hardware seed (about 20 bits) + two Newton steps, 5 instructions against the 9 + a range check of
+// the correctly rounded 1.0 / d; the result is within an ulp of it (pivots of a stiffness matrix are far from the
+// subnormal range the seed flushes).  OBGPU_FRAME_EXACT_RCP restores 1.0 / d.
+__device__ __forceinline__ double pivot_rcp(double d) {
+#ifdef OBGPU_FRAME_EXACT_RCP
+  return 1.0 / d;
+#else
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-d, r, 1.0);
+  return fma(r, e, r);
+#endif
+}
+
 // GEN: the general path (nodal rotated frames and/or non-zero prescribed displacements) is a separate
 // instantiation so that its extra state never costs the common kernel a register.
 // SPLIT: the middle kernel of the three-kernel path (k_frame_pre -> this -> k_frame_post, see below): the element records
-// arrive precomputed from global memory instead of being formed here, and stage C is left to k_frame_post.  Without the
-// element arithmetic the kernel needs fewer registers and runs more resident warps, which is what this latency-bound
-// factorisation is short of.
+// arrive precomputed from global memory instead of being formed here, and stage C is left to k_frame_post.  (Without the
+// element arithmetic it needs 80 registers instead of 128; 6, 7 or 8 CTAs per SM measured the same: the stage is bound by
+// its instruction stream and shared-memory traffic, not by occupancy.)
 template <int MAXR, bool GEN, bool SPLIT>
 __global__ void __launch_bounds__(FRAME_WARPS * 32, SPLIT ? OBGPU_FRAME_SPLIT_MINB : OBGPU_FRAME_MINB(MAXR))
     k_frame_fused(FrameArgs a, int doubles_per_warp) {
@@ -320,18 +336,17 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, SPLIT ? OBGPU_FRAME_SPLIT_MI
         if (e2) x2 = rp[2];
         if (e3) x3 = rp[3];
         if (in) f = Ff[j + lane];
-        // The 4 x 4 head of the panel (rows j..j+3) and F(j..j+3) are read by EVERY lane (broadcast loads) and factored
-        // redundantly: reciprocal pivots i_k, scaled pivot-row entries c_rk = V(j+r, j+k) / D(j+k) and t_k = y(j+k) / D(j+k)
-        // are then in registers everywhere, with no shuffle in the pivot chain.  The operations on a pivot row are the
-        // ones its own lane applies to x0..x3 below, in the same order, so both copies agree bit for bit.
-        double i0, i1 = 0.0, i2 = 0.0, i3 = 0.0;
+        // The four pivots of the panel, in order.  Straight-line code: a non-positive pivot (Eigen's LLT stops there,
+        // solver_static.cpp:97-105) latches info = its row + 1 and is replaced by 1, so that no branch separates the
+        // warp shuffles; what is computed after it is never used (info != 0 skips the back substitution).
+        double i0, i1, i2, i3;
         {  // column j
-          const double d = __shfl_sync(0xffffffffu, x0, 0);
-          if (!(d > 0.0)) {  // Eigen LLT stops at the first x <= 0 (solver_static.cpp:97-105)
-            info = j + 1;
-            break;
+          double d = __shfl_sync(0xffffffffu, x0, 0);
+          if (!(d > 0.0)) {
+            if (info == 0) info = j + 1;
+            d = 1.0;
           }
-          i0 = 1.0 / d;
+          i0 = pivot_rcp(d);
           const double t = __shfl_sync(0xffffffffu, f, 0) * i0;
           const double c1 = __shfl_sync(0xffffffffu, x0, 1) * i0, c2 = __shfl_sync(0xffffffffu, x0, 2) * i0,
                        c3 = __shfl_sync(0xffffffffu, x0, 3) * i0;
@@ -340,38 +355,38 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, SPLIT ? OBGPU_FRAME_SPLIT_MI
           if (lane >= 2) x2 -= x0 * c2;
           if (lane >= 3) x3 -= x0 * c3;
         }
-        if (nrows > 1) {  // column j+1
-          const double d = __shfl_sync(0xffffffffu, x1, 1);
+        {  // column j+1 (rows past the end of the matrix hold zeros: their "pivot" is replaced by 1 without an error)
+          double d = __shfl_sync(0xffffffffu, x1, 1);
           if (!(d > 0.0)) {
-            info = j + 2;
-            break;
+            if (info == 0 && nrows > 1) info = j + 2;
+            d = 1.0;
           }
-          i1 = 1.0 / d;
+          i1 = pivot_rcp(d);
           const double t = __shfl_sync(0xffffffffu, f, 1) * i1;
           const double c2 = __shfl_sync(0xffffffffu, x1, 2) * i1, c3 = __shfl_sync(0xffffffffu, x1, 3) * i1;
           if (lane >= 2) f -= x1 * t;
           if (lane >= 2) x2 -= x1 * c2;
           if (lane >= 3) x3 -= x1 * c3;
         }
-        if (nrows > 2) {  // column j+2
-          const double d = __shfl_sync(0xffffffffu, x2, 2);
+        {  // column j+2
+          double d = __shfl_sync(0xffffffffu, x2, 2);
           if (!(d > 0.0)) {
-            info = j + 3;
-            break;
+            if (info == 0 && nrows > 2) info = j + 3;
+            d = 1.0;
           }
-          i2 = 1.0 / d;
+          i2 = pivot_rcp(d);
           const double t = __shfl_sync(0xffffffffu, f, 2) * i2;
           const double c3 = __shfl_sync(0xffffffffu, x2, 3) * i2;
           if (lane >= 3) f -= x2 * t;
           if (lane >= 3) x3 -= x2 * c3;
         }
-        if (nrows > 3) {  // column j+3
-          const double d = __shfl_sync(0xffffffffu, x3, 3);
+        {  // column j+3
+          double d = __shfl_sync(0xffffffffu, x3, 3);
           if (!(d > 0.0)) {
-            info = j + 4;
-            break;
+            if (info == 0 && nrows > 3) info = j + 4;
+            d = 1.0;
           }
-          i3 = 1.0 / d;
+          i3 = pivot_rcp(d);
           const double t = __shfl_sync(0xffffffffu, f, 3) * i3;
           if (lane >= 4) f -= x3 * t;
         }
@@ -423,18 +438,29 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, SPLIT ? OBGPU_FRAME_SPLIT_MI
       // (j = i + hb) to its own step (hb < 32, so the rows in flight sit in distinct lanes); x(j) reaches the
       // other lanes by shuffle, so the serial chain of a step is shuffle + 2 FP64 ops with no shared-memory
       // round trip or barrier.
+      // Loop state is carried incrementally (dist = j - myrow, po = offset of V(j, myrow), the source lane of x(j)):
+      // the step is a predicated load, a shuffle, a multiply and an FMA plus four integer updates.
+      constexpr int FAR = 1 << 20;  // "no row": never within the band
       int myrow = (nf - 1) - ((nf - 1 - lane) & 31);
+      int dist = myrow >= 0 ? (nf - 1) - myrow : FAR;
+      int po = (nf - 1) * W + hb - dist;
+      int jl = (nf - 1) & 31;
       double acc = myrow >= 0 ? Ff[myrow] : 0.0;
       for (int j = nf - 1; j >= 0; j--) {
-        const double vj = (myrow >= 0 && myrow < j && j - myrow <= hb) ? band[j * W + hb - (j - myrow)] : 0.0;
-        const double xj = __shfl_sync(0xffffffffu, acc, j & 31) * Dinv[j];
-        if (lane == (j & 31)) {
+        const double vj = unsigned(dist - 1) < unsigned(hb) ? band[po] : 0.0;
+        const double xj = __shfl_sync(0xffffffffu, acc, jl) * Dinv[j];
+        if (dist == 0) {
           Ff[j] = xj;
           myrow -= 32;
+          dist = myrow >= 0 ? 32 : FAR;
+          po -= 32;
           acc = myrow >= 0 ? Ff[myrow] : 0.0;
         } else {
           acc -= vj * xj;
         }
+        dist--;
+        po -= W - 1;
+        jl = (jl - 1) & 31;
       }
       __syncwarp();
     } else if (info == 0) {
@@ -633,18 +659,16 @@ __global__ void __launch_bounds__(128, OBGPU_FRAME_PRE_MINB) k_frame_pre(FrameAr
 }
 
 // k_frame_post: stage C (postproc_stress.cpp:86-165, solver_static.cpp:196-218).  Per-warp shared memory:
-// sg[32][12] (global end forces | equivalent loads of the chunk's elements) | slots[32][6] | R[max_nb] | Eq[max_nb] |
-// sst[32][13] (stress rows, odd stride; written to global as whole lines like k_frame_pre's records)
+// sg[32][12] (global end forces | equivalent loads of the chunk's elements) | slots[32][6] | R[max_nb] | Eq[max_nb]
 constexpr int POST_WARPS = 4;
 __global__ void __launch_bounds__(POST_WARPS * 32, OBGPU_FRAME_PRE_MINB) k_frame_post(FrameArgs a, int max_nb) {
   extern __shared__ __align__(16) double smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int per_warp = 32 * 12 + 32 * 3 + 2 * max_nb + 32 * 13;
+  const int per_warp = 32 * 12 + 32 * 3 + 2 * max_nb;
   double* sg = smem + size_t(warp) * per_warp;
   int32_t* slots = reinterpret_cast<int32_t*>(sg + 32 * 12);
   double* R = sg + 32 * 12 + 32 * 3;
   double* Eq = R + max_nb;
-  double* sst = Eq + max_nb;
   const int64_t wstride = int64_t(gridDim.x) * POST_WARPS;
   for (int64_t s = int64_t(blockIdx.x) * POST_WARPS + warp; s < a.S; s += wstride) {
     const FrameMeta m = a.meta[s];
@@ -697,19 +721,18 @@ __global__ void __launch_bounds__(POST_WARPS * 32, OBGPU_FRAME_PRE_MINB) k_frame
 #pragma unroll
             for (int k = 0; k < 6; k++) ext[k] += ex[k];
           }
-          double* o = sst + lane * 13;  // {N,Vy,Vz,Mx,My,Mz} x 2 faces; face 0 negated (postproc_stress.cpp:152-165)
-          o[0] = -es[0] + ext[0]; o[1] = -es[1] + ext[1]; o[2] = 0.0; o[3] = 0.0; o[4] = 0.0; o[5] = -es[2] + ext[2];
-          o[6] = es[3] + ext[3];  o[7] = es[4] + ext[4];  o[8] = 0.0; o[9] = 0.0; o[10] = 0.0; o[11] = es[5] + ext[5];
+          // {N,Vy,Vz,Mx,My,Mz} x 2 faces; face 0 negated (postproc_stress.cpp:152-165).  96 B = three whole sectors per
+          // lane, written directly: a shared-memory transpose like k_frame_pre's measured slower here (785 against 720 us)
+          double2* o = reinterpret_cast<double2*>(a.stress + e * 12);
+          o[0] = make_double2(-es[0] + ext[0], -es[1] + ext[1]);
+          o[1] = make_double2(0.0, 0.0);
+          o[2] = make_double2(0.0, -es[2] + ext[2]);
+          o[3] = make_double2(es[3] + ext[3], es[4] + ext[4]);
+          o[4] = make_double2(0.0, 0.0);
+          o[5] = make_double2(0.0, es[5] + ext[5]);
         }
       }
       __syncwarp();
-      if (a.stress) {
-        double* o = a.stress + (m.e0 + eb) * 12;
-        for (int i = lane; i < cnt * 12; i += 32) {
-          const int r = i / 12;
-          o[i] = sst[r * 13 + (i - r * 12)];
-        }
-      }
       unsigned todo = __ballot_sync(0xffffffffu, hasb);  // elements touching a support, in element order
       while (todo) {
         const int ee = __ffs(todo) - 1;
@@ -739,7 +762,7 @@ cudaError_t launch_frame_pre(const FrameArgs& a, int sm_count, cudaStream_t st) 
 }
 
 cudaError_t launch_frame_post(const FrameArgs& a, int max_nb, int sm_count, cudaStream_t st) {
-  const size_t smem = size_t(32 * 12 + 32 * 3 + 2 * max_nb + 32 * 13) * 8 * POST_WARPS;
+  const size_t smem = size_t(32 * 12 + 32 * 3 + 2 * max_nb) * 8 * POST_WARPS;
   if (smem > 227 * 1024) return cudaErrorInvalidConfiguration;
   cudaError_t e = cudaFuncSetAttribute(k_frame_post, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   if (e != cudaSuccess) return e;
