@@ -51,7 +51,9 @@ extern "C" void obgpu_debug_frame_clocks(unsigned long long* out, int reset) {
 #endif
 constexpr int STAGE_D = 27;  // doubles staged per element: 21 stiffness + 6 equivalent loads
 constexpr int CHUNK = 16;    // elements computed and staged at a time.  Measured and rejected: 32 (the larger staging buffer costs
-                             // resident warps), and computing 32 in registers + staging in two halves (no fewer instructions)
+                             // resident warps), computing 32 in registers + staging in two halves (no fewer instructions), and
+                             // 272-byte records that carry the 27 scatter offsets precomputed (5 % fewer instructions in the
+                             // factorisation kernel, but the larger staging area costs the 56-KB class a resident CTA: slower)
 
 // per-warp shared memory: band[max_band] | Ff[max_nf] | R[max_nb] | Eq[max_nb] | Dinv[max_nf] | stage[CHUNK*STAGE_D]
 // | slots[CHUNK*6] (int).  Stage C reuses stage[] as [CHUNK][12] stress + [CHUNK][6] global end forces.
@@ -302,6 +304,18 @@ __global__ void __launch_bounds__(FRAME_WARPS * 32, SPLIT ? OBGPU_FRAME_SPLIT_MI
         for (int i = lane; i < nf; i += 32) a.F_f[c * a.nf_tot + m.f0 + (a.free_inv ? a.free_inv[m.f0 + i] : i)] = Ff[i];
     }
     }  // pass
+    if (SPLIT) {
+      // the element records of the structure this warp serves NEXT are asked into L2 now: their DRAM latency then passes
+      // behind this structure's factorisation instead of in front of the next one's copy loop
+      const int64_t it_n = it + wstride;
+      if (it_n < n_sys) {
+        const int64_t s_n = a.order[a.o0 + (it_n - (it_n / n_cls) * n_cls)];
+        const int64_t e_n = a.meta[s_n].e0;
+        const int bytes_n = a.meta[s_n].E * FRAME_EREC * 8;
+        const char* pn = reinterpret_cast<const char*>(a.erec + e_n * FRAME_EREC);
+        for (int o = lane * 128; o < bytes_n; o += 32 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(pn + o));
+      }
+    }
     // ---- stage B: banded LDL^T (row i holds columns i-hb..i at band[i*W + (j-i+hb)]) ----
     // Right-looking, one column j per step, on the UNSCALED factor V = L D (V(i,j) = L(i,j) D(j)): the column is
     // never rewritten, the only division is the reciprocal pivot (kept in Dinv), and L y = b rides along
