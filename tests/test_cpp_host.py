@@ -60,3 +60,19 @@ def test_cpp_mirror_solve(tmp_path):
     assert not np.allclose(Ui, U, rtol=1e-6)
     Ua = np.array([float(x) for x in re.findall(r"again U_f\[\d+\] (\S+)", out)])
     assert np.allclose(Ua, U, rtol=1e-12)
+
+
+@pytest.mark.gpu
+def test_cpp_batch_pipeline(tmp_path):
+    """include/obpipeline.hpp (the C++ twin of openbeam_b200/pipeline.py): sub-batches of a parametric sweep dealt to three
+    contexts on host threads return the bits a single context returns, and the reactions balance the applied loads."""
+    exe = str(tmp_path / "ob_pipeline_frames")
+    libdir = os.path.join(ROOT, "openbeam_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-pthread", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "ob_pipeline_frames.cpp"), "-L" + libdir, "-lobgpu",
+                           "-Wl,-rpath," + libdir, "-o", exe])
+    out = subprocess.check_output([exe, "0", "5", "2000", "3"], text=True)
+    assert "structures 10000 sub_batches 5 workers 3" in out
+    assert "pipeline_matches_single_context 1" in out
+    assert float(re.search(r"vertical_equilibrium_relerr (\S+)", out).group(1)) < 1e-9
+    assert 1e-5 < float(re.search(r"max_abs_U_f (\S+)", out).group(1)) < 1.0
