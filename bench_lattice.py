@@ -180,15 +180,18 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
                     "restarts": pi["restarts"], "levels": pi["levels"], "rtol": args.rtol,
                     "relerr_vs_splu": relerr},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read 335.97 MB + dram__bytes_write 15.43 MB of the fine-level k_mg_spmv_blk at 817 x 817
-                         "traffic": 351.4e6 if (args.config == "c4" and lattice_params(args)[0] == 817 and args.pcg == "mg" and "blk" in kernel_name) else None,
-                         "traffic_source": "profiles/r02q_mg_spmv_blk_ncu_full_summary.txt" if (args.config == "c4" and lattice_params(args)[0] == 817 and args.pcg == "mg" and "blk" in kernel_name) else None,
+                         # dram__bytes_read 223.3 MB + dram__bytes_write 14.2 MB of the fine-level k_mg_spmv_blk<float> at 817 x 817
+                         # (FP64 matrix copies, OBGPU_MG_FP32=0: 336.0 + 15.4 MB, profiles/r02q_mg_spmv_blk_ncu_full_summary.txt)
+                         "traffic": (237.5e6 if os.environ.get("OBGPU_MG_FP32", "1") != "0" else 351.4e6) if (args.config == "c4" and lattice_params(args)[0] == 817 and args.pcg == "mg" and "blk" in kernel_name) else None,
+                         "traffic_source": "profiles/r02s_launches_c4_mg_fp32.txt" if (args.config == "c4" and lattice_params(args)[0] == 817 and args.pcg == "mg" and "blk" in kernel_name) else None,
                          "kernel": kernel_name, "kernel_ms": k_ms,
                          "algorithmic_bytes_per_launch": k_bytes,
                          "spmv_alone": {"kernel": "k_spmv_dot_blk" if "blk" in kernel_name else "k_spmv_dot", "ms": spmv_ms, "algorithmic_bytes": spmv_bytes,
                                         "frac": spmv_bytes / (spmv_ms * 1e-3) / 1e9 / peak},
                          "note": "one launch over the first structure's rows, timed alone (50 back-to-back launches "
-                                 "between CUDA events on the ctx stream)", "peak_source": peak_src},
+                                 "between CUDA events on the ctx stream); the same kernel inside the V-cycle, per ncu: 55.9 us "
+                                 "(profiles/r02s_launches_c4_mg_fp32.txt) — the back-to-back loop is the slower figure",
+                         "peak_source": peak_src},
             "e2e": {"value": world * per * K / e2e_s, "unit": UNIT,
                     "h2d_bytes_per_step": int(h_nl.nbytes + h_q.nbytes),
                     "d2h_bytes_per_step": int(h_U.nbytes + h_Fb.nbytes + h_S.nbytes),

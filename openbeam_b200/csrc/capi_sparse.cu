@@ -276,6 +276,9 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
   static const bool use_graph = !(getenv("OBGPU_PCG_GRAPH") && atoi(getenv("OBGPU_PCG_GRAPH")) == 0);
   // iterations between convergence checks (even when replayed as a graph); a multigrid iteration is ~40 kernels and
   // the whole solve ~100 iterations, so it is checked every other iteration
+  // The multigrid V-cycle reads FP32 copies of its block-SELL matrices (vectors, products and sums stay FP64): a
+  // preconditioner needs no more, and the matrices are most of the bytes its kernels move.  OBGPU_MG_FP32=0: FP64 copies.
+  const bool mg_fp32 = use_mg && !(getenv("OBGPU_MG_FP32") && atoi(getenv("OBGPU_MG_FP32")) == 0);
   int chk = use_mg ? 2 : use_graph ? 24 : 25;   // iterations between convergence checks (even: the rz ping-pong parity)
   if (const char* ev = getenv("OBGPU_PCG_CHECK")) chk = std::max(2, atoi(ev) & ~1);
   double restarts_total = 0, worst_floor = 0;
@@ -297,6 +300,12 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
         OB_CUDA(c, launch_inv_diag(nf, d.ff_diag, d.ff_val, v_minv, c->stream));
         launches += 1;
       } else {
+        if (c->plan.ff_blk.valid && mg_fp32) {  // the V-cycle streams FP32 copies of the block matrices (40 B per block)
+          const int64_t nblk0 = int64_t(c->plan.ff_blk.map.size() / 9);
+          OB_CUDA(c, c->d_ff_bval32.reserve(size_t(10 * nblk0)));
+          OB_CUDA(c, launch_gather_blk_f32(nblk0, c->d_ff_bmap.p, d.ff_val, c->d_ff_bval32.p, c->stream));
+          launches += 1;
+        }
         // numeric setup of the hierarchy from the current K_ff: Galerkin products level by level, Jacobi diagonals and
         // Gershgorin bounds of D^-1 A (the Chebyshev intervals); the coarsest inverses are built per structure below
         const size_t nl = c->mg.lev.size();
@@ -316,7 +325,12 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
           g.c_slptr = B.sl_ptr.p; g.c_col = B.col.p; g.c_val = B.val.p;
           OB_CUDA(c, launch_mg_galerkin(g, c->stream));
           if (B.nblk) {
-            OB_CUDA(c, launch_gather(9 * B.nblk, B.bmap.p, B.val.p, B.bval.p, c->stream));
+            if (mg_fp32) {
+              OB_CUDA(c, B.bval32.reserve(size_t(10 * B.nblk)));
+              OB_CUDA(c, launch_gather_blk_f32(B.nblk, B.bmap.p, B.val.p, B.bval32.p, c->stream));
+            } else {
+              OB_CUDA(c, launch_gather(9 * B.nblk, B.bmap.p, B.val.p, B.bval.p, c->stream));
+            }
             launches += 1;
           }
           OB_CUDA(c, launch_mg_diag(0, ML.n, B.sl_ptr.p, B.col.p, B.val.p, B.minv.p, c->d_mg_lam.p + l, c->stream));
@@ -388,6 +402,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
             V.slptr = d.sl_ptr; V.col = d.ff_col; V.val = d.ff_val; V.minv = v_minv;
             static const bool fine_blk = !(getenv("OBGPU_MG_FINE_BLOCK") && atoi(getenv("OBGPU_MG_FINE_BLOCK")) == 0);
             V.bslptr = fine_blk ? a.bslptr : nullptr; V.bcol = fine_blk ? a.bcol : nullptr; V.bval = fine_blk ? a.bval : nullptr;
+            V.bval32 = (fine_blk && a.bval && mg_fp32) ? c->d_ff_bval32.p : nullptr;
             V.x = v_z; V.b = v_r; V.r = v_mr; V.d0 = v_md0; V.d1 = v_md1;
           } else {
             const MgLevel& ML = c->mg.lev[size_t(l)];
@@ -395,6 +410,7 @@ int solve_sparse(obgpu_ctx* c, const obgpu_solve_opts& o) {
             V.r0 = ML.row_off[st_i]; V.r1 = V.r0 + ML.nrows[st_i];
             V.slptr = B.sl_ptr.p; V.col = B.col.p; V.val = B.val.p; V.minv = B.minv.p;
             V.bslptr = B.nblk ? B.bsl_ptr.p : nullptr; V.bcol = B.nblk ? B.bcol.p : nullptr; V.bval = B.nblk ? B.bval.p : nullptr;
+            V.bval32 = (B.nblk && mg_fp32) ? B.bval32.p : nullptr;
             V.x = B.vec.p; V.b = V.x + ML.n; V.r = V.b + ML.n; V.d0 = V.r + ML.n; V.d1 = V.d0 + ML.n;
           }
           if (l + 1 < J.nlev) {  // transfer to the next coarser level (arrays indexed by this level's rows)
@@ -596,7 +612,8 @@ int profile_kernel(obgpu_ctx* c, int which, int reps, double* ms_avg, double* al
     if (a.bval) {  // 3x3 block-SELL: 72 B of values + 4 B of column per stored block
       const int64_t bs0 = (a.r0 / 3) >> 5, bs1 = (int64_t(a.r1) / 3 + 31) >> 5;
       const double blocks = double(c->plan.ff_blk.sl_ptr[size_t(bs1)]) - double(c->plan.ff_blk.sl_ptr[size_t(bs0)]);
-      *alg_bytes = 76.0 * blocks + (which == OBGPU_PROF_SPMV ? 20.0 : 56.0) * double(n);
+      const bool f32 = which != OBGPU_PROF_SPMV && c->mg_job[0].lv[0].bval32 != nullptr;   // the V-cycle's FP32 matrix copy
+      *alg_bytes = (f32 ? 44.0 : 76.0) * blocks + (which == OBGPU_PROF_SPMV ? 20.0 : 56.0) * double(n);
     } else {
       *alg_bytes = 12.0 * double(entries) + (which == OBGPU_PROF_SPMV ? 20.0 : 56.0) * double(n);
     }

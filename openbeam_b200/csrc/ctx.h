@@ -92,11 +92,13 @@ struct obgpu_ctx {
     obgpu::DevBuf<double> f_w, val, minv, vec;  // vec: x | b | r | d0 | d1
     obgpu::DevBuf<int32_t> bsl_ptr, bcol, bmap;  // 3x3 block-SELL view (empty when the level has none)
     obgpu::DevBuf<double> bval;
+    obgpu::DevBuf<float> bval32;   // FP32 copy streamed by the V-cycle's kernels
     int64_t nblk = 0;
   };
   std::vector<MgLevelBufs> mg_lev;
   obgpu::DevBuf<double> d_mg_lam, d_mg_cinv, d_mg_prow;
   obgpu::DevBuf<int32_t> d_ff_bslptr, d_ff_bcol, d_ff_bmap;   // K_ff in 3x3 block-SELL (SparsePlan::ff_blk), when it has one
+  obgpu::DevBuf<float> d_ff_bval32;  // FP32 copy of d_ff_bval for the V-cycle's fine-level kernels
   obgpu::DevBuf<double> d_ff_bval;   // Gershgorin bounds per level; explicit coarsest inverses, one per job slot
   obgpu::MgJob mg_job[8];
   obgpu::PcgArgs prof_args;          // obgpu_profile_kernel: iteration arguments of the last PCG solve's first structure

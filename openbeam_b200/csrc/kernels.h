@@ -114,6 +114,8 @@ cudaError_t launch_assemble(const SparseDev& d, cudaStream_t st);
 cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStream_t st);
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st);
 cudaError_t launch_gather(int64_t n, const int32_t* src, const double* in, double* out, cudaStream_t st);  // out[i] = in[src[i]] (-1: 0)
+// FP32 copy (paired layout, 10 floats per block) of a 3x3 block-SELL matrix of n_blocks block slots whose FP64 gather map is src
+cudaError_t launch_gather_blk_f32(int64_t n_blocks, const int32_t* src, const double* in, float* out, cudaStream_t st);
 cudaError_t launch_load_vector(const SparseDev& d, const double* nload_val, const double* q, const double* eai, double* F_f,
                                cudaStream_t st);
 cudaError_t launch_stress(const SparseDev& d, const double* eai, const double* q, const double* U_f, double* stress,
@@ -144,6 +146,8 @@ struct MgLevelDev {
   const double *val, *minv;
   const int32_t *bslptr, *bcol;   // 3x3 block-SELL view used by the SpMV-class kernels when present (else null)
   const double* bval;
+  const float* bval32;            // FP32 copy of bval: when set, the V-cycle's kernels stream it instead (the preconditioner
+                                  // needs no more; the PCG's own SpMV and every vector stay FP64)
   double *x, *b, *r, *d0, *d1;
   const int32_t* f_agg; const uint8_t* f_kind; const double* f_w;
   const int32_t *mem_ptr, *mem;

@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_mg_spmv(MgLevelDev L, const doubl
 }
 
 // the same on the 3x3 block-SELL view of the level: warp per slice of 32 block rows, lane = block row (3 rows)
-template <int MODE, bool DOT>
+template <int MODE, bool DOT, class T>
 __global__ void __launch_bounds__(PCG_BLOCK) k_mg_spmv_blk(MgLevelDev L, const double* __restrict__ din, const double* rin,
                                                            double* dout, double c1, double c2, const double* __restrict__ dotv,
                                                            double* dot_out, double* partial, unsigned int* counter) {
@@ -278,7 +278,8 @@ __global__ void __launch_bounds__(PCG_BLOCK) k_mg_spmv_blk(MgLevelDev L, const d
     // SLOWER on B200 than letting every lane finish its own three consecutive rows: 97.6 vs 96.0 us here, 83 vs 60 us in
     // k_spmv_dot_blk)
     double sum[3];
-    block_row_product(L.bslptr, L.bcol, L.bval, sl, lane, din, sum);
+    if (sizeof(T) == 4) block_row_product_f32(L.bslptr, L.bcol, L.bval32, sl, lane, din, sum);
+    else block_row_product(L.bslptr, L.bcol, L.bval, sl, lane, din, sum);
     const int64_t I = sl * 32 + lane;
 #pragma unroll
     for (int j = 0; j < 3; j++) {
@@ -368,11 +369,23 @@ static unsigned mg_grid(int64_t items, int sm_count, int cps) {
   return unsigned(g < 1 ? 1 : g);
 }
 
+// one launch of the block kernel, FP32 or FP64 matrix copy as the level has it
+template <int MODE, bool DOT>
+static void launch_blk(const MgLevelDev& L, int64_t slices, int sm_count, int cps, cudaStream_t st, const double* din,
+                       const double* rin, double* dout, double c1, double c2, const double* dotv, double* dot_out,
+                       double* partial, unsigned int* counter) {
+  if (L.bval32)
+    k_mg_spmv_blk<MODE, DOT, float><<<balanced_grid(k_mg_spmv_blk<MODE, DOT, float>, slices, sm_count, cps), PCG_BLOCK, 0, st>>>(
+        L, din, rin, dout, c1, c2, dotv, dot_out, partial, counter);
+  else
+    k_mg_spmv_blk<MODE, DOT, double><<<balanced_grid(k_mg_spmv_blk<MODE, DOT, double>, slices, sm_count, cps), PCG_BLOCK, 0, st>>>(
+        L, din, rin, dout, c1, c2, dotv, dot_out, partial, counter);
+}
+
 cudaError_t launch_mg_cheb_only(const MgLevelDev& L, int sm_count, cudaStream_t st) {
   if (L.bval) {
     const int64_t bs = ((int64_t(L.r1) / 3 + 31) >> 5) - ((L.r0 / 3) >> 5);
-    k_mg_spmv_blk<MG_CHEB, false><<<balanced_grid(k_mg_spmv_blk<MG_CHEB, false>, bs, sm_count, 0), PCG_BLOCK, 0, st>>>(
-        L, L.d0, L.r, L.d1, L.c1, L.c2, nullptr, nullptr, nullptr, nullptr);
+    launch_blk<MG_CHEB, false>(L, bs, sm_count, 0, st, L.d0, L.r, L.d1, L.c1, L.c2, nullptr, nullptr, nullptr, nullptr);
     return cudaGetLastError();
   }
   const int64_t threads = (((int64_t(L.r1) + 31) >> 5) - (L.r0 >> 5)) * 32;
@@ -389,12 +402,8 @@ cudaError_t launch_mg_vcycle(const MgJob& J, double* dot_out, double* partial, u
   auto blk_slices = [](const MgLevelDev& L) { return ((int64_t(L.r1) / 3 + 31) >> 5) - ((L.r0 / 3) >> 5); };
   auto cheb = [&](const MgLevelDev& L, const double* din, const double* rin, double* dout, double c1, double c2, bool dot) {
     if (L.bval) {
-      if (dot)
-        k_mg_spmv_blk<MG_CHEB, true><<<balanced_grid(k_mg_spmv_blk<MG_CHEB, true>, blk_slices(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
-            L, din, rin, dout, c1, c2, L.b, dot_out, partial, counter);
-      else
-        k_mg_spmv_blk<MG_CHEB, false><<<balanced_grid(k_mg_spmv_blk<MG_CHEB, false>, blk_slices(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
-            L, din, rin, dout, c1, c2, nullptr, nullptr, nullptr, nullptr);
+      if (dot) launch_blk<MG_CHEB, true>(L, blk_slices(L), sm_count, cps, st, din, rin, dout, c1, c2, L.b, dot_out, partial, counter);
+      else launch_blk<MG_CHEB, false>(L, blk_slices(L), sm_count, cps, st, din, rin, dout, c1, c2, nullptr, nullptr, nullptr, nullptr);
       return;
     }
     const unsigned g = mg_grid(slice_threads(L), sm_count, cps);
@@ -407,8 +416,7 @@ cudaError_t launch_mg_vcycle(const MgJob& J, double* dot_out, double* partial, u
     const MgLevelDev& L = J.lv[l];
     cheb(L, L.d0, L.b, L.d1, L.c1, L.c2, false);  // x = d0 + d1, r = b - A d0
     if (L.bval)
-      k_mg_spmv_blk<MG_RESID, false><<<balanced_grid(k_mg_spmv_blk<MG_RESID, false>, blk_slices(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
-          L, L.d1, L.r, nullptr, 0.0, 0.0, nullptr, nullptr, nullptr, nullptr);
+      launch_blk<MG_RESID, false>(L, blk_slices(L), sm_count, cps, st, L.d1, L.r, nullptr, 0.0, 0.0, nullptr, nullptr, nullptr, nullptr);
     else
       k_mg_spmv<MG_RESID, false><<<mg_grid(slice_threads(L), sm_count, cps), PCG_BLOCK, 0, st>>>(
           L, L.d1, L.r, nullptr, 0.0, 0.0, nullptr, nullptr, nullptr, nullptr);  // r = b - A x

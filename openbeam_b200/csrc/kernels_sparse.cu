@@ -174,6 +174,23 @@ __global__ void __launch_bounds__(256) k_gather(int64_t n, const int32_t* __rest
   }
 }
 
+// FP32 copy of a 3x3 block-SELL matrix in the paired layout block_row_product_f32 reads (pcg_common.cuh): float j of the
+// output belongs to block column B = j / 320, pair (j % 320) / 64, lane ((j % 320) / 2) % 32, component j & 1; the
+// FP64 layout holds value v of that block at 288 * B + 32 * v + lane of `src`
+__global__ void __launch_bounds__(256) k_gather_blk_f32(int64_t n_out, const int32_t* __restrict__ src,
+                                                        const double* __restrict__ in, float* __restrict__ out) {
+  const int64_t j = int64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (j >= n_out) return;
+  const int64_t t = j >> 1, B = t / 160;
+  const int rem = int(t - B * 160), pr = rem >> 5, lane = rem & 31, v = 2 * pr + int(j & 1);
+  float r = 0.0f;
+  if (v < 9) {
+    const int32_t s = src[B * 288 + v * 32 + lane];
+    if (s >= 0) r = float(in[s]);
+  }
+  out[j] = r;
+}
+
 __global__ void __launch_bounds__(256) k_load_vector(int64_t nf, int64_t nb, const int32_t* __restrict__ fseg_ptr,
                                                      const int32_t* __restrict__ fseg_src, const double* __restrict__ nload_val,
                                                      const double* __restrict__ eload_g, double* __restrict__ F_f,
@@ -293,6 +310,10 @@ cudaError_t launch_assemble_fused(const SparseDev& d, const double* eai, cudaStr
 }
 cudaError_t launch_gather(int64_t n, const int32_t* src, const double* in, double* out, cudaStream_t st) {
   if (n > 0) k_gather<<<nblk(n), 256, 0, st>>>(n, src, in, out);
+  return cudaGetLastError();
+}
+cudaError_t launch_gather_blk_f32(int64_t n_blocks, const int32_t* src, const double* in, float* out, cudaStream_t st) {
+  if (n_blocks > 0) k_gather_blk_f32<<<nblk(10 * n_blocks), 256, 0, st>>>(10 * n_blocks, src, in, out);
   return cudaGetLastError();
 }
 cudaError_t launch_bc_gather(const SparseDev& d, cudaStream_t st) {

@@ -100,6 +100,42 @@ __device__ __forceinline__ void block_row_product(const int32_t* __restrict__ bs
   }
 }
 
+// The same on the FP32 copy the multigrid preconditioner streams: the nine values of a block as five float2 (the tenth
+// float is padding), block column B (32 consecutive blocks of a slice) at float2 index 5 * 32 * B: 8-byte loads of 32
+// consecutive lanes like the FP64 layout, five per block instead of nine, 44 bytes per block instead of 76.  Products and
+// sums are FP64.
+constexpr int BLK32_PAIRS = 5;
+__device__ __forceinline__ void block_row_product_f32(const int32_t* __restrict__ bslptr, const int32_t* __restrict__ bcol,
+                                                      const float* __restrict__ bval32, int64_t sl, int lane,
+                                                      const double* __restrict__ x, double (&s)[3]) {
+  const int32_t base = bslptr[sl], w = (bslptr[sl + 1] - base) >> 5;
+  const int32_t* __restrict__ pc = bcol + base + lane;
+  const float2* __restrict__ pv = reinterpret_cast<const float2*>(bval32) + size_t(BLK32_PAIRS) * base + lane;
+  s[0] = s[1] = s[2] = 0.0;
+  int k = 0;
+  for (; k + 2 <= w; k += 2) {
+    const int32_t c0 = pc[32 * k], c1 = pc[32 * (k + 1)];
+    float2 m[2 * BLK32_PAIRS];
+#pragma unroll
+    for (int v = 0; v < 2 * BLK32_PAIRS; v++) m[v] = pv[(BLK32_PAIRS * k + v) * 32];
+    const double x0 = x[3 * c0], x1 = x[3 * c0 + 1], x2 = x[3 * c0 + 2];
+    const double y0 = x[3 * c1], y1 = x[3 * c1 + 1], y2 = x[3 * c1 + 2];
+    s[0] += double(m[0].x) * x0 + double(m[0].y) * x1 + double(m[1].x) * x2 + double(m[5].x) * y0 + double(m[5].y) * y1 + double(m[6].x) * y2;
+    s[1] += double(m[1].y) * x0 + double(m[2].x) * x1 + double(m[2].y) * x2 + double(m[6].y) * y0 + double(m[7].x) * y1 + double(m[7].y) * y2;
+    s[2] += double(m[3].x) * x0 + double(m[3].y) * x1 + double(m[4].x) * x2 + double(m[8].x) * y0 + double(m[8].y) * y1 + double(m[9].x) * y2;
+  }
+  for (; k < w; k++) {
+    const int32_t c0 = pc[32 * k];
+    float2 m[BLK32_PAIRS];
+#pragma unroll
+    for (int v = 0; v < BLK32_PAIRS; v++) m[v] = pv[(BLK32_PAIRS * k + v) * 32];
+    const double x0 = x[3 * c0], x1 = x[3 * c0 + 1], x2 = x[3 * c0 + 2];
+    s[0] += double(m[0].x) * x0 + double(m[0].y) * x1 + double(m[1].x) * x2;
+    s[1] += double(m[1].y) * x0 + double(m[2].x) * x1 + double(m[2].y) * x2;
+    s[2] += double(m[3].x) * x0 + double(m[3].y) * x1 + double(m[4].x) * x2;
+  }
+}
+
 // block_row_product leaves row 3 l + a of the slice in lane l; the row-local work that follows (vector reads and writes)
 // wants lane l on rows l, 32 + l, 64 + l so that every access of the warp is 32 consecutive doubles: t[j] = the sum of
 // slice row 32 j + l, fetched from lane (32 j + l) / 3, component (32 j + l) % 3

@@ -261,3 +261,20 @@ def test_pcg_rotated_frames_and_settlements(ctx, method):
         assert relerr(U[fo[s]:fo[s + 1]], od.U_f) <= RTOL, s
         assert relerr(Fb[bo[s]:bo[s + 1]], od.F_b) <= RTOL, s
         assert relerr(S[eo[s]:eo[s + 1]], od.element_stress) <= RTOL, s
+
+
+def test_mg_fp32_matrix_copies_do_not_change_the_answer(ctx, monkeypatch):
+    """The V-cycle streams FP32 copies of its block-SELL matrices (OBGPU_MG_FP32, default on; vectors, products and the
+    PCG itself stay FP64).  A preconditioner's precision must not show in the result: both variants stop on the same true
+    residual test, take the same number of iterations (to within one check interval) and agree with the oracle."""
+    st = workloads.grid_frame(34, 29)
+    o = OracleProblem(st).solveStatic()
+    got = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("OBGPU_MG_FP32", flag)
+        ctx.upload(st)
+        ctx.solve_static(method=obgpu.PCG_MG, rtol=1e-12)
+        got[flag] = (ctx.download(obgpu.RES_UF)[0].copy(), ctx.download(obgpu.RES_FB)[0].copy(), ctx.pcg_info())
+        assert relerr(got[flag][0], o.U_f) <= RTOL and relerr(got[flag][1], o.F_b) <= RTOL
+    assert abs(got["0"][2]["iters"] - got["1"][2]["iters"]) <= 2
+    assert relerr(got["1"][0], got["0"][0]) <= RTOL
