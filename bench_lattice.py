@@ -130,9 +130,11 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
             dist.all_reduce(torch.zeros(1, device=dev))
         e0.record(ext)
         iters = []
+        solve_ms = []
         for _ in range(K):
             step()
             iters.append(ctx.pcg_info()["iters"])
+            solve_ms.append(ctx.timings()["solveStatic.2_solve"])
         ctx.summaries_device(summ.data_ptr())
         if world > 1:
             sharding.gather_summaries(summ, gathered)   # the job's one exchange
@@ -176,6 +178,7 @@ def ours(args, rank, local_rank, world, emit, ClockSampler, peak_info):
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": config_dict(args, world, z, args.pcg),
             "dof_per_s": value * n_dof,
+            "solve_ms_device_events": solve_ms,
             "pcg": {"method": args.pcg, "iterations_per_step": float(np.mean(iters)), "true_relres": pi["true_relres"],
                     "restarts": pi["restarts"], "levels": pi["levels"], "rtol": args.rtol,
                     "relerr_vs_splu": relerr},

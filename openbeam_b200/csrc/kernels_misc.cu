@@ -25,8 +25,50 @@ __global__ void __launch_bounds__(256) k_summaries(SummaryArgs a) {
   }
 }
 
+// The same record for LARGE systems (the sparse route: one to a few structures of 10^5..10^6 DOFs): one CTA per system, its
+// threads stride over the DOFs, fixed-order reductions (lane tree, then warp 0 over the warp results) — deterministic,
+// and 2 M DOFs take microseconds where a single thread of k_summaries took 125 ms.
+__global__ void __launch_bounds__(256) k_summaries_block(SummaryArgs a) {
+  __shared__ double red[3][8];
+  const int64_t total = a.L * a.S;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t sys = blockIdx.x; sys < total; sys += gridDim.x) {
+    const int64_t c = sys / a.S, s = sys - c * a.S;
+    const int64_t f0 = a.free_off[s], f1 = a.free_off[s + 1], b0 = a.bnd_off[s], b1 = a.bnd_off[s + 1];
+    const double* U = a.U_f + c * a.nf_tot;
+    const double* F = a.F_b + c * a.nb_tot;
+    double v[3] = {0.0, 0.0, 0.0};  // max|U_f|, sum F_b over DX, sum F_b over DY
+    for (int64_t i = f0 + threadIdx.x; i < f1; i += 256) v[0] = fmax(v[0], fabs(U[i]));
+    for (int64_t i = b0 + threadIdx.x; i < b1; i += 256) {
+      const int d = a.bnd_dofid[i];
+      const double x = F[i];
+      if (d == OBGPU_DX) v[1] += x;
+      if (d == OBGPU_DY) v[2] += x;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      v[0] = fmax(v[0], __shfl_xor_sync(0xffffffffu, v[0], o));
+      v[1] += __shfl_xor_sync(0xffffffffu, v[1], o);
+      v[2] += __shfl_xor_sync(0xffffffffu, v[2], o);
+    }
+    if (lane == 0) { red[0][warp] = v[0]; red[1][warp] = v[1]; red[2][warp] = v[2]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double umax = 0.0, fx = 0.0, fy = 0.0;
+      for (int w = 0; w < 8; w++) { umax = fmax(umax, red[0][w]); fx += red[1][w]; fy += red[2][w]; }
+      reinterpret_cast<double4*>(a.out)[sys] = make_double4(umax, fx, fy, double(a.info[sys]));
+    }
+    __syncthreads();
+  }
+}
+
 cudaError_t launch_summaries(const SummaryArgs& a, int sm_count, cudaStream_t st) {
   const int64_t total = a.L * a.S;
+  if (a.S > 0 && a.nf_tot / a.S >= 4096) {  // large systems: a CTA each
+    int64_t g = total < int64_t(sm_count) * 8 ? total : int64_t(sm_count) * 8;
+    k_summaries_block<<<unsigned(g < 1 ? 1 : g), 256, 0, st>>>(a);
+    return cudaGetLastError();
+  }
   int64_t grid = (total + 255) / 256;
   const int64_t cap = int64_t(sm_count) * 8;
   if (grid > cap) grid = cap;

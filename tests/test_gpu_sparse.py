@@ -278,3 +278,26 @@ def test_mg_fp32_matrix_copies_do_not_change_the_answer(ctx, monkeypatch):
         assert relerr(got[flag][0], o.U_f) <= RTOL and relerr(got[flag][1], o.F_b) <= RTOL
     assert abs(got["0"][2]["iters"] - got["1"][2]["iters"]) <= 2
     assert relerr(got["1"][0], got["0"][0]) <= RTOL
+
+
+def test_summaries_of_large_structures(ctx):
+    """obgpu_summaries_device on the sparse route's few, large structures (one CTA per system, fixed-order reductions)
+    against numpy on the downloaded vectors."""
+    import torch
+    dims = [(50, 41), (33, 60)]
+    sts = [workloads.grid_frame(nx, ny, seed_index=i) for i, (nx, ny) in enumerate(dims)]
+    ctx.upload(sts)
+    ctx.solve_static(method=obgpu.PCG_MG, rtol=1e-11)
+    assert ctx.sizes()["nf_tot"] // 2 >= 4096       # the large-system kernel
+    out = torch.zeros((2, 4), dtype=torch.float64, device="cuda")
+    ctx.summaries_device(out.data_ptr())
+    ctx.synchronize()
+    got = out.cpu().numpy()
+    U, Fb = (ctx.download(w)[0] for w in (obgpu.RES_UF, obgpu.RES_FB))
+    fo, bo = ctx.offsets(obgpu.OFF_FREE), ctx.offsets(obgpu.OFF_BOUNDED)
+    for s in range(2):
+        u, f = U[fo[s]:fo[s + 1]], Fb[bo[s]:bo[s + 1]]
+        assert got[s, 0] == np.abs(u).max() and got[s, 3] == 0
+        # bounded DOFs of these frames: (DX, DY, RZ) per base node
+        assert abs(got[s, 1] - f[0::3].sum()) <= 1e-9 * np.abs(f[0::3]).sum()
+        assert abs(got[s, 2] - f[1::3].sum()) <= 1e-9 * np.abs(f[1::3]).sum()
