@@ -62,6 +62,16 @@ def test_cpp_mirror_solve(tmp_path):
     assert np.allclose(Ua, U, rtol=1e-12)
 
 
+def test_cpp_batch_pipeline_builds(tmp_path):
+    """include/obpipeline.hpp + its example compile warning-free and link against libobgpu.so (no GPU needed)"""
+    exe = str(tmp_path / "ob_pipeline_frames")
+    libdir = os.path.join(ROOT, "openbeam_b200")
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-pthread", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "ob_pipeline_frames.cpp"), "-L" + libdir, "-lobgpu",
+                           "-Wl,-rpath," + libdir, "-o", exe])
+    assert os.path.exists(exe)
+
+
 @pytest.mark.gpu
 def test_cpp_batch_pipeline(tmp_path):
     """include/obpipeline.hpp (the C++ twin of openbeam_b200/pipeline.py): sub-batches of a parametric sweep dealt to three
